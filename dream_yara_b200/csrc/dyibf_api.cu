@@ -1,0 +1,836 @@
+// dyibf_api.cu — the extern "C" layer of libdyibf.so (include/dyibf.h): handle, HBM residency of the filter,
+// sdsl-compatible .filter I/O, and the host drivers that feed the kernels.  No CPU implementation of the
+// filter lives here: every call either runs the sm_100a kernels or fails.
+//
+// On-disk format (sdsl::int_vector<1>::serialize, include/sdsl-lite/include/sdsl/int_vector.hpp:1463-1472,
+// write_header :534-544; trailer d_bloom_filter.h:255-277):
+//   u64 (1<<56 | nbits) ; ceil(nbits/64) little-endian u64 words ; the last four words are [bins, h, k, 0].
+// In HBM only the P*W data words are kept; the (all-zero) gap before the trailer and the trailer itself are
+// synthesised when the filter is downloaded or saved.
+#include "dyibf_internal.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cstdarg>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+using namespace dyibf;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) \
+    return fail(DYIBF_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
+
+const uint64_t SEED = 0x90b45d39fb6da1faULL;      // _seedValue, d_bloom_filter.h:329
+const uint64_t META_BITS = 256;                    // filterMetadataSize, d_misc_options.h:40
+const size_t   STAGE_BYTES = 32u << 20;            // pinned staging buffers for file / word transfers
+
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct Slot {                     // one stage of the host-mode pipeline
+    cudaStream_t st = nullptr;
+    DevBuf in_bytes, in_offsets, packed, meta, rows, counts;
+};
+
+enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_N };
+
+struct Pending { cudaEvent_t a, b; int kind; };
+
+} // namespace
+
+struct dyibf_filter {
+    dyibf_params prm;
+    HashParams   hp;
+    int          sm_count = 148;
+    uint64_t*    d_words = nullptr;       // P*W data words
+    uint64_t     data_words = 0;
+    bool         owns_words = true;
+    Slot         slot[2];
+    DevBuf       misc, compact_ws, build_bins, rows_all;
+    void*        stage[2] = {nullptr, nullptr};   // pinned
+    cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
+    bool         profiling = false;
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> ev_pool;
+    double       ms[K_N] = {0, 0, 0, 0, 0};
+    uint64_t     launches[K_N] = {0, 0, 0, 0, 0};
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1; bool ok = true;
+    explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; ok = cudaSetDevice(dev) == cudaSuccess; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int init_params(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, dyibf_params* prm, HashParams* hp)
+{
+    // _init, d_bloom_filter.h:245-254
+    if (bins == 0) return fail(DYIBF_ERR_ARG, "number of bins must be > 0");
+    if (h == 0 || h > DYIBF_MAX_HASH) return fail(DYIBF_ERR_ARG, "number of hash functions %u not in 1..%d", h, DYIBF_MAX_HASH);
+    if (k == 0 || k > 32) return fail(DYIBF_ERR_ARG, "k-mer size %u not in 1..32", k);
+    uint32_t W = (uint32_t)std::ceil((float)bins / 64.0f);           // std::ceil((float)_noOfBins / INT_WIDTH)
+    if (W > 65535) return fail(DYIBF_ERR_ARG, "%u bins need %u words per block; _binIntWidth is 16 bit", bins, W);
+    if ((uint64_t)W * 64 < bins) return fail(DYIBF_ERR_ARG, "bins %u not representable in float ceil", bins);
+    uint64_t S = (uint64_t)W * 64;
+    if (nbits < META_BITS + S) return fail(DYIBF_ERR_ARG, "vector of %llu bits too small for one block of %llu bits",
+                                           (unsigned long long)nbits, (unsigned long long)S);
+    uint64_t P = (nbits - META_BITS) / S;
+    prm->bins = bins; prm->n_hash = h; prm->kmer = k; prm->words_per_block = W;
+    prm->nbits = nbits; prm->n_blocks = P; prm->n_words = (nbits + 63) >> 6;
+    memset(hp, 0, sizeof *hp);
+    for (uint32_t i = 0; i < h; ++i) hp->pre[i] = (uint64_t)i ^ ((uint64_t)k * SEED);
+    hp->P = P; hp->pow2 = (P & (P - 1)) == 0;
+    hp->magic = hp->pow2 ? 0 : (uint64_t)((((unsigned __int128)1) << 64) / P);
+    hp->h = h; hp->k = k; hp->W = W; hp->bins = bins;
+    return DYIBF_OK;
+}
+
+int new_handle(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, int device, void* external, bool zero,
+               dyibf_filter** out)
+{
+    if (!out) return fail(DYIBF_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    dyibf_params prm; HashParams hp;
+    int rc = init_params(bins, h, k, nbits, &prm, &hp);
+    if (rc) return rc;
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(DYIBF_ERR_CUDA, "CUDA device %d not present (%d devices)", device, ndev);
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(DYIBF_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+    dyibf_filter* f = new dyibf_filter();
+    f->prm = prm; f->prm.device = device; f->hp = hp;
+    f->data_words = prm.n_blocks * prm.words_per_block;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) f->sm_count = prop.multiProcessorCount;
+    if (external) { f->d_words = (uint64_t*)external; f->owns_words = false; }
+    else {
+        cudaError_t e = cudaMalloc((void**)&f->d_words, f->data_words * 8);
+        if (e != cudaSuccess) { delete f; return fail(e == cudaErrorMemoryAllocation ? DYIBF_ERR_NOMEM : DYIBF_ERR_CUDA,
+                                                      "cudaMalloc of %llu filter bytes: %s", (unsigned long long)(f->data_words * 8), cudaGetErrorString(e)); }
+        if (zero) { e = cudaMemset(f->d_words, 0, f->data_words * 8); if (e != cudaSuccess) { cudaFree(f->d_words); delete f; return fail(DYIBF_ERR_CUDA, "cudaMemset: %s", cudaGetErrorString(e)); } }
+    }
+    for (int i = 0; i < 2; ++i) {
+        if (cudaStreamCreateWithFlags(&f->slot[i].st, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&f->stage_ev[i], cudaEventDisableTiming) != cudaSuccess) {
+            dyibf_destroy(f); return fail(DYIBF_ERR_CUDA, "stream/event creation failed");
+        }
+    }
+    *out = f;
+    return DYIBF_OK;
+}
+
+int ensure_stage(dyibf_filter* f)
+{
+    for (int i = 0; i < 2; ++i)
+        if (!f->stage[i]) CU(cudaMallocHost(&f->stage[i], STAGE_BYTES));
+    return DYIBF_OK;
+}
+
+// profiling: bracket a launch with events on its stream
+struct Scope {
+    dyibf_filter* f; cudaStream_t st; int kind; cudaEvent_t a = nullptr, b = nullptr;
+    static cudaEvent_t get(dyibf_filter* f) {
+        if (!f->ev_pool.empty()) { cudaEvent_t e = f->ev_pool.back(); f->ev_pool.pop_back(); return e; }
+        cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+    }
+    Scope(dyibf_filter* f_, cudaStream_t st_, int kind_) : f(f_), st(st_), kind(kind_) {
+        if (f->profiling) { a = get(f); b = get(f); cudaEventRecord(a, st); }
+    }
+    ~Scope() { if (a) { cudaEventRecord(b, st); f->pending.push_back({a, b, kind}); } }
+};
+
+void drain_profile(dyibf_filter* f)
+{
+    for (auto& p : f->pending) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+            f->ms[p.kind] += ms; f->launches[p.kind] += 1;
+        }
+        f->ev_pool.push_back(p.a); f->ev_pool.push_back(p.b);
+    }
+    f->pending.clear();
+}
+
+struct FileHeader { uint64_t nbits; uint32_t bins, h, k; uint64_t file_size; };
+
+int read_file_header(FILE* fp, const char* path, FileHeader* fh)
+{
+    uint64_t header = 0;
+    if (fread(&header, 8, 1, fp) != 1) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    if ((header >> 56) != 1) return fail(DYIBF_ERR_FORMAT, "File \"%s\" is not an sdsl bit_vector (width byte %u)", path, (unsigned)(header >> 56));
+    fh->nbits = header & ((1ULL << 56) - 1);
+    if (fh->nbits < META_BITS + 64) return fail(DYIBF_ERR_FORMAT, "File \"%s\": %llu bits is too small for a filter", path, (unsigned long long)fh->nbits);
+    if (fseeko(fp, 0, SEEK_END) != 0) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    fh->file_size = (uint64_t)ftello(fp);
+    uint64_t n_words = (fh->nbits + 63) >> 6;
+    if (fh->file_size < 8 + n_words * 8) return fail(DYIBF_ERR_FORMAT, "File \"%s\" is truncated: %llu bytes for %llu bits", path,
+                                                     (unsigned long long)fh->file_size, (unsigned long long)fh->nbits);
+    // _getMetadata, d_bloom_filter.h:255-265: three 64-bit reads at bit nbits-256 (+64, +128); they are
+    // word-aligned iff nbits is a multiple of 64, otherwise they straddle words (sdsl bits::read_int)
+    uint64_t m = fh->nbits - META_BITS;
+    uint64_t w0 = m >> 6, sh = m & 63;
+    uint64_t buf[5] = {0, 0, 0, 0, 0};
+    size_t want = (size_t)std::min<uint64_t>(5, n_words - w0);
+    if (fseeko(fp, (off_t)(8 + w0 * 8), SEEK_SET) != 0 || fread(buf, 8, want, fp) != want)
+        return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    auto get = [&](int i) { return sh ? (buf[i] >> sh) | (buf[i + 1] << (64 - sh)) : buf[i]; };
+    fh->bins = (uint32_t)get(0);           // truncation as the members have it (u32, u8, u8)
+    fh->h = (uint8_t)get(1);
+    fh->k = (uint8_t)get(2);
+    return DYIBF_OK;
+}
+
+// trailer + gap words for download/save: word index `w` of the sdsl array, w >= data_words
+void synth_tail(const dyibf_filter* f, uint64_t first, uint64_t n, uint64_t* out)
+{
+    memset(out, 0, n * 8);
+    const uint64_t m = f->prm.nbits - META_BITS;
+    const uint64_t vals[3] = {f->prm.bins, f->prm.n_hash, f->prm.kmer};
+    for (int i = 0; i < 3; ++i) {                                     // set_int at bit m + 64 i (_setMetadata :267-277)
+        uint64_t bit = m + 64 * i, w = bit >> 6, o = bit & 63;
+        if (w >= first && w < first + n) out[w - first] |= vals[i] << o;
+        if (o && w + 1 >= first && w + 1 < first + n) out[w + 1 - first] |= vals[i] >> (64 - o);
+    }
+}
+
+} // namespace
+
+extern "C" {
+
+const char* dyibf_last_error(void) { return g_err.c_str(); }
+
+int dyibf_device_count(int* count)
+{
+    if (!count) return fail(DYIBF_ERR_ARG, "count is NULL");
+    CU(cudaGetDeviceCount(count));
+    return DYIBF_OK;
+}
+
+int dyibf_create(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device, dyibf_filter** out)
+{
+    return new_handle(bins, n_hash, kmer, nbits, device, nullptr, true, out);
+}
+
+int dyibf_attach(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device, void* device_words,
+                 dyibf_filter** out)
+{
+    if (!device_words) return fail(DYIBF_ERR_ARG, "device_words is NULL");
+    if (((uintptr_t)device_words & 15) != 0) return fail(DYIBF_ERR_ARG, "device_words must be 16-byte aligned");
+    return new_handle(bins, n_hash, kmer, nbits, device, device_words, false, out);
+}
+
+void dyibf_destroy(dyibf_filter* f)
+{
+    if (!f) return;
+    DeviceGuard guard(f->prm.device);
+    cudaDeviceSynchronize();
+    drain_profile(f);
+    for (auto e : f->ev_pool) cudaEventDestroy(e);
+    for (int i = 0; i < 2; ++i) {
+        Slot& s = f->slot[i];
+        s.in_bytes.release(); s.in_offsets.release(); s.packed.release(); s.meta.release(); s.rows.release(); s.counts.release();
+        if (s.st) cudaStreamDestroy(s.st);
+        if (f->stage[i]) cudaFreeHost(f->stage[i]);
+        if (f->stage_ev[i]) cudaEventDestroy(f->stage_ev[i]);
+    }
+    f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release();
+    if (f->owns_words && f->d_words) cudaFree(f->d_words);
+    delete f;
+}
+
+int dyibf_get_params(const dyibf_filter* f, dyibf_params* out)
+{
+    if (!f || !out) return fail(DYIBF_ERR_ARG, "NULL argument");
+    *out = f->prm;
+    return DYIBF_OK;
+}
+
+double dyibf_size_mb(const dyibf_filter* f)
+{
+    // sdsl::size_in_mega_bytes = serialized bytes / 2^20: 8-byte header + words
+    return f ? (double)(8 + f->prm.n_words * 8) / (1024.0 * 1024.0) : 0.0;
+}
+
+void* dyibf_device_words(dyibf_filter* f) { return f ? f->d_words : nullptr; }
+
+int dyibf_peek_file(const char* path, uint32_t* bins, uint32_t* n_hash, uint32_t* kmer, uint64_t* nbits)
+{
+    if (!path) return fail(DYIBF_ERR_ARG, "path is NULL");
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    FileHeader fh; int rc = read_file_header(fp, path, &fh);
+    fclose(fp);
+    if (rc) return rc;
+    if (bins) *bins = fh.bins; if (n_hash) *n_hash = fh.h; if (kmer) *kmer = fh.k; if (nbits) *nbits = fh.nbits;
+    return DYIBF_OK;
+}
+
+static int load_impl(const char* path, bool expect, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits,
+                     int device, dyibf_filter** out)
+{
+    if (!path || !out) return fail(DYIBF_ERR_ARG, "NULL argument");
+    *out = nullptr;
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    FileHeader fh; int rc = read_file_header(fp, path, &fh);
+    if (rc) { fclose(fp); return rc; }
+    if (expect) {
+        if (fh.nbits != nbits) { fclose(fp); return fail(DYIBF_ERR_SIZE_MISMATCH, "Size mismatch: \n\t Loaded file \t%llu bits\n\t expected\t%llu",
+                                                          (unsigned long long)fh.nbits, (unsigned long long)nbits); }
+    } else { bins = fh.bins; n_hash = fh.h; kmer = fh.k; nbits = fh.nbits; }
+    dyibf_filter* f = nullptr;
+    rc = new_handle(bins, n_hash, kmer, nbits, device, nullptr, false, &f);
+    if (rc) { fclose(fp); return rc; }
+    DeviceGuard guard(device);
+    rc = ensure_stage(f);
+    // stream the data words: disk -> pinned (alternating) -> HBM
+    uint64_t left = f->data_words * 8, done = 0;
+    int cur = 0;
+    if (!rc && fseeko(fp, 8, SEEK_SET) != 0) rc = fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    while (!rc && left) {
+        size_t n = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
+        cudaEventSynchronize(f->stage_ev[cur]);                      // previous copy out of this buffer finished
+        if (fread(f->stage[cur], 1, n, fp) != n) { rc = fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path); break; }
+        cudaError_t e = cudaMemcpyAsync((char*)f->d_words + done, f->stage[cur], n, cudaMemcpyHostToDevice, f->slot[0].st);
+        if (e == cudaSuccess) e = cudaEventRecord(f->stage_ev[cur], f->slot[0].st);
+        if (e != cudaSuccess) { rc = fail(DYIBF_ERR_CUDA, "filter upload: %s", cudaGetErrorString(e)); break; }
+        done += n; left -= n; cur ^= 1;
+    }
+    fclose(fp);
+    if (!rc && cudaStreamSynchronize(f->slot[0].st) != cudaSuccess) rc = fail(DYIBF_ERR_CUDA, "filter upload failed");
+    if (rc) { std::string keep = g_err; dyibf_destroy(f); g_err = keep; return rc; }
+    *out = f;
+    return DYIBF_OK;
+}
+
+int dyibf_load_file(const char* path, int device, dyibf_filter** out)
+{
+    return load_impl(path, false, 0, 0, 0, 0, device, out);
+}
+
+int dyibf_load_file_expect(const char* path, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device,
+                           dyibf_filter** out)
+{
+    return load_impl(path, true, bins, n_hash, kmer, nbits, device, out);
+}
+
+int dyibf_upload_words(dyibf_filter* f, const uint64_t* host_words, uint64_t first, uint64_t n)
+{
+    if (!f || (!host_words && n)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    if (first + n > f->prm.n_words) return fail(DYIBF_ERR_ARG, "word range [%llu,+%llu) beyond %llu words",
+                                                (unsigned long long)first, (unsigned long long)n, (unsigned long long)f->prm.n_words);
+    DeviceGuard guard(f->prm.device);
+    if (first >= f->data_words) return DYIBF_OK;                      // gap / trailer: synthesised
+    n = std::min<uint64_t>(n, f->data_words - first);
+    int rc = ensure_stage(f); if (rc) return rc;
+    uint64_t left = n * 8, done = 0; int cur = 0;
+    while (left) {
+        size_t c = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
+        CU(cudaEventSynchronize(f->stage_ev[cur]));
+        memcpy(f->stage[cur], (const char*)host_words + done, c);
+        CU(cudaMemcpyAsync((char*)(f->d_words + first) + done, f->stage[cur], c, cudaMemcpyHostToDevice, f->slot[0].st));
+        CU(cudaEventRecord(f->stage_ev[cur], f->slot[0].st));
+        done += c; left -= c; cur ^= 1;
+    }
+    CU(cudaStreamSynchronize(f->slot[0].st));
+    return DYIBF_OK;
+}
+
+int dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first, uint64_t n)
+{
+    if (!f || (!host_words && n)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    if (first + n > f->prm.n_words) return fail(DYIBF_ERR_ARG, "word range [%llu,+%llu) beyond %llu words",
+                                                (unsigned long long)first, (unsigned long long)n, (unsigned long long)f->prm.n_words);
+    DeviceGuard guard(f->prm.device);
+    uint64_t nd = first < f->data_words ? std::min<uint64_t>(n, f->data_words - first) : 0;
+    if (nd) {
+        int rc = ensure_stage(f); if (rc) return rc;
+        uint64_t left = nd * 8, done = 0;
+        // two pinned buffers: the next D2H is in flight while the previous buffer is copied to the caller
+        size_t c[2] = {0, 0}; uint64_t at[2] = {0, 0}; int cur = 0;
+        auto issue = [&](int b) -> cudaError_t {
+            c[b] = (size_t)std::min<uint64_t>(left, STAGE_BYTES); at[b] = done;
+            cudaError_t e = cudaMemcpyAsync(f->stage[b], (const char*)(f->d_words + first) + done, c[b],
+                                            cudaMemcpyDeviceToHost, f->slot[0].st);
+            if (e == cudaSuccess) e = cudaEventRecord(f->stage_ev[b], f->slot[0].st);
+            done += c[b]; left -= c[b];
+            return e;
+        };
+        CU(issue(cur));
+        while (c[cur]) {
+            int nx = cur ^ 1; c[nx] = 0;
+            if (left) CU(issue(nx));
+            CU(cudaEventSynchronize(f->stage_ev[cur]));
+            memcpy((char*)host_words + at[cur], f->stage[cur], c[cur]);
+            cur = nx;
+        }
+    }
+    if (n > nd) synth_tail(f, first + nd, n - nd, host_words + nd);
+    return DYIBF_OK;
+}
+
+int dyibf_save_file(dyibf_filter* f, const char* path)
+{
+    if (!f || !path) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    int rc = ensure_stage(f); if (rc) return rc;
+    FILE* fp = fopen(path, "wb");
+    if (!fp) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
+    uint64_t header = (1ULL << 56) | f->prm.nbits;
+    bool ok = fwrite(&header, 8, 1, fp) == 1;
+    uint64_t left = f->data_words * 8, done = 0; int cur = 0;
+    size_t c[2] = {0, 0};
+    // HBM -> pinned (alternating) -> disk; the next D2H is in flight while the previous buffer is written
+    if (ok && left) {
+        c[cur] = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
+        ok = cudaMemcpyAsync(f->stage[cur], (const char*)f->d_words + done, c[cur], cudaMemcpyDeviceToHost, f->slot[0].st) == cudaSuccess &&
+             cudaEventRecord(f->stage_ev[cur], f->slot[0].st) == cudaSuccess;
+        done += c[cur]; left -= c[cur];
+    }
+    while (ok && c[cur]) {
+        int nx = cur ^ 1; c[nx] = 0;
+        if (left) {
+            c[nx] = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
+            ok = cudaMemcpyAsync(f->stage[nx], (const char*)f->d_words + done, c[nx], cudaMemcpyDeviceToHost, f->slot[0].st) == cudaSuccess &&
+                 cudaEventRecord(f->stage_ev[nx], f->slot[0].st) == cudaSuccess;
+            done += c[nx]; left -= c[nx];
+        }
+        ok = ok && cudaEventSynchronize(f->stage_ev[cur]) == cudaSuccess && fwrite(f->stage[cur], 1, c[cur], fp) == c[cur];
+        cur = nx;
+    }
+    if (ok) {
+        uint64_t tail_n = f->prm.n_words - f->data_words;
+        std::vector<uint64_t> tail(tail_n);
+        synth_tail(f, f->data_words, tail_n, tail.data());
+        ok = fwrite(tail.data(), 8, tail_n, fp) == tail_n;
+    }
+    ok = (fclose(fp) == 0) && ok;
+    if (!ok) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
+    return DYIBF_OK;
+}
+
+} // extern "C"
+
+// ============================================================================================================
+// query / compaction / build drivers
+// ============================================================================================================
+namespace {
+
+// pack + query of one device-resident batch on stream st, using the workspace of slot sl
+int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t total_bytes, int encoding, uint32_t group,
+                    int derive_rc, uint32_t threshold, uint32_t max_seq_len, uint64_t* d_rows, uint16_t* d_counts,
+                    cudaStream_t st)
+{
+    const uint64_t n_in = (uint64_t)src.n_ranges * src.cnt;
+    const uint64_t n_total = derive_rc ? 2 * n_in : n_in;
+    if (n_total == 0) return DYIBF_OK;
+    if (n_total > 0xffffffffull) return fail(DYIBF_ERR_ARG, "too many sequences in one batch");
+    const uint32_t n_rows = (uint32_t)(n_total / group);
+    const uint64_t words_one = packed_words_for(total_bytes, n_in);
+    CU(sl.packed.reserve((derive_rc ? 2 : 1) * words_one * 8));
+    CU(sl.meta.reserve(n_total * sizeof(SeqMeta)));
+    {
+        Scope sc(f, st, K_PACK);
+        CU(launch_pack(src, encoding, derive_rc, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words_one, words_one, st));
+    }
+    uint32_t max_kmers = 0;                                     // 0 = unknown -> 16-bit counters
+    if (max_seq_len) max_kmers = max_seq_len >= f->hp.k ? max_seq_len - f->hp.k + 1 : 1;
+    {
+        Scope sc(f, st, K_QUERY);
+        CU(launch_query(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, n_rows, group,
+                        threshold, max_kmers, d_rows, d_counts, f->sm_count, st));
+    }
+    return DYIBF_OK;
+}
+
+int check_query_args(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
+                     int group, int derive_rc, uint32_t threshold)
+{
+    if (!f) return fail(DYIBF_ERR_ARG, "filter is NULL");
+    if (n_seqs && (!offsets || !seqs)) return fail(DYIBF_ERR_ARG, "NULL sequence buffers");
+    if (encoding < DYIBF_ENC_DNA5 || encoding > DYIBF_ENC_ASCII) return fail(DYIBF_ERR_ARG, "unknown encoding %d", encoding);
+    if (group != 1 && group != 2 && group != 4) return fail(DYIBF_ERR_ARG, "group must be 1, 2 or 4 (got %d)", group);
+    if (derive_rc && group == 1) return fail(DYIBF_ERR_ARG, "derive_rc needs group 2 (single-end) or 4 (paired-end)");
+    const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
+    if (n_total % group) return fail(DYIBF_ERR_ARG, "%llu sequences do not divide into groups of %d", (unsigned long long)n_total, group);
+    if (threshold > 65535) return fail(DYIBF_ERR_ARG, "threshold %u exceeds uint16", threshold);
+    return DYIBF_OK;
+}
+
+// Host-mode query: the rows of [0, n_rows) are produced chunk by chunk through two stream slots
+// (H2D of chunk c+1 overlaps pack+query of chunk c overlaps D2H of chunk c-1).
+// Destination: h_rows (host, per-chunk D2H) and/or d_rows_all (device, whole batch).
+int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding, int group,
+               int derive_rc, uint32_t threshold, uint32_t max_seq_len, uint64_t* h_rows, uint64_t* d_rows_all,
+               uint16_t* h_counts)
+{
+    const uint32_t group_in = derive_rc ? group / 2 : group;
+    const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
+    const uint32_t n_rows = (uint32_t)(n_total / group);
+    if (n_rows == 0) return DYIBF_OK;
+    const uint32_t W = f->prm.words_per_block, k = f->hp.k;
+    if (!max_seq_len) {
+        uint64_t mx = 0;
+        for (uint32_t s = 0; s < n_seqs; ++s) {
+            if (offsets[s + 1] < offsets[s]) return fail(DYIBF_ERR_ARG, "offsets not monotone at %u", s);
+            mx = std::max(mx, offsets[s + 1] - offsets[s]);
+        }
+        if (mx > 0xffffffffull) return fail(DYIBF_ERR_ARG, "sequence longer than 2^32");
+        max_seq_len = (uint32_t)std::max<uint64_t>(mx, 1);
+    }
+    if (max_seq_len >= k && max_seq_len - k + 1 > 65535)
+        return fail(DYIBF_ERR_ARG, "a sequence of %u bases has more than 65535 k-mers (uint16 counts in the reference)", max_seq_len);
+
+    const uint64_t total_bytes = offsets[n_seqs] - offsets[0];
+    const uint64_t per_row = total_bytes / n_rows + 8ull * group_in + 8ull * W + 1;
+    uint64_t chunk_rows = (48ull << 20) / per_row;
+    if (h_counts) chunk_rows = std::min<uint64_t>(chunk_rows, (256ull << 20) / ((uint64_t)group * f->prm.bins * 2 + 1));
+    chunk_rows = std::max<uint64_t>(chunk_rows, 1024);
+    chunk_rows = std::min<uint64_t>(chunk_rows, n_rows);
+
+    int rc = DYIBF_OK; uint32_t c = 0;
+    for (uint64_t a = 0; a < n_rows && !rc; a += chunk_rows, ++c) {
+        const uint32_t cnt = (uint32_t)std::min<uint64_t>(chunk_rows, n_rows - a);
+        Slot& sl = f->slot[c & 1];
+        PackSource src; memset(&src, 0, sizeof src);
+        src.n_ranges = group_in; src.cnt = cnt;
+        uint64_t bytes = 0;
+        for (uint32_t g = 0; g < group_in; ++g) {
+            const uint64_t s0 = (uint64_t)g * n_rows + a;
+            src.first_off[g] = offsets[s0]; src.pack_base[g] = bytes;
+            bytes += offsets[s0 + cnt] - offsets[s0];
+        }
+        CU(sl.in_bytes.reserve(bytes + 16));
+        CU(sl.in_offsets.reserve((uint64_t)group_in * (cnt + 1) * 8));
+        CU(sl.rows.reserve((uint64_t)cnt * W * 8));
+        uint16_t* d_counts = nullptr;
+        if (h_counts) { CU(sl.counts.reserve((uint64_t)group * cnt * f->prm.bins * 2)); d_counts = (uint16_t*)sl.counts.p; }
+        for (uint32_t g = 0; g < group_in; ++g) {
+            const uint64_t s0 = (uint64_t)g * n_rows + a;
+            const uint64_t nb = offsets[s0 + cnt] - offsets[s0];
+            uint8_t* dst = (uint8_t*)sl.in_bytes.p + src.pack_base[g];
+            if (nb) CU(cudaMemcpyAsync(dst, seqs + offsets[s0], nb, cudaMemcpyHostToDevice, sl.st));
+            uint64_t* doff = (uint64_t*)sl.in_offsets.p + (uint64_t)g * (cnt + 1);
+            CU(cudaMemcpyAsync(doff, offsets + s0, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
+            src.bytes[g] = dst - src.first_off[g];
+            src.offsets[g] = doff;
+        }
+        uint64_t* d_rows = d_rows_all ? d_rows_all + a * W : (uint64_t*)sl.rows.p;
+        rc = query_on_device(f, sl, src, bytes, encoding, (uint32_t)group, derive_rc, threshold, max_seq_len, d_rows, d_counts, sl.st);
+        if (rc) break;
+        if (h_rows) CU(cudaMemcpyAsync(h_rows + a * W, d_rows, (uint64_t)cnt * W * 8, cudaMemcpyDeviceToHost, sl.st));
+        if (h_counts)
+            for (uint32_t g = 0; g < (uint32_t)group; ++g)
+                CU(cudaMemcpyAsync(h_counts + ((uint64_t)g * n_rows + a) * f->prm.bins, d_counts + (uint64_t)g * cnt * f->prm.bins,
+                                   (uint64_t)cnt * f->prm.bins * 2, cudaMemcpyDeviceToHost, sl.st));
+    }
+    cudaError_t e0 = cudaStreamSynchronize(f->slot[0].st), e1 = cudaStreamSynchronize(f->slot[1].st);
+    if (rc) return rc;
+    if (e0 != cudaSuccess || e1 != cudaSuccess)
+        return fail(DYIBF_ERR_CUDA, "query pipeline: %s", cudaGetErrorString(e0 != cudaSuccess ? e0 : e1));
+    return DYIBF_OK;
+}
+
+// compaction of device rows; bin_offsets/read_ids are device pointers; *total on the host (synchronises st)
+int compact_on_device(dyibf_filter* f, const uint64_t* d_rows, uint32_t n_rows, uint64_t* d_bin_offsets,
+                      uint32_t* d_read_ids, uint64_t capacity, uint64_t* total, cudaStream_t st)
+{
+    const uint32_t bins = f->prm.bins;
+    CU(f->compact_ws.reserve(compact_workspace_bytes(bins, n_rows)));
+    uint64_t* ws = (uint64_t*)f->compact_ws.p;
+    CU(cudaMemsetAsync(ws, 0, compact_workspace_bytes(bins, n_rows), st));
+    uint64_t tot = 0;
+    {
+        Scope sc(f, st, K_COMPACT);
+        CU(launch_compact_count(d_rows, n_rows, bins, ws, st));
+        CU(launch_compact_scan(ws, bins, n_rows, d_bin_offsets, st));
+    }
+    CU(cudaMemcpyAsync(&tot, d_bin_offsets + bins, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (total) *total = tot;
+    if (tot > capacity) return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu",
+                                    (unsigned long long)tot, (unsigned long long)capacity);
+    {
+        Scope sc(f, st, K_COMPACT);
+        CU(launch_compact_fill(d_rows, n_rows, bins, ws, d_read_ids, capacity, st));
+    }
+    return DYIBF_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+uint16_t dyibf_threshold_rate(float error_rate, uint32_t kmer, uint16_t read_len)
+{
+    // DisOptions::getThreshold, d_mapper.h:83-92 — float product truncated to uint16, unsigned arithmetic after
+    uint16_t maxError = (uint16_t)(error_rate * read_len);
+    if (kmer * (1u + maxError) > read_len) return 0;
+    return (uint16_t)(read_len - kmer * (1u + maxError) + 1);
+}
+
+uint16_t dyibf_threshold(int e_percent, uint32_t kmer, uint16_t read_len)
+{
+    return dyibf_threshold_rate((float)(e_percent / 100.0), kmer, read_len);   // d_mapper.cpp:340-342
+}
+
+int dyibf_query_batch(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
+                      int group, int derive_rc, uint32_t threshold, uint32_t max_seq_len, uint64_t* out_rows,
+                      uint16_t* out_counts, int mem, void* stream)
+{
+    int rc = check_query_args(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold);
+    if (rc) return rc;
+    if (n_seqs && !out_rows) return fail(DYIBF_ERR_ARG, "out_rows is NULL");
+    if (n_seqs == 0) return DYIBF_OK;
+    DeviceGuard guard(f->prm.device);
+    if (mem == DYIBF_MEM_HOST)
+        return query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, max_seq_len, out_rows, nullptr, out_counts);
+    if (mem != DYIBF_MEM_DEVICE) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
+    // device mode: one range, whole batch, caller's stream; total bytes are not known on the host without a
+    // read-back, so the two offsets that bound the batch are fetched (16 bytes, synchronises the stream)
+    cudaStream_t st = (cudaStream_t)stream;
+    uint64_t first = 0, last = 0;
+    CU(cudaMemcpyAsync(&first, offsets, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&last, offsets + n_seqs, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (last < first) return fail(DYIBF_ERR_ARG, "offsets not monotone");
+    if (max_seq_len >= f->hp.k && max_seq_len - f->hp.k + 1 > 65535)
+        return fail(DYIBF_ERR_ARG, "a sequence of %u bases has more than 65535 k-mers (uint16 counts in the reference)", max_seq_len);
+    PackSource src; memset(&src, 0, sizeof src);
+    src.n_ranges = 1; src.cnt = n_seqs; src.bytes[0] = seqs; src.offsets[0] = offsets; src.first_off[0] = first; src.pack_base[0] = 0;
+    // bytes[0][offsets[i]] must be base 0 of sequence i: seqs is indexed by the offsets as given
+    return query_on_device(f, f->slot[0], src, last - first, encoding, (uint32_t)group, derive_rc, threshold, max_seq_len,
+                           out_rows, out_counts, st);
+}
+
+int dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64_t* bin_offsets, uint32_t* read_ids,
+                  uint64_t capacity, uint64_t* total, int mem, void* stream)
+{
+    if (!f || !bin_offsets || (n_rows && !rows) || (capacity && !read_ids)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
+    if (mem == DYIBF_MEM_DEVICE)
+        return compact_on_device(f, rows, n_rows, bin_offsets, read_ids, capacity, total, (cudaStream_t)stream);
+    if (mem != DYIBF_MEM_HOST) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
+    Slot& sl = f->slot[0];
+    CU(sl.rows.reserve((uint64_t)n_rows * W * 8 + 8));
+    CU(f->misc.reserve((uint64_t)(bins + 1) * 8));
+    if (n_rows) CU(cudaMemcpyAsync(sl.rows.p, rows, (uint64_t)n_rows * W * 8, cudaMemcpyHostToDevice, sl.st));
+    // pass 1 + scan give the total; the id buffer is sized from it
+    uint64_t tot = 0;
+    int rc = compact_on_device(f, (const uint64_t*)sl.rows.p, n_rows, (uint64_t*)f->misc.p, nullptr, 0, &tot, sl.st);
+    if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
+    CU(cudaMemcpyAsync(bin_offsets, f->misc.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
+    CU(cudaStreamSynchronize(sl.st));
+    if (total) *total = tot;
+    if (tot > capacity) return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu",
+                                    (unsigned long long)tot, (unsigned long long)capacity);
+    if (tot == 0) return DYIBF_OK;
+    CU(sl.counts.reserve(tot * 4));
+    {
+        Scope sc(f, sl.st, K_COMPACT);
+        CU(launch_compact_fill((const uint64_t*)sl.rows.p, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)sl.counts.p, tot, sl.st));
+    }
+    CU(cudaMemcpyAsync(read_ids, sl.counts.p, tot * 4, cudaMemcpyDeviceToHost, sl.st));
+    CU(cudaStreamSynchronize(sl.st));
+    return DYIBF_OK;
+}
+
+int dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
+                   int group, int derive_rc, uint32_t threshold, uint64_t* bin_offsets, uint32_t* read_ids,
+                   uint64_t capacity, uint64_t* total)
+{
+    int rc = check_query_args(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold);
+    if (rc) return rc;
+    if (!bin_offsets || (capacity && !read_ids)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
+    const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
+    const uint32_t n_rows = (uint32_t)(n_total / group);
+    // rows of the whole batch stay in HBM; only the CSR lists cross PCIe
+    CU(f->rows_all.reserve((uint64_t)n_rows * W * 8 + 8));
+    uint64_t* d_rows = (uint64_t*)f->rows_all.p;
+    if (n_rows) {
+        rc = query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, 0, nullptr, d_rows, nullptr);
+        if (rc) return rc;
+    }
+    Slot& sl = f->slot[0];
+    CU(f->misc.reserve((uint64_t)(bins + 1) * 8));
+    uint64_t tot = 0;
+    rc = compact_on_device(f, d_rows, n_rows, (uint64_t*)f->misc.p, nullptr, 0, &tot, sl.st);
+    if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
+    CU(cudaMemcpyAsync(bin_offsets, f->misc.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
+    CU(cudaStreamSynchronize(sl.st));
+    if (total) *total = tot;
+    if (tot > capacity) return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu",
+                                    (unsigned long long)tot, (unsigned long long)capacity);
+    if (tot == 0) return DYIBF_OK;
+    CU(sl.counts.reserve(tot * 4));
+    {
+        Scope sc(f, sl.st, K_COMPACT);
+        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)sl.counts.p, tot, sl.st));
+    }
+    CU(cudaMemcpyAsync(read_ids, sl.counts.p, tot * 4, cudaMemcpyDeviceToHost, sl.st));
+    CU(cudaStreamSynchronize(sl.st));
+    return DYIBF_OK;
+}
+
+} // extern "C"
+
+// ============================================================================================================
+// build / clear / instrumentation
+// ============================================================================================================
+extern "C" {
+
+int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
+                        const uint32_t* bin_ids, int encoding, int mem, void* stream)
+{
+    if (!f) return fail(DYIBF_ERR_ARG, "filter is NULL");
+    if (n_seqs == 0) return DYIBF_OK;
+    if (!seqs || !offsets || !bin_ids) return fail(DYIBF_ERR_ARG, "NULL argument");
+    if (encoding < DYIBF_ENC_DNA5 || encoding > DYIBF_ENC_ASCII) return fail(DYIBF_ERR_ARG, "unknown encoding %d", encoding);
+    DeviceGuard guard(f->prm.device);
+    if (mem == DYIBF_MEM_DEVICE) {
+        cudaStream_t st = (cudaStream_t)stream;
+        uint64_t first = 0, last = 0;
+        CU(cudaMemcpyAsync(&first, offsets, 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(&last, offsets + n_seqs, 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (last < first) return fail(DYIBF_ERR_ARG, "offsets not monotone");
+        Slot& sl = f->slot[0];
+        PackSource src; memset(&src, 0, sizeof src);
+        src.n_ranges = 1; src.cnt = n_seqs; src.bytes[0] = seqs; src.offsets[0] = offsets; src.first_off[0] = first;
+        const uint64_t words = packed_words_for(last - first, n_seqs);
+        CU(sl.packed.reserve(words * 8));
+        CU(sl.meta.reserve((uint64_t)n_seqs * sizeof(SeqMeta)));
+        { Scope sc(f, st, K_PACK);
+          CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, st)); }
+        { Scope sc(f, st, K_BUILD);
+          CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st)); }
+        return DYIBF_OK;
+    }
+    if (mem != DYIBF_MEM_HOST) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
+    for (uint32_t s = 0; s < n_seqs; ++s) {
+        if (offsets[s + 1] < offsets[s]) return fail(DYIBF_ERR_ARG, "offsets not monotone at %u", s);
+        if (offsets[s + 1] - offsets[s] > 0xffffffffull) return fail(DYIBF_ERR_ARG, "sequence %u longer than 2^32", s);
+        if (bin_ids[s] >= f->prm.bins) return fail(DYIBF_ERR_ARG, "bin %u of sequence %u out of range (%u bins)", bin_ids[s], s, f->prm.bins);
+    }
+    // chunks of whole sequences, ~64 MB of bases each, alternating between the two stream slots
+    const uint64_t target = 64ull << 20;
+    uint32_t a = 0, c = 0;
+    while (a < n_seqs) {
+        uint32_t b = a + 1;
+        while (b < n_seqs && offsets[b + 1] - offsets[a] <= target) ++b;
+        const uint32_t cnt = b - a;
+        const uint64_t bytes = offsets[b] - offsets[a];
+        Slot& sl = f->slot[c & 1];
+        CU(sl.in_bytes.reserve(bytes + 16));
+        CU(sl.in_offsets.reserve((uint64_t)(cnt + 1) * 8));
+        CU(sl.counts.reserve((uint64_t)cnt * 4));
+        const uint64_t words = packed_words_for(bytes, cnt);
+        CU(sl.packed.reserve(words * 8));
+        CU(sl.meta.reserve((uint64_t)cnt * sizeof(SeqMeta)));
+        if (bytes) CU(cudaMemcpyAsync(sl.in_bytes.p, seqs + offsets[a], bytes, cudaMemcpyHostToDevice, sl.st));
+        CU(cudaMemcpyAsync(sl.in_offsets.p, offsets + a, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
+        CU(cudaMemcpyAsync(sl.counts.p, bin_ids + a, (uint64_t)cnt * 4, cudaMemcpyHostToDevice, sl.st));
+        PackSource src; memset(&src, 0, sizeof src);
+        src.n_ranges = 1; src.cnt = cnt; src.first_off[0] = offsets[a];
+        src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[a]; src.offsets[0] = (const uint64_t*)sl.in_offsets.p;
+        { Scope sc(f, sl.st, K_PACK);
+          CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, sl.st)); }
+        { Scope sc(f, sl.st, K_BUILD);
+          CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
+                          (const uint32_t*)sl.counts.p, cnt, words, sl.st)); }
+        a = b; ++c;
+    }
+    CU(cudaStreamSynchronize(f->slot[0].st));
+    CU(cudaStreamSynchronize(f->slot[1].st));
+    return DYIBF_OK;
+}
+
+int dyibf_clear_bins(dyibf_filter* f, const uint32_t* bins, uint32_t n)
+{
+    if (!f || (n && !bins)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    if (n == 0) return DYIBF_OK;
+    std::vector<uint32_t> cols; std::vector<uint64_t> masks;
+    {
+        std::vector<uint32_t> sorted(bins, bins + n);
+        std::sort(sorted.begin(), sorted.end());
+        for (uint32_t b : sorted) {
+            if (b >= f->prm.bins) return fail(DYIBF_ERR_ARG, "bin %u out of range (%u bins)", b, f->prm.bins);
+            if (cols.empty() || cols.back() != (b >> 6)) { cols.push_back(b >> 6); masks.push_back(0); }
+            masks.back() |= 1ull << (b & 63);
+        }
+    }
+    DeviceGuard guard(f->prm.device);
+    const uint32_t nc = (uint32_t)cols.size();
+    CU(f->misc.reserve((uint64_t)nc * 16 + 16));
+    uint64_t* d_masks = (uint64_t*)f->misc.p;
+    uint32_t* d_cols = (uint32_t*)(d_masks + nc);
+    cudaStream_t st = f->slot[0].st;
+    CU(cudaMemcpyAsync(d_masks, masks.data(), (uint64_t)nc * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_cols, cols.data(), (uint64_t)nc * 4, cudaMemcpyHostToDevice, st));
+    { Scope sc(f, st, K_CLEAR);
+      CU(launch_clear(f->hp, f->d_words, d_cols, d_masks, nc, st)); }
+    CU(cudaStreamSynchronize(st));
+    return DYIBF_OK;
+}
+
+int dyibf_profile_enable(dyibf_filter* f, int on)
+{
+    if (!f) return fail(DYIBF_ERR_ARG, "filter is NULL");
+    f->profiling = on != 0;
+    return DYIBF_OK;
+}
+
+int dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset)
+{
+    if (!f || !out) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    drain_profile(f);
+    out->pack_ms = f->ms[K_PACK]; out->query_ms = f->ms[K_QUERY]; out->compact_ms = f->ms[K_COMPACT];
+    out->build_ms = f->ms[K_BUILD]; out->clear_ms = f->ms[K_CLEAR];
+    out->pack_launches = f->launches[K_PACK]; out->query_launches = f->launches[K_QUERY];
+    out->compact_launches = f->launches[K_COMPACT]; out->build_launches = f->launches[K_BUILD];
+    out->clear_launches = f->launches[K_CLEAR];
+    if (reset) for (int i = 0; i < K_N; ++i) { f->ms[i] = 0; f->launches[i] = 0; }
+    return DYIBF_OK;
+}
+
+int dyibf_host_alloc(void** ptr, size_t bytes)
+{
+    if (!ptr) return fail(DYIBF_ERR_ARG, "ptr is NULL");
+    CU(cudaMallocHost(ptr, bytes ? bytes : 1));
+    return DYIBF_OK;
+}
+
+void dyibf_host_free(void* ptr) { if (ptr) cudaFreeHost(ptr); }
+
+} // extern "C"

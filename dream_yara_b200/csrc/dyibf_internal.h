@@ -1,0 +1,70 @@
+// dyibf_internal.h — shared between the translation units of libdyibf.so (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/dyibf.h"
+
+namespace dyibf {
+
+// Everything a kernel needs to turn a k-mer value into h block indices
+// (reference: _init d_bloom_filter.h:245-254, getHashValue :286-291).
+struct HashParams {
+    uint64_t pre[DYIBF_MAX_HASH];   // _preCalcValues[i] = i ^ (k * seed)
+    uint64_t P;                     // _noOfHashPos
+    uint64_t magic;                 // floor(2^64 / P) when P is not a power of two
+    uint32_t pow2;                  // 1: block = v & (P-1)
+    uint32_t h;
+    uint32_t k;
+    uint32_t W;                     // 64-bit words per block
+    uint32_t bins;
+};
+
+// One packed sequence: 2 bits per base, first base in the two top bits of word 0 (so that a k-mer is a
+// funnel shift of two neighbouring words), N stored as A (the reference hashes N as A, alphabet_residue.h:680-683).
+struct SeqMeta {
+    uint64_t word_off;   // first u64 of this sequence in the packed buffer (ceil(len/32)+1 words are valid)
+    uint32_t len;        // bases
+    uint32_t flags;      // bit 0: first base is N (leading-N term of SeqAn's hashInit, shape_base.h:489)
+};
+
+// up to 4 byte ranges of the caller's sequence set that make up one device batch
+struct PackSource {
+    const uint8_t*  bytes[4];     // device pointer such that bytes[g][offsets[g][i]] is base 0 of sequence i of range g
+    const uint64_t* offsets[4];   // device, cnt+1 entries each (original, un-rebased values)
+    uint64_t        pack_base[4]; // byte position of range g inside the batch (monotone; defines word_off)
+    uint64_t        first_off[4]; // offsets[g][0]
+    uint32_t        n_ranges;
+    uint32_t        cnt;          // sequences per range
+};
+
+struct Profiler;
+
+// ---- launchers (each in its own .cu) ---------------------------------------------------------
+// pack: bytes -> packed words + meta for n_in = n_ranges*cnt sequences, and (derive_rc) their reverse
+// complements as sequences n_in .. 2*n_in-1.
+cudaError_t launch_pack(const PackSource& src, int encoding, int derive_rc, uint64_t* packed, SeqMeta* meta,
+                        uint64_t total_words, uint64_t rc_word_base, cudaStream_t st);
+// words needed for a batch whose ranges total `bytes` bytes and n_in sequences (per strand)
+static inline uint64_t packed_words_for(uint64_t bytes, uint64_t n_in) { return bytes / 32 + 2 * n_in + 2; }
+
+cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
+                         uint32_t n_rows, uint32_t group, uint32_t threshold, uint32_t max_kmers,
+                         uint64_t* out_rows, uint16_t* out_counts, int sm_count, cudaStream_t st);
+
+// build: every k-mer of the n_seqs packed forward sequences ORs h bits (bin = bin_ids[s]) into the filter
+cudaError_t launch_build(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
+                         const uint32_t* bin_ids, uint32_t n_seqs, uint64_t total_words, cudaStream_t st);
+
+// clear: for every hash block, words cols[i] &= ~masks[i]
+cudaError_t launch_clear(const HashParams& hp, uint64_t* filter, const uint32_t* cols, const uint64_t* masks, uint32_t n_cols,
+                         cudaStream_t st);
+
+// compaction: rows [n_rows x W] -> CSR.  workspace: counts matrix u64[(bins * n_chunks) + 1]
+static const uint32_t COMPACT_CHUNK_ROWS = 2048;
+size_t      compact_workspace_bytes(uint32_t bins, uint32_t n_rows);
+cudaError_t launch_compact_count(const uint64_t* rows, uint32_t n_rows, uint32_t bins, uint64_t* ws, cudaStream_t st);
+cudaError_t launch_compact_scan(uint64_t* ws, uint32_t bins, uint32_t n_rows, uint64_t* bin_offsets, cudaStream_t st);
+cudaError_t launch_compact_fill(const uint64_t* rows, uint32_t n_rows, uint32_t bins, const uint64_t* ws,
+                                uint32_t* read_ids, uint64_t capacity, cudaStream_t st);
+
+} // namespace dyibf

@@ -1,0 +1,270 @@
+"""Host-side mirror of seqan::SeqAnBloomFilter (reference: src/d_bloom_filter.h:41-331) over the C ABI.
+
+Same member names, argument meaning and error behaviour as the reference class; every method forwards to
+libdyibf.so (CUDA, sm_100a).  Batched entries (`whichBinsBatch`, `addSequences`, `compact`, `classify`) are
+what a patched clasifyLoadedReads / build_filter call; the per-sequence `whichBins` / `addKmers` stay for API
+parity and are batches of one.
+"""
+import ctypes as C
+import gzip
+import sys
+
+import numpy as np
+
+from . import _lib
+from ._lib import ENC_ASCII, ENC_DNA5, ENC_DNA5Q, MEM_DEVICE, MEM_HOST, check, lib
+
+filterMetadataSize = 256   # d_misc_options.h:40
+INT_WIDTH = 0x40           # d_misc_options.h:41
+
+
+def _ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def as_batch(seqs, encoding=None):
+    """Normalise sequence input to (concat uint8, offsets uint64, encoding).
+
+    Accepts a str/bytes (one ASCII sequence), a 1-D uint8 array (one sequence of Dna5 codes), a list of those,
+    or an already concatenated (concat, offsets) pair.
+    """
+    if isinstance(seqs, tuple) and len(seqs) == 2:
+        concat = np.ascontiguousarray(seqs[0], dtype=np.uint8)
+        offsets = np.ascontiguousarray(seqs[1], dtype=np.uint64)
+        return concat, offsets, ENC_DNA5 if encoding is None else encoding
+    if isinstance(seqs, (str, bytes, np.ndarray)):
+        seqs = [seqs]
+    parts, enc = [], encoding
+    for s in seqs:
+        if isinstance(s, str):
+            s = s.encode("ascii")
+        if isinstance(s, (bytes, bytearray)):
+            this = ENC_ASCII
+            arr = np.frombuffer(bytes(s), dtype=np.uint8)
+        else:
+            this = ENC_DNA5
+            arr = np.ascontiguousarray(s, dtype=np.uint8)
+        if enc is None:
+            enc = this
+        elif encoding is None and enc != this:
+            raise ValueError("mixed ASCII and code sequences in one batch")
+        parts.append(arr)
+    offsets = np.zeros(len(parts) + 1, dtype=np.uint64)
+    if parts:
+        offsets[1:] = np.cumsum([len(p) for p in parts], dtype=np.uint64)
+        concat = np.concatenate(parts) if len(parts) > 1 else np.ascontiguousarray(parts[0])
+    else:
+        concat = np.zeros(0, dtype=np.uint8)
+    if concat.size == 0:
+        concat = np.zeros(1, dtype=np.uint8)   # keep a valid address
+    return concat, offsets, ENC_DNA5 if enc is None else enc
+
+
+def read_fasta(path):
+    """Records of a FASTA/FASTQ(.gz) file as ASCII byte strings (what SeqFileIn::readRecord yields)."""
+    opener = gzip.open if str(path).endswith(".gz") else open
+    with opener(path, "rb") as fh:
+        data = fh.read()
+    recs = []
+    if data[:1] == b"@":                                   # FASTQ: 4-line records
+        lines = data.split(b"\n")
+        i = 0
+        while i + 1 < len(lines):
+            if lines[i].startswith(b"@"):
+                recs.append(lines[i + 1].strip())
+                i += 4
+            else:
+                i += 1
+        return recs
+    for chunk in data.split(b">")[1:]:
+        nl = chunk.find(b"\n")
+        body = chunk[nl + 1:] if nl >= 0 else b""
+        recs.append(body.replace(b"\n", b"").replace(b"\r", b"").replace(b" ", b""))
+    return recs
+
+
+class SeqAnBloomFilter:
+    """IBF resident in the HBM of one B200.  Constructors as in the reference:
+
+        SeqAnBloomFilter(n_bins, n_hash_func, kmer_size, vec_size)             d_bloom_filter.h:48
+        SeqAnBloomFilter(fileName, n_bins, n_hash_func, kmer_size, vec_size)   d_bloom_filter.h:59
+        SeqAnBloomFilter(fileName)                                             d_bloom_filter.h:79
+    """
+
+    def __init__(self, *args, device=0, _handle=None, _keep=None):
+        self._h = C.c_void_p()
+        self._keep = _keep                 # object owning externally attached device memory
+        L = lib()
+        if _handle is not None:
+            self._h = _handle
+        elif len(args) == 4:
+            n_bins, n_hash, kmer, vec_size = args
+            check(L.dyibf_create(n_bins, n_hash, kmer, vec_size, device, C.byref(self._h)))
+        elif len(args) == 1:
+            rc = L.dyibf_load_file(str(args[0]).encode(), device, C.byref(self._h))
+            self._exit_like_reference(rc)
+        elif len(args) == 5:
+            fileName, n_bins, n_hash, kmer, vec_size = args
+            rc = L.dyibf_load_file_expect(str(fileName).encode(), n_bins, n_hash, kmer, vec_size, device, C.byref(self._h))
+            self._exit_like_reference(rc)
+        else:
+            raise TypeError("SeqAnBloomFilter(n_bins, n_hash_func, kmer_size, vec_size) | (fileName) | "
+                            "(fileName, n_bins, n_hash_func, kmer_size, vec_size)")
+        p = _lib.Params()
+        check(L.dyibf_get_params(self._h, C.byref(p)))
+        self._noOfBins, self._noOfHashFunc, self._kmerSize = p.bins, p.n_hash, p.kmer
+        self._binIntWidth, self._noOfBits, self._noOfHashPos = p.words_per_block, p.nbits, p.n_blocks
+        self._blockBitSize = p.words_per_block * 64
+        self.n_words, self.device = p.n_words, p.device
+
+    @staticmethod
+    def _exit_like_reference(rc):
+        # the reference prints to std::cerr and calls exit(1) on load failure / size mismatch (:66-76,:81-85)
+        if rc in (_lib.ERR_IO, _lib.ERR_SIZE_MISMATCH, _lib.ERR_FORMAT):
+            sys.stderr.write(lib().dyibf_last_error().decode("utf-8", "replace") + "\n")
+            raise SystemExit(1)
+        check(rc)
+
+    @classmethod
+    def attach(cls, n_bins, n_hash, kmer, vec_size, device_ptr, device=0, keep=None):
+        """Filter whose P*W data words already sit in device memory owned by `keep` (e.g. a torch tensor)."""
+        h = C.c_void_p()
+        check(lib().dyibf_attach(n_bins, n_hash, kmer, vec_size, device, C.c_void_p(device_ptr), C.byref(h)))
+        return cls(device=device, _handle=h, _keep=keep)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().dyibf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    # ---- reference surface ------------------------------------------------------------------------------
+    def getNumberOfBins(self):
+        return self._noOfBins
+
+    def getKmerSize(self):
+        return self._kmerSize
+
+    def size_mb(self):
+        return lib().dyibf_size_mb(self._h)
+
+    def addKmers(self, text, binNo):
+        """addKmers(text, binNo), :91-94. The reference hashes len<k texts out of bounds; here they add nothing."""
+        self.addSequences([text], [binNo])
+
+    def addFastaFile(self, fastaFile, binNo):
+        """addFastaFile, :127-147: every record of the file (len >= k) goes to bin `binNo`."""
+        try:
+            recs = read_fasta(fastaFile)
+        except OSError:
+            raise RuntimeError("Unable to open contigs File: %s" % fastaFile)   # reference: throw const char*
+        recs = [r for r in recs if len(r) >= self._kmerSize]
+        if recs:
+            self.addSequences(recs, [binNo] * len(recs), encoding=ENC_ASCII)
+
+    def clearBins(self, bins2clear, threadsCount=1):
+        """clearBins, :99-123 (threadsCount is accepted and ignored: the GPU does the pass)."""
+        b = np.ascontiguousarray(bins2clear, dtype=np.uint32)
+        check(lib().dyibf_clear_bins(self._h, _ptr(b), b.size))
+
+    def save(self, fileName):
+        """save, :150-154 -> bool"""
+        return lib().dyibf_save_file(self._h, str(fileName).encode()) == _lib.OK
+
+    def whichBins(self, text, threshold, selected=None):
+        """whichBins(selected, text, threshold) :161-224 OR-accumulates into `selected`;
+        whichBins(text, threshold) :226-231 returns a fresh vector."""
+        rows = self.whichBinsBatch([text], threshold, group=1)
+        bits = np.unpackbits(rows.view(np.uint8), bitorder="little")[: self._noOfBins].astype(bool)
+        if selected is None:
+            return bits
+        sel = np.asarray(selected)
+        sel |= bits
+        return selected
+
+    # ---- batched entries --------------------------------------------------------------------------------
+    def addSequences(self, seqs, bin_ids, encoding=None):
+        concat, offsets, enc = as_batch(seqs, encoding)
+        bins = np.ascontiguousarray(bin_ids, dtype=np.uint32)
+        n = offsets.size - 1
+        if bins.size != n:
+            raise ValueError("bin_ids must have one entry per sequence")
+        check(lib().dyibf_add_sequences(self._h, _ptr(concat), _ptr(offsets), n, _ptr(bins), enc, MEM_HOST, None))
+
+    def whichBinsBatch(self, seqs, threshold, group=1, derive_rc=False, counts=False, encoding=None, max_seq_len=0):
+        """Rows [n_rows x W] u64 (bit b of word w = bin 64w+b); with counts=True also u16 [n_total x bins]."""
+        concat, offsets, enc = as_batch(seqs, encoding)
+        n = offsets.size - 1
+        n_total = 2 * n if derive_rc else n
+        if n_total % group:
+            raise ValueError("%d sequences do not divide into groups of %d" % (n_total, group))
+        rows = np.zeros((n_total // group, self._binIntWidth), dtype=np.uint64)
+        cnt = np.zeros((n_total, self._noOfBins), dtype=np.uint16) if counts else None
+        check(lib().dyibf_query_batch(self._h, _ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)),
+                                      int(threshold), int(max_seq_len), _ptr(rows), _ptr(cnt), MEM_HOST, None))
+        return (rows, cnt) if counts else rows
+
+    def compact(self, rows):
+        """Per-bin ascending row ids (CSR) from selection rows: (bin_offsets u64[bins+1], read_ids u32[total])."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint64).reshape(-1, self._binIntWidth)
+        offs = np.zeros(self._noOfBins + 1, dtype=np.uint64)
+        total = C.c_uint64(0)
+        L = lib()
+        rc = L.dyibf_compact(self._h, _ptr(rows), rows.shape[0], _ptr(offs), None, 0, C.byref(total), MEM_HOST, None)
+        if rc not in (_lib.OK, _lib.ERR_CAPACITY):
+            check(rc)
+        ids = np.zeros(max(int(total.value), 1), dtype=np.uint32)
+        if total.value:
+            check(L.dyibf_compact(self._h, _ptr(rows), rows.shape[0], _ptr(offs), _ptr(ids), total.value,
+                                  C.byref(total), MEM_HOST, None))
+        return offs, ids[: total.value]
+
+    def classify(self, seqs, threshold, group=2, derive_rc=True, encoding=None, capacity=None):
+        """Query + compaction in one call (rows stay in HBM): (bin_offsets, read_ids)."""
+        concat, offsets, enc = as_batch(seqs, encoding)
+        n = offsets.size - 1
+        n_rows = (2 * n if derive_rc else n) // group
+        offs = np.zeros(self._noOfBins + 1, dtype=np.uint64)
+        total = C.c_uint64(0)
+        cap = int(capacity) if capacity is not None else max(4 * n_rows, 1024)
+        L = lib()
+        while True:
+            ids = np.zeros(cap, dtype=np.uint32)
+            rc = L.dyibf_classify(self._h, _ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)), int(threshold),
+                                  _ptr(offs), _ptr(ids), cap, C.byref(total))
+            if rc == _lib.ERR_CAPACITY and capacity is None:
+                cap = int(total.value)
+                continue
+            check(rc)
+            return offs, ids[: total.value]
+
+    # ---- raw words / instrumentation ---------------------------------------------------------------------
+    def download_words(self, first=0, n=None):
+        n = self.n_words - first if n is None else n
+        out = np.zeros(n, dtype=np.uint64)
+        check(lib().dyibf_download_words(self._h, _ptr(out), first, n))
+        return out
+
+    def upload_words(self, words, first=0):
+        w = np.ascontiguousarray(words, dtype=np.uint64)
+        check(lib().dyibf_upload_words(self._h, _ptr(w), first, w.size))
+
+    def device_words(self):
+        return lib().dyibf_device_words(self._h)
+
+    def profile_enable(self, on=True):
+        check(lib().dyibf_profile_enable(self._h, int(on)))
+
+    def profile(self, reset=False):
+        p = _lib.Profile()
+        check(lib().dyibf_profile_get(self._h, C.byref(p), int(reset)))
+        return {k: getattr(p, k) for k, _ in p._fields_}
+
+    # device-pointer entry used by bench.py / multi-GPU code (torch tensors' data_ptr())
+    def query_device(self, seqs_ptr, offsets_ptr, n_seqs, threshold, rows_ptr, group=2, derive_rc=True,
+                     encoding=ENC_DNA5, max_seq_len=0, counts_ptr=None, stream=None):
+        check(lib().dyibf_query_batch(self._h, C.c_void_p(seqs_ptr), C.c_void_p(offsets_ptr), n_seqs, encoding, group,
+                                      int(bool(derive_rc)), int(threshold), int(max_seq_len), C.c_void_p(rows_ptr),
+                                      C.c_void_p(counts_ptr) if counts_ptr else None, MEM_DEVICE,
+                                      C.c_void_p(stream) if stream else None))

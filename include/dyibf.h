@@ -1,0 +1,157 @@
+/*
+ * dyibf.h — C ABI of libdyibf.so: the B200 (sm_100a) implementation of DREAM-Yara's interleaved
+ * Bloom filter (IBF) read->bin prefilter.
+ *
+ * This is the drop-in boundary.  The reference (temehi/dream_yara) has no FFI for this path; its
+ * boundary is the C++ class seqan::SeqAnBloomFilter in src/d_bloom_filter.h:41-331, used by
+ * src/d_mapper.h:308-387 (clasifyLoadedReads), src/d_build_filter.cpp:217-272 and
+ * src/d_update_filter.cpp:188-252.  Every entry point below names the reference member it replaces.
+ * include/d_bloom_filter.h in this repo re-creates the class on top of these calls.
+ *
+ * Rules: plain pointers and sizes only; no CPU fallback anywhere (a missing GPU is an error);
+ * one handle = one filter (or one bin-shard of a filter) resident in the HBM of one GPU.
+ * Calls on one handle must be serialised by the caller.  All functions return DYIBF_OK (0) or a
+ * negative error code; dyibf_last_error() gives the message of the calling thread's last failure.
+ *
+ * Notation (same as the reference members): B bins, W = ceil(B/64) 64-bit words per hash block
+ * (_binIntWidth), nbits = _noOfBits (includes the 256 metadata bits), P = (nbits-256)/(64 W)
+ * hash blocks (_noOfHashPos), h hash functions, k k-mer size.
+ */
+#ifndef DYIBF_H
+#define DYIBF_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DYIBF_OK                 0
+#define DYIBF_ERR_ARG           -1   /* bad argument                                              */
+#define DYIBF_ERR_IO            -2   /* file could not be opened / read / written                 */
+#define DYIBF_ERR_CUDA          -3   /* CUDA runtime error (incl. "no device")                    */
+#define DYIBF_ERR_FORMAT        -4   /* not an sdsl bit_vector file / bad trailer                 */
+#define DYIBF_ERR_SIZE_MISMATCH -5   /* file bit count != expected (d_bloom_filter.h:71-76)       */
+#define DYIBF_ERR_CAPACITY      -6   /* caller's output buffer too small                          */
+#define DYIBF_ERR_NOMEM         -7
+
+#define DYIBF_MAX_HASH           8
+
+/* how a sequence byte maps to a Dna5 code (A,C,G,T,N = 0..4) */
+#define DYIBF_ENC_DNA5   0   /* seqan::Dna5 ordValue; anything > 4 is N                              */
+#define DYIBF_ENC_DNA5Q  1   /* seqan::Dna5Q byte (reads in the mapper, store_seqs.h:57): >=252 is N */
+#define DYIBF_ENC_ASCII  2   /* FASTA characters through Iupac->Dna5: ACGTU (any case), rest N       */
+
+/* where the caller's buffers live */
+#define DYIBF_MEM_HOST   0
+#define DYIBF_MEM_DEVICE 1
+
+typedef struct dyibf_filter dyibf_filter;
+
+typedef struct dyibf_params {
+    uint32_t bins;        /* _noOfBins      */
+    uint32_t n_hash;      /* _noOfHashFunc  */
+    uint32_t kmer;        /* _kmerSize      */
+    uint32_t words_per_block; /* _binIntWidth (W) */
+    uint64_t nbits;       /* _noOfBits      */
+    uint64_t n_blocks;    /* _noOfHashPos (P) */
+    uint64_t n_words;     /* ceil(nbits/64): the whole sdsl word array incl. trailer */
+    int      device;      /* CUDA device ordinal */
+} dyibf_params;
+
+/* accumulated device time of the kernels of one handle (CUDA events; enable with dyibf_profile_enable) */
+typedef struct dyibf_profile {
+    double   pack_ms, query_ms, compact_ms, build_ms, clear_ms;
+    uint64_t pack_launches, query_launches, compact_launches, build_launches, clear_launches;
+} dyibf_profile;
+
+const char* dyibf_last_error(void);
+int  dyibf_device_count(int* count);
+
+/* ---- construction / destruction ------------------------------------------------------------ */
+
+/* SeqAnBloomFilter(n_bins, n_hash_func, kmer_size, vec_size), d_bloom_filter.h:48-57: zeroed filter */
+int  dyibf_create(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device,
+                  dyibf_filter** out);
+/* same, but the P*W data words live in caller-owned device memory (e.g. a buffer that was the target
+ * of an NCCL broadcast); the handle neither zeroes nor frees it */
+int  dyibf_attach(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device,
+                  void* device_words, dyibf_filter** out);
+/* SeqAnBloomFilter(fileName), d_bloom_filter.h:79-89: parameters come from the file's trailer */
+int  dyibf_load_file(const char* path, int device, dyibf_filter** out);
+/* SeqAnBloomFilter(fileName, n_bins, n_hash_func, kmer_size, vec_size), d_bloom_filter.h:59-77 */
+int  dyibf_load_file_expect(const char* path, uint32_t bins, uint32_t n_hash, uint32_t kmer,
+                            uint64_t nbits, int device, dyibf_filter** out);
+/* readFilterMetadata, d_mapper.cpp:532-548 (reads exactly the 32-byte trailer + the header) */
+int  dyibf_peek_file(const char* path, uint32_t* bins, uint32_t* n_hash, uint32_t* kmer, uint64_t* nbits);
+void dyibf_destroy(dyibf_filter* f);
+
+int  dyibf_get_params(const dyibf_filter* f, dyibf_params* out);       /* getNumberOfBins/getKmerSize :233-241 */
+double dyibf_size_mb(const dyibf_filter* f);                          /* size_mb :156-159 */
+void* dyibf_device_words(dyibf_filter* f);                            /* device pointer to the P*W data words */
+
+/* raw word transfer: words [first, first+n) of the sdsl array (data words only; n_words-4.. is the trailer,
+ * which the handle synthesises).  host <-> HBM through pinned staging. */
+int  dyibf_upload_words(dyibf_filter* f, const uint64_t* host_words, uint64_t first, uint64_t n);
+int  dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first, uint64_t n);
+/* save(fileName), d_bloom_filter.h:150-154 -> sdsl::store_to_file: byte-identical file */
+int  dyibf_save_file(dyibf_filter* f, const char* path);
+
+/* ---- build --------------------------------------------------------------------------------- */
+
+/* addKmers(text, binNo), d_bloom_filter.h:91-94,293-315, for n_seqs sequences at once (atomic-OR kernel).
+ * seqs: concatenated sequence bytes; offsets[n_seqs+1]; bin_ids[n_seqs].  Sequences shorter than k are
+ * skipped (:142).  mem says where seqs/offsets/bin_ids live. */
+int  dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
+                         const uint32_t* bin_ids, int encoding, int mem, void* stream);
+/* clearBins(bins2clear, threads), d_bloom_filter.h:99-123 */
+int  dyibf_clear_bins(dyibf_filter* f, const uint32_t* bins, uint32_t n);
+
+/* ---- query --------------------------------------------------------------------------------- */
+
+/* DisOptions::getThreshold, d_mapper.h:83-92 with errorRate = (float)(e_percent/100.0) (d_mapper.cpp:340-342) */
+uint16_t dyibf_threshold(int e_percent, uint32_t kmer, uint16_t read_len);
+uint16_t dyibf_threshold_rate(float error_rate, uint32_t kmer, uint16_t read_len);
+
+/* The filtering loop of clasifyLoadedReads (d_mapper.h:338-359) = whichBins (d_bloom_filter.h:161-224)
+ * on every strand/mate of every read, OR-ed per read.
+ *   seqs/offsets : n_seqs sequences.  If derive_rc != 0 the set is first extended to 2*n_seqs by appending
+ *                  the reverse complement of every sequence in order (appendReverseComplement,
+ *                  store_seqs.h:271-290; N stays N) — on the device, so only forward bytes cross PCIe.
+ *   group        : sequences per output row: 1 (plain whichBins per sequence), 2 (single-end: [fwd | rc]),
+ *                  4 (paired-end: [m1 | m2 | m1 rc | m2 rc]).  n_rows = n_total / group and row r is the OR
+ *                  over g < group of whichBins(seq[r + g*n_rows], threshold).
+ *   out_rows     : n_rows x W u64, bit b of word w <=> bin 64w+b selected.
+ *   out_counts   : optional (NULL to skip) n_total x bins u16: the per-bin k-mer counts (`counts`, :165).
+ *   max_seq_len  : longest sequence, 0 = unknown (host mode computes it; device mode then uses the
+ *                  16-bit counters).  Sequences with more than 65535 k-mers are rejected (u16 in the reference).
+ */
+int  dyibf_query_batch(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
+                       int encoding, int group, int derive_rc, uint32_t threshold, uint32_t max_seq_len,
+                       uint64_t* out_rows, uint16_t* out_counts, int mem, void* stream);
+
+/* origReadIdMap as `--threads 1` fills it (d_mapper.h:360-368): per bin the ascending ids of the rows that
+ * selected it, as CSR.  bin_offsets[bins+1] (u64), read_ids[capacity] (u32).  *total receives the number of
+ * (row,bin) pairs; DYIBF_ERR_CAPACITY if it exceeds capacity (bin_offsets is still complete). */
+int  dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64_t* bin_offsets,
+                   uint32_t* read_ids, uint64_t capacity, uint64_t* total, int mem, void* stream);
+
+/* clasifyLoadedReads (d_mapper.h:308-375) in one call, host buffers: query + compaction with the rows kept in
+ * HBM, so only the per-bin lists come back.  Arguments as dyibf_query_batch / dyibf_compact. */
+int  dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
+                    int encoding, int group, int derive_rc, uint32_t threshold,
+                    uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
+
+/* ---- instrumentation ----------------------------------------------------------------------- */
+int  dyibf_profile_enable(dyibf_filter* f, int on);
+int  dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset);
+
+/* pinned host memory helpers (callers that want full PCIe rate allocate their buffers here) */
+int  dyibf_host_alloc(void** ptr, size_t bytes);
+void dyibf_host_free(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DYIBF_H */
