@@ -1,0 +1,261 @@
+"""GPU (B200): the CUDA path, called through the C ABI (libdyibf.so), against the oracle and the golden vectors.
+
+Bit-exact bar: identical .filter bytes, identical per-read bin sets, identical per-bin k-mer counts,
+identical per-bin read-id lists.
+"""
+import hashlib
+
+import numpy as np
+import pytest
+
+import ka
+from oracle_py import full_layout
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def genomes(golden):
+    return ka.records(golden, "genomes")
+
+
+@pytest.fixture(scope="module")
+def reads(golden):
+    return ka.records(golden, "reads")
+
+
+def _gpu_build(dy, records_per_bin, h, k, nbits=ka.GIB_BITS):
+    f = dy.SeqAnBloomFilter(len(records_per_bin), h, k, nbits)
+    seqs, bins = ka.flat(records_per_bin)
+    keep = [(s, b) for s, b in zip(seqs, bins) if len(s) >= k]
+    f.addSequences([s for s, _ in keep], [b for _, b in keep])
+    return f
+
+
+@pytest.fixture(scope="module")
+def ka1_filter(dy, genomes):
+    return _gpu_build(dy, [[g] for g in genomes], 2, 19)
+
+
+def test_ka1_build_file_md5_and_query(dy, golden, genomes, reads, ka1_filter, tmp_path):
+    f = ka1_filter
+    path = tmp_path / "gpu_ka1.filter"
+    assert f.save(path)
+    assert path.stat().st_size == 1073741864
+    assert ka.md5_file(path) == str(golden["reference_gold_md5"])
+    rows = f.whichBinsBatch(reads, 25, group=2, derive_rc=True)
+    assert np.array_equal(rows, golden["ka1_rows"])
+    # per-bin k-mer counts of single sequences
+    idx = [int(i) for i in golden["ka1_count_reads"]]
+    _, cnt = f.whichBinsBatch([reads[i] for i in idx], 25, group=1, counts=True)
+    assert np.array_equal(cnt, golden["ka1_counts"])
+    # reload from the file: parameters come from the trailer
+    g = dy.SeqAnBloomFilter(str(path))
+    assert (g.getNumberOfBins(), g.getKmerSize(), g._noOfHashFunc, g._noOfBits) == (64, 19, 2, ka.GIB_BITS)
+    assert np.array_equal(g.whichBinsBatch(reads[:500], 25, group=2, derive_rc=True), golden["ka1_rows"][:500])
+    assert dy.readFilterMetadata(str(path)) == (64, 19)
+    g.close()
+
+
+def test_ka2_baseline_config1(dy, golden, genomes, reads):
+    f = _gpu_build(dy, [[g] for g in genomes], 3, 18)
+    words = f.download_words()
+    assert ka.md5_filter_words(words, f._noOfBits) == str(golden["ka2_md5"])
+    assert np.array_equal(f.whichBinsBatch(reads, 29, group=2, derive_rc=True), golden["ka2_rows"])
+    idx = [int(i) for i in golden["ka1_count_reads"]]
+    _, cnt = f.whichBinsBatch([reads[i] for i in idx], 29, group=1, counts=True)
+    assert np.array_equal(cnt, golden["ka2_counts"])
+    f.close()
+
+
+def test_ka4_130_bins(dy, golden, genomes, reads):
+    f = _gpu_build(dy, ka.ka4_bins(genomes), 3, 18)
+    assert (f._binIntWidth, f._noOfHashPos) == (3, 44739242)
+    assert ka.md5_filter_words(f.download_words(), f._noOfBits) == str(golden["ka4_md5"])
+    assert np.array_equal(f.whichBinsBatch(reads, 29, group=2, derive_rc=True), golden["ka4_rows"])
+    f.close()
+
+
+@pytest.mark.parametrize("tag,paired", [("se", False), ("pe", True)])
+def test_ka5_clasify_loaded_reads(dy, golden, reads, ka1_filter, tag, paired):
+    """The mapper-stage mirror against the reference's own clasifyLoadedReads output (SE and PE)."""
+    if "ka5_se_threshold" not in golden.files:
+        pytest.skip("fixture made without libref_mapper.so")
+    opts = dy.DisOptions(kmerSize=19, numberOfBins=64)
+    opts.setErrorPercent(3)
+    rs = dy.ReadSet(reads, paired=paired, rc=False)
+    thr = dy.clasifyLoadedReads(rs, ka1_filter, opts)
+    assert thr == int(golden["ka5_%s_threshold" % tag])
+    bo, ids = golden["ka5_%s_bin_offsets" % tag], golden["ka5_%s_read_ids" % tag]
+    for b in range(64):
+        assert np.array_equal(opts.origReadIdMap[b], ids[int(bo[b]):int(bo[b + 1])]), b
+
+
+def test_random_cases_vs_reference_vectors(dy, golden):
+    for ci in golden["random_cases"]:
+        pre = "rc%d_" % ci
+        bins, h, k, nbits = (int(x) for x in golden[pre + "params"])
+        f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+        f.addSequences((golden[pre + "seqs"], golden[pre + "seq_offsets"]), golden[pre + "bin_ids"])
+        words = f.download_words()
+        data = words[: f._noOfHashPos * f._binIntWidth]
+        assert hashlib.sha256(data.tobytes()).hexdigest() == str(golden[pre + "words_sha256"]), pre
+        thr = int(golden[pre + "threshold"])
+        q = (golden[pre + "queries"], golden[pre + "query_offsets"])
+        rows = f.whichBinsBatch(q, thr, group=2, derive_rc=True)
+        assert np.array_equal(rows, golden[pre + "rows"]), pre
+        nq = q[1].size - 1
+        _, cnt = f.whichBinsBatch(q, thr, group=1, counts=True)
+        assert np.array_equal(cnt[:6], golden[pre + "counts6"]), pre
+        assert cnt.shape == (nq, bins)
+        f.close()
+
+
+def _random_batch(rng, n, k, lo=None, hi=250, p_n=0.01):
+    seqs = []
+    for _ in range(n):
+        L = int(rng.integers(lo if lo is not None else max(k - 3, 0), hi))
+        c = rng.integers(0, 4, size=L).astype(np.uint8)
+        c[rng.random(L) < p_n] = 4
+        if L and rng.random() < 0.1:
+            c[0] = 4
+        if L and rng.random() < 0.1:
+            c[-1] = 4
+        seqs.append(c)
+    return seqs
+
+
+@pytest.mark.parametrize("bins,h,k,nbits", [
+    (1, 2, 14, (1 << 16) + 256), (64, 3, 18, (1 << 22) + 256), (100, 2, 20, 3000001), (128, 3, 18, (1 << 22) + 256),
+    (256, 4, 24, (1 << 23) + 256), (500, 5, 32, (1 << 23) + 256), (1024, 3, 18, (1 << 26) + 256),
+    (2048, 2, 18, (1 << 24) + 256), (4000, 3, 15, 90000001), (8192, 3, 18, (1 << 27) + 256), (640, 1, 18, (1 << 22) + 256),
+    (1024, 6, 18, (1 << 24) + 256),
+])
+def test_build_query_counts_vs_oracle(dy, oracle, bins, h, k, nbits):
+    """Every kernel variant (chunk width, lanes per block, h, plane count) against the oracle: filter words,
+    counts, rows for SE and PE layouts incl. sequences shorter than k, empty sequences and N runs."""
+    rng = np.random.default_rng(bins * 131 + h * 7 + k)
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    contigs = _random_batch(rng, 60, k, lo=0, hi=3000)
+    bin_ids = rng.integers(0, bins, size=len(contigs)).astype(np.uint32)
+    bin_ids[:4] = [0, bins - 1, bins // 2, min(63, bins - 1)]
+    for c, b in zip(contigs, bin_ids):
+        oracle.add_kmers(words, p, c, int(b))
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addSequences(contigs, bin_ids)
+    nd = p.P * p.W
+    assert np.array_equal(f.download_words()[:nd], words[:nd])
+
+    # queries: substrings of the contigs (hits) + random (misses) + degenerate
+    qs = []
+    for _ in range(200):
+        c = contigs[int(rng.integers(0, len(contigs)))]
+        if len(c) > 160 and rng.random() < 0.7:
+            st = int(rng.integers(0, len(c) - 150)); q = c[st:st + int(rng.integers(k, 150))].copy()
+            m = rng.random(len(q)) < 0.02
+            q[m] = rng.integers(0, 4, int(m.sum()))
+        else:
+            q = _random_batch(rng, 1, k)[0]
+        qs.append(q)
+    qs[0] = np.zeros(0, dtype=np.uint8); qs[1] = qs[2][: k - 1]; qs[3] = np.full(40, 4, dtype=np.uint8)
+    while len(qs) % 4:
+        qs.append(qs[-1])
+    cat = np.concatenate(qs); off = np.zeros(len(qs) + 1, dtype=np.uint64); off[1:] = np.cumsum([len(q) for q in qs])
+    fcat, foff = full_layout(cat, off, oracle)
+    for thr in (0, 1, 4, 30):
+        for paired in (False, True):
+            want = oracle.classify(words, p, fcat, foff, paired, thr)
+            got = f.whichBinsBatch((cat, off), thr, group=4 if paired else 2, derive_rc=True)
+            assert np.array_equal(got, want), (thr, paired)
+            got2 = f.whichBinsBatch((fcat, foff), thr, group=4 if paired else 2, derive_rc=False)
+            assert np.array_equal(got2, want), (thr, paired, "full layout")
+    # counts per sequence (both strands)
+    _, cnt = f.whichBinsBatch((cat, off), 1, group=2, derive_rc=True, counts=True)
+    n = len(qs)
+    for i in list(range(8)) + [n - 1]:
+        assert np.array_equal(cnt[i], oracle.count_bins(words, p, qs[i])), i
+        assert np.array_equal(cnt[n + i], oracle.count_bins(words, p, oracle.revcomp(qs[i]))), ("rc", i)
+    # compaction
+    rows = f.whichBinsBatch((cat, off), 1, group=2, derive_rc=True)
+    wo, wi = oracle.compact(rows, bins)
+    go, gi = f.compact(rows)
+    assert np.array_equal(go, wo) and np.array_equal(gi, wi)
+    co, cid = f.classify((cat, off), 1, group=2, derive_rc=True)
+    assert np.array_equal(co, wo) and np.array_equal(cid, wi)
+    f.close()
+
+
+def test_long_reads_use_16bit_counters(dy, oracle):
+    bins, h, k, nbits = 1024, 3, 18, (1 << 24) + 256
+    rng = np.random.default_rng(5)
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    contig = rng.integers(0, 4, 5000).astype(np.uint8)
+    oracle.add_kmers(words, p, contig, 77)
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addSequences([contig], [77])
+    qs = [contig[100:1500], contig[:300], rng.integers(0, 4, 2000).astype(np.uint8), contig[4000:]]
+    rows, cnt = f.whichBinsBatch(qs, 900, group=1, counts=True)
+    for i, q in enumerate(qs):
+        c = oracle.count_bins(words, p, q)
+        assert np.array_equal(cnt[i], c)
+        assert np.array_equal(ka.bits_from_rows(rows[i:i + 1], bins)[0].astype(bool), c >= 900)
+    assert cnt[0][77] == 1400 - k + 1
+    f.close()
+
+
+def test_clear_bins_and_update(dy, oracle):
+    """dream_yara_update_filter's core: clearBins then re-add (d_update_filter.cpp:188-252)."""
+    bins, h, k, nbits = 200, 3, 18, (1 << 22) + 256
+    rng = np.random.default_rng(9)
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    contigs = [rng.integers(0, 4, 2000).astype(np.uint8) for _ in range(bins)]
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addSequences(contigs, np.arange(bins))
+    for b, c in enumerate(contigs):
+        oracle.add_kmers(words, p, c, b)
+    clear = [3, 64, 65, 199]
+    oracle.clear_bins(words, p, clear)
+    f.clearBins(clear, 4)
+    nd = p.P * p.W
+    assert np.array_equal(f.download_words()[:nd], words[:nd])
+    new = rng.integers(0, 4, 1500).astype(np.uint8)
+    oracle.add_kmers(words, p, new, 64); f.addKmers(new, 64)
+    assert np.array_equal(f.download_words()[:nd], words[:nd])
+    f.close()
+
+
+def test_single_sequence_api_and_errors(dy, oracle, tmp_path):
+    bins, h, k, nbits = 70, 2, 16, 70000                     # unaligned trailer
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    text = "ACGTTGCANNACGTAGCTAGCTAGCATCGATCGATCGATGCATGCATGCATCGATCGTAGCTAGCTAGCRYACGT"
+    f.addKmers(text, 69); oracle.add_kmers(words, p, oracle.encode_ascii(text), 69)
+    sel = f.whichBins(text[5:60], 3)
+    want = oracle.which_bins(words, p, oracle.encode_ascii(text[5:60]), 3).astype(bool)
+    assert np.array_equal(sel, want) and sel[69]
+    acc = np.zeros(bins, dtype=bool); acc[1] = True
+    f.whichBins(text[5:60], 3, acc)                          # OR-accumulates, never clears
+    assert acc[1] and acc[69]
+    path = tmp_path / "u.filter"
+    assert f.save(path)
+    oracle.save(words, p, tmp_path / "o.filter")
+    assert path.read_bytes() == (tmp_path / "o.filter").read_bytes()
+    g = dy.SeqAnBloomFilter(str(path))
+    assert (g.getNumberOfBins(), g._noOfHashFunc, g.getKmerSize()) == (bins, h, k)
+    g.close()
+    with pytest.raises(SystemExit):
+        dy.SeqAnBloomFilter(str(tmp_path / "missing.filter"))
+    with pytest.raises(SystemExit):
+        dy.SeqAnBloomFilter(str(path), bins, h, k, nbits + 64)   # size mismatch -> exit(1) in the reference
+    fa = tmp_path / "b.fa"
+    fa.write_text(">r1\n%s\n%s\n>short\nACGT\n>r2\nNNNNACGTACGTACGTTTGACCA\n" % (text[:40], text[40:]))
+    f.addFastaFile(str(fa), 5)
+    oracle.add_kmers(words, p, oracle.encode_ascii(text), 5)
+    oracle.add_kmers(words, p, oracle.encode_ascii("NNNNACGTACGTACGTTTGACCA"), 5)
+    nd = p.P * p.W
+    assert np.array_equal(f.download_words()[:nd], words[:nd])
+    f.close()
