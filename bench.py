@@ -121,3 +121,268 @@ def full_layout_codes(fwd):
     cat = np.concatenate([fwd.reshape(-1), rc.reshape(-1)])
     off = np.arange(2 * n + 1, dtype=np.uint64) * L
     return cat, off
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# reference arm: the reference's own CPU code on the host cores (no GPU code on this path)
+# ---------------------------------------------------------------------------------------------------------------
+class CpuFilter:
+    """The reference's SeqAnBloomFilter compiled from /root/reference (oracle/_ref/libref_ibf.so, kind
+    "reference"), or the C restatement oracle/ibf_oracle.c (kind "port") where that file is absent."""
+
+    def __init__(self, bins, h, k, nbits):
+        from oracle_py import Oracle, Ref
+        self.bins, self.h, self.k, self.nbits = bins, h, k, nbits
+        self.W = (bins + 63) // 64
+        self.cores = os.cpu_count() or 1
+        if Ref.available():
+            self.kind, self.ref = "reference", Ref()
+            self.f = self.ref.new(bins, h, k, nbits)
+            self.words = self.ref.words(self.f)
+        else:
+            self.kind, self.o = "port", Oracle()
+            self.p = self.o.params(bins, h, k, nbits)
+            self.words = self.o.new_words(self.p)
+
+    def build(self, genomes):
+        """build_filter (d_build_filter.cpp:217-272): bins over threads, addKmers per bin."""
+        from concurrent.futures import ThreadPoolExecutor
+        if self.kind == "reference":
+            fn = lambda b: self.ref.add_kmers(self.f, genomes[b], b)          # noqa: E731
+        else:
+            fn = lambda b: self.o.add_kmers(self.words, self.p, genomes[b], b)  # noqa: E731
+        with ThreadPoolExecutor(max_workers=self.cores) as ex:                # ctypes releases the GIL
+            list(ex.map(fn, range(genomes.shape[0])))
+
+    def classify(self, layout, threshold):
+        """the filtering loop of clasifyLoadedReads over a prepared [fwd | rc] read set (full_layout_codes)"""
+        cat, off = layout
+        if self.kind == "reference":
+            return self.ref.classify(self.f, cat, off, False, threshold, self.cores, self.W)
+        os.environ.setdefault("OMP_NUM_THREADS", str(self.cores))
+        return self.o.classify(self.words, self.p, cat, off, False, threshold)
+
+    def timed_sample(self, reads_fn, threshold, target_s):
+        """Time the filtering loop on a prefix of the workload sized for ~target_s seconds."""
+        n = 20_000
+        fwd = reads_fn(n); lay = full_layout_codes(fwd)
+        t = time.perf_counter(); rows = self.classify(lay, threshold); dt = time.perf_counter() - t
+        rate = n / dt
+        n2 = int(min(max(rate * target_s, n), 2_000_000))
+        if n2 > 2 * n:
+            fwd = reads_fn(n2); lay = full_layout_codes(fwd)
+            t = time.perf_counter(); rows = self.classify(lay, threshold); dt = time.perf_counter() - t
+            n = n2
+        return n / dt, n, dt, rows, fwd
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from bench_support import synth
+    nbits = args.filter_gib * (1 << 33) + 256
+    thr = None
+    cf = CpuFilter(args.bins, H, K, nbits)
+    from oracle_py import Oracle
+    thr = Oracle().threshold(E, K, args.read_len)
+    t0 = time.perf_counter()
+    genomes = synth.genomes(args.bins, args.genome_len)
+    cf.build(genomes)
+    build_s = time.perf_counter() - t0
+    # size a step for ~4 s of CPU work from a probe, then W warm-up + K timed steps on successive samples
+    rate, n_probe, _, _, _ = cf.timed_sample(lambda n: synth.reads(genomes, 2, 0, n, args.read_len), thr, 4.0)
+    n_step = int(min(max(rate * 4.0, 20_000), 2_000_000))
+    times = []
+    for s in range(args.warmup + args.steps):
+        lay = full_layout_codes(synth.reads(genomes, 2, (s % 4) * n_step, n_step, args.read_len))
+        t = time.perf_counter(); cf.classify(lay, thr); dt = time.perf_counter() - t
+        if s >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    value = n_step * args.steps / total
+    line = {
+        "impl": "reference", "metric": "IBF bin-filter reads/s (150bp,e=3)", "value": value, "unit": "reads/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": workload_config(args, thr),
+        "cpu_baseline": {"value": value, "unit": "reads/s", "cores": cf.cores, "kind": cf.kind,
+                         "sample": "%d-read prefix samples of the 10M-read workload per step; filter built on the host "
+                                   "by the same code in %.1f s" % (n_step, build_s)},
+        "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, thr):
+    return {"workload": "cfg2: synthetic %d-bin %d GiB IBF (k=%d, h=%d), %d single-end %d bp reads per GPU, e=%d "
+                        "(threshold %d), read-sharded" % (args.bins, args.filter_gib, K, H, args.reads, args.read_len, E, thr),
+            "bins": args.bins, "filter_gib": args.filter_gib, "kmer": K, "hashes": H, "reads_per_gpu": args.reads,
+            "read_len": args.read_len, "threshold": thr, "genome_bp_per_bin": args.genome_len,
+            "l2": "no flush needed: every step gathers ~%d GB at random from a %d GiB table (>> 126 MB L2)"
+                  % (round(args.reads * algorithmic_bytes_per_read(args.bins, args.read_len) / 1e9), args.filter_gib),
+            "parallelism": "read-sharded x%d (filter replicated, NCCL broadcast)" % args.gpus}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    import dream_yara_b200 as dy
+    from dream_yara_b200._lib import ENC_DNA5, MEM_HOST, check
+    from bench_support import synth
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the IBF path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = dy.lib()
+    bins, n, RL = args.bins, args.reads, args.read_len
+    nbits = args.filter_gib * (1 << 33) + 256
+    W = (bins + 63) // 64
+    P = (nbits - 256) // (64 * W)
+    thr = int(L.dyibf_threshold(E, K, RL))
+
+    # ---- setup (untimed): genomes, filter (rank 0 builds, NCCL broadcast replicates), this rank's reads
+    genomes = synth.genomes(bins, args.genome_len)
+    words = torch.zeros(P * W, dtype=torch.int64, device=dev)
+    f = dy.SeqAnBloomFilter.attach(bins, H, K, nbits, words.data_ptr(), device=local, keep=words)
+    t_build = time.perf_counter()
+    if rank == 0:
+        goff = np.arange(bins + 1, dtype=np.uint64) * args.genome_len
+        f.addSequences((genomes.reshape(-1), goff), np.arange(bins, dtype=np.uint32))
+    torch.cuda.synchronize()
+    t_build = time.perf_counter() - t_build
+    if world > 1:
+        step = 1 << 27                                                   # 1 GiB pieces
+        for a in range(0, words.numel(), step):
+            dist.broadcast(words[a:a + step], src=0)
+        torch.cuda.synchronize()
+
+    hp = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(hp), n * RL))
+    h_reads = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(n, RL))
+    synth.reads(genomes, 2, rank * n, n, RL, out=h_reads)
+    op = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(op), (n + 1) * 8))
+    h_off = np.ctypeslib.as_array(C.cast(op, C.POINTER(C.c_uint64)), shape=(n + 1,))
+    h_off[:] = np.arange(n + 1, dtype=np.uint64) * RL
+    rp = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(rp), n * W * 8))
+    h_rows = np.ctypeslib.as_array(C.cast(rp, C.POINTER(C.c_uint64)), shape=(n, W))
+    d_reads = torch.from_numpy(h_reads.reshape(-1)).to(dev)
+    d_off = torch.from_numpy(h_off.view(np.int64)).to(dev)
+    d_rows = torch.zeros(n * W, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def device_step():
+        f.query_device(d_reads.data_ptr(), d_off.data_ptr(), n, thr, d_rows.data_ptr(), group=2, derive_rc=True,
+                       encoding=ENC_DNA5, max_seq_len=RL, stream=stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: reads resident in HBM, CUDA events on the launching stream
+    for _ in range(args.warmup):
+        device_step()
+    f.profile_enable(True); f.profile(reset=True)
+    sampler = ClockSampler(local); 
+    barrier()
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        device_step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = e0.elapsed_time(e1)
+    prof = f.profile(reset=True); f.profile_enable(False)
+    t = torch.tensor([ms, prof["query_ms"] / max(prof["query_launches"], 1), prof["pack_ms"] / max(prof["pack_launches"], 1)],
+                     dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, query_ms, pack_ms = (float(x) for x in t.tolist())
+    value = world * n * args.steps / (ms_total / 1e3)
+
+    # ---- e2e: the public host-buffer call; pinned reads in, bitmask rows out, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        def host_step():
+            check(L.dyibf_query_batch(f._h, hp, op, n, ENC_DNA5, 2, 1, thr, RL, rp, None, MEM_HOST, None))
+        for _ in range(max(1, min(args.warmup, 2))):
+            host_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            host_step()
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * n * args.steps / float(dt.item()), "unit": "reads/s",
+               "h2d_bytes_per_step": world * (n * RL + (n + 1) * 8), "d2h_bytes_per_step": world * n * W * 8,
+               "timing": "host wall clock around K synchronous dyibf_query_batch(host) calls, max over ranks"}
+        # device-resident and host paths must agree bit for bit
+        assert np.array_equal(h_rows.reshape(-1).view(np.int64), d_rows.cpu().numpy()), "host-mode rows != device-mode rows"
+
+    # ---- roofline of the dominant kernel (query) against the measured HBM peak
+    bytes_per_read = algorithmic_bytes_per_read(bins, RL)
+    peak, peak_src = measured_peak()
+    achieved = n * bytes_per_read / (query_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "query_kernel<16,3,3,8>", "kernel_ms": query_ms, "pack_kernel_ms": pack_ms,
+                "algorithmic_bytes_per_launch": n * bytes_per_read, "peak_source": peak_src,
+                "frac_of_nominal_8000": achieved / 8000.0}
+    traffic_file = os.path.join(ROOT, "profiles", "query_kernel_traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            tj = json.load(open(traffic_file))
+            if tj.get("reads_per_launch"):
+                roofline["traffic"] = tj["dram_bytes_per_launch"] * (n / tj["reads_per_launch"])
+                roofline["traffic_source"] = tj.get("source")
+        except Exception:
+            pass
+
+    # ---- CPU baseline: the reference's own code on a bounded sample of the same reads (rank 0, N = 1)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cf = CpuFilter(bins, H, K, nbits)
+        nd = P * W
+        check(L.dyibf_download_words(f._h, C.c_void_p(cf.words.ctypes.data), 0, nd))   # same filter words as the GPU
+        rate, n_s, dt_s, rows_cpu, _ = cf.timed_sample(lambda m: h_reads[:m], thr, 15.0)
+        same = bool(np.array_equal(rows_cpu, h_rows[:n_s] if e2e else d_rows.cpu().numpy().view(np.uint64).reshape(n, W)[:n_s]))
+        cpu = {"value": rate, "unit": "reads/s", "cores": cf.cores, "kind": cf.kind,
+               "sample": "first %d reads of the 10M-read workload, %.1f s, same filter words (downloaded from HBM)" % (n_s, dt_s),
+               "rows_equal_gpu": same}
+        if not same:
+            raise AssertionError("GPU rows differ from the CPU reference on the sampled prefix")
+
+    if rank == 0:
+        line = {"metric": "IBF bin-filter reads/s (150bp,e=3)", "value": value, "unit": "reads/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+                "config": workload_config(args, thr), "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
+                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "impl": "b200"}
+        print(json.dumps(line), flush=True)
+    f.close()
+    for p_ in (hp, op, rp):
+        L.dyibf_host_free(p_)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
