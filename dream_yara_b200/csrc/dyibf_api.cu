@@ -53,7 +53,7 @@ struct DevBuf {
 
 struct Slot {                     // one stage of the host-mode pipeline
     cudaStream_t st = nullptr;
-    DevBuf in_bytes, in_offsets, packed, meta, rows, counts;
+    DevBuf in_bytes, in_offsets, packed, meta, rows, counts, ctr;
 };
 
 enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_N };
@@ -255,7 +255,7 @@ void dyibf_destroy(dyibf_filter* f)
     for (auto e : f->ev_pool) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         Slot& s = f->slot[i];
-        s.in_bytes.release(); s.in_offsets.release(); s.packed.release(); s.meta.release(); s.rows.release(); s.counts.release();
+        s.in_bytes.release(); s.in_offsets.release(); s.packed.release(); s.meta.release(); s.rows.release(); s.counts.release(); s.ctr.release();
         if (s.st) cudaStreamDestroy(s.st);
         if (f->stage[i]) cudaFreeHost(f->stage[i]);
         if (f->stage_ev[i]) cudaEventDestroy(f->stage_ev[i]);
@@ -456,6 +456,7 @@ int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t t
     const uint64_t words_one = packed_words_for(total_bytes, n_in);
     CU(sl.packed.reserve((derive_rc ? 2 : 1) * words_one * 8));
     CU(sl.meta.reserve(n_total * sizeof(SeqMeta)));
+    CU(sl.ctr.reserve(256));
     {
         Scope sc(f, st, K_PACK);
         CU(launch_pack(src, encoding, derive_rc, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words_one, words_one, st));
@@ -465,7 +466,7 @@ int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t t
     {
         Scope sc(f, st, K_QUERY);
         CU(launch_query(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, n_rows, group,
-                        threshold, max_kmers, d_rows, d_counts, f->sm_count, st));
+                        threshold, max_kmers, d_rows, d_counts, (uint32_t*)sl.ctr.p, f->sm_count, st));
     }
     return DYIBF_OK;
 }

@@ -49,7 +49,7 @@ static inline uint64_t packed_words_for(uint64_t bytes, uint64_t n_in) { return 
 
 cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                          uint32_t n_rows, uint32_t group, uint32_t threshold, uint32_t max_kmers,
-                         uint64_t* out_rows, uint16_t* out_counts, int sm_count, cudaStream_t st);
+                         uint64_t* out_rows, uint16_t* out_counts, uint32_t* work_counter, int sm_count, cudaStream_t st);
 
 // build: every k-mer of the n_seqs packed forward sequences ORs h bits (bin = bin_ids[s]) into the filter
 cudaError_t launch_build(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,

@@ -76,7 +76,7 @@ template <int VEC, int TL2, int H, int PLANES>
 __global__ void __launch_bounds__(128, 4)
 query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint64_t* __restrict__ packed,
              const SeqMeta* __restrict__ meta, uint32_t n_rows, uint32_t group, uint32_t thr,
-             uint64_t* __restrict__ out_rows, uint16_t* __restrict__ out_counts)
+             uint64_t* __restrict__ out_rows, uint16_t* __restrict__ out_counts, uint32_t* __restrict__ work_counter)
 {
     constexpr int T  = 1 << TL2;            // lanes per sequence
     constexpr int SG = 32 / T;              // sequences per warp
@@ -95,10 +95,17 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
     const uint32_t block_bytes = hp.W * 8u;
     const uint32_t chunks = block_bytes / VEC;
     const uint32_t n_tiles = (chunks + T - 1) / T;
-    const uint32_t warps_total = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-
-    for (uint64_t r0 = (uint64_t)warp_id * SG; r0 < n_rows; r0 += (uint64_t)warps_total * SG) {
+    // Work items (SG rows each) are claimed from a global counter: SMs do not all see the same HBM latency
+    // (two dies, near/far L2 slices), so a static split leaves the fast ones idle at the end.  The next claim
+    // is issued before the current item is processed, so its round trip is off the critical path.
+    const uint32_t n_items = (n_rows + SG - 1) / SG;
+    uint32_t next_item = 0;
+    if (lane == 0) next_item = atomicAdd(work_counter, 1u);
+    for (;;) {
+        const uint32_t item = __shfl_sync(0xffffffffu, next_item, 0);
+        if (item >= n_items) break;
+        if (lane == 0) next_item = atomicAdd(work_counter, 1u);
+        const uint64_t r0 = (uint64_t)item * SG;
         const uint64_t r = r0 + sub;
         const bool row_ok = r < n_rows;
         for (uint32_t tile = 0; tile < n_tiles; ++tile) {
@@ -261,7 +268,7 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
 template <int VEC, int TL2, int H, int PLANES>
 static cudaError_t launch_one(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                               uint32_t n_rows, uint32_t group, uint32_t thr, uint64_t* out_rows, uint16_t* out_counts,
-                              int sm_count, cudaStream_t st)
+                              uint32_t* work_counter, int sm_count, cudaStream_t st)
 {
     auto kern = query_kernel<VEC, TL2, H, PLANES>;
     int per_sm = 0;
@@ -274,29 +281,31 @@ static cudaError_t launch_one(const HashParams& hp, const uint64_t* filter, cons
     uint64_t cap = (uint64_t)sm_count * per_sm;
     if (blocks > cap) blocks = cap;
     if (blocks == 0) return cudaSuccess;
+    e = cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
     kern<<<(unsigned)blocks, 128, 0, st>>>(hp, reinterpret_cast<const uint8_t*>(filter), packed, meta, n_rows, group,
-                                           thr, out_rows, out_counts);
+                                           thr, out_rows, out_counts, work_counter);
     return cudaGetLastError();
 }
 
 template <int VEC, int H, int PLANES>
 static cudaError_t launch_tl2(int tl2, const HashParams& hp, const uint64_t* filter, const uint64_t* packed,
                               const SeqMeta* meta, uint32_t n_rows, uint32_t group, uint32_t thr, uint64_t* out_rows,
-                              uint16_t* out_counts, int sm_count, cudaStream_t st)
+                              uint16_t* out_counts, uint32_t* work_counter, int sm_count, cudaStream_t st)
 {
     switch (tl2) {
-        case 0: return launch_one<VEC, 0, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, sm_count, st);
-        case 1: return launch_one<VEC, 1, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, sm_count, st);
-        case 2: return launch_one<VEC, 2, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, sm_count, st);
-        case 3: return launch_one<VEC, 3, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, sm_count, st);
-        case 4: return launch_one<VEC, 4, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, sm_count, st);
-        default: return launch_one<VEC, 5, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, sm_count, st);
+        case 0: return launch_one<VEC, 0, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
+        case 1: return launch_one<VEC, 1, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
+        case 2: return launch_one<VEC, 2, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
+        case 3: return launch_one<VEC, 3, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
+        case 4: return launch_one<VEC, 4, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
+        default: return launch_one<VEC, 5, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
     }
 }
 
 cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                          uint32_t n_rows, uint32_t group, uint32_t threshold, uint32_t max_kmers,
-                         uint64_t* out_rows, uint16_t* out_counts, int sm_count, cudaStream_t st)
+                         uint64_t* out_rows, uint16_t* out_counts, uint32_t* work_counter, int sm_count, cudaStream_t st)
 {
     if (n_rows == 0) return cudaSuccess;
     const bool vec16 = (hp.W % 2u) == 0;
@@ -305,7 +314,7 @@ cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uin
     while (tl2 < 5 && (1u << tl2) < chunks) ++tl2;
     const bool fast = (hp.h == 2 || hp.h == 3) && max_kmers != 0 && max_kmers <= 255 && hp.P <= (1ull << 32);
 #define DYIBF_GO(VEC, H, PLANES) \
-    return launch_tl2<VEC, H, PLANES>(tl2, hp, filter, packed, meta, n_rows, group, threshold, out_rows, out_counts, sm_count, st)
+    return launch_tl2<VEC, H, PLANES>(tl2, hp, filter, packed, meta, n_rows, group, threshold, out_rows, out_counts, work_counter, sm_count, st)
     if (fast) {
         if (vec16) { if (hp.h == 2) DYIBF_GO(16, 2, 8); else DYIBF_GO(16, 3, 8); }
         else       { if (hp.h == 2) DYIBF_GO(8, 2, 8);  else DYIBF_GO(8, 3, 8); }
