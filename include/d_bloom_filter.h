@@ -1,0 +1,230 @@
+// ==========================================================================
+//                     d_bloom_filter.h  (B200 drop-in)
+// ==========================================================================
+// Drop-in replacement for DREAM-Yara's src/d_bloom_filter.h (temehi/dream_yara, lines 41-331):
+// the same class seqan::SeqAnBloomFilter<TString> with the same public members, argument meaning and error
+// behaviour, but the filter lives in the HBM of a B200 and every member forwards to the C ABI of libdyibf.so
+// (include/dyibf.h; hand-written sm_100a CUDA).  There is no CPU fallback.
+//
+// Use: put this directory before the reference's src/ on the include path (or overwrite the file), add
+// `-ldyibf` to the link line.  The three translation units that include the header compile unchanged
+// (src/d_build_filter.cpp:61, src/d_update_filter.cpp:61, src/d_mapper.cpp:92).
+//
+// Per-sequence whichBins()/addKmers() are batches of one — correct, but a PCIe round trip each.  The two call
+// sites that matter should use the batched members added at the bottom (whichBinsBatch / classify /
+// addSequences); include/d_mapper_filter.h holds the replacement body of clasifyLoadedReads, INTEGRATION.md the
+// patches.
+//
+// Like the original, this header expects <seqan/sequence.h>, <seqan/seq_io.h> and d_misc_options.h
+// (INT_WIDTH, filterMetadataSize) to have been included before it.
+#ifndef APP_YARA_DIS_BLOOM_FILTER_B200_H_
+#define APP_YARA_DIS_BLOOM_FILTER_B200_H_
+
+#include <cstdint>
+#include <cstdlib>
+#include <iostream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "dyibf.h"
+
+namespace seqan
+{
+    template<typename TString = Dna5String>
+    class SeqAnBloomFilter
+    {
+    public:
+        typedef Shape<Dna, SimpleShape> TShape;     // kept for source compatibility; hashing happens on the GPU
+
+        // d_bloom_filter.h:48
+        SeqAnBloomFilter(uint32_t n_bins, uint8_t n_hash_func, uint8_t kmer_size, uint64_t vec_size, int device = 0)
+        {
+            _check(dyibf_create(n_bins, n_hash_func, kmer_size, vec_size, device, &_h));
+            _cacheParams();
+        }
+
+        // d_bloom_filter.h:59 — load failure / size mismatch: message on std::cerr, exit(1)
+        SeqAnBloomFilter(const char *fileName, uint32_t n_bins, uint8_t n_hash_func, uint8_t kmer_size, uint64_t vec_size,
+                         int device = 0)
+        {
+            _exitOnLoadFailure(dyibf_load_file_expect(fileName, n_bins, n_hash_func, kmer_size, vec_size, device, &_h));
+            _cacheParams();
+        }
+
+        // d_bloom_filter.h:79 — parameters from the file's trailer
+        explicit SeqAnBloomFilter(const char *fileName, int device = 0)
+        {
+            _exitOnLoadFailure(dyibf_load_file(fileName, device, &_h));
+            _cacheParams();
+        }
+
+        ~SeqAnBloomFilter() { dyibf_destroy(_h); }
+
+        // the object owns a device handle: movable, not copyable (the reference object was never copied either)
+        SeqAnBloomFilter(SeqAnBloomFilter const &) = delete;
+        SeqAnBloomFilter & operator=(SeqAnBloomFilter const &) = delete;
+        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _prm(o._prm) { o._h = nullptr; }
+
+        // d_bloom_filter.h:91
+        void addKmers(TString const & text, uint32_t const & binNo)
+        {
+            if (length(text) < _prm.kmer) return;               // reference: out-of-bounds hashing; here: nothing
+            uint64_t offsets[2] = {0, (uint64_t)length(text)};
+            _check(dyibf_add_sequences(_h, _bytes(text), offsets, 1, &binNo, _encoding(text), DYIBF_MEM_HOST, nullptr));
+        }
+
+        // d_bloom_filter.h:99 — threadsCount is accepted for source compatibility; the GPU does the pass
+        void clearBins(std::vector<uint32_t> & bins2clear, uint32_t & /*threadsCount*/)
+        {
+            _check(dyibf_clear_bins(_h, bins2clear.data(), (uint32_t)bins2clear.size()));
+        }
+
+        // d_bloom_filter.h:127 — same reader, same Iupac -> TString conversion, one kernel batch per file
+        void addFastaFile(CharString const & fastaFile, uint32_t const & binNo)
+        {
+            CharString id;
+            IupacString seq;
+            SeqFileIn seqFileIn;
+            if (!open(seqFileIn, toCString(fastaFile)))
+            {
+                std::string msg = "Unable to open contigs File: ";
+                msg += toCString(fastaFile);
+                throw std::runtime_error(msg);                   // reference throws a dangling const char* (:133-138)
+            }
+            std::vector<uint8_t> concat;
+            std::vector<uint64_t> offsets(1, 0);
+            while (!atEnd(seqFileIn))
+            {
+                readRecord(id, seq, seqFileIn);
+                if (length(seq) < _prm.kmer)
+                    continue;
+                TString text = seq;                               // Iupac -> Dna5 exactly as the reference converts
+                const uint8_t * p = _bytes(text);
+                concat.insert(concat.end(), p, p + length(text));
+                offsets.push_back(concat.size());
+            }
+            close(seqFileIn);
+            if (offsets.size() > 1)
+            {
+                std::vector<uint32_t> bins(offsets.size() - 1, binNo);
+                _check(dyibf_add_sequences(_h, concat.data(), offsets.data(), (uint32_t)bins.size(), bins.data(),
+                                           _encodingOf((typename Value<TString>::Type *)nullptr), DYIBF_MEM_HOST, nullptr));
+            }
+        }
+
+        // d_bloom_filter.h:150
+        bool save(const char *fileName)
+        {
+            return dyibf_save_file(_h, fileName) == DYIBF_OK;
+        }
+
+        // d_bloom_filter.h:156
+        double size_mb()
+        {
+            return dyibf_size_mb(_h);
+        }
+
+        // d_bloom_filter.h:161 — OR-accumulates into `selected`, never clears
+        inline void whichBins(std::vector<bool> & selected, TString const & text, uint16_t const & threshold) const
+        {
+            if (length(text) < _prm.kmer) return;               // reference: uint16 wrap + out-of-bounds reads
+            uint64_t offsets[2] = {0, (uint64_t)length(text)};
+            std::vector<uint64_t> row(_prm.words_per_block, 0);
+            _check(dyibf_query_batch(_h, _bytes(text), offsets, 1, _encoding(text), 1, 0, threshold, 0, row.data(), nullptr,
+                                     DYIBF_MEM_HOST, nullptr));
+            for (uint32_t binNo = 0; binNo < _prm.bins; ++binNo)
+                if ((row[binNo >> 6] >> (binNo & 63)) & 1)
+                    selected[binNo] = true;
+        }
+
+        // d_bloom_filter.h:226
+        std::vector<bool> whichBins(TString const & text, uint16_t const & threshold) const
+        {
+            std::vector<bool> selected(_prm.bins, false);
+            whichBins(selected, text, threshold);
+            return selected;
+        }
+
+        uint32_t getNumberOfBins() const { return _prm.bins; }          // :233
+        uint8_t  getKmerSize() const { return (uint8_t)_prm.kmer; }     // :238
+
+        // ------------------------------------------------------------------------------------------------
+        // batched entries (new): what the patched clasifyLoadedReads / build_filter call
+        // ------------------------------------------------------------------------------------------------
+
+        // Many sequences at once, laid out as a ConcatDirect StringSet holds them: `concat` bytes + `limits`.
+        // group/derive_rc as in dyibf_query_batch. rows: n_rows x getBinWidth() u64.
+        void whichBinsBatch(std::vector<uint64_t> & rows, const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs,
+                            int encoding, int group, bool derive_rc, uint16_t threshold) const
+        {
+            uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
+            rows.assign((n_total / group) * _prm.words_per_block, 0);
+            _check(dyibf_query_batch(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold, 0,
+                                     rows.data(), nullptr, DYIBF_MEM_HOST, nullptr));
+        }
+
+        // Query + compaction: per bin the ascending ids of the reads (pairs) that select it.
+        void classify(std::vector<std::vector<uint32_t> > & readIdsPerBin, const uint8_t * concat, const uint64_t * limits,
+                      uint32_t n_seqs, int encoding, int group, bool derive_rc, uint16_t threshold) const
+        {
+            std::vector<uint64_t> binOffsets(_prm.bins + 1, 0);
+            uint64_t n_rows = (derive_rc ? 2ull * n_seqs : n_seqs) / group;
+            std::vector<uint32_t> ids(std::max<uint64_t>(4 * n_rows, 1024));
+            uint64_t total = 0;
+            int rc = dyibf_classify(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
+                                    binOffsets.data(), ids.data(), ids.size(), &total);
+            if (rc == DYIBF_ERR_CAPACITY)
+            {
+                ids.resize(total);
+                rc = dyibf_classify(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
+                                    binOffsets.data(), ids.data(), ids.size(), &total);
+            }
+            _check(rc);
+            readIdsPerBin.assign(_prm.bins, std::vector<uint32_t>());
+            for (uint32_t b = 0; b < _prm.bins; ++b)
+                readIdsPerBin[b].assign(ids.begin() + binOffsets[b], ids.begin() + binOffsets[b + 1]);
+        }
+
+        void addSequences(const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs, const uint32_t * binIds, int encoding)
+        {
+            _check(dyibf_add_sequences(_h, concat, limits, n_seqs, binIds, encoding, DYIBF_MEM_HOST, nullptr));
+        }
+
+        uint32_t getBinWidth() const { return _prm.words_per_block; }
+        dyibf_filter * handle() const { return _h; }
+
+    private:
+        static void _check(int rc)
+        {
+            if (rc != DYIBF_OK)
+                throw std::runtime_error(std::string("dyibf: ") + dyibf_last_error());
+        }
+
+        static void _exitOnLoadFailure(int rc)
+        {
+            if (rc == DYIBF_OK) return;
+            std::cerr << dyibf_last_error() << std::endl;         // "File ... could not be read." / "Size mismatch: ..."
+            exit(1);
+        }
+
+        void _cacheParams() { _check(dyibf_get_params(_h, &_prm)); }
+
+        // SeqAn alphabets are SimpleType<unsigned char, ...>: one byte per character, contiguous in Alloc strings
+        static int _encodingOf(Dna5 *)  { return DYIBF_ENC_DNA5; }
+        static int _encodingOf(Dna5Q *) { return DYIBF_ENC_DNA5Q; }
+        static int _encodingOf(Dna *)   { return DYIBF_ENC_DNA5; }
+        static int _encodingOf(char *)  { return DYIBF_ENC_ASCII; }
+        template <typename T> static int _encoding(T const &) { return _encodingOf((typename Value<T>::Type *)nullptr); }
+        template <typename T> static const uint8_t * _bytes(T const & s)
+        {
+            static_assert(sizeof(typename Value<T>::Type) == 1, "one byte per character expected");
+            return reinterpret_cast<const uint8_t *>(&*begin(s, Standard()));
+        }
+
+        dyibf_filter *  _h = nullptr;
+        dyibf_params    _prm;
+    };
+}
+
+#endif  // APP_YARA_DIS_BLOOM_FILTER_B200_H_

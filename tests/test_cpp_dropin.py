@@ -1,0 +1,67 @@
+"""The C++ drop-in (include/d_bloom_filter.h, include/d_mapper_filter.h) with real SeqAn types.
+
+CPU: the driver compiles against the SeqAn vendored in the reference tree (only where /root/reference exists).
+GPU: the prebuilt driver (tests/cpp/_bin/dropin_test; SeqAn is needed at compile time only) builds the reference's
+test filter from FASTA files, queries and classifies the test reads; outputs are compared with the vectors the
+unmodified reference produced (tests/golden)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import ka
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+BIN = os.path.join(HERE, "cpp", "_bin", "dropin_test")
+REF = "/root/reference"
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "include", "seqan")), reason="needs the reference's vendored SeqAn")
+def test_dropin_headers_compile_against_seqan(dy):
+    r = subprocess.run(["make", "-C", os.path.join(HERE, "cpp")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-4000:]
+    assert os.path.exists(BIN)
+
+
+def _write_fasta(path, records):
+    with open(path, "wb") as fh:
+        for name, seq in records:
+            fh.write(b">" + name.encode() + b"\n")
+            for j in range(0, len(seq), 80):
+                fh.write(seq[j:j + 80] + b"\n")
+
+
+@pytest.mark.gpu
+def test_dropin_build_query_classify(golden, tmp_path):
+    if not os.path.exists(BIN):
+        pytest.skip("tests/cpp/_bin/dropin_test was not prebuilt (needs /root/reference at build time)")
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    bins_dir = tmp_path / "bins"; bins_dir.mkdir()
+    for b, g in enumerate(genomes):
+        _write_fasta(bins_dir / ("%d.fa" % b), [("bin%d" % b, g)])
+    _write_fasta(tmp_path / "reads.fa", [("r%d" % i, r) for i, r in enumerate(reads)])
+    filt = tmp_path / "f.filter"
+    r = subprocess.run([BIN, "build", "64", "2", "19", str(ka.GIB_BITS), str(bins_dir), str(filt)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert ka.md5_file(filt) == str(golden["reference_gold_md5"])
+    # per-read whichBins through the class, Dna5Q reads as in the mapper (first 400 reads: one PCIe round trip each)
+    _write_fasta(tmp_path / "reads400.fa", [("r%d" % i, r) for i, r in enumerate(reads[:400])])
+    r = subprocess.run([BIN, "query", str(filt), str(tmp_path / "reads400.fa"), "25", str(tmp_path / "q.txt")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want = ka.bits_from_rows(golden["ka1_rows"][:400], 64)
+    for i, line in enumerate(open(tmp_path / "q.txt")):
+        assert [int(x) for x in line.split()] == list(np.nonzero(want[i])[0]), i
+    # the batched clasifyLoadedReads replacement, SE and PE, vs the reference's own clasifyLoadedReads
+    for tag, paired in (("se", 0), ("pe", 1)):
+        out = tmp_path / ("c_%s.txt" % tag)
+        r = subprocess.run([BIN, "classify", str(filt), str(tmp_path / "reads.fa"), "3", str(paired), str(out)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        bo, ids = golden["ka5_%s_bin_offsets" % tag], golden["ka5_%s_read_ids" % tag]
+        lines = open(out).read().split("\n")
+        for b in range(64):
+            assert [int(x) for x in lines[b].split()] == list(ids[int(bo[b]):int(bo[b + 1])]), (tag, b)
+        assert "bin 0\t173" in r.stderr                         # -vv dump, d_mapper.h:380-386
+    # load failure: message + exit(1) as the reference
+    r = subprocess.run([BIN, "query", str(tmp_path / "nope.filter"), str(tmp_path / "reads400.fa"), "25", str(tmp_path / "x")], capture_output=True, text=True)
+    assert r.returncode == 1 and "could not be read" in r.stderr
