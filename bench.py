@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--read-len", type=int, default=150)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-early-exit", action="store_true", help="skip the extra DYIBF_OPT_EARLY_EXIT measurement")
     return ap.parse_args()
 
 
@@ -334,6 +335,48 @@ def run_b200(args):
         # device-resident and host paths must agree bit for bit
         assert np.array_equal(h_rows.reshape(-1).view(np.int64), d_rows.cpu().numpy()), "host-mode rows != device-mode rows"
 
+    # ---- extra (not the headline): the same step with DYIBF_OPT_EARLY_EXIT — identical rows, fewer lookups
+    early = None
+    if not args.no_early_exit:
+        full_rows = d_rows.clone()
+        full_lookups = prof["query_lookups"] / max(prof["query_launches"], 1)
+        f.set_early_exit(True)
+        for _ in range(2):
+            device_step()
+        f.profile_enable(True); f.profile(reset=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            device_step()
+        e1.record()
+        barrier()
+        p2 = f.profile(reset=True); f.profile_enable(False)
+        same = bool(torch.equal(full_rows, d_rows))
+        t2 = torch.tensor([e0.elapsed_time(e1), p2["query_ms"] / max(p2["query_launches"], 1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        early = {"value": world * n * args.steps / (float(t2[0]) / 1e3), "unit": "reads/s", "kernel_ms": float(t2[1]),
+                 "lookups_frac": (p2["query_lookups"] / max(p2["query_launches"], 1)) / max(full_lookups, 1),
+                 "rows_equal_full": same,
+                 "note": "DYIBF_OPT_EARLY_EXIT=1: a sequence stops once no remaining k-mer can change its bin set; "
+                         "off by default, not used for value/e2e/roofline"}
+        if not same:
+            raise AssertionError("early-exit rows differ from the full pass")
+        if not args.no_e2e:
+            host_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                host_step()
+            barrier()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            early["e2e"] = world * n * args.steps / float(dt.item())
+            assert np.array_equal(h_rows.reshape(-1).view(np.int64), full_rows.cpu().numpy()), "early-exit host rows differ"
+        f.set_early_exit(False)
+        del full_rows
+
     # ---- roofline of the dominant kernel (query) against the measured HBM peak
     bytes_per_read = algorithmic_bytes_per_read(bins, RL)
     peak, peak_src = measured_peak()
@@ -371,7 +414,7 @@ def run_b200(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
                 "config": workload_config(args, thr), "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
-                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "impl": "b200"}
+                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "impl": "b200"}
         print(json.dumps(line), flush=True)
     f.close()
     for p_ in (hp, op, rp):

@@ -10,6 +10,7 @@ OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_FORMAT, ERR_SIZE_MISMATCH, ERR_CAPACITY, ERR_
 ENC_DNA5, ENC_DNA5Q, ENC_ASCII = 0, 1, 2
 MEM_HOST, MEM_DEVICE = 0, 1
 MAX_HASH = 8
+OPT_EARLY_EXIT = 1
 
 
 class Params(C.Structure):
@@ -21,7 +22,7 @@ class Profile(C.Structure):
     _fields_ = [("pack_ms", C.c_double), ("query_ms", C.c_double), ("compact_ms", C.c_double),
                 ("build_ms", C.c_double), ("clear_ms", C.c_double),
                 ("pack_launches", C.c_uint64), ("query_launches", C.c_uint64), ("compact_launches", C.c_uint64),
-                ("build_launches", C.c_uint64), ("clear_launches", C.c_uint64)]
+                ("build_launches", C.c_uint64), ("clear_launches", C.c_uint64), ("query_lookups", C.c_uint64)]
 
 
 # every symbol include/dyibf.h declares: name -> (restype, argtypes)
@@ -51,6 +52,8 @@ SYMBOLS = {
     "dyibf_compact": (C.c_int, [_P, _U64P, C.c_uint32, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, _P]),
     "dyibf_classify": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32,
                                  _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dyibf_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
+    "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),
     "dyibf_profile_get": (C.c_int, [_P, C.POINTER(Profile), C.c_int]),
     "dyibf_host_alloc": (C.c_int, [C.POINTER(_P), C.c_size_t]),

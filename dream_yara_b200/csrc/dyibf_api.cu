@@ -70,7 +70,8 @@ struct dyibf_filter {
     uint64_t     data_words = 0;
     bool         owns_words = true;
     Slot         slot[2];
-    DevBuf       misc, compact_ws, build_bins, rows_all;
+    DevBuf       misc, compact_ws, build_bins, rows_all, stats;
+    uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
     bool         profiling = false;
@@ -260,7 +261,7 @@ void dyibf_destroy(dyibf_filter* f)
         if (f->stage[i]) cudaFreeHost(f->stage[i]);
         if (f->stage_ev[i]) cudaEventDestroy(f->stage_ev[i]);
     }
-    f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release();
+    f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release(); f->stats.release();
     if (f->owns_words && f->d_words) cudaFree(f->d_words);
     delete f;
 }
@@ -466,7 +467,8 @@ int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t t
     {
         Scope sc(f, st, K_QUERY);
         CU(launch_query(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, n_rows, group,
-                        threshold, max_kmers, d_rows, d_counts, (uint32_t*)sl.ctr.p, f->sm_count, st));
+                        threshold, max_kmers, d_rows, d_counts, (uint32_t*)sl.ctr.p, f->query_flags,
+                        f->profiling ? (unsigned long long*)f->stats.p : nullptr, f->sm_count, st));
     }
     return DYIBF_OK;
 }
@@ -804,9 +806,35 @@ int dyibf_clear_bins(dyibf_filter* f, const uint32_t* bins, uint32_t n)
     return DYIBF_OK;
 }
 
+int dyibf_set_option(dyibf_filter* f, int option, int64_t value)
+{
+    if (!f) return fail(DYIBF_ERR_ARG, "filter is NULL");
+    switch (option) {
+        case DYIBF_OPT_EARLY_EXIT:
+            if (value) f->query_flags |= QUERY_EARLY_EXIT; else f->query_flags &= ~QUERY_EARLY_EXIT;
+            return DYIBF_OK;
+        default:
+            return fail(DYIBF_ERR_ARG, "unknown option %d", option);
+    }
+}
+
+int dyibf_get_option(const dyibf_filter* f, int option, int64_t* value)
+{
+    if (!f || !value) return fail(DYIBF_ERR_ARG, "NULL argument");
+    switch (option) {
+        case DYIBF_OPT_EARLY_EXIT: *value = (f->query_flags & QUERY_EARLY_EXIT) ? 1 : 0; return DYIBF_OK;
+        default: return fail(DYIBF_ERR_ARG, "unknown option %d", option);
+    }
+}
+
 int dyibf_profile_enable(dyibf_filter* f, int on)
 {
     if (!f) return fail(DYIBF_ERR_ARG, "filter is NULL");
+    DeviceGuard guard(f->prm.device);
+    if (on && !f->stats.p) {
+        CU(f->stats.reserve(64));
+        CU(cudaMemset(f->stats.p, 0, 64));
+    }
     f->profiling = on != 0;
     return DYIBF_OK;
 }
@@ -821,6 +849,12 @@ int dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset)
     out->pack_launches = f->launches[K_PACK]; out->query_launches = f->launches[K_QUERY];
     out->compact_launches = f->launches[K_COMPACT]; out->build_launches = f->launches[K_BUILD];
     out->clear_launches = f->launches[K_CLEAR];
+    out->query_lookups = 0;
+    if (f->stats.p) {                                                  // all launches have drained above
+        CU(cudaDeviceSynchronize());
+        CU(cudaMemcpy(&out->query_lookups, f->stats.p, 8, cudaMemcpyDeviceToHost));
+        if (reset) CU(cudaMemset(f->stats.p, 0, 64));
+    }
     if (reset) for (int i = 0; i < K_N; ++i) { f->ms[i] = 0; f->launches[i] = 0; }
     return DYIBF_OK;
 }

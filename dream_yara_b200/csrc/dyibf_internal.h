@@ -47,9 +47,14 @@ cudaError_t launch_pack(const PackSource& src, int encoding, int derive_rc, uint
 // words needed for a batch whose ranges total `bytes` bytes and n_in sequences (per strand)
 static inline uint64_t packed_words_for(uint64_t bytes, uint64_t n_in) { return bytes / 32 + 2 * n_in + 2; }
 
+// flags of launch_query
+static const uint32_t QUERY_EARLY_EXIT = 1u;   // stop a sequence once no further k-mer can change its bin set (rows only)
+
+// lookup_stat (optional, device): += number of (sequence, column tile, k-mer) lookups actually performed
 cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                          uint32_t n_rows, uint32_t group, uint32_t threshold, uint32_t max_kmers,
-                         uint64_t* out_rows, uint16_t* out_counts, uint32_t* work_counter, int sm_count, cudaStream_t st);
+                         uint64_t* out_rows, uint16_t* out_counts, uint32_t* work_counter, uint32_t flags,
+                         unsigned long long* lookup_stat, int sm_count, cudaStream_t st);
 
 // build: every k-mer of the n_seqs packed forward sequences ORs h bits (bin = bin_ids[s]) into the filter
 cudaError_t launch_build(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,

@@ -76,7 +76,8 @@ template <int VEC, int TL2, int H, int PLANES>
 __global__ void __launch_bounds__(128, 4)
 query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint64_t* __restrict__ packed,
              const SeqMeta* __restrict__ meta, uint32_t n_rows, uint32_t group, uint32_t thr,
-             uint64_t* __restrict__ out_rows, uint16_t* __restrict__ out_counts, uint32_t* __restrict__ work_counter)
+             uint64_t* __restrict__ out_rows, uint16_t* __restrict__ out_counts, uint32_t* __restrict__ work_counter,
+             const uint32_t flags, unsigned long long* __restrict__ lookup_stat)
 {
     constexpr int T  = 1 << TL2;            // lanes per sequence
     constexpr int SG = 32 / T;              // sequences per warp
@@ -99,6 +100,9 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
     // (two dies, near/far L2 slices), so a static split leaves the fast ones idle at the end.  The next claim
     // is issued before the current item is processed, so its round trip is off the critical path.
     const uint32_t n_items = (n_rows + SG - 1) / SG;
+    const bool early_exit = (flags & QUERY_EARLY_EXIT) != 0 && out_counts == nullptr;
+    const uint32_t sub_mask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << (sub * T);
+    uint32_t n_lookups = 0;                 // k-mer lookups this lane took part in (statistics only)
     uint32_t next_item = 0;
     if (lane == 0) next_item = atomicAdd(work_counter, 1u);
     for (;;) {
@@ -134,7 +138,14 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
                     #pragma unroll
                     for (int p = 0; p < PLANES; ++p) pl[w][p] = 0;
 
-                for (uint32_t base = 0; base < nk_max; base += KR) {
+                // Early exit (optional): the result of a sequence is decided as soon as every bin either reached the
+                // threshold, was selected by an earlier strand/mate of the row, or cannot reach it any more with the
+                // k-mers that are left; the remaining lookups cannot change `sel` and are skipped.  `open_mask` holds
+                // the lanes of this warp whose sequence is still undecided.
+                bool seq_open = nk > 0;
+                if (early_exit && (thr == 0 || (PLANES < 32 && thr >= (1u << PLANES)))) seq_open = false;
+                uint32_t open_mask = 0xffffffffu;
+                for (uint32_t base = 0; base < nk_max && open_mask; base += KR) {
                     // --- hash round: lane li computes the block indices of k-mers base + li + m*T
                     idx_t blk[M][HM];
                     #pragma unroll
@@ -152,14 +163,15 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
                     // --- load batches of U k-mers
                     #pragma unroll 1
                     for (uint32_t ub = 0; ub < KR; ub += U) {
-                        if (base + ub >= nk_max) break;
+                        if (base + ub >= nk_max || !open_mask) break;
                         uint32_t x[U][NW];
                         if constexpr (H != 0) {
                             Chunk<VEC> v[U][HM];
                             #pragma unroll
                             for (int u = 0; u < U; ++u) {
                                 const uint32_t step = ub + u;
-                                const bool on = lane_on && (base + step < nk);
+                                const bool on = lane_on && seq_open && (base + step < nk);
+                                n_lookups += on;
                                 #pragma unroll
                                 for (int j = 0; j < HM; ++j) {
                                     const idx_t b = __shfl_sync(0xffffffffu, blk[M == 1 ? 0 : (u / T)][j],
@@ -184,7 +196,8 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
                             bool on[U];
                             #pragma unroll
                             for (int u = 0; u < U; ++u) {
-                                on[u] = lane_on && (base + ub + u < nk);
+                                on[u] = lane_on && seq_open && (base + ub + u < nk);
+                                n_lookups += on[u];
                                 #pragma unroll
                                 for (int w = 0; w < NW; ++w) x[u][w] = on[u] ? 0xffffffffu : 0u;
                             }
@@ -227,6 +240,23 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
                                 ripple<PLANES>(pl[w], 1, c2);
                             }
                         }
+                        if (early_exit) {
+                            const uint32_t done_k = base + ub + U;                 // k-mers of this sequence consumed
+                            bool undecided = false;
+                            if (seq_open && done_k < nk) {
+                                const uint32_t left = nk - done_k;
+                                undecided = true;
+                                if (left < thr) {                                  // bins below thr - left are dead
+                                    uint32_t u_any = 0;
+                                    #pragma unroll
+                                    for (int w = 0; w < NW; ++w)
+                                        u_any |= ge_threshold<PLANES>(pl[w], thr - left) & ~ge_threshold<PLANES>(pl[w], thr) & ~sel[w];
+                                    undecided = lane_on && u_any != 0;
+                                }
+                            }
+                            open_mask = __ballot_sync(0xffffffffu, undecided);
+                            seq_open = seq_open && (open_mask & sub_mask) != 0;
+                        }
                     }
                 }
                 // --- threshold (whichBins :219-223: OR-accumulates; a sequence shorter than k selects nothing)
@@ -263,12 +293,16 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
             }
         }
     }
+    if (lookup_stat != nullptr) {                                   // lane 0 of every sub-group holds its sequence's count
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, li == 0 ? n_lookups : 0u);
+        if (lane == 0 && tot) atomicAdd(lookup_stat, (unsigned long long)tot);
+    }
 }
 
 template <int VEC, int TL2, int H, int PLANES>
 static cudaError_t launch_one(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                               uint32_t n_rows, uint32_t group, uint32_t thr, uint64_t* out_rows, uint16_t* out_counts,
-                              uint32_t* work_counter, int sm_count, cudaStream_t st)
+                              uint32_t* work_counter, uint32_t flags, unsigned long long* lookup_stat, int sm_count, cudaStream_t st)
 {
     auto kern = query_kernel<VEC, TL2, H, PLANES>;
     int per_sm = 0;
@@ -284,28 +318,28 @@ static cudaError_t launch_one(const HashParams& hp, const uint64_t* filter, cons
     e = cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
     kern<<<(unsigned)blocks, 128, 0, st>>>(hp, reinterpret_cast<const uint8_t*>(filter), packed, meta, n_rows, group,
-                                           thr, out_rows, out_counts, work_counter);
+                                           thr, out_rows, out_counts, work_counter, flags, lookup_stat);
     return cudaGetLastError();
 }
 
 template <int VEC, int H, int PLANES>
 static cudaError_t launch_tl2(int tl2, const HashParams& hp, const uint64_t* filter, const uint64_t* packed,
                               const SeqMeta* meta, uint32_t n_rows, uint32_t group, uint32_t thr, uint64_t* out_rows,
-                              uint16_t* out_counts, uint32_t* work_counter, int sm_count, cudaStream_t st)
+                              uint16_t* out_counts, uint32_t* work_counter, uint32_t flags, unsigned long long* lookup_stat, int sm_count, cudaStream_t st)
 {
     switch (tl2) {
-        case 0: return launch_one<VEC, 0, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
-        case 1: return launch_one<VEC, 1, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
-        case 2: return launch_one<VEC, 2, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
-        case 3: return launch_one<VEC, 3, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
-        case 4: return launch_one<VEC, 4, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
-        default: return launch_one<VEC, 5, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, sm_count, st);
+        case 0: return launch_one<VEC, 0, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st);
+        case 1: return launch_one<VEC, 1, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st);
+        case 2: return launch_one<VEC, 2, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st);
+        case 3: return launch_one<VEC, 3, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st);
+        case 4: return launch_one<VEC, 4, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st);
+        default: return launch_one<VEC, 5, H, PLANES>(hp, filter, packed, meta, n_rows, group, thr, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st);
     }
 }
 
 cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                          uint32_t n_rows, uint32_t group, uint32_t threshold, uint32_t max_kmers,
-                         uint64_t* out_rows, uint16_t* out_counts, uint32_t* work_counter, int sm_count, cudaStream_t st)
+                         uint64_t* out_rows, uint16_t* out_counts, uint32_t* work_counter, uint32_t flags, unsigned long long* lookup_stat, int sm_count, cudaStream_t st)
 {
     if (n_rows == 0) return cudaSuccess;
     const bool vec16 = (hp.W % 2u) == 0;
@@ -314,7 +348,7 @@ cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uin
     while (tl2 < 5 && (1u << tl2) < chunks) ++tl2;
     const bool fast = (hp.h == 2 || hp.h == 3) && max_kmers != 0 && max_kmers <= 255 && hp.P <= (1ull << 32);
 #define DYIBF_GO(VEC, H, PLANES) \
-    return launch_tl2<VEC, H, PLANES>(tl2, hp, filter, packed, meta, n_rows, group, threshold, out_rows, out_counts, work_counter, sm_count, st)
+    return launch_tl2<VEC, H, PLANES>(tl2, hp, filter, packed, meta, n_rows, group, threshold, out_rows, out_counts, work_counter, flags, lookup_stat, sm_count, st)
     if (fast) {
         if (vec16) { if (hp.h == 2) DYIBF_GO(16, 2, 8); else DYIBF_GO(16, 3, 8); }
         else       { if (hp.h == 2) DYIBF_GO(8, 2, 8);  else DYIBF_GO(8, 3, 8); }

@@ -253,6 +253,10 @@ class SeqAnBloomFilter:
     def device_words(self):
         return lib().dyibf_device_words(self._h)
 
+    def set_early_exit(self, on=True):
+        """DYIBF_OPT_EARLY_EXIT: stop a sequence once its bin set is decided (rows identical, fewer lookups)."""
+        check(lib().dyibf_set_option(self._h, _lib.OPT_EARLY_EXIT, int(bool(on))))
+
     def profile_enable(self, on=True):
         check(lib().dyibf_profile_enable(self._h, int(on)))
 

@@ -64,6 +64,7 @@ typedef struct dyibf_params {
 typedef struct dyibf_profile {
     double   pack_ms, query_ms, compact_ms, build_ms, clear_ms;
     uint64_t pack_launches, query_launches, compact_launches, build_launches, clear_launches;
+    uint64_t query_lookups;   /* k-mer lookups (h block fetches each) the query kernel performed while profiling was on */
 } dyibf_profile;
 
 const char* dyibf_last_error(void);
@@ -142,6 +143,18 @@ int  dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint6
 int  dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
                     int encoding, int group, int derive_rc, uint32_t threshold,
                     uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
+
+/* ---- options ------------------------------------------------------------------------------- */
+
+/* DYIBF_OPT_EARLY_EXIT (default 0).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it
+ * thresholds the counts (:219-223).  With this option on, and when no per-bin counts are requested, the query kernel
+ * stops a sequence as soon as its bin set is decided: every bin has either reached the threshold, was already selected
+ * by an earlier strand/mate of the same row (the selection only ever ORs), or cannot reach the threshold with the
+ * k-mers left (count + remaining < threshold).  The rows are bit-identical to the full pass; only memory traffic
+ * drops (e.g. 150 bp, k=18, e=3: ~57 % of the lookups). */
+#define DYIBF_OPT_EARLY_EXIT 1
+int  dyibf_set_option(dyibf_filter* f, int option, int64_t value);
+int  dyibf_get_option(const dyibf_filter* f, int option, int64_t* value);
 
 /* ---- instrumentation ----------------------------------------------------------------------- */
 int  dyibf_profile_enable(dyibf_filter* f, int on);

@@ -45,6 +45,9 @@ def test_ka1_build_file_md5_and_query(dy, golden, genomes, reads, ka1_filter, tm
     assert ka.md5_file(path) == str(golden["reference_gold_md5"])
     rows = f.whichBinsBatch(reads, 25, group=2, derive_rc=True)
     assert np.array_equal(rows, golden["ka1_rows"])
+    f.set_early_exit(True)
+    assert np.array_equal(f.whichBinsBatch(reads, 25, group=2, derive_rc=True), golden["ka1_rows"])
+    f.set_early_exit(False)
     # per-bin k-mer counts of single sequences
     idx = [int(i) for i in golden["ka1_count_reads"]]
     _, cnt = f.whichBinsBatch([reads[i] for i in idx], 25, group=1, counts=True)
@@ -72,6 +75,8 @@ def test_ka4_130_bins(dy, golden, genomes, reads):
     f = _gpu_build(dy, ka.ka4_bins(genomes), 3, 18)
     assert (f._binIntWidth, f._noOfHashPos) == (3, 44739242)
     assert ka.md5_filter_words(f.download_words(), f._noOfBits) == str(golden["ka4_md5"])
+    assert np.array_equal(f.whichBinsBatch(reads, 29, group=2, derive_rc=True), golden["ka4_rows"])
+    f.set_early_exit(True)
     assert np.array_equal(f.whichBinsBatch(reads, 29, group=2, derive_rc=True), golden["ka4_rows"])
     f.close()
 
@@ -170,6 +175,23 @@ def test_build_query_counts_vs_oracle(dy, oracle, bins, h, k, nbits):
             assert np.array_equal(got, want), (thr, paired)
             got2 = f.whichBinsBatch((fcat, foff), thr, group=4 if paired else 2, derive_rc=False)
             assert np.array_equal(got2, want), (thr, paired, "full layout")
+    # early-exit mode (DYIBF_OPT_EARLY_EXIT): identical rows from fewer lookups, at every threshold
+    f.profile_enable(True)
+    for thr in (0, 1, 4, 30, 61, 120, 133, 200, 300):
+        for paired in (False, True):
+            want = oracle.classify(words, p, fcat, foff, paired, thr)
+            f.set_early_exit(False); f.profile(reset=True)
+            full = f.whichBinsBatch((cat, off), thr, group=4 if paired else 2, derive_rc=True)
+            n_full = f.profile(reset=True)["query_lookups"]
+            f.set_early_exit(True)
+            got = f.whichBinsBatch((cat, off), thr, group=4 if paired else 2, derive_rc=True)
+            n_ee = f.profile(reset=True)["query_lookups"]
+            assert np.array_equal(full, want) and np.array_equal(got, want), (thr, paired, "early exit")
+            assert n_ee <= n_full and (thr < 30 or n_ee < n_full), (thr, n_ee, n_full)
+    n_tiles = -(-(p.W // 2 if p.W % 2 == 0 else p.W) // 32)
+    total_kmers = sum(max(len(q) - k + 1, 0) for q in qs) * 2
+    assert n_full == total_kmers * n_tiles                          # full mode looks every k-mer of both strands up
+    f.set_early_exit(False); f.profile_enable(False)
     # counts per sequence (both strands)
     _, cnt = f.whichBinsBatch((cat, off), 1, group=2, derive_rc=True, counts=True)
     n = len(qs)
