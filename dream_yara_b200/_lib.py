@@ -52,6 +52,10 @@ SYMBOLS = {
     "dyibf_compact": (C.c_int, [_P, _U64P, C.c_uint32, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, _P]),
     "dyibf_classify": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32,
                                  _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dyibf_classify_fetch": (C.c_int, [_P, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dyibf_sorted_bins": (C.c_int, [_U64P, C.c_uint32, _U32P]),
+    "dyibf_gather_reads": (C.c_int, [_P, C.c_uint32, _U8P, C.c_uint64, _U64P, _U32P, C.c_uint64,
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "dyibf_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
     "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),

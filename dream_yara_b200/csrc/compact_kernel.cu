@@ -192,20 +192,29 @@ cudaError_t launch_compact_count(const uint64_t* rows, uint32_t n_rows, uint32_t
     return cudaGetLastError();
 }
 
+size_t scan_workspace_elems(uint64_t n)
+{
+    return (size_t)(n + 1 + (n + SCAN_TILE - 1) / SCAN_TILE + 1);
+}
+
+// a[0..n) -> exclusive prefix sums in place, a[n] = total; a[n+1..] is scratch (scan_workspace_elems(n) elements in all)
+cudaError_t launch_scan_u64(uint64_t* a, uint64_t n, cudaStream_t st)
+{
+    const uint64_t n_blocks = (n + SCAN_TILE - 1) / SCAN_TILE;
+    uint64_t* block_sums = a + n + 1;
+    if (n == 0) return cudaMemsetAsync(a, 0, sizeof(uint64_t), st);
+    scan_local<<<(unsigned)n_blocks, 1024, 0, st>>>(a, n, block_sums);
+    scan_block_sums<<<1, 1024, 0, st>>>(block_sums, n_blocks, a + n);
+    scan_add<<<(unsigned)n_blocks, 1024, 0, st>>>(a, n, block_sums);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_compact_scan(uint64_t* ws, uint32_t bins, uint32_t n_rows, uint64_t* bin_offsets, cudaStream_t st)
 {
     CompactGeom g = compact_geom(bins, n_rows);
     const uint64_t n = (uint64_t)bins * g.n_chunks;
-    const uint64_t n_blocks = (n + SCAN_TILE - 1) / SCAN_TILE;
-    uint64_t* block_sums = ws + n + 1;
-    if (n == 0) {
-        cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(uint64_t), st);
-        if (e != cudaSuccess) return e;
-    } else {
-        scan_local<<<(unsigned)n_blocks, 1024, 0, st>>>(ws, n, block_sums);
-        scan_block_sums<<<1, 1024, 0, st>>>(block_sums, n_blocks, ws + n);
-        scan_add<<<(unsigned)n_blocks, 1024, 0, st>>>(ws, n, block_sums);
-    }
+    cudaError_t e = launch_scan_u64(ws, n, st);
+    if (e != cudaSuccess) return e;
     gather_bin_offsets<<<(bins + 1 + 255) / 256, 256, 0, st>>>(ws, bins, g.n_chunks, n, bin_offsets);
     return cudaGetLastError();
 }

@@ -71,6 +71,10 @@ struct dyibf_filter {
     bool         owns_words = true;
     Slot         slot[2];
     DevBuf       misc, compact_ws, build_bins, rows_all, stats;
+    // the read batch and the per-bin lists of the last dyibf_classify stay resident for dyibf_gather_reads
+    DevBuf       batch_bytes, batch_offsets, csr_off, csr_ids, gather_ws, gather_out, gather_ids;
+    struct { bool valid = false; uint32_t n_fwd = 0, group = 0, encoding = 0; uint64_t first_off = 0; } batch;
+    std::vector<uint64_t> h_csr_off;
     uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
@@ -262,6 +266,8 @@ void dyibf_destroy(dyibf_filter* f)
         if (f->stage_ev[i]) cudaEventDestroy(f->stage_ev[i]);
     }
     f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release(); f->stats.release();
+    f->batch_bytes.release(); f->batch_offsets.release(); f->csr_off.release(); f->csr_ids.release();
+    f->gather_ws.release(); f->gather_out.release(); f->gather_ids.release();
     if (f->owns_words && f->d_words) cudaFree(f->d_words);
     delete f;
 }
@@ -492,7 +498,7 @@ int check_query_args(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offse
 // Destination: h_rows (host, per-chunk D2H) and/or d_rows_all (device, whole batch).
 int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding, int group,
                int derive_rc, uint32_t threshold, uint32_t max_seq_len, uint64_t* h_rows, uint64_t* d_rows_all,
-               uint16_t* h_counts)
+               uint16_t* h_counts, bool keep_batch = false)
 {
     const uint32_t group_in = derive_rc ? group / 2 : group;
     const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
@@ -518,6 +524,11 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
     chunk_rows = std::max<uint64_t>(chunk_rows, 1024);
     chunk_rows = std::min<uint64_t>(chunk_rows, n_rows);
 
+    if (keep_batch) {                     // the whole forward set stays in HBM, laid out like the caller's buffer
+        f->batch.valid = false;
+        CU(f->batch_bytes.reserve(total_bytes + 16));
+        CU(f->batch_offsets.reserve((uint64_t)(n_seqs + 1) * 8));
+    }
     int rc = DYIBF_OK; uint32_t c = 0;
     for (uint64_t a = 0; a < n_rows && !rc; a += chunk_rows, ++c) {
         const uint32_t cnt = (uint32_t)std::min<uint64_t>(chunk_rows, n_rows - a);
@@ -530,17 +541,21 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
             src.first_off[g] = offsets[s0]; src.pack_base[g] = bytes;
             bytes += offsets[s0 + cnt] - offsets[s0];
         }
-        CU(sl.in_bytes.reserve(bytes + 16));
-        CU(sl.in_offsets.reserve((uint64_t)group_in * (cnt + 1) * 8));
+        if (!keep_batch) {
+            CU(sl.in_bytes.reserve(bytes + 16));
+            CU(sl.in_offsets.reserve((uint64_t)group_in * (cnt + 1) * 8));
+        }
         CU(sl.rows.reserve((uint64_t)cnt * W * 8));
         uint16_t* d_counts = nullptr;
         if (h_counts) { CU(sl.counts.reserve((uint64_t)group * cnt * f->prm.bins * 2)); d_counts = (uint16_t*)sl.counts.p; }
         for (uint32_t g = 0; g < group_in; ++g) {
             const uint64_t s0 = (uint64_t)g * n_rows + a;
             const uint64_t nb = offsets[s0 + cnt] - offsets[s0];
-            uint8_t* dst = (uint8_t*)sl.in_bytes.p + src.pack_base[g];
+            uint8_t* dst = keep_batch ? (uint8_t*)f->batch_bytes.p + (offsets[s0] - offsets[0])
+                                      : (uint8_t*)sl.in_bytes.p + src.pack_base[g];
             if (nb) CU(cudaMemcpyAsync(dst, seqs + offsets[s0], nb, cudaMemcpyHostToDevice, sl.st));
-            uint64_t* doff = (uint64_t*)sl.in_offsets.p + (uint64_t)g * (cnt + 1);
+            uint64_t* doff = keep_batch ? (uint64_t*)f->batch_offsets.p + s0
+                                        : (uint64_t*)sl.in_offsets.p + (uint64_t)g * (cnt + 1);
             CU(cudaMemcpyAsync(doff, offsets + s0, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
             src.bytes[g] = dst - src.first_off[g];
             src.offsets[g] = doff;
@@ -558,6 +573,10 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
     if (rc) return rc;
     if (e0 != cudaSuccess || e1 != cudaSuccess)
         return fail(DYIBF_ERR_CUDA, "query pipeline: %s", cudaGetErrorString(e0 != cudaSuccess ? e0 : e1));
+    if (keep_batch) {
+        f->batch.valid = true; f->batch.n_fwd = n_seqs; f->batch.group = (uint32_t)group; f->batch.encoding = (uint32_t)encoding;
+        f->batch.first_off = offsets[0];
+    }
     return DYIBF_OK;
 }
 
@@ -666,6 +685,23 @@ int dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64
     return DYIBF_OK;
 }
 
+// copy the per-bin lists of the last dyibf_classify to the host
+static int classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total)
+{
+    const uint32_t bins = f->prm.bins;
+    if (f->h_csr_off.size() != (size_t)bins + 1) return fail(DYIBF_ERR_ARG, "no dyibf_classify result is resident");
+    memcpy(bin_offsets, f->h_csr_off.data(), (size_t)(bins + 1) * 8);
+    const uint64_t tot = f->h_csr_off[bins];
+    if (total) *total = tot;
+    if (tot > capacity) return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu",
+                                    (unsigned long long)tot, (unsigned long long)capacity);
+    if (tot == 0) return DYIBF_OK;
+    cudaStream_t st = f->slot[0].st;
+    CU(cudaMemcpyAsync(read_ids, f->csr_ids.p, tot * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return DYIBF_OK;
+}
+
 int dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
                    int group, int derive_rc, uint32_t threshold, uint64_t* bin_offsets, uint32_t* read_ids,
                    uint64_t capacity, uint64_t* total)
@@ -677,31 +713,90 @@ int dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets
     const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
     const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
     const uint32_t n_rows = (uint32_t)(n_total / group);
-    // rows of the whole batch stay in HBM; only the CSR lists cross PCIe
+    f->h_csr_off.clear(); f->batch.valid = false;
+    // rows of the whole batch stay in HBM; only the CSR lists cross PCIe.  With derive_rc the forward read set stays
+    // resident as well, so that dyibf_gather_reads can build the per-bin read sets without a second upload.
     CU(f->rows_all.reserve((uint64_t)n_rows * W * 8 + 8));
     uint64_t* d_rows = (uint64_t*)f->rows_all.p;
     if (n_rows) {
-        rc = query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, 0, nullptr, d_rows, nullptr);
+        rc = query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, 0, nullptr, d_rows, nullptr,
+                        derive_rc != 0);
         if (rc) return rc;
     }
     Slot& sl = f->slot[0];
-    CU(f->misc.reserve((uint64_t)(bins + 1) * 8));
+    CU(f->csr_off.reserve((uint64_t)(bins + 1) * 8));
     uint64_t tot = 0;
-    rc = compact_on_device(f, d_rows, n_rows, (uint64_t*)f->misc.p, nullptr, 0, &tot, sl.st);
+    rc = compact_on_device(f, d_rows, n_rows, (uint64_t*)f->csr_off.p, nullptr, 0, &tot, sl.st);
     if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
-    CU(cudaMemcpyAsync(bin_offsets, f->misc.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
-    CU(cudaStreamSynchronize(sl.st));
-    if (total) *total = tot;
-    if (tot > capacity) return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu",
-                                    (unsigned long long)tot, (unsigned long long)capacity);
-    if (tot == 0) return DYIBF_OK;
-    CU(sl.counts.reserve(tot * 4));
-    {
+    f->h_csr_off.resize((size_t)bins + 1);
+    CU(cudaMemcpyAsync(f->h_csr_off.data(), f->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
+    if (tot) {
+        CU(f->csr_ids.reserve(tot * 4));
         Scope sc(f, sl.st, K_COMPACT);
-        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)sl.counts.p, tot, sl.st));
+        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)f->csr_ids.p, tot, sl.st));
     }
-    CU(cudaMemcpyAsync(read_ids, sl.counts.p, tot * 4, cudaMemcpyDeviceToHost, sl.st));
     CU(cudaStreamSynchronize(sl.st));
+    return classify_fetch(f, bin_offsets, read_ids, capacity, total);
+}
+
+int dyibf_classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total)
+{
+    if (!f || !bin_offsets || (capacity && !read_ids)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    return classify_fetch(f, bin_offsets, read_ids, capacity, total);
+}
+
+int dyibf_sorted_bins(const uint64_t* bin_offsets, uint32_t bins, uint32_t* out_bins)
+{
+    // sortedBins, d_mapper.h:843-854: iota, then std::sort by descending list size — the same (unstable) std::sort
+    // call with the same comparator, so ties come out as the reference's do when built with the same C++ library
+    if (!bin_offsets || !out_bins) return fail(DYIBF_ERR_ARG, "NULL argument");
+    std::vector<uint32_t> idx(bins);
+    for (uint32_t i = 0; i < bins; ++i) idx[i] = i;
+    std::sort(idx.begin(), idx.end(), [bin_offsets](size_t i1, size_t i2) {
+        return bin_offsets[i1 + 1] - bin_offsets[i1] > bin_offsets[i2 + 1] - bin_offsets[i2]; });
+    memcpy(out_bins, idx.data(), (size_t)bins * 4);
+    return DYIBF_OK;
+}
+
+int dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_t capacity_bytes, uint64_t* out_limits,
+                       uint32_t* out_ids, uint64_t capacity_seqs, uint64_t* n_seqs_out, uint64_t* n_bytes_out)
+{
+    if (!f) return fail(DYIBF_ERR_ARG, "filter is NULL");
+    if (!f->batch.valid || f->h_csr_off.size() != (size_t)f->prm.bins + 1)
+        return fail(DYIBF_ERR_ARG, "no read batch is resident: call dyibf_classify with derive_rc != 0 first");
+    if (bin >= f->prm.bins) return fail(DYIBF_ERR_ARG, "bin %u out of range (%u bins)", bin, f->prm.bins);
+    DeviceGuard guard(f->prm.device);
+    const uint64_t m = f->h_csr_off[bin + 1] - f->h_csr_off[bin];
+    const uint64_t n_out = m * f->batch.group;
+    if (n_out > 0xffffffffull) return fail(DYIBF_ERR_ARG, "too many sequences");
+    if (n_seqs_out) *n_seqs_out = n_out;
+    if (n_bytes_out) *n_bytes_out = 0;
+    if (n_out == 0) { if (out_limits) out_limits[0] = 0; return DYIBF_OK; }
+    cudaStream_t st = f->slot[0].st;
+    GatherArgs a;
+    a.bytes = (const uint8_t*)f->batch_bytes.p - f->batch.first_off;
+    a.offsets = (const uint64_t*)f->batch_offsets.p;
+    a.ids = (const uint32_t*)f->csr_ids.p + f->h_csr_off[bin];
+    a.m = (uint32_t)m; a.group = f->batch.group; a.n_fwd = f->batch.n_fwd; a.encoding = f->batch.encoding;
+    CU(f->gather_ws.reserve(scan_workspace_elems(n_out) * 8));
+    CU(f->gather_ids.reserve(n_out * 4));
+    uint64_t* lens = (uint64_t*)f->gather_ws.p;
+    CU(launch_gather_plan(a, lens, (uint32_t*)f->gather_ids.p, st));
+    CU(launch_scan_u64(lens, n_out, st));
+    uint64_t n_bytes = 0;
+    CU(cudaMemcpyAsync(&n_bytes, lens + n_out, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (n_bytes_out) *n_bytes_out = n_bytes;
+    if (n_out > capacity_seqs || n_bytes > capacity_bytes)
+        return fail(DYIBF_ERR_CAPACITY, "bin %u needs %llu sequences / %llu bytes", bin, (unsigned long long)n_out, (unsigned long long)n_bytes);
+    if (!out_limits || !out_ids || (n_bytes && !out_seqs)) return fail(DYIBF_ERR_ARG, "NULL output");
+    CU(f->gather_out.reserve(n_bytes + 16));
+    CU(launch_gather_copy(a, lens, (uint8_t*)f->gather_out.p, st));
+    if (n_bytes) CU(cudaMemcpyAsync(out_seqs, f->gather_out.p, n_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out_limits, lens, (n_out + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out_ids, f->gather_ids.p, n_out * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     return DYIBF_OK;
 }
 

@@ -72,4 +72,22 @@ cudaError_t launch_compact_scan(uint64_t* ws, uint32_t bins, uint32_t n_rows, ui
 cudaError_t launch_compact_fill(const uint64_t* rows, uint32_t n_rows, uint32_t bins, const uint64_t* ws,
                                 uint32_t* read_ids, uint64_t capacity, cudaStream_t st);
 
+// exclusive scan of u64 a[0..n) in place, total in a[n]; `a` must hold scan_workspace_elems(n) elements
+size_t      scan_workspace_elems(uint64_t n);
+cudaError_t launch_scan_u64(uint64_t* a, uint64_t n, cudaStream_t st);
+
+// gather (loadFilteredReads, d_mapper.h:393-443): the read set one bin's mapper receives.
+//   fwd sequences of the resident batch: bytes[offsets[i] - first_off ...], n_fwd of them (SE: reads; PE: m1 then m2)
+//   ids[m]: the bin's read (pair) ids.  Output sequence j of m*group: section j/m = fwd | (mate fwd) | rc...
+struct GatherArgs {
+    const uint8_t*  bytes;        // device, base such that bytes[offsets[i]] is base 0 of forward sequence i
+    const uint64_t* offsets;      // device, n_fwd + 1
+    const uint32_t* ids;          // device, m
+    uint32_t        m, group, n_fwd, encoding;
+};
+// pass 1: lens[j] (u64, to be scanned) and out_ids[j]
+cudaError_t launch_gather_plan(const GatherArgs& a, uint64_t* lens, uint32_t* out_ids, cudaStream_t st);
+// pass 2: copy / reverse-complement into out_bytes at limits[j]
+cudaError_t launch_gather_copy(const GatherArgs& a, const uint64_t* limits, uint8_t* out_bytes, cudaStream_t st);
+
 } // namespace dyibf

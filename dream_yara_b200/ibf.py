@@ -229,15 +229,39 @@ class SeqAnBloomFilter:
         total = C.c_uint64(0)
         cap = int(capacity) if capacity is not None else max(4 * n_rows, 1024)
         L = lib()
-        while True:
+        ids = np.zeros(cap, dtype=np.uint32)
+        rc = L.dyibf_classify(self._h, _ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)), int(threshold),
+                              _ptr(offs), _ptr(ids), cap, C.byref(total))
+        if rc == _lib.ERR_CAPACITY and capacity is None:          # lists are still in HBM: fetch, don't re-run
+            cap = int(total.value)
             ids = np.zeros(cap, dtype=np.uint32)
-            rc = L.dyibf_classify(self._h, _ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)), int(threshold),
-                                  _ptr(offs), _ptr(ids), cap, C.byref(total))
-            if rc == _lib.ERR_CAPACITY and capacity is None:
-                cap = int(total.value)
-                continue
+            rc = L.dyibf_classify_fetch(self._h, _ptr(offs), _ptr(ids), cap, C.byref(total))
+        check(rc)
+        return offs, ids[: total.value]
+
+    def gatherReads(self, binNo):
+        """loadFilteredReads (d_mapper.h:393-443) for one bin of the last classify(derive_rc=True):
+        (bytes u8, limits u64[n+1], ids u32[n]) — fwd reads, [second mates,] then all reverse complements."""
+        L = lib()
+        ns, nb = C.c_uint64(0), C.c_uint64(0)
+        rc = L.dyibf_gather_reads(self._h, int(binNo), None, 0, None, None, 0, C.byref(ns), C.byref(nb))
+        if rc not in (_lib.OK, _lib.ERR_CAPACITY):
             check(rc)
-            return offs, ids[: total.value]
+        out = np.zeros(max(nb.value, 1), dtype=np.uint8)
+        lim = np.zeros(ns.value + 1, dtype=np.uint64)
+        ids = np.zeros(max(ns.value, 1), dtype=np.uint32)
+        if ns.value:
+            check(L.dyibf_gather_reads(self._h, int(binNo), _ptr(out), nb.value, _ptr(lim), _ptr(ids), ns.value,
+                                       C.byref(ns), C.byref(nb)))
+        return out[: nb.value], lim, ids[: ns.value]
+
+    @staticmethod
+    def sortedBins(bin_offsets):
+        """sortedBins (d_mapper.h:843-854): bins by descending list size."""
+        offs = np.ascontiguousarray(bin_offsets, dtype=np.uint64)
+        out = np.zeros(offs.size - 1, dtype=np.uint32)
+        check(lib().dyibf_sorted_bins(_ptr(offs), offs.size - 1, _ptr(out)))
+        return out
 
     # ---- raw words / instrumentation ---------------------------------------------------------------------
     def download_words(self, first=0, n=None):

@@ -3,6 +3,8 @@
     DisOptions.getThreshold      d_mapper.h:83-92
     clasifyLoadedReads           d_mapper.h:308-387
     readFilterMetadata           d_mapper.cpp:532-548
+    loadFilteredReads            d_mapper.h:393-443
+    sortedBins                   d_mapper.h:843-854
 
 The read set has the layout loadReads + appendReverseComplement leave behind (src/mapper.h:444-469,
 src/store_seqs.h:271-290): single-end [fwd | rc], paired-end [m1 | m2 | m1 rc | m2 rc].  `ReadSet` holds the
@@ -15,7 +17,7 @@ import time
 import numpy as np
 
 from ._lib import ENC_DNA5, lib, check
-from .ibf import as_batch
+from .ibf import SeqAnBloomFilter, as_batch
 
 
 def readFilterMetadata(filterFile):
@@ -97,6 +99,7 @@ def clasifyLoadedReads(reads, filter, disOptions, stderr=None):
     group = 4 if reads.paired else 2
     offs, ids = filter.classify((reads.concat, reads.offsets), threshold, group=group, derive_rc=not reads.rc,
                                 encoding=reads.encoding)
+    disOptions.binOffsets = offs
     disOptions.origReadIdMap = []
     for b in range(bins):
         lst = ids[int(offs[b]):int(offs[b + 1])]
@@ -106,3 +109,23 @@ def clasifyLoadedReads(reads, filter, disOptions, stderr=None):
         for b in range(bins):
             err.write("bin %d\t%d\n" % (b, len(disOptions.origReadIdMap[b])))
     return threshold
+
+
+def sortedBins(disOptions):
+    """Bin numbers by descending number of reads (d_mapper.h:843-854)."""
+    sizes = np.array([len(x) for x in disOptions.origReadIdMap], dtype=np.uint64)
+    offs = np.zeros(sizes.size + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(sizes)
+    return SeqAnBloomFilter.sortedBins(offs)
+
+
+def loadFilteredReads(filter, disOptions, binNo):
+    """The read set the mapper of bin `binNo` receives (d_mapper.h:393-443), built on the device from the batch the last
+    clasifyLoadedReads left resident: returns ReadSet-style (bytes, limits) and extends disOptions.origReadIdMap[binNo]
+    exactly as the reference does (mate ids, then reverse-strand ids appended).  Not valid after threshold == 0
+    batches (the reference's double-push quirk makes the list differ from the filter's)."""
+    t0 = time.perf_counter()
+    seq_bytes, limits, ids = filter.gatherReads(binNo)
+    disOptions.origReadIdMap[binNo] = ids
+    disOptions.copyReads = getattr(disOptions, "copyReads", 0.0) + time.perf_counter() - t0
+    return seq_bytes, limits

@@ -23,6 +23,8 @@
 #include <cstdint>
 #include <cstdlib>
 #include <iostream>
+#include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -64,19 +66,21 @@ namespace seqan
         // the object owns a device handle: movable, not copyable (the reference object was never copied either)
         SeqAnBloomFilter(SeqAnBloomFilter const &) = delete;
         SeqAnBloomFilter & operator=(SeqAnBloomFilter const &) = delete;
-        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _prm(o._prm) { o._h = nullptr; }
+        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _prm(o._prm), _mtx(std::move(o._mtx)) { o._h = nullptr; }
 
         // d_bloom_filter.h:91
         void addKmers(TString const & text, uint32_t const & binNo)
         {
             if (length(text) < _prm.kmer) return;               // reference: out-of-bounds hashing; here: nothing
             uint64_t offsets[2] = {0, (uint64_t)length(text)};
+            std::lock_guard<std::mutex> lock(*_mtx);
             _check(dyibf_add_sequences(_h, _bytes(text), offsets, 1, &binNo, _encoding(text), DYIBF_MEM_HOST, nullptr));
         }
 
         // d_bloom_filter.h:99 — threadsCount is accepted for source compatibility; the GPU does the pass
         void clearBins(std::vector<uint32_t> & bins2clear, uint32_t & /*threadsCount*/)
         {
+            std::lock_guard<std::mutex> lock(*_mtx);
             _check(dyibf_clear_bins(_h, bins2clear.data(), (uint32_t)bins2clear.size()));
         }
 
@@ -108,6 +112,7 @@ namespace seqan
             if (offsets.size() > 1)
             {
                 std::vector<uint32_t> bins(offsets.size() - 1, binNo);
+                std::lock_guard<std::mutex> lock(*_mtx);     // the reference calls this from several threads (one per bin range)
                 _check(dyibf_add_sequences(_h, concat.data(), offsets.data(), (uint32_t)bins.size(), bins.data(),
                                            _encodingOf((typename Value<TString>::Type *)nullptr), DYIBF_MEM_HOST, nullptr));
             }
@@ -116,6 +121,7 @@ namespace seqan
         // d_bloom_filter.h:150
         bool save(const char *fileName)
         {
+            std::lock_guard<std::mutex> lock(*_mtx);
             return dyibf_save_file(_h, fileName) == DYIBF_OK;
         }
 
@@ -131,6 +137,7 @@ namespace seqan
             if (length(text) < _prm.kmer) return;               // reference: uint16 wrap + out-of-bounds reads
             uint64_t offsets[2] = {0, (uint64_t)length(text)};
             std::vector<uint64_t> row(_prm.words_per_block, 0);
+            std::lock_guard<std::mutex> lock(*_mtx);             // called from threadsCount std::async tasks (d_mapper.h:338-375)
             _check(dyibf_query_batch(_h, _bytes(text), offsets, 1, _encoding(text), 1, 0, threshold, 0, row.data(), nullptr,
                                      DYIBF_MEM_HOST, nullptr));
             for (uint32_t binNo = 0; binNo < _prm.bins; ++binNo)
@@ -160,6 +167,7 @@ namespace seqan
         {
             uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
             rows.assign((n_total / group) * _prm.words_per_block, 0);
+            std::lock_guard<std::mutex> lock(*_mtx);
             _check(dyibf_query_batch(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold, 0,
                                      rows.data(), nullptr, DYIBF_MEM_HOST, nullptr));
         }
@@ -172,13 +180,13 @@ namespace seqan
             uint64_t n_rows = (derive_rc ? 2ull * n_seqs : n_seqs) / group;
             std::vector<uint32_t> ids(std::max<uint64_t>(4 * n_rows, 1024));
             uint64_t total = 0;
+            std::lock_guard<std::mutex> lock(*_mtx);
             int rc = dyibf_classify(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
                                     binOffsets.data(), ids.data(), ids.size(), &total);
-            if (rc == DYIBF_ERR_CAPACITY)
+            if (rc == DYIBF_ERR_CAPACITY)                        // the lists are still in HBM: fetch, no second pass
             {
                 ids.resize(total);
-                rc = dyibf_classify(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
-                                    binOffsets.data(), ids.data(), ids.size(), &total);
+                rc = dyibf_classify_fetch(_h, binOffsets.data(), ids.data(), ids.size(), &total);
             }
             _check(rc);
             readIdsPerBin.assign(_prm.bins, std::vector<uint32_t>());
@@ -186,8 +194,36 @@ namespace seqan
                 readIdsPerBin[b].assign(ids.begin() + binOffsets[b], ids.begin() + binOffsets[b + 1]);
         }
 
+        // loadFilteredReads (d_mapper.h:393-443) for one bin of the last classify(derive_rc = true): the read set the
+        // bin's mapper receives (bytes + limits, a ConcatDirect layout) and origReadIdMap[bin] as the reference extends it.
+        void gatherReads(uint32_t binNo, std::vector<uint8_t> & bytes, std::vector<uint64_t> & limits,
+                         std::vector<uint32_t> & ids) const
+        {
+            uint64_t ns = 0, nb = 0;
+            std::lock_guard<std::mutex> lock(*_mtx);
+            int rc = dyibf_gather_reads(_h, binNo, nullptr, 0, nullptr, nullptr, 0, &ns, &nb);
+            if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) _check(rc);
+            bytes.resize(nb); limits.assign(ns + 1, 0); ids.resize(ns);
+            if (ns)
+                _check(dyibf_gather_reads(_h, binNo, bytes.data(), nb, limits.data(), ids.data(), ns, &ns, &nb));
+        }
+
+        // sortedBins (d_mapper.h:843-854) from per-bin list sizes
+        static std::vector<uint32_t> sortedBins(std::vector<std::vector<uint32_t> > const & readIdsPerBin)
+        {
+            std::vector<uint64_t> offs(readIdsPerBin.size() + 1, 0);
+            for (size_t b = 0; b < readIdsPerBin.size(); ++b) offs[b + 1] = offs[b] + readIdsPerBin[b].size();
+            std::vector<uint32_t> out(readIdsPerBin.size());
+            _check(dyibf_sorted_bins(offs.data(), (uint32_t)readIdsPerBin.size(), out.data()));
+            return out;
+        }
+
+        // DYIBF_OPT_EARLY_EXIT (see dyibf.h): identical bin sets from fewer lookups
+        void setEarlyExit(bool on) { _check(dyibf_set_option(_h, DYIBF_OPT_EARLY_EXIT, on ? 1 : 0)); }
+
         void addSequences(const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs, const uint32_t * binIds, int encoding)
         {
+            std::lock_guard<std::mutex> lock(*_mtx);
             _check(dyibf_add_sequences(_h, concat, limits, n_seqs, binIds, encoding, DYIBF_MEM_HOST, nullptr));
         }
 
@@ -224,6 +260,8 @@ namespace seqan
 
         dyibf_filter *  _h = nullptr;
         dyibf_params    _prm;
+        // a handle is stream-ordered: calls are serialised here, as the reference's callers use one object from many threads
+        std::unique_ptr<std::mutex> _mtx{new std::mutex()};
     };
 }
 

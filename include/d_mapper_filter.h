@@ -20,6 +20,7 @@
 #define APP_YARA_DIS_MAPPER_FILTER_B200_H_
 
 #include <cstdint>
+#include <cstring>
 #include <iostream>
 #include <vector>
 
@@ -83,6 +84,42 @@ inline void clasifyLoadedReadsB200(TReadSeqs & readSeqs, TFilter const & filter,
         for (uint32_t binNo = 0; binNo < disOptions.numberOfBins; ++binNo)
             std::cerr << "bin " << binNo << "\t" << disOptions.origReadIdMap[binNo].size() << std::endl;
     }
+}
+
+// sortedBins (src/d_mapper.h:843-854): same std::sort call, same comparator.
+template <typename TDisOptions>
+inline std::vector<uint32_t> sortedBinsB200(TDisOptions const & disOptions)
+{
+    std::vector<uint64_t> offs(disOptions.numberOfBins + 1, 0);
+    for (uint32_t b = 0; b < disOptions.numberOfBins; ++b)
+        offs[b + 1] = offs[b] + disOptions.origReadIdMap[b].size();
+    std::vector<uint32_t> out(disOptions.numberOfBins);
+    dyibf_sorted_bins(offs.data(), disOptions.numberOfBins, out.data());
+    return out;
+}
+
+// Replacement body for loadFilteredReads (src/d_mapper.h:393-443), filterType != NONE: the child mapper's read set
+// [fwd | (mates) | reverse complements] is assembled on the GPU from the batch clasifyLoadedReadsB200 left resident
+// and arrives as one bytes + limits pair; origReadIdMap[currentBinNo] is extended exactly as the reference does.
+// Not valid for threshold == 0 batches (the reference's double-pushed lists): fall back to the reference body there.
+//     loadFilteredReadsB200(me.reads.seqs, filter, disOptions);
+template <typename TReadSeqs, typename TFilter, typename TDisOptions>
+inline void loadFilteredReadsB200(TReadSeqs & childSeqs, TFilter const & filter, TDisOptions & disOptions)
+{
+    std::vector<uint8_t> bytes;
+    std::vector<uint64_t> limits;
+    std::vector<uint32_t> ids;
+    filter.gatherReads(disOptions.currentBinNo, bytes, limits, ids);
+    typedef typename Value<typename Value<TReadSeqs>::Type>::Type TAlphabet;
+    static_assert(sizeof(TAlphabet) == 1, "one byte per base expected");
+    clear(childSeqs);
+    resize(concat(childSeqs), bytes.size(), Exact());
+    if (!bytes.empty())
+        std::memcpy(reinterpret_cast<uint8_t *>(&*begin(concat(childSeqs), Standard())), bytes.data(), bytes.size());
+    resize(stringSetLimits(childSeqs), limits.size(), Exact());
+    for (size_t i = 0; i < limits.size(); ++i)
+        stringSetLimits(childSeqs)[i] = limits[i];
+    disOptions.origReadIdMap[disOptions.currentBinNo] = ids;
 }
 
 }

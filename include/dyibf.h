@@ -144,6 +144,24 @@ int  dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offset
                     int encoding, int group, int derive_rc, uint32_t threshold,
                     uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
 
+/* The per-bin lists of the last dyibf_classify again (they stay in HBM): for a caller whose first buffer was too
+ * small (DYIBF_ERR_CAPACITY) — no second pass over the reads. */
+int  dyibf_classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
+
+/* sortedBins, d_mapper.h:843-854: bin numbers by descending list size (std::sort, same comparator). bin_offsets[bins+1]
+ * as dyibf_classify / dyibf_compact return them. */
+int  dyibf_sorted_bins(const uint64_t* bin_offsets, uint32_t bins, uint32_t* out_bins);
+
+/* loadFilteredReads, d_mapper.h:393-443, for one bin after dyibf_classify(derive_rc != 0) — the read batch and the
+ * lists are still resident in HBM, nothing is uploaded again.  With m = the bin's list length the output holds
+ * m*group sequences in the reference's order: the m forward reads (first mates), [paired-end: the m second mates,]
+ * then the reverse complements of all of those (Dna5Q: quality kept, N stays N), as bytes + limits (n+1 entries, a
+ * ConcatDirect StringSet's layout), and out_ids = origReadIdMap[bin] as loadFilteredReads leaves it:
+ * id, [id+numPairs,] then each of those + numReads.  *n_seqs_out / *n_bytes_out always receive the needed sizes;
+ * DYIBF_ERR_CAPACITY if either buffer is too small. */
+int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_t capacity_bytes, uint64_t* out_limits,
+                        uint32_t* out_ids, uint64_t capacity_seqs, uint64_t* n_seqs_out, uint64_t* n_bytes_out);
+
 /* ---- options ------------------------------------------------------------------------------- */
 
 /* DYIBF_OPT_EARLY_EXIT (default 0).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it

@@ -232,6 +232,49 @@ uint64_t ibf_compact(const uint64_t *rows, uint32_t numReads, uint32_t bins, uin
     return total;
 }
 
+/* reverseComplement of a Dna5Q string as appendReverseComplement applies it to the reads (store_seqs.h:271-290):
+ * FunctorComplement<Dna5Q> (modifier_functors.h:276-284) complements the base and re-assigns the quality;
+ * N (byte 252, no quality: alphabet_residue.h:287,357-365) stays 252. */
+void ibf_revcomp_dna5q(const uint8_t *bytes, uint64_t len, uint8_t *out)
+{
+    for (uint64_t i = 0; i < len; ++i) {
+        uint8_t b = bytes[len - 1 - i];
+        out[i] = b >= 252 ? 252 : (uint8_t)((b & 0xFC) | (3 - (b & 3)));
+    }
+}
+
+/* loadFilteredReads, d_mapper.h:393-443 (filterType != NONE), over flat buffers.
+ * seqs/offsets: the main mapper's FULL read set (n_seqs sequences incl. reverse complements; any byte encoding —
+ * sequences are copied verbatim).  ids[m] = origReadIdMap[bin] as the filter left it.  Output: the child read set
+ * (out_bytes, out_limits[n_out+1]) and the extended id list out_ids[n_out]; n_out = 2m (SE) or 4m (PE).
+ * Returns n_out. */
+uint64_t ibf_load_filtered_reads(const uint8_t *seqs, const uint64_t *offsets, uint32_t n_seqs, int paired,
+                                 const uint32_t *ids, uint32_t m, uint8_t *out_bytes, uint64_t *out_limits, uint32_t *out_ids)
+{
+    uint32_t numReads = n_seqs / 2;            /* getReadsCount, bits_reads.h:57-62 */
+    uint32_t numPairs = n_seqs / 4;            /* getPairsCount, bits_reads.h:64-69 */
+    uint64_t n_out = 0, nb = 0;
+    uint32_t numFiltered = m;
+    out_limits[0] = 0;
+    for (uint32_t i = 0; i < m; ++i) out_ids[i] = ids[i];
+    #define IBF_APPEND(src_) do { uint32_t s__ = (src_); uint64_t l__ = offsets[s__ + 1] - offsets[s__]; \
+        memcpy(out_bytes + nb, seqs + offsets[s__], l__); nb += l__; out_limits[++n_out] = nb; } while (0)
+    for (uint32_t i = 0; i < numFiltered; ++i) IBF_APPEND(out_ids[i]);                       /* :413-417 forward reads */
+    if (paired) {
+        for (uint32_t i = 0; i < numFiltered; ++i) {                                          /* :423-428 mates */
+            IBF_APPEND(out_ids[i] + numPairs);
+            out_ids[numFiltered + i] = out_ids[i] + numPairs;
+        }
+        numFiltered *= 2;                                                                     /* :429 */
+    }
+    for (uint32_t i = 0; i < numFiltered; ++i) {                                              /* :433-438 reverse reads */
+        IBF_APPEND(out_ids[i] + numReads);
+        out_ids[numFiltered + i] = out_ids[i] + numReads;
+    }
+    #undef IBF_APPEND
+    return n_out;
+}
+
 /* clearBins, d_bloom_filter.h:99-123: clear bit p*S+bin for every hash block */
 void ibf_clear_bins(uint64_t *words, const ibf_params *p, const uint32_t *bins, uint32_t n)
 {

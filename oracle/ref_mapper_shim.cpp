@@ -100,7 +100,72 @@ static void run_classify(const char* filterFile, const uint8_t* codes, const uin
     bin_offsets[disOptions.numberOfBins] = pos;
 }
 
+// loadFilteredReads (d_mapper.h:393-443) + sortedBins (:843-854) after clasifyLoadedReads, for the requested bins.
+// The reads carry qualities so that the Dna5Q bytes (and their reverse complements) are exercised.
+template <typename TSequencing>
+static void run_gather(const char* filterFile, const uint8_t* codes, const uint8_t* quals, const uint64_t* offsets,
+                       uint32_t n_seqs, int e_percent, const uint32_t* bins, uint32_t n_req,
+                       uint8_t* fwd_bytes, uint8_t* out_bytes, uint64_t cap_bytes, uint64_t* out_limits, uint32_t* out_ids,
+                       uint64_t cap_seqs, uint64_t* seq_start, uint32_t* sorted_bins)
+{
+    typedef ReadMapperConfig<Parallel, TSequencing, EditDistance, uint8_t, uint32_t, uint32_t> TMainConfig;
+    DisOptions disOptions;
+    disOptions.errorRate = e_percent / 100.0;
+    disOptions.threadsCount = 1;
+    disOptions.verbose = 0;
+    disOptions.filterType = BLOOM;
+    SeqAnBloomFilter<> filter(filterFile);
+    disOptions.kmerSize = filter.getKmerSize();
+    disOptions.numberOfBins = filter.getNumberOfBins();
+    Mapper<void, TMainConfig> mainMapper(disOptions);
+    for (uint32_t s = 0; s < n_seqs; ++s)
+    {
+        String<Dna5Q> r;
+        resize(r, offsets[s + 1] - offsets[s]);
+        for (uint64_t i = 0; i < length(r); ++i)
+        {
+            r[i] = Dna5(codes[offsets[s] + i]);
+            assignQualityValue(r[i], (int)quals[offsets[s] + i]);
+        }
+        appendValue(mainMapper.reads.seqs, r);
+    }
+    for (uint64_t i = 0; i < offsets[n_seqs]; ++i)         // the forward bytes exactly as the ConcatDirect set holds them
+        fwd_bytes[i] = concat(mainMapper.reads.seqs)[i].value;
+    appendReverseComplement(mainMapper.reads);
+    clasifyLoadedReads(mainMapper, filter, disOptions);
+    std::vector<uint32_t> sb = sortedBins(disOptions);
+    for (uint32_t b = 0; b < disOptions.numberOfBins; ++b) sorted_bins[b] = sb[b];
+    uint64_t n_out = 0, n_bytes = 0;
+    out_limits[0] = 0;
+    for (uint32_t q = 0; q < n_req; ++q)
+    {
+        seq_start[q] = n_out;
+        disOptions.currentBinNo = bins[q];
+        Mapper<void, TMainConfig> me(disOptions);
+        loadFilteredReads(me, mainMapper, disOptions);
+        std::vector<uint32_t> const & ids = disOptions.origReadIdMap[bins[q]];
+        for (uint32_t i = 0; i < length(me.reads.seqs); ++i)
+        {
+            if (n_out >= cap_seqs) return;
+            for (uint64_t x = 0; x < length(me.reads.seqs[i]); ++x)
+                if (n_bytes < cap_bytes) out_bytes[n_bytes++] = me.reads.seqs[i][x].value;
+            out_ids[n_out] = ids[i];
+            out_limits[++n_out] = n_bytes;
+        }
+    }
+    seq_start[n_req] = n_out;
+}
+
 extern "C" {
+
+void refm_gather(const char* filterFile, const uint8_t* codes, const uint8_t* quals, const uint64_t* offsets, uint32_t n_seqs,
+                 int paired, int e_percent, const uint32_t* bins, uint32_t n_req, uint8_t* fwd_bytes,
+                 uint8_t* out_bytes, uint64_t cap_bytes, uint64_t* out_limits, uint32_t* out_ids, uint64_t cap_seqs,
+                 uint64_t* seq_start, uint32_t* sorted_bins)
+{
+    if (paired) run_gather<PairedEnd>(filterFile, codes, quals, offsets, n_seqs, e_percent, bins, n_req, fwd_bytes, out_bytes, cap_bytes, out_limits, out_ids, cap_seqs, seq_start, sorted_bins);
+    else        run_gather<SingleEnd>(filterFile, codes, quals, offsets, n_seqs, e_percent, bins, n_req, fwd_bytes, out_bytes, cap_bytes, out_limits, out_ids, cap_seqs, seq_start, sorted_bins);
+}
 
 // DisOptions::getThreshold with errorRate set the way the CLI parser sets it
 uint16_t refm_threshold(int e_percent, uint32_t kmerSize, uint16_t readLen)

@@ -22,6 +22,12 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def gather_golden():
+    """loadFilteredReads / sortedBins vectors from the unmodified reference (tests/golden/make_golden_gather.py)."""
+    return np.load(os.path.join(HERE, "golden", "gather_vectors.npz"))
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle_py import Oracle
     return Oracle()

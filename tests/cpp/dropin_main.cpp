@@ -7,6 +7,8 @@
 //   dropin_test build    <bins> <h> <k> <nbits> <dir with 0.fa..> <out.filter>
 //   dropin_test query    <filter> <reads.fa> <threshold> <out.txt>      per-read whichBins(fwd) | whichBins(rc)
 //   dropin_test classify <filter> <reads.fa> <e percent> <paired 0/1> <out.txt>
+//   dropin_test gather   <filter> <reads.fa> <e percent> <paired 0/1> <out.txt>   classify, then sortedBins and
+//                        loadFilteredReads for every bin in that order (reads get synthetic qualities)
 #include <climits>
 #include <limits.h>
 #undef INT_WIDTH
@@ -39,6 +41,7 @@ struct MiniDisOptions
     uint32_t    numberOfBins = 64;
     int         verbose = 0;
     double      filterReads = 0;
+    uint32_t    currentBinNo = 0;
     std::vector<std::vector<uint32_t> > origReadIdMap;
     uint16_t getThreshold(uint16_t readLen) { return dyibf_threshold_rate(errorRate, kmerSize, readLen); }
 };
@@ -100,6 +103,44 @@ int main(int argc, char ** argv)
             {
                 for (uint32_t r : opt.origReadIdMap[b]) out << r << ' ';
                 out << '\n';
+            }
+            return 0;
+        }
+        if (mode == "gather" && argc == 7)
+        {
+            SeqAnBloomFilter<> filter(argv[2]);
+            bool paired = std::stoi(argv[5]) != 0;
+            StringSet<String<Dna5Q>, Owner<ConcatDirect<> > > seqs;
+            SeqFileIn in(argv[3]);
+            CharString id; String<Dna5Q> seq;
+            uint64_t pos = 0;
+            while (!atEnd(in))
+            {
+                readRecord(id, seq, in);
+                for (uint64_t i = 0; i < length(seq); ++i, ++pos) assignQualityValue(seq[i], (int)((pos * 7 + 11) % 63));
+                appendValue(seqs, seq);
+            }
+            uint32_t n = length(seqs);
+            for (uint32_t i = 0; i < n; ++i) { String<Dna5Q> rc = seqs[i]; reverseComplement(rc); appendValue(seqs, rc); }
+            MiniDisOptions opt;
+            opt.errorRate = std::stoi(argv[4]) / 100.0;
+            opt.kmerSize = filter.getKmerSize(); opt.numberOfBins = filter.getNumberOfBins();
+            MiniTimer timer;
+            clasifyLoadedReadsB200(seqs, filter, opt, paired, timer);
+            std::ofstream out(argv[6]);
+            for (uint32_t b : sortedBinsB200(opt))
+            {
+                opt.currentBinNo = b;
+                StringSet<String<Dna5Q>, Owner<ConcatDirect<> > > child;
+                loadFilteredReadsB200(child, filter, opt);
+                out << "bin " << b << ' ' << length(child) << '\n';
+                for (uint32_t r : opt.origReadIdMap[b]) out << r << ' ';
+                out << '\n';
+                for (uint32_t i = 0; i < length(child); ++i)
+                {
+                    for (uint64_t x = 0; x < length(child[i]); ++x) out << (unsigned)child[i][x].value << ' ';
+                    out << '\n';
+                }
             }
             return 0;
         }

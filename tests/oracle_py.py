@@ -64,6 +64,9 @@ class Oracle:
         l.ibf_load.argtypes = [C.c_char_p, _V, C.c_uint64, C.POINTER(IbfParams)]
         l.ibf_encode_ascii.argtypes = [C.c_char_p, C.c_uint64, _V]
         l.ibf_revcomp.argtypes = [_V, C.c_uint64, _V]
+        l.ibf_revcomp_dna5q.argtypes = [_V, C.c_uint64, _V]
+        l.ibf_load_filtered_reads.restype = C.c_uint64
+        l.ibf_load_filtered_reads.argtypes = [_V, _V, C.c_uint32, C.c_int, _V, C.c_uint32, _V, _V, _V]
 
     def params(self, bins, h, k, nbits):
         p = IbfParams()
@@ -136,6 +139,35 @@ class Oracle:
         ids = np.zeros(max(total, 1), dtype=np.uint32)
         self.l.ibf_compact(_p(rows), n, bins, _p(offs), _p(ids))
         return offs.astype(np.uint64), ids[:total]
+
+    def full_layout_dna5q(self, concat, offsets):
+        """appendReverseComplement on raw Dna5Q bytes (quality kept, N stays 252): [fwd | rc] concat, offsets."""
+        concat = np.ascontiguousarray(concat, dtype=np.uint8); offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = offsets.size - 1
+        base = int(offsets[0]); total = int(offsets[-1]) - base
+        cat = np.zeros(2 * total, dtype=np.uint8)
+        cat[:total] = concat[base:base + total]
+        off = np.zeros(2 * n + 1, dtype=np.uint64)
+        off[: n + 1] = offsets - offsets[0]
+        for i in range(n):
+            a, b = int(off[i]), int(off[i + 1])
+            out = np.zeros(max(b - a, 1), dtype=np.uint8)
+            self.l.ibf_revcomp_dna5q(_p(np.ascontiguousarray(cat[a:b])), b - a, _p(out))
+            cat[total + a: total + b] = out[: b - a]
+            off[n + 1 + i] = total + b
+        return cat, off
+
+    def load_filtered_reads(self, full_concat, full_offsets, paired, ids):
+        """loadFilteredReads over the FULL read set: (bytes, limits, extended ids)."""
+        fc = np.ascontiguousarray(full_concat, dtype=np.uint8); fo = np.ascontiguousarray(full_offsets, dtype=np.uint64)
+        ids = np.ascontiguousarray(ids, dtype=np.uint32)
+        n_out = ids.size * (4 if paired else 2)
+        longest = int(np.max(np.diff(fo.astype(np.int64)))) if fo.size > 1 else 0
+        ob = np.zeros(max(n_out * longest, 1), dtype=np.uint8)
+        ol = np.zeros(n_out + 1, dtype=np.uint64); oi = np.zeros(max(n_out, 1), dtype=np.uint32)
+        n = self.l.ibf_load_filtered_reads(_p(fc), _p(fo), fo.size - 1, int(paired), _p(ids), ids.size, _p(ob), _p(ol), _p(oi))
+        assert n == n_out
+        return ob[: int(ol[n_out])], ol, oi[:n_out]
 
     def clear_bins(self, words, p, bins):
         b = np.ascontiguousarray(bins, dtype=np.uint32)

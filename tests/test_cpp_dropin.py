@@ -62,6 +62,30 @@ def test_dropin_build_query_classify(golden, tmp_path):
         for b in range(64):
             assert [int(x) for x in lines[b].split()] == list(ids[int(bo[b]):int(bo[b + 1])]), (tag, b)
         assert "bin 0\t173" in r.stderr                         # -vv dump, d_mapper.h:380-386
+    # sortedBins + loadFilteredReads replacements vs the reference's own output (Dna5Q bytes incl. qualities)
+    gg = np.load(os.path.join(HERE, "golden", "gather_vectors.npz"))
+    for tag, paired in (("se", 0), ("pe", 1)):
+        out = tmp_path / ("g_%s.txt" % tag)
+        r = subprocess.run([BIN, "gather", str(filt), str(tmp_path / "reads.fa"), "3", str(paired), str(out)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        lines = open(out).read().split("\n")
+        order, at, per_bin = [], 0, {}
+        while at < len(lines) and lines[at].startswith("bin "):
+            _, b, n = lines[at].split()
+            b, n = int(b), int(n)
+            order.append(b)
+            per_bin[b] = (lines[at + 1], lines[at + 2: at + 2 + n])
+            at += 2 + n
+        assert order == list(gg[tag + "_sorted_bins"])
+        lim, ss = gg[tag + "_limits"], gg[tag + "_seq_start"]
+        for q, b in enumerate(gg["bins"]):
+            a, e = int(ss[q]), int(ss[q + 1])
+            ids_line, seq_lines = per_bin[int(b)]
+            assert [int(x) for x in ids_line.split()] == list(gg[tag + "_ids"][a:e]), (tag, b)
+            assert len(seq_lines) == e - a
+            for j, ln in enumerate(seq_lines):
+                want = gg[tag + "_bytes"][int(lim[a + j]):int(lim[a + j + 1])]
+                assert [int(x) for x in ln.split()] == list(want), (tag, b, j)
     # load failure: message + exit(1) as the reference
     r = subprocess.run([BIN, "query", str(tmp_path / "nope.filter"), str(tmp_path / "reads400.fa"), "25", str(tmp_path / "x")], capture_output=True, text=True)
     assert r.returncode == 1 and "could not be read" in r.stderr

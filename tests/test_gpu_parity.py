@@ -281,3 +281,57 @@ def test_single_sequence_api_and_errors(dy, oracle, tmp_path):
     nd = p.P * p.W
     assert np.array_equal(f.download_words()[:nd], words[:nd])
     f.close()
+
+
+@pytest.mark.parametrize("tag,paired", [("se", False), ("pe", True)])
+def test_gather_reads_and_sorted_bins_vs_reference(dy, golden, gather_golden, ka1_filter, tag, paired):
+    """loadFilteredReads + sortedBins on the device against the reference's own output
+    (Dna5Q bytes with qualities; SE and PE)."""
+    if "ka5_se_threshold" not in golden.files:
+        pytest.skip("fixture made without libref_mapper.so")
+    g = gather_golden
+    f = ka1_filter
+    thr = int(golden["ka5_%s_threshold" % tag])
+    offs, ids = f.classify((g[tag + "_fwd_bytes"], golden["reads_offsets"]), thr, group=4 if paired else 2, derive_rc=True,
+                           encoding=dy.ENC_DNA5Q)
+    assert np.array_equal(offs, golden["ka5_%s_bin_offsets" % tag])
+    assert np.array_equal(ids, golden["ka5_%s_read_ids" % tag])
+    assert np.array_equal(f.sortedBins(offs), g[tag + "_sorted_bins"])
+    lim, ss = g[tag + "_limits"], g[tag + "_seq_start"]
+    for q, b in enumerate(g["bins"]):
+        ob, ol, oi = f.gatherReads(int(b))
+        a, e = int(ss[q]), int(ss[q + 1])
+        assert np.array_equal(oi, g[tag + "_ids"][a:e]), (tag, b)
+        assert np.array_equal(ol, lim[a:e + 1] - lim[a]), (tag, b)
+        assert np.array_equal(ob, g[tag + "_bytes"][int(lim[a]):int(lim[e])]), (tag, b)
+
+
+@pytest.mark.parametrize("paired", [False, True])
+def test_gather_reads_random_vs_oracle(dy, oracle, paired):
+    """Ragged read lengths (incl. empty reads and reads shorter than k), every bin, capacity retry path."""
+    bins, h, k, nbits = 96, 3, 18, (1 << 22) + 256
+    rng = np.random.default_rng(77 + paired)
+    contigs = [rng.integers(0, 4, 3000).astype(np.uint8) for _ in range(bins)]
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addSequences(contigs, np.arange(bins))
+    reads = []
+    for i in range(400):
+        c = contigs[int(rng.integers(0, bins))]
+        L = int(rng.integers(0, 160))
+        st = int(rng.integers(0, len(c) - 160))
+        q = (rng.integers(0, 63, L) << 2).astype(np.uint8) | c[st:st + L]
+        q[rng.random(L) < 0.02] = 252
+        reads.append(q.astype(np.uint8))
+    cat = np.concatenate(reads); off = np.zeros(len(reads) + 1, dtype=np.uint64); off[1:] = np.cumsum([len(r) for r in reads])
+    offs, ids = f.classify((cat, off), 5, group=4 if paired else 2, derive_rc=True, encoding=dy.ENC_DNA5Q, capacity=None)
+    fcat, foff = oracle.full_layout_dna5q(cat, off)
+    assert int(offs[-1]) > 100
+    for b in range(bins):
+        mine = ids[int(offs[b]):int(offs[b + 1])]
+        wb, wl, wi = oracle.load_filtered_reads(fcat, foff, paired, mine)
+        ob, ol, oi = f.gatherReads(b)
+        assert np.array_equal(oi, wi) and np.array_equal(ol, wl) and np.array_equal(ob, wb), b
+    sb = f.sortedBins(offs)
+    sizes = np.diff(offs.astype(np.int64))
+    assert sorted(sb.tolist()) == list(range(bins)) and np.all(np.diff(sizes[sb]) <= 0)
+    f.close()

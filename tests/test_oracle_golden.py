@@ -179,3 +179,28 @@ def test_oracle_vs_compiled_reference_direct(oracle):
         for thr in (1, 3, 50):
             assert np.array_equal(ref.which_bins(f, q, thr, bins), oracle.which_bins(words, p, q, thr))
     ref.free(f)
+
+
+@pytest.mark.parametrize("tag,paired", [("se", False), ("pe", True)])
+def test_load_filtered_reads_vs_reference(oracle, golden, gather_golden, tag, paired):
+    """loadFilteredReads restatement (d_mapper.h:393-443) and the Dna5Q reverse complement against the per-bin read
+    sets the reference's own loadFilteredReads produced (qualities set, SE and PE)."""
+    if "ka5_se_threshold" not in golden.files:
+        pytest.skip("fixture made without libref_mapper.so")
+    g = gather_golden
+    fwd = g[tag + "_fwd_bytes"]
+    fcat, foff = oracle.full_layout_dna5q(fwd, golden["reads_offsets"])
+    bo, ids = golden["ka5_%s_bin_offsets" % tag], golden["ka5_%s_read_ids" % tag]
+    lim, ss = g[tag + "_limits"], g[tag + "_seq_start"]
+    for q, b in enumerate(g["bins"]):
+        mine = ids[int(bo[b]):int(bo[b + 1])]
+        ob, ol, oi = oracle.load_filtered_reads(fcat, foff, paired, mine)
+        a, e = int(ss[q]), int(ss[q + 1])
+        assert e - a == mine.size * (4 if paired else 2)
+        assert np.array_equal(oi, g[tag + "_ids"][a:e]), (tag, b)
+        assert np.array_equal(ol, lim[a:e + 1] - lim[a]), (tag, b)
+        assert np.array_equal(ob, g[tag + "_bytes"][int(lim[a]):int(lim[e])]), (tag, b)
+    # sortedBins: sizes non-increasing along the reference's order
+    sizes = np.diff(bo.astype(np.int64))
+    sb = g[tag + "_sorted_bins"]
+    assert sorted(sb.tolist()) == list(range(64)) and np.all(np.diff(sizes[sb]) <= 0)

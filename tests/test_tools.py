@@ -1,0 +1,86 @@
+"""The standalone builder / updater (tools/dyibf_build_filter.cpp, tools/dyibf_update_filter.cpp): the reference's
+dream_yara_build_filter / dream_yara_update_filter command lines on top of the C ABI."""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import ka
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+TOOLS = os.path.join(os.path.dirname(HERE), "tools")
+BUILD = os.path.join(TOOLS, "bin", "dyibf_build_filter")
+UPDATE = os.path.join(TOOLS, "bin", "dyibf_update_filter")
+
+
+@pytest.fixture(scope="module")
+def tools(dy):
+    r = subprocess.run(["make", "-C", TOOLS], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return BUILD, UPDATE
+
+
+def _write_fasta(path, records, width=80, gz=False):
+    op = gzip.open if gz else open
+    with op(path, "wb") as fh:
+        for name, seq in records:
+            fh.write(b">" + name.encode() + b" some description\n")
+            for j in range(0, len(seq), width):
+                fh.write(seq[j:j + width] + b"\n")
+
+
+def test_cli_argument_checks(tools, tmp_path):
+    build, update = tools
+    r = subprocess.run([build, "-bs", "3", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 1 and "should be a power of 2" in r.stderr          # d_build_filter.cpp:198-210
+    r = subprocess.run([build, "-k", "40", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 1
+    r = subprocess.run([build, "-ft", "kmer_direct", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 1 and "bloom" in r.stderr
+    r = subprocess.run([update, str(tmp_path / "x.filter"), str(tmp_path / "abc.fna")], capture_output=True, text=True)
+    assert r.returncode == 1 and "doesn't have a valid name" in r.stderr        # d_update_filter.cpp:158-162
+
+
+@pytest.mark.gpu
+def test_build_and_update_cli(tools, golden, oracle, tmp_path):
+    build, update = tools
+    genomes = ka.records(golden, "genomes")
+    d = tmp_path / "bins"; d.mkdir()
+    for b, g in enumerate(genomes):
+        _write_fasta(d / ("%d.fna" % b), [("bin%d" % b, g)])
+    filt = tmp_path / "cli.filter"
+    # the reference's own test command line (tests/run_tests.py:116-122), incl. its "-nh ' 2'"
+    r = subprocess.run([build, "-b", "64", "-t", "4", "-k", "19", "-nh", " 2", "-bs", "1", "-v", str(d), "-o", str(filt)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Finshed in" in r.stderr and "[bin 63] Done adding kmers!" in r.stderr
+    assert filt.stat().st_size == 1073741864
+    assert ka.md5_file(filt) == str(golden["reference_gold_md5"])
+
+    # update bins 5 and 40: multi-record gzip FASTA with a short record and lower-case / IUPAC characters
+    rng = np.random.default_rng(3)
+    new5 = [bytes(rng.choice(list(b"ACGTacgtNRY"), 3000).astype(np.uint8)), b"ACGT", bytes(rng.choice(list(b"ACGT"), 500).astype(np.uint8))]
+    new40 = [genomes[7][::-1]]
+    u = tmp_path / "upd"; u.mkdir()
+    _write_fasta(u / "5.fa.gz", [("a", new5[0]), ("short", new5[1]), ("c", new5[2])], width=60, gz=True)
+    with open(u / "40.fastq", "wb") as fh:                   # FASTQ whose quality line starts with '@' and contains '+'
+        fh.write(b"@x desc\n" + new40[0] + b"\n+\n@" + b"+" * (len(new40[0]) - 1) + b"\n")
+    r = subprocess.run([update, "-t", "2", "-v", str(filt), str(u / "5.fa.gz"), str(u / "40.fastq")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    p = oracle.params(64, 2, 19, ka.GIB_BITS)
+    words = oracle.new_words(p)
+    for b, g in enumerate(genomes):
+        oracle.add_kmers(words, p, oracle.encode_ascii(g), b)
+    oracle.clear_bins(words, p, [5, 40])
+    for rec in new5:
+        if len(rec) >= 19:
+            oracle.add_kmers(words, p, oracle.encode_ascii(rec), 5)
+    oracle.add_kmers(words, p, oracle.encode_ascii(new40[0]), 40)
+    oracle.save(words, p, tmp_path / "want.filter")
+    assert ka.md5_file(filt) == ka.md5_file(tmp_path / "want.filter")
+    # a bin beyond the filter's range is refused like the reference does
+    _write_fasta(u / "64.fna", [("x", genomes[0])])
+    r = subprocess.run([update, str(filt), str(u / "64.fna")], capture_output=True, text=True)
+    assert r.returncode == 1 and "has only 64 Bins" in r.stderr
