@@ -41,22 +41,36 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--bins", type=int, default=1024)
-    ap.add_argument("--filter-gib", type=int, default=16)
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4"],
+                    help="BASELINE.json configs[1] (default, the headline), configs[2] (paired-end, e sweep) or configs[3] "
+                         "(bin-sharded, 1024 bins and a 64 GiB shard per GPU)")
+    ap.add_argument("--bins", type=int, default=None, help="bins (cfg4: per GPU); default 1024")
+    ap.add_argument("--filter-gib", type=int, default=None, help="filter size in GiB (cfg4: per GPU shard); default 16 / 64")
     ap.add_argument("--genome-len", type=int, default=4_000_000)
-    ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU per step")
-    ap.add_argument("--read-len", type=int, default=150)
+    ap.add_argument("--reads", type=int, default=10_000_000,
+                    help="reads (cfg3: pairs) per GPU per step; cfg4: reads per step, seen by every GPU")
+    ap.add_argument("--read-len", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-early-exit", action="store_true", help="skip the extra DYIBF_OPT_EARLY_EXIT measurement")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.paired = a.workload == "cfg3"
+    a.bin_sharded = a.workload == "cfg4"
+    a.bins = a.bins or 1024
+    a.filter_gib = a.filter_gib or (64 if a.bin_sharded else 16)
+    a.read_len = a.read_len or (100 if a.bin_sharded else 150)
+    a.unit = "pairs/s" if a.paired else "reads/s"
+    a.metric = {"cfg2": "IBF bin-filter reads/s (150bp,e=3)", "cfg3": "IBF bin-filter pairs/s (2x150bp,e=3)",
+                "cfg4": "IBF bin-filter reads/s (100bp,e=3), bin-sharded"}[a.workload]
+    return a
 
 
-def algorithmic_bytes_per_read(bins, read_len):
-    """per k-mer lookup h * 32*ceil(W*8/32) sector bytes; 2 strands per single-end read."""
+def algorithmic_bytes_per_read(bins, read_len, paired=False):
+    """per k-mer lookup h * 32*ceil(W*8/32) sector bytes; 2 strands per read, 4 sequences per pair.
+    `bins` = the bins resident on ONE GPU (cfg4: the shard's)."""
     W = (bins + 63) // 64
     per_lookup = H * SECTOR * ((W * 8 + SECTOR - 1) // SECTOR)
-    return (read_len - K + 1) * 2 * per_lookup
+    return (read_len - K + 1) * (4 if paired else 2) * per_lookup
 
 
 def measured_peak():
@@ -115,7 +129,9 @@ class ClockSampler:
 
 
 def full_layout_codes(fwd):
-    """appendReverseComplement on a [n, L] Dna5 code array -> concat [fwd | rc], offsets."""
+    """appendReverseComplement on a [n, L] (single-end) or [2, n, L] (paired-end: [m1 | m2]) Dna5 code array ->
+    concat [fwd | rc], offsets."""
+    fwd = fwd.reshape(-1, fwd.shape[-1])
     rc = fwd[:, ::-1]
     rc = np.where(rc >= 4, 4, 3 - rc).astype(np.uint8)
     n, L = fwd.shape
@@ -155,35 +171,43 @@ class CpuFilter:
         with ThreadPoolExecutor(max_workers=self.cores) as ex:                # ctypes releases the GIL
             list(ex.map(fn, range(genomes.shape[0])))
 
-    def classify(self, layout, threshold):
+    def classify(self, layout, threshold, paired=False):
         """the filtering loop of clasifyLoadedReads over a prepared [fwd | rc] read set (full_layout_codes)"""
         cat, off = layout
         if self.kind == "reference":
-            return self.ref.classify(self.f, cat, off, False, threshold, self.cores, self.W)
+            return self.ref.classify(self.f, cat, off, paired, threshold, self.cores, self.W)
         os.environ.setdefault("OMP_NUM_THREADS", str(self.cores))
-        return self.o.classify(self.words, self.p, cat, off, False, threshold)
+        return self.o.classify(self.words, self.p, cat, off, paired, threshold)
 
-    def timed_sample(self, reads_fn, threshold, target_s):
+    def timed_sample(self, reads_fn, threshold, target_s, paired=False):
         """Time the filtering loop on a prefix of the workload sized for ~target_s seconds."""
         n = 20_000
         fwd = reads_fn(n); lay = full_layout_codes(fwd)
-        t = time.perf_counter(); rows = self.classify(lay, threshold); dt = time.perf_counter() - t
+        t = time.perf_counter(); rows = self.classify(lay, threshold, paired); dt = time.perf_counter() - t
         rate = n / dt
         n2 = int(min(max(rate * target_s, n), 2_000_000))
         if n2 > 2 * n:
             fwd = reads_fn(n2); lay = full_layout_codes(fwd)
-            t = time.perf_counter(); rows = self.classify(lay, threshold); dt = time.perf_counter() - t
+            t = time.perf_counter(); rows = self.classify(lay, threshold, paired); dt = time.perf_counter() - t
             n = n2
         return n / dt, n, dt, rows, fwd
 
 
+def synth_fwd(synth, genomes, args, first, n, out=None):
+    """forward read set of the workload: [n, L] reads (cfg2/cfg4) or [2, n, L] = [m1 | m2] pairs (cfg3)"""
+    if args.paired:
+        return synth.pairs(genomes, 3, first, n, args.read_len, out=out)
+    return synth.reads(genomes, 4 if args.bin_sharded else 2, first, n, args.read_len, out=out)
+
+
 def run_reference(args):
+    """The reference's own CPU path (oracle/_ref) on the host cores, same config/metric as the B200 arm; cfg4: one
+    GPU's 1024-bin shard (the whole 8192-bin table does not fit host RAM; the per-shard work is what a GPU does)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from bench_support import synth
     nbits = args.filter_gib * (1 << 33) + 256
-    thr = None
     cf = CpuFilter(args.bins, H, K, nbits)
     from oracle_py import Oracle
     thr = Oracle().threshold(E, K, args.read_len)
@@ -192,38 +216,54 @@ def run_reference(args):
     cf.build(genomes)
     build_s = time.perf_counter() - t0
     # size a step for ~4 s of CPU work from a probe, then W warm-up + K timed steps on successive samples
-    rate, n_probe, _, _, _ = cf.timed_sample(lambda n: synth.reads(genomes, 2, 0, n, args.read_len), thr, 4.0)
+    rate, n_probe, _, _, _ = cf.timed_sample(lambda n: synth_fwd(synth, genomes, args, 0, n), thr, 4.0, args.paired)
     n_step = int(min(max(rate * 4.0, 20_000), 2_000_000))
     times = []
     for s in range(args.warmup + args.steps):
-        lay = full_layout_codes(synth.reads(genomes, 2, (s % 4) * n_step, n_step, args.read_len))
-        t = time.perf_counter(); cf.classify(lay, thr); dt = time.perf_counter() - t
+        lay = full_layout_codes(synth_fwd(synth, genomes, args, (s % 4) * n_step, n_step))
+        t = time.perf_counter(); cf.classify(lay, thr, args.paired); dt = time.perf_counter() - t
         if s >= args.warmup:
             times.append(dt)
     total = sum(times)
     value = n_step * args.steps / total
+    what = "pair" if args.paired else "read"
     line = {
-        "impl": "reference", "metric": "IBF bin-filter reads/s (150bp,e=3)", "value": value, "unit": "reads/s",
+        "impl": "reference", "metric": args.metric, "value": value, "unit": args.unit,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": workload_config(args, thr),
-        "cpu_baseline": {"value": value, "unit": "reads/s", "cores": cf.cores, "kind": cf.kind,
-                         "sample": "%d-read prefix samples of the 10M-read workload per step; filter built on the host "
-                                   "by the same code in %.1f s" % (n_step, build_s)},
-        "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": workload_config(args, thr, args.gpus),
+        "cpu_baseline": {"value": value, "unit": args.unit, "cores": cf.cores, "kind": cf.kind,
+                         "sample": "%d-%s prefix samples of the workload per step; filter built on the host "
+                                   "by the same code in %.1f s" % (n_step, what, build_s)},
+        "e2e": {"value": value, "unit": args.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, thr):
-    return {"workload": "cfg2: synthetic %d-bin %d GiB IBF (k=%d, h=%d), %d single-end %d bp reads per GPU, e=%d "
-                        "(threshold %d), read-sharded" % (args.bins, args.filter_gib, K, H, args.reads, args.read_len, E, thr),
-            "bins": args.bins, "filter_gib": args.filter_gib, "kmer": K, "hashes": H, "reads_per_gpu": args.reads,
-            "read_len": args.read_len, "threshold": thr, "genome_bp_per_bin": args.genome_len,
-            "l2": "no flush needed: every step gathers ~%d GB at random from a %d GiB table (>> 126 MB L2)"
-                  % (round(args.reads * algorithmic_bytes_per_read(args.bins, args.read_len) / 1e9), args.filter_gib),
-            "parallelism": "read-sharded x%d (filter replicated, NCCL broadcast)" % args.gpus}
+def workload_config(args, thr, world):
+    per_unit = algorithmic_bytes_per_read(args.bins, args.read_len, args.paired)
+    gather_gb = round(args.reads * per_unit / 1e9)
+    if args.workload == "cfg2":
+        desc = ("cfg2: synthetic %d-bin %d GiB IBF (k=%d, h=%d), %d single-end %d bp reads per GPU, e=%d (threshold %d), "
+                "read-sharded" % (args.bins, args.filter_gib, K, H, args.reads, args.read_len, E, thr))
+        par = "read-sharded x%d (filter replicated, NCCL broadcast)" % world
+    elif args.workload == "cfg3":
+        desc = ("cfg3: synthetic %d-bin %d GiB IBF (k=%d, h=%d), %d paired-end 2x%d bp pairs per GPU per step, e=%d "
+                "(threshold %d) + e=0..5 sweep, read-sharded" % (args.bins, args.filter_gib, K, H, args.reads, args.read_len, E, thr))
+        par = "read-sharded x%d (filter replicated, NCCL broadcast)" % world
+    else:
+        desc = ("cfg4: synthetic %d-bin %d GiB IBF (k=%d, h=%d) bin-sharded over %d GPU(s) (%d bins, %d GiB per GPU), "
+                "%d single-end %d bp reads per step seen by every GPU, e=%d (threshold %d)"
+                % (args.bins * world, args.filter_gib * world, K, H, world, args.bins, args.filter_gib, args.reads, args.read_len, E, thr))
+        par = "bin-sharded x%d (each GPU owns a contiguous bin range of every hash block; reads all-gathered over NCCL; no reduction)" % world
+    return {"workload": desc, "bins": args.bins * (world if args.bin_sharded else 1),
+            "filter_gib": args.filter_gib * (world if args.bin_sharded else 1), "kmer": K, "hashes": H,
+            "reads_per_gpu": args.reads, "read_len": args.read_len, "paired": args.paired, "threshold": thr,
+            "genome_bp_per_bin": args.genome_len,
+            "l2": "no flush needed: every step gathers ~%d GB at random from a %d GiB table per GPU (>> 126 MB L2)"
+                  % (gather_gb, args.filter_gib),
+            "parallelism": par}
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -252,37 +292,52 @@ def run_b200(args):
     P = (nbits - 256) // (64 * W)
     thr = int(L.dyibf_threshold(E, K, RL))
 
-    # ---- setup (untimed): genomes, filter (rank 0 builds, NCCL broadcast replicates), this rank's reads
-    genomes = synth.genomes(bins, args.genome_len)
+    # ---- setup (untimed): genomes, filter, this rank's reads
+    paired, sharded = args.paired, args.bin_sharded
+    group = 4 if paired else 2
+    n_seq = n * (2 if paired else 1)                                     # forward sequences per step ([m1 | m2] for pairs)
+    units_world = 1 if sharded else world                                # cfg4: every GPU sees every read
+    genomes = synth.genomes(bins, args.genome_len, first_bin=rank * bins if sharded else 0)
     words = torch.zeros(P * W, dtype=torch.int64, device=dev)
     f = dy.SeqAnBloomFilter.attach(bins, H, K, nbits, words.data_ptr(), device=local, keep=words)
     t_build = time.perf_counter()
-    if rank == 0:
+    if rank == 0 or sharded:                                             # cfg4: every rank builds its own bin shard
         goff = np.arange(bins + 1, dtype=np.uint64) * args.genome_len
         f.addSequences((genomes.reshape(-1), goff), np.arange(bins, dtype=np.uint32))
     torch.cuda.synchronize()
     t_build = time.perf_counter() - t_build
-    if world > 1:
+    if world > 1 and not sharded:                                        # read-sharded: replicate over NVLink
         step = 1 << 27                                                   # 1 GiB pieces
         for a in range(0, words.numel(), step):
             dist.broadcast(words[a:a + step], src=0)
         torch.cuda.synchronize()
 
-    hp = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(hp), n * RL))
-    h_reads = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(n, RL))
-    synth.reads(genomes, 2, rank * n, n, RL, out=h_reads)
-    op = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(op), (n + 1) * 8))
-    h_off = np.ctypeslib.as_array(C.cast(op, C.POINTER(C.c_uint64)), shape=(n + 1,))
-    h_off[:] = np.arange(n + 1, dtype=np.uint64) * RL
+    hp = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(hp), n_seq * RL))
+    h_reads = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(2, n, RL) if paired else (n, RL))
+    if sharded and world > 1:
+        # every rank draws n/world reads from its own bins; one NCCL all-gather gives every GPU the whole batch
+        per = n // world
+        assert per * world == n, "--reads must be divisible by the number of GPUs for cfg4"
+        mine = torch.from_numpy(synth_fwd(synth, genomes, args, rank * per, per)).to(dev)
+        allr = torch.empty((n, RL), dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allr, mine)
+        h_reads[:] = allr.cpu().numpy()
+        del mine, allr
+    else:
+        synth_fwd(synth, genomes, args, rank * n, n, out=h_reads)
+    op = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(op), (n_seq + 1) * 8))
+    h_off = np.ctypeslib.as_array(C.cast(op, C.POINTER(C.c_uint64)), shape=(n_seq + 1,))
+    h_off[:] = np.arange(n_seq + 1, dtype=np.uint64) * RL
     rp = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(rp), n * W * 8))
     h_rows = np.ctypeslib.as_array(C.cast(rp, C.POINTER(C.c_uint64)), shape=(n, W))
     d_reads = torch.from_numpy(h_reads.reshape(-1)).to(dev)
     d_off = torch.from_numpy(h_off.view(np.int64)).to(dev)
     d_rows = torch.zeros(n * W, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
+    cur_thr = [thr]
 
     def device_step():
-        f.query_device(d_reads.data_ptr(), d_off.data_ptr(), n, thr, d_rows.data_ptr(), group=2, derive_rc=True,
+        f.query_device(d_reads.data_ptr(), d_off.data_ptr(), n_seq, cur_thr[0], d_rows.data_ptr(), group=group, derive_rc=True,
                        encoding=ENC_DNA5, max_seq_len=RL, stream=stream)
 
     def barrier():
@@ -312,13 +367,13 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, query_ms, pack_ms = (float(x) for x in t.tolist())
-    value = world * n * args.steps / (ms_total / 1e3)
+    value = units_world * n * args.steps / (ms_total / 1e3)
 
     # ---- e2e: the public host-buffer call; pinned reads in, bitmask rows out, copies inside the timed region
     e2e = None
     if not args.no_e2e:
         def host_step():
-            check(L.dyibf_query_batch(f._h, hp, op, n, ENC_DNA5, 2, 1, thr, RL, rp, None, MEM_HOST, None))
+            check(L.dyibf_query_batch(f._h, hp, op, n_seq, ENC_DNA5, group, 1, thr, RL, rp, None, MEM_HOST, None))
         for _ in range(max(1, min(args.warmup, 2))):
             host_step()
         barrier()
@@ -329,8 +384,8 @@ def run_b200(args):
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n * args.steps / float(dt.item()), "unit": "reads/s",
-               "h2d_bytes_per_step": world * (n * RL + (n + 1) * 8), "d2h_bytes_per_step": world * n * W * 8,
+        e2e = {"value": units_world * n * args.steps / float(dt.item()), "unit": args.unit,
+               "h2d_bytes_per_step": world * (n_seq * RL + (n_seq + 1) * 8), "d2h_bytes_per_step": world * n * W * 8,
                "timing": "host wall clock around K synchronous dyibf_query_batch(host) calls, max over ranks"}
         # device-resident and host paths must agree bit for bit
         assert np.array_equal(h_rows.reshape(-1).view(np.int64), d_rows.cpu().numpy()), "host-mode rows != device-mode rows"
@@ -355,7 +410,7 @@ def run_b200(args):
         t2 = torch.tensor([e0.elapsed_time(e1), p2["query_ms"] / max(p2["query_launches"], 1)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-        early = {"value": world * n * args.steps / (float(t2[0]) / 1e3), "unit": "reads/s", "kernel_ms": float(t2[1]),
+        early = {"value": units_world * n * args.steps / (float(t2[0]) / 1e3), "unit": args.unit, "kernel_ms": float(t2[1]),
                  "lookups_frac": (p2["query_lookups"] / max(p2["query_launches"], 1)) / max(full_lookups, 1),
                  "rows_equal_full": same,
                  "note": "DYIBF_OPT_EARLY_EXIT=1: a sequence stops once no remaining k-mer can change its bin set; "
@@ -372,13 +427,13 @@ def run_b200(args):
             dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
             if world > 1:
                 dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-            early["e2e"] = world * n * args.steps / float(dt.item())
+            early["e2e"] = units_world * n * args.steps / float(dt.item())
             assert np.array_equal(h_rows.reshape(-1).view(np.int64), full_rows.cpu().numpy()), "early-exit host rows differ"
         f.set_early_exit(False)
         del full_rows
 
     # ---- roofline of the dominant kernel (query) against the measured HBM peak
-    bytes_per_read = algorithmic_bytes_per_read(bins, RL)
+    bytes_per_read = algorithmic_bytes_per_read(bins, RL, paired)
     peak, peak_src = measured_peak()
     achieved = n * bytes_per_read / (query_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -386,7 +441,7 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": n * bytes_per_read, "peak_source": peak_src,
                 "frac_of_nominal_8000": achieved / 8000.0}
     traffic_file = os.path.join(ROOT, "profiles", "query_kernel_traffic.json")
-    if os.path.exists(traffic_file):
+    if os.path.exists(traffic_file) and args.workload == "cfg2" and bins == 1024 and RL == 150:
         try:
             tj = json.load(open(traffic_file))
             if tj.get("reads_per_launch"):
@@ -401,20 +456,57 @@ def run_b200(args):
         cf = CpuFilter(bins, H, K, nbits)
         nd = P * W
         check(L.dyibf_download_words(f._h, C.c_void_p(cf.words.ctypes.data), 0, nd))   # same filter words as the GPU
-        rate, n_s, dt_s, rows_cpu, _ = cf.timed_sample(lambda m: h_reads[:m], thr, 15.0)
-        same = bool(np.array_equal(rows_cpu, h_rows[:n_s] if e2e else d_rows.cpu().numpy().view(np.uint64).reshape(n, W)[:n_s]))
-        cpu = {"value": rate, "unit": "reads/s", "cores": cf.cores, "kind": cf.kind,
-               "sample": "first %d reads of the 10M-read workload, %.1f s, same filter words (downloaded from HBM)" % (n_s, dt_s),
+        prefix = (lambda m: h_reads[:, :m]) if paired else (lambda m: h_reads[:m])
+        if paired:
+            # the GPU rows of a prefix of pairs need that prefix queried on its own ([m1 | m2] halves move with n)
+            def gpu_rows(m):
+                sub = np.ascontiguousarray(h_reads[:, :m]).reshape(-1)
+                off = np.arange(2 * m + 1, dtype=np.uint64) * RL
+                return f.whichBinsBatch((sub, off), thr, group=4, derive_rc=True, encoding=ENC_DNA5, max_seq_len=RL)
+        rate, n_s, dt_s, rows_cpu, _ = cf.timed_sample(prefix, thr, 15.0, paired)
+        if paired:
+            rows_gpu = gpu_rows(n_s)
+        else:
+            rows_gpu = h_rows[:n_s] if e2e else d_rows.cpu().numpy().view(np.uint64).reshape(n, W)[:n_s]
+        same = bool(np.array_equal(rows_cpu, rows_gpu))
+        cpu = {"value": rate, "unit": args.unit, "cores": cf.cores, "kind": cf.kind,
+               "sample": "first %d %s of the workload, %.1f s, same filter words (downloaded from HBM)"
+                         % (n_s, "pairs" if paired else "reads", dt_s),
                "rows_equal_gpu": same}
         if not same:
             raise AssertionError("GPU rows differ from the CPU reference on the sampled prefix")
 
+    # ---- cfg3: the e = 0..5 sweep BASELINE.json names (thresholds 133,115,79,61,25,7), full pass and early exit
+    sweep = None
+    if args.workload == "cfg3":
+        sweep = {}
+        for e in range(6):
+            cur_thr[0] = int(L.dyibf_threshold(e, K, RL))
+            res = {"threshold": cur_thr[0]}
+            for mode in ("full", "early_exit"):
+                f.set_early_exit(mode == "early_exit")
+                device_step()
+                barrier()
+                e0.record()
+                for _ in range(2):
+                    device_step()
+                e1.record()
+                barrier()
+                tt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                res[mode] = units_world * n * 2 / (float(tt.item()) / 1e3)
+            sweep["e%d" % e] = res
+        f.set_early_exit(False); cur_thr[0] = thr
+
     if rank == 0:
-        line = {"metric": "IBF bin-filter reads/s (150bp,e=3)", "value": value, "unit": "reads/s", "n_gpus": world,
+        line = {"metric": args.metric, "value": value, "unit": args.unit, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-                "config": workload_config(args, thr), "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
+                "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
                 "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "impl": "b200"}
+        if sweep is not None:
+            line["e_sweep"] = sweep
         print(json.dumps(line), flush=True)
     f.close()
     for p_ in (hp, op, rp):

@@ -108,3 +108,56 @@ void synth_reads(const uint8_t *genomes, uint32_t bins, uint64_t glen, uint32_t 
         if (origin) origin[q] = src_bin;
     }
 }
+
+/* paired-end reads (cfg3): pairs [first, first+n), mates of L bases each.  90 %: a fragment of length
+ * L + 50 .. 2L + 250 at a uniform (bin, position); mate 1 = its first L bases, mate 2 = the reverse complement of
+ * its last L bases (FR orientation), the whole fragment flipped for half of the pairs; 1 %/base substitutions in
+ * both mates.  10 %: two uniform random mates.  0.5 % of the mates get 1..3 N.  m1[(p-first)*L + i], m2 likewise. */
+void synth_pairs(const uint8_t *genomes, uint32_t bins, uint64_t glen, uint32_t cfg, uint64_t first, uint64_t n,
+                 uint32_t L, uint8_t *m1, uint8_t *m2)
+{
+    const uint64_t seed = splitmix64(0xBEEF0000ULL + cfg);
+    #pragma omp parallel for schedule(static)
+    for (uint64_t q = 0; q < n; ++q) {
+        const uint64_t r = first + q;
+        const uint64_t s = splitmix64(seed ^ (r * 0xD6E8FEB86659FD93ULL));
+        uint8_t *o[2] = { m1 + q * L, m2 + q * L };
+        if (L > 1024 || glen < 3ull * L + 300) { memset(o[0], 0, L); memset(o[1], 0, L); continue; }
+        if (s % 10 != 0) {
+            const uint64_t a = splitmix64(s + 1), b = splitmix64(s + 2);
+            const uint32_t bin = (uint32_t)(a % bins);
+            const uint32_t frag = L + 50 + (uint32_t)((a >> 32) % (L + 201));
+            const uint64_t pos = b % (glen - frag - 1);
+            const uint8_t *g = genomes + (uint64_t)bin * glen + pos;
+            const int flip = (int)((a >> 61) & 1);
+            /* left end forward, right end reverse-complemented; flip swaps which mate is which */
+            uint8_t *left = o[flip], *right = o[1 - flip];
+            memcpy(left, g, L);
+            for (uint32_t i = 0; i < L; ++i) { uint8_t c = g[frag - 1 - i]; right[i] = c >= 4 ? 4 : (uint8_t)(3 - c); }
+            uint64_t t = splitmix64(s + 3);
+            for (int m = 0; m < 2; ++m)
+                for (uint32_t i = 0; i < L; ++i) {
+                    t = t * 6364136223846793005ULL + 1442695040888963407ULL;
+                    if ((t >> 33) % 100 == 0) o[m][i] = (uint8_t)((t >> 20) & 3);
+                }
+        } else {
+            uint64_t t = splitmix64(s + 4);
+            for (int m = 0; m < 2; ++m)
+                for (uint32_t i = 0; i < L; ++i) {
+                    if ((i & 31) == 0) t = splitmix64(t + i + 1000 * m);
+                    o[m][i] = (uint8_t)((t >> (2 * (i & 31))) & 3);
+                }
+        }
+        for (int m = 0; m < 2; ++m) {
+            uint64_t nn = splitmix64(s + 5 + m);
+            if (nn % 200 == 0) {
+                uint32_t cnt = 1 + (uint32_t)((nn >> 8) % 3);
+                for (uint32_t j = 0; j < cnt; ++j) {
+                    uint64_t w = splitmix64(nn + j);
+                    uint32_t pos = (w % 4 == 0) ? 0 : (w % 4 == 1) ? L - 1 : (uint32_t)((w >> 8) % L);
+                    o[m][pos] = 4;
+                }
+            }
+        }
+    }
+}

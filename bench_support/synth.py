@@ -21,6 +21,8 @@ def _lib():
         _l.synth_genome.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
         _l.synth_reads.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32,
                                    C.c_void_p, C.c_void_p]
+        _l.synth_pairs.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32,
+                                   C.c_void_p, C.c_void_p]
     return _l
 
 
@@ -43,3 +45,12 @@ def reads(genomes_arr, cfg, first, n, L, out=None, origin=False):
     _lib().synth_reads(genomes_arr.ctypes.data, bins, glen, cfg, first, n, L, out.ctypes.data,
                        org.ctypes.data if origin else None)
     return (out, org) if origin else out
+
+
+def pairs(genomes_arr, cfg, first, n, L, out=None):
+    """uint8 [2, n, L]: mates 1 and mates 2 of pairs first .. first+n-1 (the [m1 | m2] forward read set of the mapper)."""
+    bins, glen = genomes_arr.shape
+    if out is None:
+        out = np.empty((2, n, L), dtype=np.uint8)
+    _lib().synth_pairs(genomes_arr.ctypes.data, bins, glen, cfg, first, n, L, out[0].ctypes.data, out[1].ctypes.data)
+    return out
