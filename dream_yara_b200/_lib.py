@@ -11,6 +11,7 @@ ENC_DNA5, ENC_DNA5Q, ENC_ASCII = 0, 1, 2
 MEM_HOST, MEM_DEVICE = 0, 1
 MAX_HASH = 8
 OPT_EARLY_EXIT = 1
+OPT_BUILD_BUCKET_MIB = 2
 
 
 class Params(C.Structure):

@@ -76,6 +76,8 @@ struct dyibf_filter {
     struct { bool valid = false; uint32_t n_fwd = 0, group = 0, encoding = 0; uint64_t first_off = 0; } batch;
     std::vector<uint64_t> h_csr_off;
     uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
+    int64_t      bucket_mib = -1;         // DYIBF_OPT_BUILD_BUCKET_MIB: -1 auto, 0 direct atomics only
+    DevBuf       bucket_records, bucket_cursors;
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
     bool         profiling = false;
@@ -268,6 +270,7 @@ void dyibf_destroy(dyibf_filter* f)
     f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release(); f->stats.release();
     f->batch_bytes.release(); f->batch_offsets.release(); f->csr_off.release(); f->csr_ids.release();
     f->gather_ws.release(); f->gather_out.release(); f->gather_ids.release();
+    f->bucket_records.release(); f->bucket_cursors.release();
     if (f->owns_words && f->d_words) cudaFree(f->d_words);
     delete f;
 }
@@ -805,6 +808,60 @@ int dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_
 // ============================================================================================================
 // build / clear / instrumentation
 // ============================================================================================================
+namespace {
+
+// One dyibf_add_sequences call's use of the bucketed build (build_kernel.cu): records accumulate in HBM across the
+// call's chunks and are applied region by region when the buffer is nearly full and at the end of the call.
+struct BucketRun {
+    bool active = false;
+    uint32_t R = 0, n_regions = 0;
+    uint64_t cap = 0, pending = 0, limit = 0;      // pending: upper bound of the records appended since the last apply
+};
+
+int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
+{
+    br->active = false;
+    if (f->bucket_mib == 0) return DYIBF_OK;
+    if (f->data_words * 8 <= (256ull << 20)) return DYIBF_OK;       // table (nearly) fits the L2: direct atomics are L2 hits
+    if (expected_records < (32ull << 20)) return DYIBF_OK;          // too few updates per region sector to pay for a sweep
+    uint64_t budget = f->bucket_mib > 0 ? (uint64_t)f->bucket_mib << 20 : 8ull << 30;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return DYIBF_OK;
+    free_b += f->bucket_records.cap;
+    if (f->bucket_mib < 0 && budget > free_b / 3) budget = free_b / 3;
+    const uint64_t want = expected_records * 4 + expected_records / 4 + (64ull << 20);   // the whole call in one pass
+    if (budget > want) budget = want;
+    if (!bucket_plan(f->data_words, budget, &br->R, &br->n_regions, &br->cap)) return DYIBF_OK;
+    if (f->bucket_records.reserve((uint64_t)br->n_regions * br->cap * 4) != cudaSuccess) {
+        cudaGetLastError();                                          // not enough memory: direct atomics
+        return DYIBF_OK;
+    }
+    CU(f->bucket_cursors.reserve((uint64_t)br->n_regions * 8));
+    CU(cudaMemset(f->bucket_cursors.p, 0, (uint64_t)br->n_regions * 8));
+    br->limit = (uint64_t)((double)br->n_regions * (double)br->cap / 1.06);
+    br->pending = 0;
+    br->active = true;
+    return DYIBF_OK;
+}
+
+int buckets_apply(dyibf_filter* f, BucketRun* br, cudaStream_t st)
+{
+    if (!br->active || br->pending == 0) return DYIBF_OK;
+    Scope sc(f, st, K_BUILD);
+    CU(launch_build_apply(f->d_words, (const uint32_t*)f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p,
+                          br->R, br->n_regions, br->cap, br->cap, st));
+    br->pending = 0;
+    return DYIBF_OK;
+}
+
+void buckets_end(dyibf_filter* f, BucketRun* br)
+{
+    br->active = false;
+    if (f->bucket_records.cap > (1ull << 30)) f->bucket_records.release();   // do not sit on gigabytes between calls
+}
+
+} // namespace
+
 extern "C" {
 
 int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
@@ -830,8 +887,29 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         CU(sl.meta.reserve((uint64_t)n_seqs * sizeof(SeqMeta)));
         { Scope sc(f, st, K_PACK);
           CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, st)); }
-        { Scope sc(f, st, K_BUILD);
-          CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st)); }
+        BucketRun br;
+        int brc = buckets_begin(f, (last - first) * f->hp.h, &br);
+        if (brc) return brc;
+        if (!br.active) {
+            Scope sc(f, st, K_BUILD);
+            CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st));
+            return DYIBF_OK;
+        }
+        // stream-ordered passes over word ranges whose updates fit the record buffer: scatter, apply, next range
+        uint64_t per_pass = br.limit / (32ull * f->hp.h);
+        per_pass -= per_pass % BUILD_SCATTER_ALIGN;
+        if (per_pass < BUILD_SCATTER_ALIGN) per_pass = BUILD_SCATTER_ALIGN;
+        for (uint64_t w0 = 0; w0 < words; w0 += per_pass) {
+            const uint64_t w1 = std::min<uint64_t>(words, w0 + per_pass);
+            { Scope sc(f, st, K_BUILD);
+              CU(launch_build_scatter(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs,
+                                      w0, w1, br.R, br.n_regions, br.cap, (uint32_t*)f->bucket_records.p,
+                                      (unsigned long long*)f->bucket_cursors.p, st)); }
+            br.pending = (w1 - w0) * 32ull * f->hp.h;
+            brc = buckets_apply(f, &br, st);
+            if (brc) return brc;
+        }
+        // the record buffer stays allocated: the kernels above may still be running (stream-ordered call)
         return DYIBF_OK;
     }
     if (mem != DYIBF_MEM_HOST) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
@@ -842,6 +920,9 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
     }
     // chunks of whole sequences, ~64 MB of bases each, alternating between the two stream slots
     const uint64_t target = 64ull << 20;
+    BucketRun br;
+    int brc = buckets_begin(f, (offsets[n_seqs] - offsets[0]) * f->hp.h, &br);
+    if (brc) return brc;
     uint32_t a = 0, c = 0;
     while (a < n_seqs) {
         uint32_t b = a + 1;
@@ -863,13 +944,35 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[a]; src.offsets[0] = (const uint64_t*)sl.in_offsets.p;
         { Scope sc(f, sl.st, K_PACK);
           CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, sl.st)); }
-        { Scope sc(f, sl.st, K_BUILD);
-          CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
-                          (const uint32_t*)sl.counts.p, cnt, words, sl.st)); }
+        if (br.active) {
+            const uint64_t ub = words * 32ull * f->hp.h;                       // upper bound of this chunk's records
+            if (br.pending && br.pending + ub > br.limit) {                    // buffer nearly full: apply, then go on
+                CU(cudaStreamSynchronize(f->slot[0].st));
+                CU(cudaStreamSynchronize(f->slot[1].st));
+                brc = buckets_apply(f, &br, sl.st);
+                if (brc) return brc;
+                CU(cudaStreamSynchronize(sl.st));
+            }
+            Scope sc(f, sl.st, K_BUILD);
+            CU(launch_build_scatter(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
+                                    (const uint32_t*)sl.counts.p, cnt, 0, words, br.R, br.n_regions, br.cap,
+                                    (uint32_t*)f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p, sl.st));
+            br.pending += ub;
+        } else {
+            Scope sc(f, sl.st, K_BUILD);
+            CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
+                            (const uint32_t*)sl.counts.p, cnt, words, sl.st));
+        }
         a = b; ++c;
     }
     CU(cudaStreamSynchronize(f->slot[0].st));
     CU(cudaStreamSynchronize(f->slot[1].st));
+    if (br.active) {
+        brc = buckets_apply(f, &br, f->slot[0].st);
+        if (brc) return brc;
+        CU(cudaStreamSynchronize(f->slot[0].st));
+        buckets_end(f, &br);
+    }
     return DYIBF_OK;
 }
 
@@ -908,6 +1011,10 @@ int dyibf_set_option(dyibf_filter* f, int option, int64_t value)
         case DYIBF_OPT_EARLY_EXIT:
             if (value) f->query_flags |= QUERY_EARLY_EXIT; else f->query_flags &= ~QUERY_EARLY_EXIT;
             return DYIBF_OK;
+        case DYIBF_OPT_BUILD_BUCKET_MIB:
+            if (value < -1) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_BUCKET_MIB must be -1 (auto), 0 (off) or a size in MiB");
+            f->bucket_mib = value;
+            return DYIBF_OK;
         default:
             return fail(DYIBF_ERR_ARG, "unknown option %d", option);
     }
@@ -918,6 +1025,7 @@ int dyibf_get_option(const dyibf_filter* f, int option, int64_t* value)
     if (!f || !value) return fail(DYIBF_ERR_ARG, "NULL argument");
     switch (option) {
         case DYIBF_OPT_EARLY_EXIT: *value = (f->query_flags & QUERY_EARLY_EXIT) ? 1 : 0; return DYIBF_OK;
+        case DYIBF_OPT_BUILD_BUCKET_MIB: *value = f->bucket_mib; return DYIBF_OK;
         default: return fail(DYIBF_ERR_ARG, "unknown option %d", option);
     }
 }

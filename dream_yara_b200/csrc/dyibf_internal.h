@@ -60,6 +60,15 @@ cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uin
 cudaError_t launch_build(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                          const uint32_t* bin_ids, uint32_t n_seqs, uint64_t total_words, cudaStream_t st);
 
+// bucketed build (see build_kernel.cu): scatter appends 32-bit update records to per-region buckets, apply ORs them in.
+bool        bucket_plan(uint64_t data_words, uint64_t budget_bytes, uint32_t* R, uint32_t* n_regions, uint64_t* cap);
+cudaError_t launch_build_scatter(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
+                                 const uint32_t* bin_ids, uint32_t n_seqs, uint64_t word_begin, uint64_t total_words, uint32_t R,
+                                 uint32_t n_regions, uint64_t cap, uint32_t* records, unsigned long long* cursors, cudaStream_t st);
+static const uint64_t BUILD_SCATTER_ALIGN = 1024;   // word_begin of a scatter launch must be a multiple of this
+cudaError_t launch_build_apply(uint64_t* filter, const uint32_t* records, unsigned long long* cursors, uint32_t R,
+                               uint32_t n_regions, uint64_t cap, uint64_t max_fill, cudaStream_t st);
+
 // clear: for every hash block, words cols[i] &= ~masks[i]
 cudaError_t launch_clear(const HashParams& hp, uint64_t* filter, const uint32_t* cols, const uint64_t* masks, uint32_t n_cols,
                          cudaStream_t st);

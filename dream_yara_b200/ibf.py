@@ -281,6 +281,10 @@ class SeqAnBloomFilter:
         """DYIBF_OPT_EARLY_EXIT: stop a sequence once its bin set is decided (rows identical, fewer lookups)."""
         check(lib().dyibf_set_option(self._h, _lib.OPT_EARLY_EXIT, int(bool(on))))
 
+    def set_build_bucket_mib(self, mib):
+        """DYIBF_OPT_BUILD_BUCKET_MIB: scratch size of the bucketed build (-1 auto, 0 = direct atomics only)."""
+        check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_BUCKET_MIB, int(mib)))
+
     def profile_enable(self, on=True):
         check(lib().dyibf_profile_enable(self._h, int(on)))
 

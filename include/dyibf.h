@@ -171,6 +171,12 @@ int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64
  * k-mers left (count + remaining < threshold).  The rows are bit-identical to the full pass; only memory traffic
  * drops (e.g. 150 bp, k=18, e=3: ~57 % of the lookups). */
 #define DYIBF_OPT_EARLY_EXIT 1
+/* DYIBF_OPT_BUILD_BUCKET_MIB (default -1 = auto: up to 8 GiB, at most a third of the free HBM; 0 = off).  _insertKmer's
+ * single-bit ORs land at uniformly random words of the table.  For tables larger than the L2 and calls with at least 32 M
+ * updates, dyibf_add_sequences first appends the updates as 32-bit records to per-region buckets in a scratch buffer of
+ * this size and then ORs them in region by region, so that DRAM sees streaming instead of random sector traffic.  The
+ * filter is bit-identical either way (OR is commutative and idempotent). */
+#define DYIBF_OPT_BUILD_BUCKET_MIB 2
 int  dyibf_set_option(dyibf_filter* f, int option, int64_t value);
 int  dyibf_get_option(const dyibf_filter* f, int option, int64_t* value);
 

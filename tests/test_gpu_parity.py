@@ -335,3 +335,50 @@ def test_gather_reads_random_vs_oracle(dy, oracle, paired):
     sizes = np.diff(offs.astype(np.int64))
     assert sorted(sb.tolist()) == list(range(bins)) and np.all(np.diff(sizes[sb]) <= 0)
     f.close()
+
+
+def test_bucketed_build_equals_direct_and_oracle(dy, oracle):
+    """The bucketed build (DYIBF_OPT_BUILD_BUCKET_MIB; tables larger than the L2, >= 32 M updates per call) against the
+    oracle and the direct atomic kernel: auto budget, a budget so small that most updates overflow into the direct
+    fallback, and the device-pointer entry with several scatter/apply passes."""
+    import torch
+    from bench_support import synth
+    bins, h, k, nbits = 1000, 3, 18, (1 << 32) + 256            # 512 MiB table: 32 regions of 16 MiB
+    glen = 13_000
+    genomes = synth.genomes(bins, glen)                           # 13 M bases -> 39 M updates, N runs, leading-N bins
+    genomes[5, :40] = 4
+    off = np.arange(bins + 1, dtype=np.uint64) * glen
+    ids = np.arange(bins, dtype=np.uint32)
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    for b in range(bins):
+        oracle.add_kmers(words, p, genomes[b], b)
+    nd = p.P * p.W
+    want = words[:nd]
+
+    def built(mib, device_mode=False):
+        f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+        f.set_build_bucket_mib(mib)
+        f.profile_enable(True)
+        if device_mode:
+            d_seq = torch.from_numpy(genomes.reshape(-1)).cuda()
+            d_off = torch.from_numpy(off.view(np.int64)).cuda()
+            d_ids = torch.from_numpy(ids.view(np.int32)).cuda()
+            from dream_yara_b200._lib import check
+            check(dy.lib().dyibf_add_sequences(f._h, d_seq.data_ptr(), d_off.data_ptr(), bins, d_ids.data_ptr(), dy.ENC_DNA5, 1, None))
+            torch.cuda.synchronize()
+        else:
+            f.addSequences((genomes.reshape(-1), off), ids)
+        got = f.download_words()[:nd]
+        launches = f.profile()["build_launches"]
+        f.close()
+        return got, launches
+
+    direct, n0 = built(0)
+    assert np.array_equal(direct, want) and n0 == 1
+    auto, n1 = built(-1)
+    assert np.array_equal(auto, want) and n1 == 2                 # one scatter + one apply
+    tiny, n2 = built(16)                                           # 16 MiB of records for 39 M updates: overflow path
+    assert np.array_equal(tiny, want) and n2 == 2
+    dev, n3 = built(48, device_mode=True)                          # device entry, several passes
+    assert np.array_equal(dev, want) and n3 >= 6
