@@ -41,9 +41,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4"],
-                    help="BASELINE.json configs[1] (default, the headline), configs[2] (paired-end, e sweep) or configs[3] "
-                         "(bin-sharded, 1024 bins and a 64 GiB shard per GPU)")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4", "cfg5"],
+                    help="BASELINE.json configs[1] (default, the headline), configs[2] (paired-end, e sweep), configs[3] "
+                         "(bin-sharded, 1024 bins and a 64 GiB shard per GPU) or configs[4] (IBF build: one step = addKmers "
+                         "over 1024 bins x --genome-len bases, successive steps add new contigs to the same filter)")
     ap.add_argument("--bins", type=int, default=None, help="bins (cfg4: per GPU); default 1024")
     ap.add_argument("--filter-gib", type=int, default=None, help="filter size in GiB (cfg4: per GPU shard); default 16 / 64")
     ap.add_argument("--genome-len", type=int, default=4_000_000)
@@ -59,8 +60,9 @@ def parse():
     a.bins = a.bins or 1024
     a.filter_gib = a.filter_gib or (64 if a.bin_sharded else 16)
     a.read_len = a.read_len or (100 if a.bin_sharded else 150)
-    a.unit = "pairs/s" if a.paired else "reads/s"
-    a.metric = {"cfg2": "IBF bin-filter reads/s (150bp,e=3)", "cfg3": "IBF bin-filter pairs/s (2x150bp,e=3)",
+    a.unit = "pairs/s" if a.paired else ("k-mers/s" if a.workload == "cfg5" else "reads/s")
+    a.metric = {"cfg5": "IBF build k-mers/s (addKmers, 1024 bins, k=18, h=3)",
+                "cfg2": "IBF bin-filter reads/s (150bp,e=3)", "cfg3": "IBF bin-filter pairs/s (2x150bp,e=3)",
                 "cfg4": "IBF bin-filter reads/s (100bp,e=3), bin-sharded"}[a.workload]
     return a
 
@@ -162,14 +164,10 @@ class CpuFilter:
             self.words = self.o.new_words(self.p)
 
     def build(self, genomes):
-        """build_filter (d_build_filter.cpp:217-272): bins over threads, addKmers per bin."""
-        from concurrent.futures import ThreadPoolExecutor
-        if self.kind == "reference":
-            fn = lambda b: self.ref.add_kmers(self.f, genomes[b], b)          # noqa: E731
-        else:
-            fn = lambda b: self.o.add_kmers(self.words, self.p, genomes[b], b)  # noqa: E731
-        with ThreadPoolExecutor(max_workers=self.cores) as ex:                # ctypes releases the GIL
-            list(ex.map(fn, range(genomes.shape[0])))
+        """build_filter (d_build_filter.cpp:217-272): bins over threads, addKmers per bin; a thread owns whole 64-bin
+        columns so that the reference's non-atomic `word |= mask` never races (see bench_support/build_bench.py)."""
+        from bench_support.build_bench import _cpu_build
+        _cpu_build(self, genomes, np.arange(genomes.shape[0], dtype=np.uint32))
 
     def classify(self, layout, threshold, paired=False):
         """the filtering loop of clasifyLoadedReads over a prepared [fwd | rc] read set (full_layout_codes)"""
@@ -517,7 +515,10 @@ def run_b200(args):
 
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.workload == "cfg5":
+        from bench_support import build_bench
+        (build_bench.run_reference if a.impl == "reference" else build_bench.run_b200)(a, sys.modules[__name__])
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)

@@ -13,6 +13,7 @@
 #include <stdint.h>
 #include <stddef.h>
 #include <string.h>
+#include <immintrin.h>
 
 static inline uint64_t splitmix64(uint64_t x)
 {
@@ -32,6 +33,13 @@ void synth_genome(uint32_t bin, uint64_t len, uint8_t *out)
     for (uint64_t blk = 0; blk < (len + 31) / 32; ++blk) {
         uint64_t r = splitmix64(seed ^ (blk * 0x2545F4914F6CDD1DULL));
         uint64_t end = (blk + 1) * 32 < len ? (blk + 1) * 32 : len;
+        if (end - blk * 32 == 32) {                /* 8 bases per store: bits 2j..2j+1 -> byte j */
+            for (int q = 0; q < 4; ++q) {
+                uint64_t v = _pdep_u64(r >> (16 * q), 0x0303030303030303ULL);
+                memcpy(out + blk * 32 + 8 * q, &v, 8);
+            }
+            continue;
+        }
         for (uint64_t i = blk * 32; i < end; ++i) { out[i] = (uint8_t)(r & 3); r >>= 2; }
     }
     /* N runs: one per 10 000-base block */
