@@ -12,6 +12,7 @@ MEM_HOST, MEM_DEVICE = 0, 1
 MAX_HASH = 8
 OPT_EARLY_EXIT = 1
 OPT_BUILD_BUCKET_MIB = 2
+OPT_BUILD_CHUNK_MIB = 3
 
 
 class Params(C.Structure):
@@ -23,7 +24,8 @@ class Profile(C.Structure):
     _fields_ = [("pack_ms", C.c_double), ("query_ms", C.c_double), ("compact_ms", C.c_double),
                 ("build_ms", C.c_double), ("clear_ms", C.c_double),
                 ("pack_launches", C.c_uint64), ("query_launches", C.c_uint64), ("compact_launches", C.c_uint64),
-                ("build_launches", C.c_uint64), ("clear_launches", C.c_uint64), ("query_lookups", C.c_uint64)]
+                ("build_launches", C.c_uint64), ("clear_launches", C.c_uint64), ("query_lookups", C.c_uint64),
+                ("build_apply_ms", C.c_double), ("build_apply_launches", C.c_uint64)]
 
 
 # every symbol include/dyibf.h declares: name -> (restype, argtypes)

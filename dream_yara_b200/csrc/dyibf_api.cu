@@ -56,7 +56,7 @@ struct Slot {                     // one stage of the host-mode pipeline
     DevBuf in_bytes, in_offsets, packed, meta, rows, counts, ctr;
 };
 
-enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_N };
+enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_APPLY, K_N };
 
 struct Pending { cudaEvent_t a, b; int kind; };
 
@@ -77,14 +77,15 @@ struct dyibf_filter {
     std::vector<uint64_t> h_csr_off;
     uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
     int64_t      bucket_mib = -1;         // DYIBF_OPT_BUILD_BUCKET_MIB: -1 auto, 0 direct atomics only
+    int64_t      build_chunk_mib = 256;   // DYIBF_OPT_BUILD_CHUNK_MIB: bases per host-mode build chunk
     DevBuf       bucket_records, bucket_cursors;
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
     bool         profiling = false;
     std::vector<Pending> pending;
     std::vector<cudaEvent_t> ev_pool;
-    double       ms[K_N] = {0, 0, 0, 0, 0};
-    uint64_t     launches[K_N] = {0, 0, 0, 0, 0};
+    double       ms[K_N] = {0, 0, 0, 0, 0, 0};
+    uint64_t     launches[K_N] = {0, 0, 0, 0, 0, 0};
 };
 
 namespace {
@@ -810,12 +811,12 @@ int dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_
 // ============================================================================================================
 namespace {
 
-// One dyibf_add_sequences call's use of the bucketed build (build_kernel.cu): records accumulate in HBM across the
+// One dyibf_add_sequences call's use of the bucketed build (build_bucket.cu): records accumulate in HBM across the
 // call's chunks and are applied region by region when the buffer is nearly full and at the end of the call.
 struct BucketRun {
     bool active = false;
-    uint32_t R = 0, n_regions = 0;
-    uint64_t cap = 0, pending = 0, limit = 0;      // pending: upper bound of the records appended since the last apply
+    BucketPlan plan;
+    uint64_t pending = 0, limit = 0;               // pending: upper bound of the records appended since the last apply
 };
 
 int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
@@ -824,21 +825,24 @@ int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
     if (f->bucket_mib == 0) return DYIBF_OK;
     if (f->data_words * 8 <= (256ull << 20)) return DYIBF_OK;       // table (nearly) fits the L2: direct atomics are L2 hits
     if (expected_records < (32ull << 20)) return DYIBF_OK;          // too few updates per region sector to pay for a sweep
-    uint64_t budget = f->bucket_mib > 0 ? (uint64_t)f->bucket_mib << 20 : 8ull << 30;
+    uint64_t budget = f->bucket_mib > 0 ? (uint64_t)f->bucket_mib << 20 : 48ull << 30;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return DYIBF_OK;
     free_b += f->bucket_records.cap;
     if (f->bucket_mib < 0 && budget > free_b / 3) budget = free_b / 3;
-    const uint64_t want = expected_records * 4 + expected_records / 4 + (64ull << 20);   // the whole call in one pass
-    if (budget > want) budget = want;
-    if (!bucket_plan(f->data_words, budget, &br->R, &br->n_regions, &br->cap)) return DYIBF_OK;
-    if (f->bucket_records.reserve((uint64_t)br->n_regions * br->cap * 4) != cudaSuccess) {
+    if (!bucket_plan(f->data_words, budget, &br->plan)) return DYIBF_OK;
+    // the whole call in one pass if the budget allows (slack: see limit below)
+    const uint64_t rec_bytes = 4 + br->plan.rec1_bytes;
+    const uint64_t want = expected_records * rec_bytes + expected_records * rec_bytes / 8 + (256ull << 20);
+    if (budget > want && !bucket_plan(f->data_words, want, &br->plan)) return DYIBF_OK;
+    if (f->bucket_records.reserve(br->plan.bytes_final + br->plan.bytes_level1) != cudaSuccess) {
         cudaGetLastError();                                          // not enough memory: direct atomics
         return DYIBF_OK;
     }
-    CU(f->bucket_cursors.reserve((uint64_t)br->n_regions * 8));
-    CU(cudaMemset(f->bucket_cursors.p, 0, (uint64_t)br->n_regions * 8));
-    br->limit = (uint64_t)((double)br->n_regions * (double)br->cap / 1.06);
+    CU(f->bucket_cursors.reserve(bucket_cursor_slots(br->plan) * 8));
+    CU(cudaMemset(f->bucket_cursors.p, 0, bucket_cursor_slots(br->plan) * 8));
+    // 10 % slack per bucket: the hash is uniform; every writing warp may leave a chunk of padding lines per bucket
+    br->limit = (uint64_t)((double)br->plan.n_regions * (double)br->plan.cap / 1.10);
     br->pending = 0;
     br->active = true;
     return DYIBF_OK;
@@ -847,9 +851,9 @@ int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
 int buckets_apply(dyibf_filter* f, BucketRun* br, cudaStream_t st)
 {
     if (!br->active || br->pending == 0) return DYIBF_OK;
-    Scope sc(f, st, K_BUILD);
-    CU(launch_build_apply(f->d_words, (const uint32_t*)f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p,
-                          br->R, br->n_regions, br->cap, br->cap, st));
+    Scope sc(f, st, K_APPLY);
+    CU(launch_bucket_apply(f->d_words, f->data_words, br->plan, f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p,
+                           br->pending, st));
     br->pending = 0;
     return DYIBF_OK;
 }
@@ -902,9 +906,8 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         for (uint64_t w0 = 0; w0 < words; w0 += per_pass) {
             const uint64_t w1 = std::min<uint64_t>(words, w0 + per_pass);
             { Scope sc(f, st, K_BUILD);
-              CU(launch_build_scatter(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs,
-                                      w0, w1, br.R, br.n_regions, br.cap, (uint32_t*)f->bucket_records.p,
-                                      (unsigned long long*)f->bucket_cursors.p, st)); }
+              CU(launch_bucket_split(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs,
+                                     w0, w1, br.plan, f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p, 0, st)); }
             br.pending = (w1 - w0) * 32ull * f->hp.h;
             brc = buckets_apply(f, &br, st);
             if (brc) return brc;
@@ -918,8 +921,9 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         if (offsets[s + 1] - offsets[s] > 0xffffffffull) return fail(DYIBF_ERR_ARG, "sequence %u longer than 2^32", s);
         if (bin_ids[s] >= f->prm.bins) return fail(DYIBF_ERR_ARG, "bin %u of sequence %u out of range (%u bins)", bin_ids[s], s, f->prm.bins);
     }
-    // chunks of whole sequences, ~64 MB of bases each, alternating between the two stream slots
-    const uint64_t target = 64ull << 20;
+    // chunks of whole sequences, ~256 MB of bases each by default (8192 scatter work items: enough warps for every SM),
+    // alternating between the two stream slots
+    const uint64_t target = (uint64_t)f->build_chunk_mib << 20;
     BucketRun br;
     int brc = buckets_begin(f, (offsets[n_seqs] - offsets[0]) * f->hp.h, &br);
     if (brc) return brc;
@@ -954,9 +958,9 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
                 CU(cudaStreamSynchronize(sl.st));
             }
             Scope sc(f, sl.st, K_BUILD);
-            CU(launch_build_scatter(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
-                                    (const uint32_t*)sl.counts.p, cnt, 0, words, br.R, br.n_regions, br.cap,
-                                    (uint32_t*)f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p, sl.st));
+            CU(launch_bucket_split(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
+                                   (const uint32_t*)sl.counts.p, cnt, 0, words, br.plan, f->bucket_records.p,
+                                   (unsigned long long*)f->bucket_cursors.p, c & 1, sl.st));
             br.pending += ub;
         } else {
             Scope sc(f, sl.st, K_BUILD);
@@ -1015,6 +1019,10 @@ int dyibf_set_option(dyibf_filter* f, int option, int64_t value)
             if (value < -1) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_BUCKET_MIB must be -1 (auto), 0 (off) or a size in MiB");
             f->bucket_mib = value;
             return DYIBF_OK;
+        case DYIBF_OPT_BUILD_CHUNK_MIB:
+            if (value < 1 || value > 4096) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_CHUNK_MIB must be 1..4096");
+            f->build_chunk_mib = value;
+            return DYIBF_OK;
         default:
             return fail(DYIBF_ERR_ARG, "unknown option %d", option);
     }
@@ -1026,6 +1034,7 @@ int dyibf_get_option(const dyibf_filter* f, int option, int64_t* value)
     switch (option) {
         case DYIBF_OPT_EARLY_EXIT: *value = (f->query_flags & QUERY_EARLY_EXIT) ? 1 : 0; return DYIBF_OK;
         case DYIBF_OPT_BUILD_BUCKET_MIB: *value = f->bucket_mib; return DYIBF_OK;
+        case DYIBF_OPT_BUILD_CHUNK_MIB: *value = f->build_chunk_mib; return DYIBF_OK;
         default: return fail(DYIBF_ERR_ARG, "unknown option %d", option);
     }
 }
@@ -1048,9 +1057,10 @@ int dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset)
     DeviceGuard guard(f->prm.device);
     drain_profile(f);
     out->pack_ms = f->ms[K_PACK]; out->query_ms = f->ms[K_QUERY]; out->compact_ms = f->ms[K_COMPACT];
-    out->build_ms = f->ms[K_BUILD]; out->clear_ms = f->ms[K_CLEAR];
+    out->build_ms = f->ms[K_BUILD] + f->ms[K_APPLY]; out->clear_ms = f->ms[K_CLEAR];
+    out->build_apply_ms = f->ms[K_APPLY]; out->build_apply_launches = f->launches[K_APPLY];
     out->pack_launches = f->launches[K_PACK]; out->query_launches = f->launches[K_QUERY];
-    out->compact_launches = f->launches[K_COMPACT]; out->build_launches = f->launches[K_BUILD];
+    out->compact_launches = f->launches[K_COMPACT]; out->build_launches = f->launches[K_BUILD] + f->launches[K_APPLY];
     out->clear_launches = f->launches[K_CLEAR];
     out->query_lookups = 0;
     if (f->stats.p) {                                                  // all launches have drained above

@@ -60,14 +60,30 @@ cudaError_t launch_query(const HashParams& hp, const uint64_t* filter, const uin
 cudaError_t launch_build(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
                          const uint32_t* bin_ids, uint32_t n_seqs, uint64_t total_words, cudaStream_t st);
 
-// bucketed build (see build_kernel.cu): scatter appends 32-bit update records to per-region buckets, apply ORs them in.
-bool        bucket_plan(uint64_t data_words, uint64_t budget_bytes, uint32_t* R, uint32_t* n_regions, uint64_t* cap);
-cudaError_t launch_build_scatter(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
-                                 const uint32_t* bin_ids, uint32_t n_seqs, uint64_t word_begin, uint64_t total_words, uint32_t R,
-                                 uint32_t n_regions, uint64_t cap, uint32_t* records, unsigned long long* cursors, cudaStream_t st);
-static const uint64_t BUILD_SCATTER_ALIGN = 1024;   // word_begin of a scatter launch must be a multiple of this
-cudaError_t launch_build_apply(uint64_t* filter, const uint32_t* records, unsigned long long* cursors, uint32_t R,
-                               uint32_t n_regions, uint64_t cap, uint64_t max_fill, cudaStream_t st);
+// bucketed build (build_bucket.cu): a radix split appends 32-bit update records to per-region buckets, apply ORs them in.
+struct BucketPlan {
+    uint32_t R;            // log2(words per region)
+    uint32_t n_regions;    // final buckets (<= 1024)
+    uint32_t n_super;      // level-1 buckets of a two-level split (regions / 32, rounded up); 1: single level
+    uint32_t rec1_bytes;   // size of a level-1 record: 4, or 8 when R + 5 + 6 bits do not fit 32; 0: single level
+    uint64_t cap;          // records per final bucket
+    uint64_t cap1;         // records per level-1 bucket (32 * cap); 0: single level
+    uint64_t bytes_final;  // the record buffer holds the final buckets first, then the level-1 buckets
+    uint64_t bytes_level1;
+};
+bool        bucket_plan(uint64_t data_words, uint64_t budget_bytes, BucketPlan* plan);
+// cursors: n_regions final fill counts, 32 level-1 fill counts, 2 level-1 work counters (+2 pad), 32 level-2 work counters
+static inline uint64_t bucket_cursor_slots(const BucketPlan& p) { return (uint64_t)p.n_regions + 32 + 4 + 32; }
+static const uint64_t BUILD_SCATTER_ALIGN = 1024;   // word_begin of a split launch must be a multiple of this
+// level 1 (or the only level) over packed words [word_begin, total_words); launches that may overlap on different
+// streams use different counter slots (0 / 1)
+cudaError_t launch_bucket_split(const HashParams& hp, uint64_t* filter, const uint64_t* packed, const SeqMeta* meta,
+                                const uint32_t* bin_ids, uint32_t n_seqs, uint64_t word_begin, uint64_t total_words,
+                                const BucketPlan& plan, void* records, unsigned long long* cursors, uint32_t counter_slot,
+                                cudaStream_t st);
+// level 2 (two-level plans) + apply + cursor reset; max_fill: upper bound of the records appended since the last apply
+cudaError_t launch_bucket_apply(uint64_t* filter, uint64_t data_words, const BucketPlan& plan, void* records,
+                                unsigned long long* cursors, uint64_t max_fill, cudaStream_t st);
 
 // clear: for every hash block, words cols[i] &= ~masks[i]
 cudaError_t launch_clear(const HashParams& hp, uint64_t* filter, const uint32_t* cols, const uint64_t* masks, uint32_t n_cols,

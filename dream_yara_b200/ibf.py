@@ -285,6 +285,10 @@ class SeqAnBloomFilter:
         """DYIBF_OPT_BUILD_BUCKET_MIB: scratch size of the bucketed build (-1 auto, 0 = direct atomics only)."""
         check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_BUCKET_MIB, int(mib)))
 
+    def set_build_chunk_mib(self, mib):
+        """DYIBF_OPT_BUILD_CHUNK_MIB: bases per staged chunk of addSequences on host buffers."""
+        check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_CHUNK_MIB, int(mib)))
+
     def profile_enable(self, on=True):
         check(lib().dyibf_profile_enable(self._h, int(on)))
 

@@ -65,6 +65,8 @@ typedef struct dyibf_profile {
     double   pack_ms, query_ms, compact_ms, build_ms, clear_ms;
     uint64_t pack_launches, query_launches, compact_launches, build_launches, clear_launches;
     uint64_t query_lookups;   /* k-mer lookups (h block fetches each) the query kernel performed while profiling was on */
+    double   build_apply_ms;  /* the part of build_ms / build_launches spent in the bucketed build's apply sweeps */
+    uint64_t build_apply_launches;
 } dyibf_profile;
 
 const char* dyibf_last_error(void);
@@ -171,12 +173,15 @@ int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64
  * k-mers left (count + remaining < threshold).  The rows are bit-identical to the full pass; only memory traffic
  * drops (e.g. 150 bp, k=18, e=3: ~57 % of the lookups). */
 #define DYIBF_OPT_EARLY_EXIT 1
-/* DYIBF_OPT_BUILD_BUCKET_MIB (default -1 = auto: up to 8 GiB, at most a third of the free HBM; 0 = off).  _insertKmer's
+/* DYIBF_OPT_BUILD_BUCKET_MIB (default -1 = auto: what the call's updates need, up to 48 GiB, at most a third of the free HBM; 0 = off).  _insertKmer's
  * single-bit ORs land at uniformly random words of the table.  For tables larger than the L2 and calls with at least 32 M
  * updates, dyibf_add_sequences first appends the updates as 32-bit records to per-region buckets in a scratch buffer of
  * this size and then ORs them in region by region, so that DRAM sees streaming instead of random sector traffic.  The
  * filter is bit-identical either way (OR is commutative and idempotent). */
 #define DYIBF_OPT_BUILD_BUCKET_MIB 2
+/* DYIBF_OPT_BUILD_CHUNK_MIB (default 256): dyibf_add_sequences(host) stages whole sequences in chunks of about this many
+ * MiB of bases, alternating between two streams so that the copy of one chunk overlaps the kernels of the other. */
+#define DYIBF_OPT_BUILD_CHUNK_MIB 3
 int  dyibf_set_option(dyibf_filter* f, int option, int64_t value);
 int  dyibf_get_option(const dyibf_filter* f, int option, int64_t* value);
 

@@ -337,13 +337,15 @@ def test_gather_reads_random_vs_oracle(dy, oracle, paired):
     f.close()
 
 
-def test_bucketed_build_equals_direct_and_oracle(dy, oracle):
+@pytest.mark.parametrize("log2_bits", [32, 33])
+def test_bucketed_build_equals_direct_and_oracle(dy, oracle, log2_bits):
     """The bucketed build (DYIBF_OPT_BUILD_BUCKET_MIB; tables larger than the L2, >= 32 M updates per call) against the
     oracle and the direct atomic kernel: auto budget, a budget so small that most updates overflow into the direct
-    fallback, and the device-pointer entry with several scatter/apply passes."""
+    fallback, and the device-pointer entry with several scatter/apply passes.  512 MiB table: 32 regions of 16 MiB, one
+    split level; 1 GiB table: 64 regions, two split levels."""
     import torch
     from bench_support import synth
-    bins, h, k, nbits = 1000, 3, 18, (1 << 32) + 256            # 512 MiB table: 32 regions of 16 MiB
+    bins, h, k, nbits = 1000, 3, 18, (1 << log2_bits) + 256
     glen = 13_000
     genomes = synth.genomes(bins, glen)                           # 13 M bases -> 39 M updates, N runs, leading-N bins
     genomes[5, :40] = 4
@@ -356,9 +358,11 @@ def test_bucketed_build_equals_direct_and_oracle(dy, oracle):
     nd = p.P * p.W
     want = words[:nd]
 
-    def built(mib, device_mode=False):
+    def built(mib, device_mode=False, chunk_mib=None):
         f = dy.SeqAnBloomFilter(bins, h, k, nbits)
         f.set_build_bucket_mib(mib)
+        if chunk_mib:
+            f.set_build_chunk_mib(chunk_mib)
         f.profile_enable(True)
         if device_mode:
             d_seq = torch.from_numpy(genomes.reshape(-1)).cuda()
@@ -377,8 +381,38 @@ def test_bucketed_build_equals_direct_and_oracle(dy, oracle):
     direct, n0 = built(0)
     assert np.array_equal(direct, want) and n0 == 1
     auto, n1 = built(-1)
-    assert np.array_equal(auto, want) and n1 == 2                 # one scatter + one apply
-    tiny, n2 = built(16)                                           # 16 MiB of records for 39 M updates: overflow path
+    assert np.array_equal(auto, want) and n1 == 2                 # one split + one apply sweep
+    tiny, n2 = built(32)                                           # 32 MiB of records for 39 M updates: overflow path
     assert np.array_equal(tiny, want) and n2 == 2
-    dev, n3 = built(48, device_mode=True)                          # device entry, several passes
-    assert np.array_equal(dev, want) and n3 >= 6
+    dev, n3 = built(96, device_mode=True)                          # device entry, several passes
+    assert np.array_equal(dev, want) and n3 >= 4
+    many, n4 = built(-1, chunk_mib=1)                              # 13 host chunks: scatter launches overlap on two streams
+    assert np.array_equal(many, want) and n4 >= 13
+
+
+def test_bucketed_build_wide_records_equals_direct(dy):
+    """Tables above 16 GiB have regions of more than 2^21 words, so the level-1 records of the two-level split are 64 bit
+    wide.  32 GiB table, GPU against GPU: the bucketed build must leave exactly the words the direct atomic kernel (pinned
+    against the oracle at smaller sizes above) leaves."""
+    import torch
+    from bench_support import synth
+    bins, h, k, nbits = 1024, 3, 18, (1 << 38) + 256
+    glen = 40_000                                                 # 123 M updates: enough for the bucketed path on 1024 regions
+    genomes = synth.genomes(bins, glen)
+    off = np.arange(bins + 1, dtype=np.uint64) * glen
+    ids = np.arange(bins, dtype=np.uint32)
+    tables = []
+    for mib in (0, -1):
+        W = (bins + 63) // 64
+        nd = ((nbits - 256) // (64 * W)) * W
+        words = torch.zeros(nd, dtype=torch.int64, device="cuda")
+        f = dy.SeqAnBloomFilter.attach(bins, h, k, nbits, words.data_ptr(), device=0, keep=words)
+        f.set_build_bucket_mib(mib)
+        f.profile_enable(True)
+        f.addSequences((genomes.reshape(-1), off), ids)
+        torch.cuda.synchronize()
+        assert f.profile()["build_apply_launches"] == (0 if mib == 0 else 1)
+        f.close()
+        tables.append(words)
+    assert int(torch.count_nonzero(tables[0])) > 100_000_000
+    assert torch.equal(tables[0], tables[1])
