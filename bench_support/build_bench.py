@@ -201,10 +201,10 @@ def run_b200(args, B):
     clocks = sampler.stop() if rank == 0 else None
     prof = f_dev.profile(reset=True); f_dev.profile_enable(False)
     t = torch.tensor([e0.elapsed_time(e1), prof["build_ms"] / args.steps, prof["pack_ms"] / args.steps,
-                      prof["build_apply_ms"] / args.steps], dtype=torch.float64, device=dev)
+                      prof["build_apply_ms"] / args.steps, prof["build_split2_ms"] / args.steps], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, build_ms, pack_ms, apply_ms = (float(x) for x in t.tolist())
+    ms_total, build_ms, pack_ms, apply_ms, split2_ms = (float(x) for x in t.tolist())
     value = world * kmers_step * args.steps / (ms_total / 1e3)
     launches = int(prof["build_launches"] + prof["pack_launches"])
     bucket = C.c_int64(0)
@@ -275,9 +275,9 @@ def run_b200(args, B):
     achieved = alg / (build_ms / 1e3) / 1e9
     model = kmers_step * H * 8 + 2 * P * W * 8
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": "build_scatter_kernel<3> + build_apply_kernel" if bucket.value != 0 else "build_kernel<3>",
-                "kernel_ms": build_ms, "scatter_ms": build_ms - apply_ms, "apply_ms": apply_ms,
-                "passes_per_step": prof["build_apply_launches"] / args.steps, "pack_kernel_ms": pack_ms, "algorithmic_bytes_per_launch": alg, "peak_source": peak_src,
+                "kernel": "split1_kernel<3,u32> + split2_kernel<u32> + bucket_apply_kernel" if bucket.value != 0 else "build_kernel<3>",
+                "kernel_ms": build_ms, "split1_ms": build_ms - apply_ms - split2_ms, "split2_ms": split2_ms, "apply_ms": apply_ms,
+                "sweeps_per_step": prof["build_apply_launches"] / args.steps, "pack_kernel_ms": pack_ms, "algorithmic_bytes_per_launch": alg, "peak_source": peak_src,
                 "bucketed_model_bytes_per_step": model, "bucketed_model_gbs": model / (build_ms / 1e3) / 1e9,
                 "note": "algorithmic bytes = the random-RMW sector model (192 B/k-mer); the bucketed build moves "
                         "~%.0f B/k-mer instead (records + one table sweep per step)" % (model / kmers_step)}

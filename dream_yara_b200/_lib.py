@@ -25,7 +25,8 @@ class Profile(C.Structure):
                 ("build_ms", C.c_double), ("clear_ms", C.c_double),
                 ("pack_launches", C.c_uint64), ("query_launches", C.c_uint64), ("compact_launches", C.c_uint64),
                 ("build_launches", C.c_uint64), ("clear_launches", C.c_uint64), ("query_lookups", C.c_uint64),
-                ("build_apply_ms", C.c_double), ("build_apply_launches", C.c_uint64)]
+                ("build_apply_ms", C.c_double), ("build_apply_launches", C.c_uint64),
+                ("build_split2_ms", C.c_double), ("build_split2_launches", C.c_uint64)]
 
 
 # every symbol include/dyibf.h declares: name -> (restype, argtypes)

@@ -401,11 +401,13 @@ bool bucket_plan(uint64_t data_words, uint64_t budget_bytes, BucketPlan* p)
     p->R = R; p->n_regions = (uint32_t)n_regions;
     p->n_super = n_regions > 32 ? (uint32_t)((n_regions + 31) / 32) : 1;
     p->rec1_bytes = p->n_super > 1 ? (R + 5 + 6 > 32 ? 8 : 4) : 0;
-    uint64_t cap = budget_bytes / (4 + p->rec1_bytes) / (p->n_super > 1 ? (uint64_t)p->n_super * 32 : n_regions);
+    // final buckets: n_regions x cap x 4 bytes; level-1 buckets: n_super x (8 x cap) x rec1_bytes
+    uint64_t cap = budget_bytes / (4 * n_regions + 8ull * (p->n_super > 1 ? p->n_super : 0) * p->rec1_bytes);
     if (cap > MAX_BUCKET_CAP) cap = MAX_BUCKET_CAP;
     cap -= cap % (32 * CHUNK_LINES);                              // whole reservation chunks of 128-byte lines
     if (cap < 65536) return false;
-    p->cap = cap; p->cap1 = p->n_super > 1 ? 32 * cap : 0;
+    p->cap = cap; p->cap1 = p->n_super > 1 ? 8 * cap : 0;
+    p->bytes_per_record_x4 = 16 + p->rec1_bytes;
     p->bytes_final = n_regions * cap * 4;
     p->bytes_level1 = (uint64_t)p->n_super * p->cap1 * p->rec1_bytes;
     return true;
@@ -463,33 +465,37 @@ cudaError_t launch_bucket_split(const HashParams& hp, uint64_t* filter, const ui
                                    reinterpret_cast<uint32_t*>(base + p.bytes_final), cursors1, work_counter, (unsigned)blocks, st);
 }
 
+cudaError_t launch_bucket_split2(uint64_t* filter, const BucketPlan& p, void* records, unsigned long long* cursors,
+                                 uint64_t max_fill1, cudaStream_t st)
+{
+    if (p.n_super <= 1 || max_fill1 == 0) return cudaSuccess;
+    char* base = static_cast<char*>(records);
+    const uint64_t fill1 = max_fill1 < p.cap1 ? max_fill1 : p.cap1;
+    unsigned long long* work_counters = cursors + p.n_regions + 32 + 4;
+    cudaError_t e = cudaMemsetAsync(work_counters, 0, 32 * sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    uint64_t blocks = (((fill1 + SPLIT2_ITEM - 1) / SPLIT2_ITEM) * p.n_super + 7) / 8;
+    if (blocks > 148ull * 6) blocks = 148ull * 6;
+    if (blocks < 4) blocks = 4;                                    // 32 warps: every super-bucket has at least one
+    const size_t smem = 8 * 1024 * sizeof(uint32_t);
+    if (p.rec1_bytes == 8)
+        split2_kernel<uint64_t><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const uint64_t*>(base + p.bytes_final),
+            cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters);
+    else
+        split2_kernel<uint32_t><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const uint32_t*>(base + p.bytes_final),
+            cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return cudaMemsetAsync(cursors + p.n_regions, 0, 32 * sizeof(unsigned long long), st);
+}
+
 cudaError_t launch_bucket_apply(uint64_t* filter, uint64_t data_words, const BucketPlan& p, void* records,
                                 unsigned long long* cursors, uint64_t max_fill, cudaStream_t st)
 {
-    // max_fill: upper bound of the records appended since the last apply, known to the host; bounds the grids
+    // max_fill: upper bound of the records appended since the last apply, known to the host; bounds the grid
     if (max_fill == 0) return cudaSuccess;
     char* base = static_cast<char*>(records);
     cudaError_t e;
-    if (p.n_super > 1) {
-        const uint64_t fill1 = max_fill < p.cap1 ? max_fill : p.cap1;
-        unsigned long long* work_counters = cursors + p.n_regions + 32 + 4;
-        e = cudaMemsetAsync(work_counters, 0, 32 * sizeof(unsigned long long), st);
-        if (e != cudaSuccess) return e;
-        uint64_t blocks = (((fill1 + SPLIT2_ITEM - 1) / SPLIT2_ITEM) * p.n_super + 7) / 8;
-        if (blocks > 148ull * 6) blocks = 148ull * 6;
-        if (blocks < 4) blocks = 4;                                // 32 warps: every super-bucket has at least one
-        const size_t smem = 8 * 1024 * sizeof(uint32_t);
-        if (p.rec1_bytes == 8)
-            split2_kernel<uint64_t><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const uint64_t*>(base + p.bytes_final),
-                cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters);
-        else
-            split2_kernel<uint32_t><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const uint32_t*>(base + p.bytes_final),
-                cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters);
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-        e = cudaMemsetAsync(cursors + p.n_regions, 0, 32 * sizeof(unsigned long long), st);
-        if (e != cudaSuccess) return e;
-    }
     // padding lines (copies of real records) count like records: every bucket may hold up to its capacity
     const uint64_t fill = max_fill + (uint64_t)32 * CHUNK_LINES * 148 * 48 < p.cap ? max_fill + (uint64_t)32 * CHUNK_LINES * 148 * 48 : p.cap;
     const uint32_t bpr = (uint32_t)((fill + APPLY_CHUNK - 1) / APPLY_CHUNK);

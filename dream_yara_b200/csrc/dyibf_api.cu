@@ -56,7 +56,7 @@ struct Slot {                     // one stage of the host-mode pipeline
     DevBuf in_bytes, in_offsets, packed, meta, rows, counts, ctr;
 };
 
-enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_APPLY, K_N };
+enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_APPLY, K_SPLIT2, K_N };
 
 struct Pending { cudaEvent_t a, b; int kind; };
 
@@ -84,8 +84,8 @@ struct dyibf_filter {
     bool         profiling = false;
     std::vector<Pending> pending;
     std::vector<cudaEvent_t> ev_pool;
-    double       ms[K_N] = {0, 0, 0, 0, 0, 0};
-    uint64_t     launches[K_N] = {0, 0, 0, 0, 0, 0};
+    double       ms[K_N] = {0, 0, 0, 0, 0, 0, 0};
+    uint64_t     launches[K_N] = {0, 0, 0, 0, 0, 0, 0};
 };
 
 namespace {
@@ -811,12 +811,15 @@ int dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_
 // ============================================================================================================
 namespace {
 
-// One dyibf_add_sequences call's use of the bucketed build (build_bucket.cu): records accumulate in HBM across the
-// call's chunks and are applied region by region when the buffer is nearly full and at the end of the call.
+// One dyibf_add_sequences call's use of the bucketed build (build_bucket.cu).  Update records accumulate in HBM across
+// the call's chunks: level 1 of the split fills the (smaller) super-bucket buffer, level 2 empties it into the final
+// per-region buckets, and the final buckets are OR-ed into the table (one sweep over the table) when they are nearly
+// full and at the end of the call.
 struct BucketRun {
     bool active = false;
     BucketPlan plan;
-    uint64_t pending = 0, limit = 0;               // pending: upper bound of the records appended since the last apply
+    uint64_t pending1 = 0, limit1 = 0;             // level-1 buffer: upper bound of the records in it / what it may hold
+    uint64_t pending = 0, limit = 0;               // final buckets (pending + pending1 <= limit at all times)
 };
 
 int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
@@ -825,15 +828,15 @@ int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
     if (f->bucket_mib == 0) return DYIBF_OK;
     if (f->data_words * 8 <= (256ull << 20)) return DYIBF_OK;       // table (nearly) fits the L2: direct atomics are L2 hits
     if (expected_records < (32ull << 20)) return DYIBF_OK;          // too few updates per region sector to pay for a sweep
-    uint64_t budget = f->bucket_mib > 0 ? (uint64_t)f->bucket_mib << 20 : 48ull << 30;
+    uint64_t budget = f->bucket_mib > 0 ? (uint64_t)f->bucket_mib << 20 : 64ull << 30;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return DYIBF_OK;
     free_b += f->bucket_records.cap;
-    if (f->bucket_mib < 0 && budget > free_b / 3) budget = free_b / 3;
+    if (f->bucket_mib < 0 && budget > free_b / 2) budget = free_b / 2;
     if (!bucket_plan(f->data_words, budget, &br->plan)) return DYIBF_OK;
-    // the whole call in one pass if the budget allows (slack: see limit below)
-    const uint64_t rec_bytes = 4 + br->plan.rec1_bytes;
-    const uint64_t want = expected_records * rec_bytes + expected_records * rec_bytes / 8 + (256ull << 20);
+    // the whole call in one sweep if the budget allows (slack: see the limits below)
+    const uint64_t per_rec = br->plan.bytes_per_record_x4;          // bytes per record of final capacity, times 4
+    const uint64_t want = expected_records * per_rec / 4 + expected_records * per_rec / 32 + (256ull << 20);
     if (budget > want && !bucket_plan(f->data_words, want, &br->plan)) return DYIBF_OK;
     if (f->bucket_records.reserve(br->plan.bytes_final + br->plan.bytes_level1) != cudaSuccess) {
         cudaGetLastError();                                          // not enough memory: direct atomics
@@ -843,18 +846,78 @@ int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
     CU(cudaMemset(f->bucket_cursors.p, 0, bucket_cursor_slots(br->plan) * 8));
     // 10 % slack per bucket: the hash is uniform; every writing warp may leave a chunk of padding lines per bucket
     br->limit = (uint64_t)((double)br->plan.n_regions * (double)br->plan.cap / 1.10);
-    br->pending = 0;
+    br->limit1 = br->plan.n_super > 1 ? (uint64_t)((double)br->plan.n_super * (double)br->plan.cap1 / 1.10) : br->limit;
+    br->pending = br->pending1 = 0;
     br->active = true;
+    return DYIBF_OK;
+}
+
+// level 2: the super-bucket buffer -> the final buckets (two-level plans; stream-ordered on st)
+int buckets_flush_level1(dyibf_filter* f, BucketRun* br, cudaStream_t st)
+{
+    if (!br->active || br->pending1 == 0) return DYIBF_OK;
+    if (br->plan.n_super > 1) {
+        Scope sc(f, st, K_SPLIT2);
+        CU(launch_bucket_split2(f->d_words, br->plan, f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p, br->pending1, st));
+    }
+    br->pending += br->pending1;
+    br->pending1 = 0;
     return DYIBF_OK;
 }
 
 int buckets_apply(dyibf_filter* f, BucketRun* br, cudaStream_t st)
 {
-    if (!br->active || br->pending == 0) return DYIBF_OK;
+    if (!br->active) return DYIBF_OK;
+    int rc = buckets_flush_level1(f, br, st);
+    if (rc) return rc;
+    if (br->pending == 0) return DYIBF_OK;
     Scope sc(f, st, K_APPLY);
     CU(launch_bucket_apply(f->d_words, f->data_words, br->plan, f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p,
                            br->pending, st));
     br->pending = 0;
+    return DYIBF_OK;
+}
+
+// Split the updates of packed words [0, words) of one pack buffer into the buckets, in word ranges that fit the buffers;
+// makes room first (level 2, apply) where needed.  sync_all: the call uses both stream slots (host mode), so everything
+// in flight is waited for before a buffer is emptied; otherwise the work is stream-ordered on st.
+int buckets_scatter(dyibf_filter* f, BucketRun* br, const uint64_t* packed, const SeqMeta* meta, const uint32_t* bin_ids,
+                    uint32_t n_seqs, uint64_t words, uint32_t counter_slot, bool sync_all, cudaStream_t st)
+{
+    const uint64_t per_word = 32ull * f->hp.h;                      // upper bound of the records one packed word yields
+    const bool two = br->plan.n_super > 1;
+    uint64_t max_words = (two ? br->limit1 : br->limit) / per_word;
+    max_words -= max_words % BUILD_SCATTER_ALIGN;
+    if (max_words < BUILD_SCATTER_ALIGN) max_words = BUILD_SCATTER_ALIGN;
+    for (uint64_t w0 = 0; w0 < words;) {
+        uint64_t room = ((two ? br->limit1 - br->pending1 : br->limit - br->pending) / per_word);
+        room -= room % BUILD_SCATTER_ALIGN;
+        const uint64_t left = words - w0;
+        if (room < left && room < max_words) {
+            // not enough room for a full-sized range: empty the level-1 buffer, and the final buckets if they could not
+            // take what level 1 may still hold plus a full range
+            if (sync_all) { CU(cudaStreamSynchronize(f->slot[0].st)); CU(cudaStreamSynchronize(f->slot[1].st)); }
+            int rc = buckets_flush_level1(f, br, st);
+            if (rc) return rc;
+            const uint64_t next = std::min(left, max_words) * per_word;
+            if (br->pending && br->pending + next > br->limit) { rc = buckets_apply(f, br, st); if (rc) return rc; }
+            if (sync_all) CU(cudaStreamSynchronize(st));
+            continue;
+        }
+        const uint64_t n = std::min(left, std::min(room, max_words));
+        const uint64_t add = n * per_word;
+        if (two && br->pending + br->pending1 + add > br->limit) {   // the final buckets must be able to take level 1's content
+            if (sync_all) { CU(cudaStreamSynchronize(f->slot[0].st)); CU(cudaStreamSynchronize(f->slot[1].st)); }
+            int rc = buckets_apply(f, br, st);
+            if (rc) return rc;
+            if (sync_all) CU(cudaStreamSynchronize(st));
+        }
+        { Scope sc(f, st, K_BUILD);
+          CU(launch_bucket_split(f->hp, f->d_words, packed, meta, bin_ids, n_seqs, w0, w0 + n, br->plan, f->bucket_records.p,
+                                 (unsigned long long*)f->bucket_cursors.p, counter_slot, st)); }
+        if (two) br->pending1 += add; else br->pending += add;
+        w0 += n;
+    }
     return DYIBF_OK;
 }
 
@@ -899,21 +962,11 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
             CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st));
             return DYIBF_OK;
         }
-        // stream-ordered passes over word ranges whose updates fit the record buffer: scatter, apply, next range
-        uint64_t per_pass = br.limit / (32ull * f->hp.h);
-        per_pass -= per_pass % BUILD_SCATTER_ALIGN;
-        if (per_pass < BUILD_SCATTER_ALIGN) per_pass = BUILD_SCATTER_ALIGN;
-        for (uint64_t w0 = 0; w0 < words; w0 += per_pass) {
-            const uint64_t w1 = std::min<uint64_t>(words, w0 + per_pass);
-            { Scope sc(f, st, K_BUILD);
-              CU(launch_bucket_split(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs,
-                                     w0, w1, br.plan, f->bucket_records.p, (unsigned long long*)f->bucket_cursors.p, 0, st)); }
-            br.pending = (w1 - w0) * 32ull * f->hp.h;
-            brc = buckets_apply(f, &br, st);
-            if (brc) return brc;
-        }
+        // stream-ordered: split, level 2, apply, next word range
+        brc = buckets_scatter(f, &br, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, 0, false, st);
+        if (brc) return brc;
         // the record buffer stays allocated: the kernels above may still be running (stream-ordered call)
-        return DYIBF_OK;
+        return buckets_apply(f, &br, st);
     }
     if (mem != DYIBF_MEM_HOST) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
     for (uint32_t s = 0; s < n_seqs; ++s) {
@@ -949,19 +1002,9 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         { Scope sc(f, sl.st, K_PACK);
           CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, sl.st)); }
         if (br.active) {
-            const uint64_t ub = words * 32ull * f->hp.h;                       // upper bound of this chunk's records
-            if (br.pending && br.pending + ub > br.limit) {                    // buffer nearly full: apply, then go on
-                CU(cudaStreamSynchronize(f->slot[0].st));
-                CU(cudaStreamSynchronize(f->slot[1].st));
-                brc = buckets_apply(f, &br, sl.st);
-                if (brc) return brc;
-                CU(cudaStreamSynchronize(sl.st));
-            }
-            Scope sc(f, sl.st, K_BUILD);
-            CU(launch_bucket_split(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
-                                   (const uint32_t*)sl.counts.p, cnt, 0, words, br.plan, f->bucket_records.p,
-                                   (unsigned long long*)f->bucket_cursors.p, c & 1, sl.st));
-            br.pending += ub;
+            brc = buckets_scatter(f, &br, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, (const uint32_t*)sl.counts.p,
+                                  cnt, words, c & 1, true, sl.st);
+            if (brc) return brc;
         } else {
             Scope sc(f, sl.st, K_BUILD);
             CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
@@ -1057,10 +1100,11 @@ int dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset)
     DeviceGuard guard(f->prm.device);
     drain_profile(f);
     out->pack_ms = f->ms[K_PACK]; out->query_ms = f->ms[K_QUERY]; out->compact_ms = f->ms[K_COMPACT];
-    out->build_ms = f->ms[K_BUILD] + f->ms[K_APPLY]; out->clear_ms = f->ms[K_CLEAR];
+    out->build_ms = f->ms[K_BUILD] + f->ms[K_SPLIT2] + f->ms[K_APPLY]; out->clear_ms = f->ms[K_CLEAR];
     out->build_apply_ms = f->ms[K_APPLY]; out->build_apply_launches = f->launches[K_APPLY];
+    out->build_split2_ms = f->ms[K_SPLIT2]; out->build_split2_launches = f->launches[K_SPLIT2];
     out->pack_launches = f->launches[K_PACK]; out->query_launches = f->launches[K_QUERY];
-    out->compact_launches = f->launches[K_COMPACT]; out->build_launches = f->launches[K_BUILD] + f->launches[K_APPLY];
+    out->compact_launches = f->launches[K_COMPACT]; out->build_launches = f->launches[K_BUILD] + f->launches[K_SPLIT2] + f->launches[K_APPLY];
     out->clear_launches = f->launches[K_CLEAR];
     out->query_lookups = 0;
     if (f->stats.p) {                                                  // all launches have drained above

@@ -67,7 +67,9 @@ struct BucketPlan {
     uint32_t n_super;      // level-1 buckets of a two-level split (regions / 32, rounded up); 1: single level
     uint32_t rec1_bytes;   // size of a level-1 record: 4, or 8 when R + 5 + 6 bits do not fit 32; 0: single level
     uint64_t cap;          // records per final bucket
-    uint64_t cap1;         // records per level-1 bucket (32 * cap); 0: single level
+    uint64_t cap1;         // records per level-1 bucket (8 * cap: a quarter of its 32 regions' buckets — level 2 empties
+                           // the level-1 buffer several times per sweep over the table); 0: single level
+    uint64_t bytes_per_record_x4;   // buffer bytes per record of final capacity, times 4
     uint64_t bytes_final;  // the record buffer holds the final buckets first, then the level-1 buckets
     uint64_t bytes_level1;
 };
@@ -81,7 +83,11 @@ cudaError_t launch_bucket_split(const HashParams& hp, uint64_t* filter, const ui
                                 const uint32_t* bin_ids, uint32_t n_seqs, uint64_t word_begin, uint64_t total_words,
                                 const BucketPlan& plan, void* records, unsigned long long* cursors, uint32_t counter_slot,
                                 cudaStream_t st);
-// level 2 (two-level plans) + apply + cursor reset; max_fill: upper bound of the records appended since the last apply
+// level 2 (two-level plans): super-buckets -> final buckets, resets the level-1 cursors; max_fill1: upper bound of the
+// records in the level-1 buffer
+cudaError_t launch_bucket_split2(uint64_t* filter, const BucketPlan& plan, void* records, unsigned long long* cursors,
+                                 uint64_t max_fill1, cudaStream_t st);
+// apply + cursor reset; max_fill: upper bound of the records appended since the last apply
 cudaError_t launch_bucket_apply(uint64_t* filter, uint64_t data_words, const BucketPlan& plan, void* records,
                                 unsigned long long* cursors, uint64_t max_fill, cudaStream_t st);
 

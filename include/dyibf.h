@@ -67,6 +67,8 @@ typedef struct dyibf_profile {
     uint64_t query_lookups;   /* k-mer lookups (h block fetches each) the query kernel performed while profiling was on */
     double   build_apply_ms;  /* the part of build_ms / build_launches spent in the bucketed build's apply sweeps */
     uint64_t build_apply_launches;
+    double   build_split2_ms; /* ... and in the second level of its radix split */
+    uint64_t build_split2_launches;
 } dyibf_profile;
 
 const char* dyibf_last_error(void);
@@ -173,7 +175,7 @@ int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64
  * k-mers left (count + remaining < threshold).  The rows are bit-identical to the full pass; only memory traffic
  * drops (e.g. 150 bp, k=18, e=3: ~57 % of the lookups). */
 #define DYIBF_OPT_EARLY_EXIT 1
-/* DYIBF_OPT_BUILD_BUCKET_MIB (default -1 = auto: what the call's updates need, up to 48 GiB, at most a third of the free HBM; 0 = off).  _insertKmer's
+/* DYIBF_OPT_BUILD_BUCKET_MIB (default -1 = auto: what the call's updates need, up to 64 GiB, at most half of the free HBM; 0 = off).  _insertKmer's
  * single-bit ORs land at uniformly random words of the table.  For tables larger than the L2 and calls with at least 32 M
  * updates, dyibf_add_sequences first appends the updates as 32-bit records to per-region buckets in a scratch buffer of
  * this size and then ORs them in region by region, so that DRAM sees streaming instead of random sector traffic.  The

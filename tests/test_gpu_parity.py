@@ -374,20 +374,22 @@ def test_bucketed_build_equals_direct_and_oracle(dy, oracle, log2_bits):
         else:
             f.addSequences((genomes.reshape(-1), off), ids)
         got = f.download_words()[:nd]
-        launches = f.profile()["build_launches"]
+        prof = f.profile()
         f.close()
-        return got, launches
+        return got, prof
 
-    direct, n0 = built(0)
-    assert np.array_equal(direct, want) and n0 == 1
-    auto, n1 = built(-1)
-    assert np.array_equal(auto, want) and n1 == 2                 # one split + one apply sweep
-    tiny, n2 = built(32)                                           # 32 MiB of records for 39 M updates: overflow path
-    assert np.array_equal(tiny, want) and n2 == 2
-    dev, n3 = built(96, device_mode=True)                          # device entry, several passes
-    assert np.array_equal(dev, want) and n3 >= 4
-    many, n4 = built(-1, chunk_mib=1)                              # 13 host chunks: scatter launches overlap on two streams
-    assert np.array_equal(many, want) and n4 >= 13
+    two_level = log2_bits > 32
+    direct, p0 = built(0)
+    assert np.array_equal(direct, want) and p0["build_launches"] == 1
+    auto, p1 = built(-1)                                           # everything in one sweep over the table
+    assert np.array_equal(auto, want) and p1["build_apply_launches"] == 1
+    assert (p1["build_split2_launches"] >= 1) == two_level
+    tiny, p2 = built(32)                                           # 32 MiB of records for 39 M updates: overflow path
+    assert np.array_equal(tiny, want) and p2["build_apply_launches"] >= 1
+    dev, p3 = built(96, device_mode=True)                          # device entry, several sweeps
+    assert np.array_equal(dev, want) and p3["build_apply_launches"] >= 2
+    many, p4 = built(-1, chunk_mib=1)                              # 13 host chunks: split launches overlap on two streams
+    assert np.array_equal(many, want) and p4["build_launches"] >= 14 and p4["build_apply_launches"] == 1
 
 
 def test_bucketed_build_wide_records_equals_direct(dy):
