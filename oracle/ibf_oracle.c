@@ -357,3 +357,61 @@ int ibf_load(const char *path, uint64_t *words, uint64_t nwords, ibf_params *p)
     ibf_get_metadata(words, nbits, &bins, &h, &k);
     return ibf_params_init(p, bins, h, k, nbits);
 }
+
+/* ---- reading sequence records (the step before the filter) ----------------------------------------------------
+ * readRecords(me.names, me.seqs, fileIn) (src/store_seqs.h:175-188, called by loadReads src/mapper.h:451) and the
+ * readRecord loop of addFastaFile (src/d_bloom_filter.h:127-147) over SeqAn's tokenizer:
+ * seqan seq_io/fasta_fastq.h:268-282 (Fasta), :302-345 (Fastq, qualities inside seq), sequence_file.h:340-343 (loop
+ * until atEnd), stream/tokenization.h:51-58 (IsInAlphabet), :145-149 (IsWhitespace = ' ' '\t' '\n' '\r'). */
+static int ibf_is_ws(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
+static int ibf_is_nl(unsigned char c) { return c == '\n' || c == '\r'; }
+
+/* IsInAlphabet<TValue>: convert<char>(TValue(c)) == toUpperValue(c).  Dna5Q (reads): ACGTN either case; Iupac (contigs
+ * of addFastaFile): the sixteen letters "UTAWCYMHGKRDSBVN" (alphabet_residue_tabs.h:58-62) either case. */
+int ibf_in_alphabet(unsigned char c, int iupac)
+{
+    unsigned char u = (c >= 'a' && c <= 'z') ? (unsigned char)(c - 32) : c;
+    if (!iupac) return u == 'A' || u == 'C' || u == 'G' || u == 'T' || u == 'N';
+    return u != 0 && strchr("UTAWCYMHGKRDSBVN", u) != NULL;
+}
+
+/* format 0 = Fasta, 1 = Fastq.  out_seqs receives the sequence characters as they stand in the text (ignored
+ * whitespace removed, case kept), limits[r] / limits[r+1] bracket record r.  Returns the number of records, -1 on a
+ * ParseError / UnexpectedEnd of the reference, -2 when an output capacity is exceeded. */
+int64_t ibf_parse_records(const char *text, uint64_t n, int format, int iupac, uint8_t *out_seqs, uint64_t cap_bytes,
+                          uint64_t *limits, uint64_t cap_seqs, uint64_t *n_bases)
+{
+    const unsigned char *t = (const unsigned char *)text;
+    const unsigned char begin = format ? '@' : '>';
+    uint64_t i = 0, nb = 0; int64_t nr = 0;
+    limits[0] = 0;
+    while (i < n) {                                            /* for (; !atEnd(file); ) readRecord(...) */
+        while (i < n && t[i] != begin) ++i;                    /* skipUntil(iter, TFastaBegin / TFastqBegin) */
+        if (i >= n) return -1;                                 /* skipOne at the end: UnexpectedEnd */
+        ++i;                                                   /* skipOne */
+        while (i < n && !ibf_is_nl(t[i])) ++i;                 /* readLine(meta): to the newline ... */
+        if (i < n) { if (t[i] == '\r' && i + 1 < n && t[i + 1] == '\n') ++i; ++i; }   /* ... and over "\r\n" / "\n" / "\r" */
+        if ((uint64_t)nr >= cap_seqs) return -2;
+        const unsigned char stop = format ? '+' : '>';
+        uint64_t len = 0;
+        for (; i < n && t[i] != stop; ++i) {                   /* readUntil(seq, iter, stop, IgnoreOrAssert) */
+            if (ibf_is_ws(t[i])) continue;
+            if (!ibf_in_alphabet(t[i], iupac)) return -1;      /* AssertFunctor<IsInAlphabet>: ParseError */
+            if (nb >= cap_bytes) return -2;
+            out_seqs[nb++] = t[i]; ++len;
+        }
+        if (format) {
+            if (i >= n) return -1;                             /* skipOne(iter, '+') at the end: UnexpectedEnd */
+            ++i;
+            while (i < n && !ibf_is_nl(t[i])) ++i;             /* skipLine */
+            if (i < n) { if (t[i] == '\r' && i + 1 < n && t[i + 1] == '\n') ++i; ++i; }
+            uint64_t left = len;                               /* CountDownFunctor<Not<IsWhitespace>>(length(seq)) */
+            for (; i < n && left; ++i) if (!ibf_is_ws(t[i])) --left;
+            while (i < n && ibf_is_ws(t[i])) ++i;              /* skipUntil(NotFunctor<IsWhitespace>) */
+            if (i < n && t[i] != '@') return -1;               /* "quality string is expected to be of the same length" */
+        }
+        limits[++nr] = nb;
+    }
+    *n_bases = nb;
+    return nr;
+}

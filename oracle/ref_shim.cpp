@@ -182,4 +182,43 @@ void ref_classify(void* f, const uint8_t* seqs, const uint64_t* offsets, uint32_
     for (auto&& t : tasks) t.get();
 }
 
+// readRecords(me.names, me.seqs, fileIn) exactly as the mapper's loadReads drives it (src/store_seqs.h:175-188 with
+// SeqConfig: Dna5Q, ConcatDirect; src/mapper.h:451), or — iupac != 0 — the readRecord loop of addFastaFile
+// (src/d_bloom_filter.h:127-147: IupacString records, implicitly converted to Dna5 for addKmers; records shorter
+// than k are NOT dropped here).  Output: Dna5 codes of all records + limits.  Returns the number of records, -1 when
+// SeqAn throws (ParseError / UnexpectedEnd), -2 when a capacity is exceeded, -3 when the file cannot be opened.
+int64_t ref_read_records(const char* path, int iupac, uint8_t* codes, uint64_t cap_bytes, uint64_t* limits, uint64_t cap_seqs,
+                         uint64_t* n_bases)
+{
+    SeqFileIn in;
+    if (!open(in, path)) return -3;
+    uint64_t nb = 0; int64_t nr = 0;
+    limits[0] = 0;
+    try {
+        if (iupac) {
+            CharString id; IupacString seq;
+            while (!atEnd(in)) {
+                readRecord(id, seq, in);
+                Dna5String d = seq;
+                if ((uint64_t)nr >= cap_seqs || nb + length(d) > cap_bytes) return -2;
+                for (uint64_t i = 0; i < length(d); ++i) codes[nb++] = ordValue(d[i]);
+                limits[++nr] = nb;
+            }
+        } else {
+            SeqStore<void, SeqConfig<void> > store;
+            readRecords(store, in);
+            nr = length(store.seqs);
+            if ((uint64_t)nr > cap_seqs || lengthSum(store.seqs) > cap_bytes) return -2;
+            for (int64_t r = 0; r < nr; ++r) {
+                for (uint64_t i = 0; i < length(store.seqs[r]); ++i) codes[nb++] = ordValue(Dna5(store.seqs[r][i]));
+                limits[r + 1] = nb;
+            }
+        }
+    } catch (seqan::Exception const&) {
+        return -1;
+    }
+    *n_bases = nb;
+    return nr;
+}
+
 } // extern "C"
