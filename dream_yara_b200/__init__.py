@@ -6,5 +6,6 @@ multi-GPU shardings (dist.py).  Nothing in this package has a CPU implementation
 """
 from ._lib import ENC_ASCII, ENC_DNA5, ENC_DNA5Q, DyibfError, lib          # noqa: F401
 from .ibf import SeqAnBloomFilter, as_batch, read_fasta                    # noqa: F401
+from .ingest import parseRecords, readRecords                               # noqa: F401
 from .mapper import (DisOptions, ReadSet, clasifyLoadedReads, loadFilteredReads, readFilterMetadata,  # noqa: F401
-                     sortedBins)
+                     sortedBins, loadReads)

@@ -9,6 +9,8 @@ LIB_PATH = os.path.join(HERE, "libdyibf.so")
 OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_FORMAT, ERR_SIZE_MISMATCH, ERR_CAPACITY, ERR_NOMEM = 0, -1, -2, -3, -4, -5, -6, -7
 ENC_DNA5, ENC_DNA5Q, ENC_ASCII = 0, 1, 2
 MEM_HOST, MEM_DEVICE = 0, 1
+FMT_FASTA, FMT_FASTQ = 0, 1
+ALPHA_DNA5, ALPHA_IUPAC = 0, 1
 MAX_HASH = 8
 OPT_EARLY_EXIT = 1
 OPT_BUILD_BUCKET_MIB = 2
@@ -60,6 +62,8 @@ SYMBOLS = {
     "dyibf_sorted_bins": (C.c_int, [_U64P, C.c_uint32, _U32P]),
     "dyibf_gather_reads": (C.c_int, [_P, C.c_uint32, _U8P, C.c_uint64, _U64P, _U32P, C.c_uint64,
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "dyibf_parse_records": (C.c_int, [C.c_int, _P, C.c_uint64, C.c_int, C.c_int, _U8P, C.c_uint64, _U64P, C.c_uint64, C.c_uint64,
+                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int, _P]),
     "dyibf_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
     "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),

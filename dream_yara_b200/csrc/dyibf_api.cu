@@ -804,6 +804,78 @@ int dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_
     return DYIBF_OK;
 }
 
+/* ---- ingest: SeqAn's readRecords on the device (ingest_kernel.cu) ---------------------------------------- */
+int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int format, int alphabet, uint8_t* out_seqs,
+                        uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs, uint64_t limit_base,
+                        uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream)
+{
+    if (!n_seqs || !n_bases) return fail(DYIBF_ERR_ARG, "dyibf_parse_records: NULL size output");
+    if ((format != DYIBF_FMT_FASTA && format != DYIBF_FMT_FASTQ) || (alphabet != DYIBF_ALPHA_DNA5 && alphabet != DYIBF_ALPHA_IUPAC) ||
+        (mem != DYIBF_MEM_HOST && mem != DYIBF_MEM_DEVICE) || (n_bytes && !text))
+        return fail(DYIBF_ERR_ARG, "dyibf_parse_records: bad format / alphabet / mem / text");
+    *n_seqs = 0; *n_bases = 0;
+    const bool sizing = !out_seqs && !out_limits;
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(DYIBF_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+    cudaStream_t st = (cudaStream_t)stream;
+    struct Tmp {                                              // scratch of this call
+        void* p[4] = {nullptr, nullptr, nullptr, nullptr};
+        ~Tmp() { for (void* q : p) if (q) cudaFree(q); }
+    } tmp;
+    if (n_bytes == 0) {                                       // readRecords on an empty file: no records
+        if (sizing) return DYIBF_OK;
+        if (!out_limits) return fail(DYIBF_ERR_ARG, "dyibf_parse_records: NULL out_limits");
+        if (mem == DYIBF_MEM_HOST) { out_limits[0] = limit_base; return DYIBF_OK; }
+        CU(cudaMemcpyAsync(out_limits, &limit_base, 8, cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));
+        return DYIBF_OK;
+    }
+    const uint8_t* d_text = reinterpret_cast<const uint8_t*>(text);
+    if (mem == DYIBF_MEM_HOST) {
+        CU(cudaMalloc(&tmp.p[0], n_bytes));
+        CU(cudaMemcpyAsync(tmp.p[0], text, n_bytes, cudaMemcpyHostToDevice, st));
+        d_text = static_cast<const uint8_t*>(tmp.p[0]);
+    }
+    CU(cudaMalloc(&tmp.p[1], ingest_workspace_bytes(n_bytes)));
+    uint64_t* ws = static_cast<uint64_t*>(tmp.p[1]);
+    const int iupac = alphabet == DYIBF_ALPHA_IUPAC;
+    CU(launch_ingest_count(d_text, n_bytes, format, iupac, ws, st));
+    uint64_t tot[6];
+    CU(ingest_read_totals(ws, n_bytes, tot, st));
+    static const char* const what[] = {"", "character outside the sequence alphabet", "not in the four-line FASTQ layout",
+                                       "quality string and sequence differ in length", "truncated FASTQ record"};
+    auto format_error = [&](uint64_t word) {
+        const uint64_t pos = word >> 8; const unsigned code = (unsigned)(word & 0xff);
+        return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: %s at byte %llu", code < 5 ? what[code] : "parse error", (unsigned long long)pos);
+    };
+    if (format == DYIBF_FMT_FASTA && tot[3] == ~0ull)
+        return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: no '>' in a non-empty FASTA text (SeqAn: UnexpectedEnd)");
+    if (format == DYIBF_FMT_FASTQ && tot[4] == 0)
+        return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: no '@' in a non-empty FASTQ text (SeqAn: UnexpectedEnd)");
+    if (tot[5] != ~0ull) return format_error(tot[5]);
+    *n_seqs = tot[0]; *n_bases = tot[1];
+    if (sizing && format == DYIBF_FMT_FASTA) return DYIBF_OK;             // FASTQ: the length checks run in the last pass
+    if (!sizing && (!out_limits || (tot[1] && !out_seqs))) return fail(DYIBF_ERR_ARG, "dyibf_parse_records: NULL output");
+    if (!sizing && (tot[0] > capacity_seqs || tot[1] > capacity_bytes))
+        return fail(DYIBF_ERR_CAPACITY, "dyibf_parse_records: %llu records / %llu sequence characters do not fit the output buffers",
+                    (unsigned long long)tot[0], (unsigned long long)tot[1]);
+    uint8_t* d_seqs = out_seqs; uint64_t* d_limits = out_limits;
+    if (mem == DYIBF_MEM_HOST || sizing) {
+        CU(cudaMalloc(&tmp.p[2], tot[1] + 16));
+        CU(cudaMalloc(&tmp.p[3], (tot[0] + 1) * 8));
+        d_seqs = static_cast<uint8_t*>(tmp.p[2]); d_limits = static_cast<uint64_t*>(tmp.p[3]);
+    }
+    CU(launch_ingest_emit(d_text, n_bytes, format, iupac, ws, d_seqs, d_limits, limit_base, tot[0], tot[1], st));
+    CU(ingest_read_totals(ws, n_bytes, tot, st));
+    if (tot[5] != ~0ull) { *n_seqs = 0; *n_bases = 0; return format_error(tot[5]); }
+    if (mem == DYIBF_MEM_HOST && !sizing) {
+        if (tot[1]) CU(cudaMemcpyAsync(out_seqs, d_seqs, tot[1], cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(out_limits, d_limits, (tot[0] + 1) * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    return DYIBF_OK;
+}
+
 } // extern "C"
 
 // ============================================================================================================

@@ -121,4 +121,13 @@ cudaError_t launch_gather_plan(const GatherArgs& a, uint64_t* lens, uint32_t* ou
 // pass 2: copy / reverse-complement into out_bytes at limits[j]
 cudaError_t launch_gather_copy(const GatherArgs& a, const uint64_t* limits, uint8_t* out_bytes, cudaStream_t st);
 
+// ingest (ingest_kernel.cu): FASTA / FASTQ text -> sequence characters + limits, SeqAn's readRecords on the device
+size_t      ingest_workspace_bytes(uint64_t n_bytes);
+cudaError_t launch_ingest_count(const uint8_t* text, uint64_t n, int format, int iupac, uint64_t* ws, cudaStream_t st);
+// totals: records, sequence characters, quality characters, first '>' offset, effective end, first error word
+// (offset << 8 | code; all ones = none); synchronises the stream
+cudaError_t ingest_read_totals(const uint64_t* ws, uint64_t n, uint64_t totals[6], cudaStream_t st);
+cudaError_t launch_ingest_emit(const uint8_t* text, uint64_t n, int format, int iupac, uint64_t* ws, uint8_t* out_seqs,
+                               uint64_t* out_limits, uint64_t limit_base, uint64_t n_records, uint64_t n_bases, cudaStream_t st);
+
 } // namespace dyibf

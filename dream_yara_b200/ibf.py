@@ -60,27 +60,12 @@ def as_batch(seqs, encoding=None):
     return concat, offsets, ENC_DNA5 if enc is None else enc
 
 
-def read_fasta(path):
-    """Records of a FASTA/FASTQ(.gz) file as ASCII byte strings (what SeqFileIn::readRecord yields)."""
-    opener = gzip.open if str(path).endswith(".gz") else open
-    with opener(path, "rb") as fh:
-        data = fh.read()
-    recs = []
-    if data[:1] == b"@":                                   # FASTQ: 4-line records
-        lines = data.split(b"\n")
-        i = 0
-        while i + 1 < len(lines):
-            if lines[i].startswith(b"@"):
-                recs.append(lines[i + 1].strip())
-                i += 4
-            else:
-                i += 1
-        return recs
-    for chunk in data.split(b">")[1:]:
-        nl = chunk.find(b"\n")
-        body = chunk[nl + 1:] if nl >= 0 else b""
-        recs.append(body.replace(b"\n", b"").replace(b"\r", b"").replace(b" ", b""))
-    return recs
+def read_fasta(path, iupac=True, device=0):
+    """Records of a FASTA/FASTQ(.gz) file as ASCII byte strings (what SeqFileIn::readRecord yields); tokenised on the
+    device (ingest.readRecords)."""
+    from .ingest import readRecords
+    cat, lim = readRecords(path, iupac=iupac, device=device)
+    return [cat[int(lim[i]):int(lim[i + 1])].tobytes() for i in range(lim.size - 1)]
 
 
 class SeqAnBloomFilter:
@@ -155,13 +140,14 @@ class SeqAnBloomFilter:
 
     def addFastaFile(self, fastaFile, binNo):
         """addFastaFile, :127-147: every record of the file (len >= k) goes to bin `binNo`."""
+        from .ingest import readRecords
         try:
-            recs = read_fasta(fastaFile)
+            cat, lim = readRecords(fastaFile, iupac=True, device=self.device)
         except OSError:
             raise RuntimeError("Unable to open contigs File: %s" % fastaFile)   # reference: throw const char*
-        recs = [r for r in recs if len(r) >= self._kmerSize]
-        if recs:
-            self.addSequences(recs, [binNo] * len(recs), encoding=ENC_ASCII)
+        n = lim.size - 1
+        if n:                                                # records shorter than k are skipped by the build (:142)
+            self.addSequences((cat if cat.size else np.zeros(1, np.uint8), lim), np.full(n, binNo, dtype=np.uint32), encoding=ENC_ASCII)
 
     def clearBins(self, bins2clear, threadsCount=1):
         """clearBins, :99-123 (threadsCount is accepted and ignored: the GPU does the pass)."""

@@ -53,6 +53,25 @@ class ReadSet:
         return len(self) // 4
 
 
+def loadReads(readsFile, matesFile=None, device=0):
+    """loadReads (src/mapper.h:444-469) for the filter's purposes: the forward read set of one or two FASTA / FASTQ
+    (.gz) files, tokenised on the device (SeqAn's readRecords, ingest.py); paired-end files become [mates 1 | mates 2]
+    as readRecords(records, pair) leaves them (src/file_pair.h:82-88).  The reverse complements the reference appends
+    next (appendReverseComplement) are derived on the GPU by the query (ReadSet rc=False)."""
+    from .ingest import readRecords
+    from ._lib import ENC_ASCII
+    cat, lim = readRecords(readsFile, device=device)
+    if matesFile is not None:
+        cat2, lim2 = readRecords(matesFile, device=device)
+        if lim2.size != lim.size:
+            raise ValueError("the two read files hold %d and %d records" % (lim.size - 1, lim2.size - 1))
+        cat = np.concatenate([cat, cat2])
+        lim = np.concatenate([lim, lim2[1:] + lim[-1]])
+    if cat.size == 0:
+        cat = np.zeros(1, dtype=np.uint8)
+    return ReadSet((cat, lim), paired=matesFile is not None, rc=False, encoding=ENC_ASCII)
+
+
 class DisOptions:
     """The fields of DisOptions/Options the filtering stage reads (d_mapper.h:49-94, mapper.h:49-131)."""
 

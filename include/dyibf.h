@@ -166,6 +166,29 @@ int  dyibf_sorted_bins(const uint64_t* bin_offsets, uint32_t bins, uint32_t* out
 int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_t capacity_bytes, uint64_t* out_limits,
                         uint32_t* out_ids, uint64_t capacity_seqs, uint64_t* n_seqs_out, uint64_t* n_bytes_out);
 
+/* ---- ingest -------------------------------------------------------------------------------- */
+
+#define DYIBF_FMT_FASTA   0
+#define DYIBF_FMT_FASTQ   1
+#define DYIBF_ALPHA_DNA5  0   /* reads: SeqAn target Dna5Q, valid characters ACGTN (either case)                  */
+#define DYIBF_ALPHA_IUPAC 1   /* contigs of addFastaFile: target IupacString, valid the 16 IUPAC letters           */
+
+/* readRecords(me.names, me.seqs, fileIn) of loadReads (src/mapper.h:451, src/store_seqs.h:175-188) and the readRecord
+ * loop of addFastaFile (d_bloom_filter.h:127-147), i.e. SeqAn's FASTA / FASTQ tokenizer (seq_io/fasta_fastq.h:268-345),
+ * on the device: `text` (n_bytes of an uncompressed FASTA or FASTQ file, or of a chunk that holds whole records) ->
+ * the sequence characters of all records with whitespace removed (out_seqs, case kept: feed them to dyibf_query_batch /
+ * dyibf_add_sequences with DYIBF_ENC_ASCII) and out_limits[n_seqs + 1] = limit_base + the start of every record
+ * (a ConcatDirect StringSet's limits).  Ids and qualities are not extracted: the filter does not read them.
+ * *n_seqs / *n_bases always receive the sizes; out_seqs == NULL and out_limits == NULL is a sizing call.
+ * Errors: DYIBF_ERR_FORMAT where SeqAn throws (a character outside the alphabet, no record in a non-empty text, a
+ * FASTQ quality string whose length differs from its sequence's) — and for FASTQ that is not in the four-line layout
+ * (sequence / qualities wrapped over several lines, blank lines between records), which SeqAn's sequential reader
+ * accepts and this parser refuses rather than mis-parses; DYIBF_ERR_CAPACITY when an output buffer is too small.
+ * mem says where text, out_seqs and out_limits live (all three on the same side). */
+int  dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int format, int alphabet,
+                         uint8_t* out_seqs, uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs,
+                         uint64_t limit_base, uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream);
+
 /* ---- options ------------------------------------------------------------------------------- */
 
 /* DYIBF_OPT_EARLY_EXIT (default 0).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it

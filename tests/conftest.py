@@ -28,6 +28,12 @@ def gather_golden():
 
 
 @pytest.fixture(scope="session")
+def ingest_golden():
+    """FASTA / FASTQ record-reader vectors from the unmodified reference (tests/golden/make_golden_ingest.py)."""
+    return np.load(os.path.join(HERE, "golden", "ingest_vectors.npz"))
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle_py import Oracle
     return Oracle()

@@ -67,6 +67,9 @@ class Oracle:
         l.ibf_revcomp_dna5q.argtypes = [_V, C.c_uint64, _V]
         l.ibf_load_filtered_reads.restype = C.c_uint64
         l.ibf_load_filtered_reads.argtypes = [_V, _V, C.c_uint32, C.c_int, _V, C.c_uint32, _V, _V, _V]
+        l.ibf_parse_records.restype = C.c_int64
+        l.ibf_parse_records.argtypes = [C.c_char_p, C.c_uint64, C.c_int, C.c_int, _V, C.c_uint64, _V, C.c_uint64,
+                                        C.POINTER(C.c_uint64)]
 
     def params(self, bins, h, k, nbits):
         p = IbfParams()
@@ -169,6 +172,18 @@ class Oracle:
         assert n == n_out
         return ob[: int(ol[n_out])], ol, oi[:n_out]
 
+    def parse_records(self, text, fmt, iupac=False):
+        """SeqAn's readRecords over FASTA (fmt 0) / FASTQ (fmt 1) text -> (sequence characters, limits), or None where
+        the reference throws a ParseError / UnexpectedEnd."""
+        text = bytes(text)
+        seqs = np.zeros(max(len(text), 1), dtype=np.uint8)
+        limits = np.zeros(len(text) + 2, dtype=np.uint64)
+        nb = C.c_uint64(0)
+        n = self.l.ibf_parse_records(text, len(text), fmt, int(iupac), _p(seqs), seqs.size, _p(limits), len(text) + 1, C.byref(nb))
+        if n < 0:
+            return None
+        return seqs[: nb.value].copy(), limits[: n + 1].copy()
+
     def clear_bins(self, words, p, bins):
         b = np.ascontiguousarray(bins, dtype=np.uint32)
         self.l.ibf_clear_bins(_p(words), C.byref(p), _p(b), b.size)
@@ -228,6 +243,9 @@ class Ref:
         l.ref_revcomp.argtypes = [_V, C.c_uint64, _V]
         l.ref_ascii_to_dna5.argtypes = [C.c_char_p, C.c_uint64, _V]
         l.ref_classify.argtypes = [_V, _V, _V, C.c_uint32, C.c_int, C.c_uint16, C.c_uint32, _V]
+        if hasattr(l, "ref_read_records"):
+            l.ref_read_records.restype = C.c_int64
+            l.ref_read_records.argtypes = [C.c_char_p, C.c_int, _V, C.c_uint64, _V, C.c_uint64, C.POINTER(C.c_uint64)]
 
     def new(self, bins, h, k, nbits):
         return self.l.ref_new(bins, h, k, nbits)
@@ -280,6 +298,19 @@ class Ref:
         out = np.zeros(max(len(text), 1), dtype=np.uint8)
         self.l.ref_ascii_to_dna5(text, len(text), _p(out))
         return out[: len(text)]
+
+    def read_records(self, path, iupac=False):
+        """SeqAn's own reader on a file (extension selects the format): (Dna5 codes, limits), or None where it throws."""
+        size = os.path.getsize(path)
+        codes = np.zeros(max(size, 1), dtype=np.uint8)
+        limits = np.zeros(size + 2, dtype=np.uint64)
+        nb = C.c_uint64(0)
+        n = self.l.ref_read_records(str(path).encode(), int(iupac), _p(codes), codes.size, _p(limits), size + 1, C.byref(nb))
+        if n == -3:
+            raise OSError("cannot open %s" % path)
+        if n < 0:
+            return None
+        return codes[: nb.value].copy(), limits[: n + 1].copy()
 
     def classify(self, f, concat, offsets, paired, threshold, threads, W):
         concat = np.ascontiguousarray(concat, dtype=np.uint8)

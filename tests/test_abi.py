@@ -74,12 +74,3 @@ def test_host_mirror_helpers(dy):
     assert enc == dy.ENC_DNA5 and list(off) == [0, 3, 3]
     rs = dy.ReadSet(["ACGT", "TTTT"], paired=True)
     assert len(rs) == 4 and rs.getReadsCount() == 2 and rs.getPairsCount() == 1 and rs.lengthSum() == 16
-
-
-def test_fasta_reader(dy, tmp_path):
-    p = tmp_path / "x.fa"
-    p.write_text(">a desc\nACGT\nNNRY\n>b\n\n>c\nTTTT\n")
-    assert dy.read_fasta(p) == [b"ACGTNNRY", b"", b"TTTT"]
-    q = tmp_path / "x.fq"
-    q.write_text("@r1\nACGT\n+\nIIII\n@r2\nGGCC\n+\nIIII\n")
-    assert dy.read_fasta(q) == [b"ACGT", b"GGCC"]

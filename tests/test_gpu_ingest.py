@@ -1,0 +1,115 @@
+"""GPU (B200): dyibf_parse_records — SeqAn's FASTA / FASTQ record reader on the device — against the oracle's restatement
+and the golden vectors of the unmodified reference, and the chain text -> parse -> filter."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import ka
+from ingest_cases import ASCII_TO_DNA5, cases
+
+pytestmark = pytest.mark.gpu
+
+CASES = cases()
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_device_reader_vs_oracle_and_reference(dy, oracle, ingest_golden, case):
+    name, fmt, iupac, text, device_ok = case
+    want = oracle.parse_records(text, fmt, iupac)
+    if want is None or not device_ok:
+        with pytest.raises(dy.DyibfError) as ei:
+            dy.parseRecords(text, fmt, iupac=iupac)
+        assert ei.value.code == -4                                   # DYIBF_ERR_FORMAT
+        return
+    seqs, limits = dy.parseRecords(text, fmt, iupac=iupac)
+    assert np.array_equal(seqs, want[0]) and np.array_equal(limits, want[1])
+    assert np.array_equal(ASCII_TO_DNA5[seqs], ingest_golden[name + "_codes"])
+    assert np.array_equal(limits, ingest_golden[name + "_limits"])
+    if text:
+        from dream_yara_b200.ingest import countRecords
+        assert countRecords(text, fmt, iupac=iupac) == (limits.size - 1, seqs.size)
+
+
+def test_device_reader_random_texts(dy, oracle):
+    """tile boundaries everywhere: random record lengths, line widths, CRLF, ids with '>' '@' '+', qualities with
+    every printable character; sizes from a few bytes to several tiles"""
+    rng = np.random.default_rng(99)
+    for t in range(60):
+        fq = t % 2
+        crlf = b"\r\n" if t % 3 == 0 else b"\n"
+        recs = []
+        for i in range(int(rng.integers(1, 400 if t > 20 else 12))):
+            n = int(rng.integers(0, 400))
+            s = bytes(rng.choice(np.frombuffer(b"ACGTNacgtn", dtype=np.uint8), n).tobytes())
+            if fq:
+                q = bytes(rng.integers(33, 127, n, dtype=np.uint8).tobytes())
+                recs.append(b"@r%d +@> \t x" % i + crlf + s + crlf + b"+" + (b"r%d" % i if i % 2 else b"") + crlf + q + crlf)
+            else:
+                w = int(rng.integers(1, 90))
+                recs.append(b">r%d > @ + x" % i + crlf + crlf.join(s[j:j + w] for j in range(0, n, w)) + crlf)
+        text = b"".join(recs)
+        if t % 5 == 0:
+            text = text.rstrip()                                     # no trailing newline
+        want = oracle.parse_records(text, fq)
+        assert want is not None
+        seqs, limits = dy.parseRecords(text, fq)
+        assert np.array_equal(limits, want[1]), "case %d" % t
+        assert np.array_equal(seqs, want[0]), "case %d" % t
+
+
+def test_device_reader_first_error_offset(dy):
+    text = b">r1\nACGT\n>r2\nAC" + b"G" * 9000 + b"X" + b"ACGT" * 3000 + b"-\n"
+    with pytest.raises(dy.DyibfError) as ei:
+        dy.parseRecords(text, 0)
+    assert "at byte %d" % text.index(b"X") in str(ei.value)
+    with pytest.raises(dy.DyibfError) as ei:
+        dy.parseRecords(b"@r\nACGT\n+\nIII\n@r2\nAC\n+\nII\n", 1)
+    assert ei.value.code == -4 and "differ in length" in str(ei.value)
+
+
+def test_device_reader_device_memory_limit_base_and_capacity(dy):
+    import torch
+    from dream_yara_b200.ingest import parseRecordsDevice
+    L = dy.lib()
+    text = b"".join(b"@r%d\n%s\n+\n%s\n" % (i, b"ACGTN" * (i % 40), b"I" * (5 * (i % 40))) for i in range(3000))
+    want_seqs, want_limits = dy.parseRecords(text, 1)
+    d_text = torch.frombuffer(bytearray(b"\0" + text), dtype=torch.uint8).cuda()[1:]      # a mis-aligned device pointer
+    d_seqs = torch.zeros(want_seqs.size + 8, dtype=torch.uint8, device="cuda")
+    d_lim = torch.zeros(want_limits.size, dtype=torch.int64, device="cuda")
+    n, nb = parseRecordsDevice(d_text.data_ptr(), len(text), 1, d_seqs.data_ptr(), d_seqs.numel(), d_lim.data_ptr(),
+                               d_lim.numel() - 1, limit_base=1000)
+    assert (n, nb) == (want_limits.size - 1, want_seqs.size)
+    assert np.array_equal(d_seqs.cpu().numpy()[:nb], want_seqs)
+    assert np.array_equal(d_lim.cpu().numpy().view(np.uint64), want_limits + np.uint64(1000))
+    ns, nbb = C.c_uint64(), C.c_uint64()
+    rc = L.dyibf_parse_records(0, C.c_void_p(d_text.data_ptr()), len(text), 1, 0, C.c_void_p(d_seqs.data_ptr()), 10,
+                               C.c_void_p(d_lim.data_ptr()), d_lim.numel() - 1, 0, C.byref(ns), C.byref(nbb), 1, None)
+    assert rc == -6 and (ns.value, nbb.value) == (n, nb)              # DYIBF_ERR_CAPACITY, sizes reported
+
+
+def test_text_to_bins_end_to_end(dy, golden, tmp_path):
+    """FASTA text of the reference's 64 viral genomes and 6400 test reads -> device reader -> build + classify: the
+    reference's own gold md5 and its per-read bin sets (KA1), and loadReads / addFastaFile of the host mirror."""
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    f = dy.SeqAnBloomFilter(64, 2, 19, ka.GIB_BITS)
+    for b, g in enumerate(genomes):                                   # one FASTA file per bin, 70 columns, as build_filter reads them
+        p = tmp_path / ("%d.fa" % b)
+        p.write_bytes(b">genome %d\n" % b + b"\n".join(g[j:j + 70] for j in range(0, len(g), 70)) + b"\n")
+        f.addFastaFile(str(p), b)
+    assert ka.md5_filter_words(f.download_words(), f._noOfBits) == str(golden["reference_gold_md5"])
+    rp = tmp_path / "reads.fa"
+    rp.write_bytes(b"".join(b">read.%d\n%s\n" % (i, r) for i, r in enumerate(reads)))
+    rs = dy.loadReads(str(rp))
+    assert rs.getReadsCount() == 6400 and not rs.paired
+    rows = f.whichBinsBatch((rs.concat, rs.offsets), 25, group=2, derive_rc=True, encoding=rs.encoding)
+    assert np.array_equal(rows, golden["ka1_rows"])
+    q1, q2 = tmp_path / "m1.fq", tmp_path / "m2.fq"
+    q1.write_bytes(b"".join(b"@p%d/1\n%s\n+\n%s\n" % (i, r, b"I" * len(r)) for i, r in enumerate(reads[:3200])))
+    q2.write_bytes(b"".join(b"@p%d/2\n%s\n+\n%s\n" % (i, r, b"@" * len(r)) for i, r in enumerate(reads[3200:])))
+    pe = dy.loadReads(str(q1), str(q2))
+    assert pe.paired and pe.getPairsCount() == 3200
+    rows_pe = f.whichBinsBatch((pe.concat, pe.offsets), 25, group=4, derive_rc=True, encoding=pe.encoding)
+    assert np.array_equal(rows_pe, golden["ka1_rows"][:3200] | golden["ka1_rows"][3200:])
+    assert dy.read_fasta(rp, iupac=False)[:2] == reads[:2]
+    f.close()
