@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--read-len", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-ingest", action="store_true", help="skip the extra device FASTQ-reader measurement (cfg2)")
     ap.add_argument("--no-early-exit", action="store_true", help="skip the extra DYIBF_OPT_EARLY_EXIT measurement")
     a = ap.parse_args()
     a.paired = a.workload == "cfg3"
@@ -430,6 +431,46 @@ def run_b200(args):
         f.set_early_exit(False)
         del full_rows
 
+    # ---- extra: the step in front of the filter — FASTQ text of the first reads -> sequences, on the device
+    ingest = None
+    if args.workload == "cfg2" and not args.no_ingest:
+        from dream_yara_b200.ingest import parseRecordsDevice
+        n_ing = min(n, 2_000_000)
+        rec = np.empty((n_ing, 2 * RL + 7), dtype=np.uint8)                  # "@r\n" seq "\n+\n" qual "\n"
+        rec[:, 0:3] = np.frombuffer(b"@r\n", dtype=np.uint8)
+        rec[:, 3:3 + RL] = np.frombuffer(b"ACGTN", dtype=np.uint8)[np.minimum(h_reads[:n_ing], 4)]
+        rec[:, 3 + RL:6 + RL] = np.frombuffer(b"\n+\n", dtype=np.uint8)
+        rec[:, 6 + RL:6 + 2 * RL] = ord("I")
+        rec[:, 6 + 2 * RL] = ord("\n")
+        d_text = torch.from_numpy(rec.reshape(-1)).to(dev)
+        d_seq_out = torch.empty(n_ing * RL + 16, dtype=torch.uint8, device=dev)
+        d_lim_out = torch.empty(n_ing + 1, dtype=torch.int64, device=dev)
+        def ingest_step():
+            return parseRecordsDevice(d_text.data_ptr(), d_text.numel(), 1, d_seq_out.data_ptr(), d_seq_out.numel(),
+                                      d_lim_out.data_ptr(), n_ing, device=local, stream=stream)
+        for _ in range(2):
+            got = ingest_step()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            ingest_step()
+        e1.record()
+        barrier()
+        ing_ms = e0.elapsed_time(e1) / args.steps
+        lut = torch.full((256,), 4, dtype=torch.uint8, device=dev)
+        for ch, v in ((b"Aa", 0), (b"Cc", 1), (b"Gg", 2), (b"Tt", 3)):
+            for b_ in ch:
+                lut[b_] = v
+        same = got == (n_ing, n_ing * RL) and bool(torch.equal(lut[d_seq_out[:n_ing * RL].long()], d_reads[:n_ing * RL].clamp(max=4))) \
+            and bool(torch.equal(d_lim_out, torch.arange(n_ing + 1, dtype=torch.int64, device=dev) * RL))
+        if not same:
+            raise AssertionError("device FASTQ reader output differs from the reads it was written from")
+        ingest = {"value": n_ing / (ing_ms / 1e3), "unit": "reads/s", "text_gbs": d_text.numel() / (ing_ms / 1e3) / 1e9,
+                  "ms": ing_ms, "reads": n_ing, "text_bytes": int(d_text.numel()), "output_equal_reads": True,
+                  "note": "dyibf_parse_records (FASTQ, device-resident text of the first reads of the workload -> sequence "
+                          "characters + limits, 5 passes incl. per-call scratch allocation); not part of value/e2e"}
+        del d_text, d_seq_out, d_lim_out, rec
+
     # ---- roofline of the dominant kernel (query) against the measured HBM peak
     bytes_per_read = algorithmic_bytes_per_read(bins, RL, paired)
     peak, peak_src = measured_peak()
@@ -502,7 +543,7 @@ def run_b200(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
                 "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
-                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "impl": "b200"}
+                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "ingest": ingest, "impl": "b200"}
         if sweep is not None:
             line["e_sweep"] = sweep
         print(json.dumps(line), flush=True)
