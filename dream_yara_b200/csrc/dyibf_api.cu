@@ -100,7 +100,8 @@ int init_params(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, dyibf_par
 {
     // _init, d_bloom_filter.h:245-254
     if (bins == 0) return fail(DYIBF_ERR_ARG, "number of bins must be > 0");
-    if (h == 0 || h > DYIBF_MAX_HASH) return fail(DYIBF_ERR_ARG, "number of hash functions %u not in 1..%d", h, DYIBF_MAX_HASH);
+    // h == 0: a kmer_direct filter (SeqAnKDXFilter::_init, d_kdx_filter.h:212-217; its trailer has no hash count :234-239)
+    if (h > DYIBF_MAX_HASH) return fail(DYIBF_ERR_ARG, "number of hash functions %u not in 0..%d", h, DYIBF_MAX_HASH);
     if (k == 0 || k > 32) return fail(DYIBF_ERR_ARG, "k-mer size %u not in 1..32", k);
     uint32_t W = (uint32_t)std::ceil((float)bins / 64.0f);           // std::ceil((float)_noOfBins / INT_WIDTH)
     if (W > 65535) return fail(DYIBF_ERR_ARG, "%u bins need %u words per block; _binIntWidth is 16 bit", bins, W);
@@ -115,7 +116,8 @@ int init_params(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, dyibf_par
     for (uint32_t i = 0; i < h; ++i) hp->pre[i] = (uint64_t)i ^ ((uint64_t)k * SEED);
     hp->P = P; hp->pow2 = (P & (P - 1)) == 0;
     hp->magic = hp->pow2 ? 0 : (uint64_t)((((unsigned __int128)1) << 64) / P);
-    hp->h = h; hp->k = k; hp->W = W; hp->bins = bins;
+    hp->h = h ? h : 1; hp->k = k; hp->W = W; hp->bins = bins;
+    hp->direct = h == 0; hp->sink = P;
     return DYIBF_OK;
 }
 
@@ -137,11 +139,17 @@ int new_handle(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, int device
     f->data_words = prm.n_blocks * prm.words_per_block;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) f->sm_count = prop.multiProcessorCount;
+    // kmer_direct: two extra blocks behind the data — block P stays zero (queries of k-mers outside the table), block P+1
+    // takes the builds of such k-mers; neither is ever saved
+    const uint64_t extra_words = hp.direct ? 2ull * prm.words_per_block : 0;
+    if (external && hp.direct) { delete f; return fail(DYIBF_ERR_ARG, "dyibf_attach: kmer_direct filters own their memory"); }
     if (external) { f->d_words = (uint64_t*)external; f->owns_words = false; }
     else {
-        cudaError_t e = cudaMalloc((void**)&f->d_words, f->data_words * 8);
+        cudaError_t e = cudaMalloc((void**)&f->d_words, (f->data_words + extra_words) * 8);
         if (e != cudaSuccess) { delete f; return fail(e == cudaErrorMemoryAllocation ? DYIBF_ERR_NOMEM : DYIBF_ERR_CUDA,
                                                       "cudaMalloc of %llu filter bytes: %s", (unsigned long long)(f->data_words * 8), cudaGetErrorString(e)); }
+        if (e == cudaSuccess && extra_words) e = cudaMemset(f->d_words + f->data_words, 0, extra_words * 8);
+        if (e != cudaSuccess) { cudaFree(f->d_words); delete f; return fail(DYIBF_ERR_CUDA, "cudaMemset: %s", cudaGetErrorString(e)); }
         if (zero) { e = cudaMemset(f->d_words, 0, f->data_words * 8); if (e != cudaSuccess) { cudaFree(f->d_words); delete f; return fail(DYIBF_ERR_CUDA, "cudaMemset: %s", cudaGetErrorString(e)); } }
     }
     for (int i = 0; i < 2; ++i) {
@@ -887,6 +895,9 @@ namespace {
 // the call's chunks: level 1 of the split fills the (smaller) super-bucket buffer, level 2 empties it into the final
 // per-region buckets, and the final buckets are OR-ed into the table (one sweep over the table) when they are nearly
 // full and at the end of the call.
+// the build's view of the hash parameters: k-mers outside a kmer_direct table OR into the scratch block
+HashParams build_params(const dyibf_filter* f) { HashParams hp = f->hp; if (hp.direct) hp.sink = hp.P + 1; return hp; }
+
 struct BucketRun {
     bool active = false;
     BucketPlan plan;
@@ -897,7 +908,7 @@ struct BucketRun {
 int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
 {
     br->active = false;
-    if (f->bucket_mib == 0) return DYIBF_OK;
+    if (f->bucket_mib == 0 || f->hp.direct) return DYIBF_OK;         // kmer_direct tables are built with the direct kernel
     if (f->data_words * 8 <= (256ull << 20)) return DYIBF_OK;       // table (nearly) fits the L2: direct atomics are L2 hits
     if (expected_records < (32ull << 20)) return DYIBF_OK;          // too few updates per region sector to pay for a sweep
     uint64_t budget = f->bucket_mib > 0 ? (uint64_t)f->bucket_mib << 20 : 64ull << 30;
@@ -1031,7 +1042,7 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         if (brc) return brc;
         if (!br.active) {
             Scope sc(f, st, K_BUILD);
-            CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st));
+            CU(launch_build(build_params(f), f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st));
             return DYIBF_OK;
         }
         // stream-ordered: split, level 2, apply, next word range
@@ -1079,7 +1090,7 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
             if (brc) return brc;
         } else {
             Scope sc(f, sl.st, K_BUILD);
-            CU(launch_build(f->hp, f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
+            CU(launch_build(build_params(f), f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
                             (const uint32_t*)sl.counts.p, cnt, words, sl.st));
         }
         a = b; ++c;

@@ -17,6 +17,10 @@ struct HashParams {
     uint32_t k;
     uint32_t W;                     // 64-bit words per block
     uint32_t bins;
+    // kmer_direct filter (SeqAnKDXFilter, src/d_kdx_filter.h): the one "hash" is the k-mer value itself; k-mers whose value
+    // is not a block of the table go to block `sink` (query: an all-zero block behind the data, build: a scratch block)
+    uint32_t direct;
+    uint64_t sink;
 };
 
 // One packed sequence: 2 bits per base, first base in the two top bits of word 0 (so that a k-mer is a

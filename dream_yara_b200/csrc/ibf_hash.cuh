@@ -44,6 +44,7 @@ __device__ __forceinline__ uint64_t mod_blocks(uint64_t v, const HashParams& hp)
 
 __device__ __forceinline__ uint64_t block_index(uint64_t kmer, uint32_t i, const HashParams& hp)
 {
+    if (hp.direct) return kmer < hp.P ? kmer : hp.sink;             // d_kdx_filter.h:171-175,287-291
     uint64_t v = hp.pre[i] * kmer;
     v ^= v >> 27;
     return mod_blocks(v, hp);

@@ -290,3 +290,31 @@ class SeqAnBloomFilter:
                                       int(bool(derive_rc)), int(threshold), int(max_seq_len), C.c_void_p(rows_ptr),
                                       C.c_void_p(counts_ptr) if counts_ptr else None, MEM_DEVICE,
                                       C.c_void_p(stream) if stream else None))
+
+
+class SeqAnKDXFilter(SeqAnBloomFilter):
+    """The kmer_direct filter (`-ft kmer_direct`; reference: seqan::SeqAnKDXFilter, src/d_kdx_filter.h:41-311): same layout,
+    file format and members as the IBF, but the block of a k-mer is its value — no hashing.  Constructors as in the reference:
+
+        SeqAnKDXFilter(n_bins, kmer_size, vec_size)     d_kdx_filter.h:49-56   (vec_size = 4^k * n_bins + 256 in build_filter)
+        SeqAnKDXFilter(fileName)                        d_kdx_filter.h:58-67
+
+    On the C ABI it is a filter with zero hash functions.  Where the reference indexes out of bounds (a k-mer value that is
+    not a block of the table: sequences that start with N, tables smaller than 4^k blocks; clearBins walking 64 x the
+    blocks there are) this class skips the k-mer / covers the real blocks."""
+
+    def __init__(self, *args, device=0):
+        if len(args) == 3:
+            n_bins, kmer, vec_size = args
+            super().__init__(n_bins, 0, kmer, vec_size, device=device)
+        elif len(args) == 1:
+            super().__init__(args[0], device=device)
+            if self._noOfHashFunc != 0:
+                raise ValueError("%s is a bloom filter file (%d hash functions), not kmer_direct" % (args[0], self._noOfHashFunc))
+        else:
+            raise TypeError("SeqAnKDXFilter(n_bins, kmer_size, vec_size) | (fileName)")
+
+    @staticmethod
+    def vectorSize(n_bins, kmer_size):
+        """vec_size as dream_yara_build_filter computes it, d_build_filter.cpp:307-309 (u32 shift: k <= 15)"""
+        return ((1 << (2 * kmer_size)) & 0xFFFFFFFF) * n_bins + filterMetadataSize

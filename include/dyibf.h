@@ -76,7 +76,12 @@ int  dyibf_device_count(int* count);
 
 /* ---- construction / destruction ------------------------------------------------------------ */
 
-/* SeqAnBloomFilter(n_bins, n_hash_func, kmer_size, vec_size), d_bloom_filter.h:48-57: zeroed filter */
+/* SeqAnBloomFilter(n_bins, n_hash_func, kmer_size, vec_size), d_bloom_filter.h:48-57: zeroed filter.
+ * n_hash == 0 makes a kmer_direct filter — SeqAnKDXFilter(n_bins, kmer_size, vec_size), src/d_kdx_filter.h:49-56
+ * (`-ft kmer_direct`): block = the k-mer value itself, no hashing; its trailer is [bins, 0, k, 0] (:234-239), so
+ * dyibf_load_file recognises such a file by the zero.  Every other entry point works on both kinds.  A k-mer whose
+ * value is not a block of the table ((nbits-256)/(64 W) blocks) adds nothing and matches nothing (the reference
+ * indexes out of bounds there: leading-N k-mers, or a table smaller than 4^k blocks). */
 int  dyibf_create(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device,
                   dyibf_filter** out);
 /* same, but the P*W data words live in caller-owned device memory (e.g. a buffer that was the target

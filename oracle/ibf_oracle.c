@@ -415,3 +415,69 @@ int64_t ibf_parse_records(const char *text, uint64_t n, int format, int iupac, u
     *n_bases = nb;
     return nr;
 }
+
+/* ---- kmer_direct filter: SeqAnKDXFilter, src/d_kdx_filter.h ------------------------------------------------------
+ * Same bit layout and trailer as the IBF (trailer [bins, 0, k, 0]: _setMetadata :234-239 writes no hash count), but the
+ * block of a k-mer is its SeqAn hash value itself.  _init (:212-217) sets _noOfHashPos = (N-256)/_binIntWidth — 64 times
+ * the number of blocks the vector really has — and `kmerHash >= _noOfHashPos` (:171, :288) is the only guard, so for
+ * hashes in [(N-256)/S, (N-256)/W) the reference reads / writes beyond the vector (undefined behaviour; reachable with
+ * leading-N sequences or a vector smaller than 4^k blocks).  Here those k-mers are skipped; inside the table the
+ * restatement is exact.  Use ibf_params_init-like fields: W, S as for the IBF; P = true number of blocks. */
+int kdx_params_init(ibf_params *p, uint32_t bins, uint32_t k, uint64_t nbits)
+{
+    if (!bins || !k || k > 32 || nbits < IBF_META_BITS + 64) return -1;
+    memset(p, 0, sizeof *p);
+    p->bins = bins; p->h = 0; p->k = k; p->nbits = nbits;
+    p->W = (uint32_t)ceilf((float)bins / 64.0f);
+    p->S = (uint64_t)p->W * 64u;
+    p->P = (nbits - IBF_META_BITS) / p->S;
+    return p->P ? 0 : -1;
+}
+
+/* _addKmers, d_kdx_filter.h:279-292 */
+void kdx_add_kmers(uint64_t *words, const ibf_params *p, const uint8_t *codes, uint64_t len, uint32_t bin)
+{
+    if (len < p->k) return;
+    uint64_t n = len - p->k + 1;
+    uint64_t *hashes = (uint64_t *)malloc(n * sizeof(uint64_t));
+    ibf_kmer_hashes(codes, len, p->k, hashes);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (hashes[i] >= p->P) continue;                       /* reference: >= (N-256)/W, then out of bounds */
+        uint64_t bit = p->S * hashes[i] + bin;                 /* _filterVector[_blockBitSize * kmerHash + binNo] = 1 */
+        words[bit >> 6] |= 1ULL << (bit & 63);
+    }
+    free(hashes);
+}
+
+/* whichBins, d_kdx_filter.h:152-207: counts[bin] = number of k-mers of the text whose block has the bin's bit set */
+void kdx_count_bins(const uint64_t *words, const ibf_params *p, const uint8_t *codes, uint64_t len, uint16_t *counts)
+{
+    memset(counts, 0, p->bins * sizeof(uint16_t));
+    if (len < p->k) return;
+    uint64_t n = len - p->k + 1;
+    uint64_t *hashes = (uint64_t *)malloc(n * sizeof(uint64_t));
+    ibf_kmer_hashes(codes, len, p->k, hashes);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (hashes[i] >= p->P) continue;
+        const uint64_t *blk = words + hashes[i] * p->W;        /* get_int(kmerHash * S + 64 batchNo, 64) */
+        for (uint32_t w = 0; w < p->W; ++w) {
+            uint64_t t = blk[w];
+            while (t) {                                        /* :181-196: every set bit, LSB first */
+                uint32_t b = 64 * w + (uint32_t)__builtin_ctzll(t);
+                t &= t - 1;
+                if (b < p->bins) ++counts[b];                  /* bits >= bins are never set by the build */
+            }
+        }
+    }
+    free(hashes);
+}
+
+/* the thresholding tail of whichBins (:200-205): OR-accumulates into `selected` */
+void kdx_which_bins(const uint64_t *words, const ibf_params *p, const uint8_t *codes, uint64_t len, uint16_t threshold, uint8_t *selected)
+{
+    uint16_t *counts = (uint16_t *)malloc(p->bins * sizeof(uint16_t));
+    kdx_count_bins(words, p, codes, len, counts);
+    if (len >= p->k)
+        for (uint32_t b = 0; b < p->bins; ++b) if (counts[b] >= threshold) selected[b] = 1;
+    free(counts);
+}

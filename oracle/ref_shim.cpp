@@ -40,6 +40,7 @@
 // very same filter words the GPU holds, and tests need to read them back without a 16 GiB file.
 #define private public
 #include "d_bloom_filter.h"
+#include "d_kdx_filter.h"
 #undef private
 
 using namespace seqan;
@@ -219,6 +220,45 @@ int64_t ref_read_records(const char* path, int iupac, uint8_t* codes, uint64_t c
     }
     *n_bases = nb;
     return nr;
+}
+
+// ---- kmer_direct filter: the UNMODIFIED seqan::SeqAnKDXFilter (src/d_kdx_filter.h:41-311) ------------------------------
+typedef SeqAnKDXFilter<> TKdx;
+void* ref_kdx_new(uint32_t bins, uint32_t k, uint64_t nbits) { return new TKdx(bins, (uint8_t)k, nbits); }
+void* ref_kdx_load(const char* path) { return new TKdx(path); }
+void ref_kdx_free(void* f) { delete (TKdx*)f; }
+uint64_t* ref_kdx_words(void* f) { return (uint64_t*)((TKdx*)f)->_filterVector.data(); }
+uint64_t ref_kdx_nwords(void* f) { return (((TKdx*)f)->_filterVector.bit_size() + 63) >> 6; }
+void ref_kdx_params(void* f, uint32_t* bins, uint32_t* k, uint64_t* nbits, uint64_t* hashpos)
+{
+    TKdx* x = (TKdx*)f;
+    *bins = x->_noOfBins; *k = x->_kmerSize; *nbits = x->_noOfBits; *hashpos = x->_noOfHashPos;
+}
+void ref_kdx_add_kmers(void* f, const uint8_t* codes, uint64_t len, uint32_t bin)
+{
+    Dna5String s = codes_to_dna5(codes, len);
+    ((TKdx*)f)->addKmers(s, bin);
+}
+int ref_kdx_add_fasta(void* f, const char* path, uint32_t bin)
+{
+    try { ((TKdx*)f)->addFastaFile(CharString(path), bin); } catch (...) { return -1; }
+    return 0;
+}
+void ref_kdx_clear_bins(void* f, const uint32_t* bins, uint32_t n, uint32_t threads)
+{
+    std::vector<uint32_t> v(bins, bins + n);
+    ((TKdx*)f)->clearBins(v, threads);
+}
+int ref_kdx_save(void* f, const char* path) { return ((TKdx*)f)->save(path) ? 0 : -1; }
+void ref_kdx_which_bins(void* f, const uint8_t* codes, uint64_t len, uint16_t threshold, uint8_t* selected)
+{
+    TKdx* x = (TKdx*)f;
+    uint32_t bins = x->getNumberOfBins();
+    std::vector<bool> sel(bins);
+    for (uint32_t b = 0; b < bins; ++b) sel[b] = selected[b] != 0;
+    Dna5String s = codes_to_dna5(codes, len);
+    x->whichBins(sel, s, threshold);
+    for (uint32_t b = 0; b < bins; ++b) selected[b] = sel[b] ? 1 : 0;
 }
 
 } // extern "C"

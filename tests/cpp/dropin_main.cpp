@@ -9,6 +9,8 @@
 //   dropin_test classify <filter> <reads.fa> <e percent> <paired 0/1> <out.txt>
 //   dropin_test gather   <filter> <reads.fa> <e percent> <paired 0/1> <out.txt>   classify, then sortedBins and
 //                        loadFilteredReads for every bin in that order (reads get synthetic qualities)
+//   dropin_test kdx      <bins> <k> <dir with 0.fa..> <out.filter> <reads.fa> <threshold> <out.txt>
+//                        SeqAnKDXFilter (-ft kmer_direct): build as build_filter does, save, reload, per-read whichBins
 #include <climits>
 #include <limits.h>
 #undef INT_WIDTH
@@ -24,6 +26,7 @@
 #include <seqan/modifier.h>
 
 #include "d_bloom_filter.h"
+#include "d_kdx_filter.h"
 #include "d_mapper_filter.h"
 
 using namespace seqan;
@@ -63,6 +66,40 @@ int main(int argc, char ** argv)
             }
             std::cerr << "size_mb " << filter.size_mb() << std::endl;
             return filter.save(argv[7]) ? 0 : 1;
+        }
+        if (mode == "kdx" && argc == 9)
+        {
+            uint32_t bins = std::stoul(argv[2]);
+            uint8_t k = (uint8_t)std::stoul(argv[3]);
+            {
+                uint64_t vec_size = (1u << (2 * k));                 // src/d_build_filter.cpp:307-310
+                vec_size *= bins;
+                vec_size += 256;
+                SeqAnKDXFilter<> filter(bins, k, vec_size);
+                for (uint32_t b = 0; b < bins; ++b)
+                {
+                    CharString path = std::string(argv[4]) + "/" + std::to_string(b) + ".fa";
+                    filter.addFastaFile(path, b);
+                }
+                if (!filter.save(argv[5])) return 1;
+            }
+            SeqAnKDXFilter<> filter(argv[5]);                        // src/d_mapper.h:926
+            if (filter.getNumberOfBins() != bins || filter.getKmerSize() != k) return 3;
+            uint16_t thr = (uint16_t)std::stoul(argv[7]);
+            SeqFileIn in(argv[6]);
+            std::ofstream out(argv[8]);
+            CharString id; String<Dna5Q> seq;
+            while (!atEnd(in))
+            {
+                readRecord(id, seq, in);
+                String<Dna5Q> rc = seq; reverseComplement(rc);
+                std::vector<bool> sel(filter.getNumberOfBins(), false);
+                filter.whichBins(sel, seq, thr);
+                filter.whichBins(sel, rc, thr);
+                for (uint32_t b = 0; b < sel.size(); ++b) if (sel[b]) out << b << ' ';
+                out << '\n';
+            }
+            return 0;
         }
         if (mode == "query" && argc == 6)
         {

@@ -184,6 +184,45 @@ class Oracle:
             return None
         return seqs[: nb.value].copy(), limits[: n + 1].copy()
 
+    # ---- kmer_direct filter (src/d_kdx_filter.h)
+    def kdx_params(self, bins, k, nbits):
+        l = self.l
+        l.kdx_params_init.argtypes = [C.POINTER(IbfParams), C.c_uint32, C.c_uint32, C.c_uint64]
+        l.kdx_add_kmers.argtypes = [_V, C.POINTER(IbfParams), _V, C.c_uint64, C.c_uint32]
+        l.kdx_count_bins.argtypes = [_V, C.POINTER(IbfParams), _V, C.c_uint64, _V]
+        l.kdx_which_bins.argtypes = [_V, C.POINTER(IbfParams), _V, C.c_uint64, C.c_uint16, _V]
+        p = IbfParams()
+        if l.kdx_params_init(C.byref(p), bins, k, nbits) != 0:
+            raise ValueError("bad kmer_direct filter parameters")
+        return p
+
+    def kdx_add_kmers(self, words, p, codes, bin_no):
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        self.l.kdx_add_kmers(_p(words), C.byref(p), _p(codes), codes.size, bin_no)
+
+    def kdx_count_bins(self, words, p, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        counts = np.zeros(p.bins, dtype=np.uint16)
+        self.l.kdx_count_bins(_p(words), C.byref(p), _p(codes), codes.size, _p(counts))
+        return counts
+
+    def kdx_which_bins(self, words, p, codes, threshold, selected=None):
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        sel = np.zeros(p.bins, dtype=np.uint8) if selected is None else selected
+        self.l.kdx_which_bins(_p(words), C.byref(p), _p(codes), codes.size, threshold, _p(sel))
+        return sel
+
+    def kdx_rows(self, words, p, reads_codes, threshold):
+        """one row per read: whichBins(fwd) OR whichBins(revcomp), as clasifyLoadedReads combines them"""
+        W = p.W
+        rows = np.zeros((len(reads_codes), W), dtype=np.uint64)
+        for i, c in enumerate(reads_codes):
+            sel = self.kdx_which_bins(words, p, c, threshold)
+            self.kdx_which_bins(words, p, self.revcomp(c), threshold, sel)
+            bits = np.zeros(W * 64, dtype=np.uint8); bits[: p.bins] = sel
+            rows[i] = np.packbits(bits, bitorder="little").view(np.uint64)
+        return rows
+
     def clear_bins(self, words, p, bins):
         b = np.ascontiguousarray(bins, dtype=np.uint32)
         self.l.ibf_clear_bins(_p(words), C.byref(p), _p(b), b.size)
@@ -319,3 +358,64 @@ class Ref:
         rows = np.zeros((n_seqs // (4 if paired else 2), W), dtype=np.uint64)
         self.l.ref_classify(f, _p(concat), _p(offsets), n_seqs, int(paired), threshold, threads, _p(rows))
         return rows
+
+
+class RefKdx:
+    """The unmodified seqan::SeqAnKDXFilter behind oracle/ref_shim.cpp (ref_kdx_*)."""
+
+    @staticmethod
+    def available():
+        return os.path.exists(REF_SO) and hasattr(C.CDLL(REF_SO), "ref_kdx_new")
+
+    def __init__(self):
+        self.l = C.CDLL(REF_SO)
+        l = self.l
+        l.ref_kdx_new.restype = _V; l.ref_kdx_new.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64]
+        l.ref_kdx_load.restype = _V; l.ref_kdx_load.argtypes = [C.c_char_p]
+        l.ref_kdx_free.argtypes = [_V]
+        l.ref_kdx_words.restype = _V; l.ref_kdx_words.argtypes = [_V]
+        l.ref_kdx_nwords.restype = C.c_uint64; l.ref_kdx_nwords.argtypes = [_V]
+        l.ref_kdx_params.argtypes = [_V, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        l.ref_kdx_add_kmers.argtypes = [_V, _V, C.c_uint64, C.c_uint32]
+        l.ref_kdx_add_fasta.argtypes = [_V, C.c_char_p, C.c_uint32]
+        l.ref_kdx_clear_bins.argtypes = [_V, _V, C.c_uint32, C.c_uint32]
+        l.ref_kdx_save.argtypes = [_V, C.c_char_p]
+        l.ref_kdx_which_bins.argtypes = [_V, _V, C.c_uint64, C.c_uint16, _V]
+
+    def new(self, bins, k, nbits):
+        return self.l.ref_kdx_new(bins, k, nbits)
+
+    def load(self, path):
+        return self.l.ref_kdx_load(str(path).encode())
+
+    def free(self, f):
+        self.l.ref_kdx_free(f)
+
+    def words(self, f):
+        n = self.l.ref_kdx_nwords(f)
+        return np.ctypeslib.as_array(C.cast(self.l.ref_kdx_words(f), C.POINTER(C.c_uint64)), shape=(n,))
+
+    def params(self, f):
+        b, k, nb, hp = C.c_uint32(), C.c_uint32(), C.c_uint64(), C.c_uint64()
+        self.l.ref_kdx_params(f, C.byref(b), C.byref(k), C.byref(nb), C.byref(hp))
+        return b.value, k.value, nb.value, hp.value
+
+    def add_kmers(self, f, codes, bin_no):
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        self.l.ref_kdx_add_kmers(f, _p(codes), codes.size, bin_no)
+
+    def add_fasta(self, f, path, bin_no):
+        return self.l.ref_kdx_add_fasta(f, str(path).encode(), bin_no)
+
+    def clear_bins(self, f, bins, threads=1):
+        b = np.ascontiguousarray(bins, dtype=np.uint32)
+        self.l.ref_kdx_clear_bins(f, _p(b), b.size, threads)
+
+    def save(self, f, path):
+        return self.l.ref_kdx_save(f, str(path).encode())
+
+    def which_bins(self, f, codes, threshold, bins, selected=None):
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        sel = np.zeros(bins, dtype=np.uint8) if selected is None else selected
+        self.l.ref_kdx_which_bins(f, _p(codes), codes.size, threshold, _p(sel))
+        return sel

@@ -89,3 +89,25 @@ def test_dropin_build_query_classify(golden, tmp_path):
     # load failure: message + exit(1) as the reference
     r = subprocess.run([BIN, "query", str(tmp_path / "nope.filter"), str(tmp_path / "reads400.fa"), "25", str(tmp_path / "x")], capture_output=True, text=True)
     assert r.returncode == 1 and "could not be read" in r.stderr
+
+
+@pytest.mark.gpu
+def test_dropin_kdx_filter(golden, tmp_path):
+    """include/d_kdx_filter.h (SeqAnKDXFilter, -ft kmer_direct) against the vectors of the unmodified reference class"""
+    if not os.path.exists(BIN):
+        pytest.skip("tests/cpp/_bin/dropin_test was not prebuilt (needs /root/reference at build time)")
+    kg = np.load(os.path.join(HERE, "golden", "kdx_vectors.npz"))
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    reads = [reads[int(i)] for i in kg["read_idx"]][:300]
+    bins_dir = tmp_path / "bins"; bins_dir.mkdir()
+    for b, g in enumerate(genomes):
+        _write_fasta(bins_dir / ("%d.fa" % b), [("bin%d" % b, g)])
+    _write_fasta(tmp_path / "reads.fa", [("r%d" % i, r) for i, r in enumerate(reads)])
+    filt, out = tmp_path / "kx.filter", tmp_path / "kx.txt"
+    r = subprocess.run([BIN, "kdx", "64", str(int(kg["kx1_k"])), str(bins_dir), str(filt), str(tmp_path / "reads.fa"), "53", str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert ka.md5_file(filt) == str(kg["kx1_md5"])
+    want = ka.bits_from_rows(kg["kx1_rows"][:300], 64)
+    for i, line in enumerate(open(out)):
+        assert [int(x) for x in line.split()] == list(np.nonzero(want[i])[0]), i

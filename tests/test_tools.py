@@ -37,8 +37,10 @@ def test_cli_argument_checks(tools, tmp_path):
     assert r.returncode == 1 and "should be a power of 2" in r.stderr          # d_build_filter.cpp:198-210
     r = subprocess.run([build, "-k", "40", str(tmp_path)], capture_output=True, text=True)
     assert r.returncode == 1
-    r = subprocess.run([build, "-ft", "kmer_direct", str(tmp_path)], capture_output=True, text=True)
-    assert r.returncode == 1 and "bloom" in r.stderr
+    r = subprocess.run([build, "-ft", "none", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 1 and "bloom or kmer_direct" in r.stderr
+    r = subprocess.run([build, "-ft", "kmer_direct", "-k", "16", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 1 and "-k <= 15" in r.stderr                        # the reference computes 1u << 2k
     r = subprocess.run([update, str(tmp_path / "x.filter"), str(tmp_path / "abc.fna")], capture_output=True, text=True)
     assert r.returncode == 1 and "doesn't have a valid name" in r.stderr        # d_update_filter.cpp:158-162
 
@@ -84,3 +86,38 @@ def test_build_and_update_cli(tools, golden, oracle, tmp_path):
     _write_fasta(u / "64.fna", [("x", genomes[0])])
     r = subprocess.run([update, str(filt), str(u / "64.fna")], capture_output=True, text=True)
     assert r.returncode == 1 and "has only 64 Bins" in r.stderr
+
+
+@pytest.mark.gpu
+def test_build_cli_kmer_direct(tools, golden, oracle, dy, tmp_path):
+    """dream_yara_build_filter -ft kmer_direct (d_build_filter.cpp:305-313): 4^k * bins + 256 bits, trailer [bins, 0, k, 0]"""
+    build, update = tools
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    d = tmp_path / "bins"; d.mkdir()
+    for b, g in enumerate(genomes):
+        _write_fasta(d / ("%d.fa" % b), [("bin%d" % b, g)])
+    filt = tmp_path / "kdx.filter"
+    r = subprocess.run([build, "-b", "64", "-t", "2", "-ft", "kmer_direct", "-k", "14", str(d), "-o", str(filt)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    nbits = (1 << 28) * 64 + 256
+    assert filt.stat().st_size == 8 + nbits // 8
+    p = oracle.kdx_params(64, 14, nbits)
+    words = oracle.new_words(p)
+    for b, g in enumerate(genomes):
+        oracle.kdx_add_kmers(words, p, oracle.encode_ascii(g), b)
+    oracle.set_metadata(words, p)
+    f = dy.SeqAnKDXFilter(str(filt))
+    assert (f.getNumberOfBins(), f.getKmerSize(), f._noOfHashFunc) == (64, 14, 0)
+    assert np.array_equal(f.download_words(), words)
+    # update: clear + re-add bin 7 from a new file; the kind comes from the trailer
+    _write_fasta(tmp_path / "7.fa", [("new7", genomes[7][::-1])])
+    r = subprocess.run([update, "-ft", "kmer_direct", str(filt), str(tmp_path / "7.fa")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    oracle.clear_bins(words, p, [7])
+    oracle.kdx_add_kmers(words, p, oracle.encode_ascii(genomes[7][::-1]), 7)
+    oracle.set_metadata(words, p)
+    g2 = dy.SeqAnKDXFilter(str(filt))
+    assert np.array_equal(g2.download_words(), words)
+    codes = [oracle.encode_ascii(x) for x in reads[:200]]
+    assert np.array_equal(g2.whichBinsBatch(reads[:200], 45, group=2, derive_rc=True), oracle.kdx_rows(words, p, codes, 45))
+    f.close(); g2.close()

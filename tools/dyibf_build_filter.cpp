@@ -28,6 +28,7 @@ struct Options
     uint32_t kmerSize = 20, numberOfBins = 64, numberOfHashes = 4, threadsCount = 1;     // d_build_filter.cpp:88-96
     uint64_t bloomFilterSize = 8589934592ull + 256;                                       // 1 GiB + filterMetadataSize
     bool verbose = false;
+    bool kmerDirect = false;
     int device = 0;
 };
 
@@ -39,7 +40,7 @@ double now() { return std::chrono::duration<double>(std::chrono::steady_clock::n
     std::cerr << "usage: dyibf_build_filter [OPTIONS] <REFERENCE FILES DIR>\n"
                  "  -b, --number-of-bins INT   1..4194300 (default 64)\n"
                  "  -t, --threads INT          host reader threads (default 1)\n"
-                 "  -ft, --filter-type STR     bloom (kmer_direct / none are not provided by the B200 library)\n"
+                 "  -ft, --filter-type STR     bloom | kmer_direct (default bloom; kmer_direct: 4^k blocks, -k <= 15, -nh / -bs ignored)\n"
                  "  -k, --kmer-size INT        14..32 (default 20)\n"
                  "  -nh, --num-hash INT        2..5 (default 4)\n"
                  "  -bs, --bloom-size INT      GB, power of two, 1..512 (default 1)\n"
@@ -87,7 +88,8 @@ Options parse(int argc, char ** argv)
         {
             if (i + 1 >= argc) usage("missing value for -ft");
             const std::string v = argv[++i];
-            if (v != "bloom") usage("only -ft bloom is provided by the B200 library");
+            if (v == "kmer_direct") o.kmerDirect = true;
+            else if (v != "bloom") usage("-ft must be bloom or kmer_direct");
         }
         else if (a == "-o" || a == "--output-file")
         {
@@ -103,6 +105,12 @@ Options parse(int argc, char ** argv)
     if (o.contigsDir.empty()) usage("missing <REFERENCE FILES DIR>");
     if (o.contigsDir.back() != '/') o.contigsDir += '/';                                  // appendTrailingSlash
     if (!haveOut) o.filterFile = o.contigsDir + "bloom.filter";                           // :186-190
+    if (o.kmerDirect)                                                                     // d_build_filter.cpp:305-310
+    {
+        if (o.kmerSize > 15) usage("-ft kmer_direct needs -k <= 15 (the reference computes 1u << 2k)");
+        o.bloomFilterSize = (uint64_t)(1u << (2 * o.kmerSize)) * o.numberOfBins + 256;
+        o.numberOfHashes = 0;                                                             // the C ABI's mark of a kmer_direct filter
+    }
     return o;
 }
 

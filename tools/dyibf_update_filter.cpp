@@ -61,7 +61,8 @@ int main(int argc, char ** argv)
         else if (a == "-ft" || a == "--filter-type")
         {
             if (++i >= argc) usage("missing value for -ft");
-            if (std::string(argv[i]) != "bloom") usage("only -ft bloom is provided by the B200 library");
+            const std::string v = argv[i];                              // the kind is read from the file's trailer anyway
+            if (v != "bloom" && v != "kmer_direct") usage("-ft must be bloom or kmer_direct");
         }
         else if (!a.empty() && a[0] == '-') usage(("unknown option " + a).c_str());
         else if (filterFile.empty()) filterFile = a;
