@@ -14,6 +14,7 @@
 #include <cstring>
 #include <cstdarg>
 #include <cmath>
+#include <mutex>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -844,8 +845,13 @@ int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int form
         CU(cudaMemcpyAsync(tmp.p[0], text, n_bytes, cudaMemcpyHostToDevice, st));
         d_text = static_cast<const uint8_t*>(tmp.p[0]);
     }
-    CU(cudaMalloc(&tmp.p[1], ingest_workspace_bytes(n_bytes)));
-    uint64_t* ws = static_cast<uint64_t*>(tmp.p[1]);
+    // the tile tables are kept per device between calls (a cudaMalloc / cudaFree pair costs as much as a pass over the text)
+    static std::mutex ws_mutex;
+    static DevBuf ws_cache[64];
+    std::lock_guard<std::mutex> ws_lock(ws_mutex);
+    DevBuf& wsb = ws_cache[device & 63];
+    CU(wsb.reserve(ingest_workspace_bytes(n_bytes)));
+    uint64_t* ws = static_cast<uint64_t*>(wsb.p);
     const int iupac = alphabet == DYIBF_ALPHA_IUPAC;
     CU(launch_ingest_count(d_text, n_bytes, format, iupac, ws, st));
     uint64_t tot[6];

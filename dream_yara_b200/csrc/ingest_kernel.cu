@@ -6,7 +6,7 @@
 // :302-345 (Fastq), stream/tokenization.h:51-58 (IsInAlphabet), :145-149 (whitespace = ' ' '\t' '\n' '\r').
 //
 // Both formats are state machines whose state at a byte is a prefix function of the text, so the text is cut into tiles
-// of 4 KiB (256 threads x 16 bytes) and parsed in five streaming passes:
+// of 8 KiB (256 threads x 32 bytes) and parsed in five streaming passes:
 //   1 summary : per tile, what a later tile needs to know about it (below);       one read of the text
 //   2 scan    : tile summaries -> state at the start of every tile                (n/4096 elements)
 //   3 count   : per tile, records started / sequence characters / quality characters, and validation;  second read
@@ -25,6 +25,13 @@
 //   must agree — which is also SeqAn's own check (:341-344).  Trailing whitespace after the last record is ignored.
 // Characters outside the target alphabet are SeqAn ParseErrors (reads: ACGTN, contigs: the 16 IUPAC letters; either
 // case); here the smallest offending offset is reported through dyibf_last_error.
+//
+// Inside a tile nothing walks byte by byte: a thread turns its 32 bytes into 32-bit masks with byte-wise SIMD compares
+// (newline, '>', '@', '+', whitespace, alphabet), derives "sequence character" / "quality character" / "record start" masks
+// from them with one short loop over the delimiters it holds (usually none or one), counts with popc, and the emit pass
+// stages the tile's sequence characters in shared memory — shifted so that 16-byte chunks line up with the output — and
+// writes them as whole 16-byte stores.  (v1 walked the bytes with a four-way branch per byte: lanes of a warp sit in
+// different lines of a record, so every branch diverged; 93 GB/s of text.  profiles/r01_ingest_*.)
 #include "dyibf_internal.h"
 
 #include <cstdio>
@@ -35,80 +42,172 @@ namespace {
 
 const uint32_t FULL = 0xffffffffu;
 const int      IT = 256;                   // threads per tile
-const int      IB = 16;                    // bytes per thread
+const int      IB = 32;                    // bytes per thread: one bit per byte in a 32-bit mask
 const uint64_t TILE = (uint64_t)IT * IB;
 
 enum { G_BEGIN = 0, G_END = 1, G_ERR = 2, G_N = 4 };     // device globals: first '>' / effective end / first error
 enum { E_ALPHABET = 1, E_FQ_LAYOUT = 2, E_FQ_QUAL = 3, E_FQ_TRUNC = 4 };
 enum { D_NONE = 0, D_NL = 1, D_GT = 2 };
 
-__device__ __forceinline__ bool is_ws(uint32_t c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
-__device__ __forceinline__ bool is_nl(uint32_t c) { return c == '\n' || c == '\r'; }
-
-// IsInAlphabet<Dna5Q> / IsInAlphabet<Iupac>: the character, upper-cased, is one of the alphabet's letters
-__device__ __forceinline__ bool in_alphabet(uint32_t c, int iupac)
-{
-    const uint32_t u = (c >= 'a' && c <= 'z') ? c - 32 : c;
-    if (u < 'A' || u > 'Z') return false;
-    const uint32_t dna5 = (1u << ('A' - 'A')) | (1u << ('C' - 'A')) | (1u << ('G' - 'A')) | (1u << ('T' - 'A')) | (1u << ('N' - 'A'));
-    const uint32_t more = (1u << ('U' - 'A')) | (1u << ('W' - 'A')) | (1u << ('Y' - 'A')) | (1u << ('M' - 'A')) | (1u << ('H' - 'A')) |
-                          (1u << ('K' - 'A')) | (1u << ('R' - 'A')) | (1u << ('D' - 'A')) | (1u << ('S' - 'A')) | (1u << ('B' - 'A')) |
-                          (1u << ('V' - 'A'));
-    return ((iupac ? (dna5 | more) : dna5) >> (u - 'A')) & 1u;
-}
-
-// the 16 bytes of one thread, in registers
+// ---- 32 bytes of text in registers, and masks over them ----------------------------------------------------------
 struct Chunk {
-    uint32_t w[4];
-    uint32_t m;                // valid bytes (0..16)
-    __device__ __forceinline__ uint32_t at(int j) const { return (w[j >> 2] >> (8 * (j & 3))) & 0xffu; }
+    uint32_t w[8];
+    uint32_t valid;            // bit j: byte j exists (below the end of the text)
 };
 
 __device__ __forceinline__ Chunk load_chunk(const uint8_t* __restrict__ text, uint64_t i0, uint64_t end, bool aligned)
 {
-    Chunk c; c.w[0] = c.w[1] = c.w[2] = c.w[3] = 0;
-    c.m = i0 >= end ? 0u : (uint32_t)(end - i0 < (uint64_t)IB ? end - i0 : (uint64_t)IB);
-    if (c.m == IB && aligned) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(text + i0));
-        c.w[0] = v.x; c.w[1] = v.y; c.w[2] = v.z; c.w[3] = v.w;
+    Chunk c;
+    #pragma unroll
+    for (int q = 0; q < 8; ++q) c.w[q] = 0;
+    const uint32_t m = i0 >= end ? 0u : (uint32_t)(end - i0 < (uint64_t)IB ? end - i0 : (uint64_t)IB);
+    c.valid = m == 32 ? FULL : ((1u << m) - 1u);
+    if (m == IB && aligned) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(text + i0));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(text + i0 + 16));
+        c.w[0] = a.x; c.w[1] = a.y; c.w[2] = a.z; c.w[3] = a.w; c.w[4] = b.x; c.w[5] = b.y; c.w[6] = b.z; c.w[7] = b.w;
     } else {
-        for (uint32_t j = 0; j < c.m; ++j) c.w[j >> 2] |= (uint32_t)__ldg(text + i0 + j) << (8 * (j & 3));
+        #pragma unroll
+        for (int j = 0; j < IB; ++j)
+            if ((uint32_t)j < m) c.w[j >> 2] |= (uint32_t)__ldg(text + i0 + j) << (8 * (j & 3));
     }
     return c;
 }
 
-struct OpSum  { __device__ __forceinline__ uint64_t operator()(uint64_t a, uint64_t b) const { return a + b; } };
-struct OpLast { __device__ __forceinline__ uint64_t operator()(uint64_t a, uint64_t b) const { return b ? b : a; } };   // a earlier
+// 0x80 in every byte of x that equals ch, 0 elsewhere (exact: no borrow between bytes; __vcmpeq4 is emulated with more)
+__device__ __forceinline__ uint32_t eq4(uint32_t x, uint32_t ch)
+{
+    const uint32_t d = x ^ (ch * 0x01010101u);                        // zero byte <=> equal
+    return ~(((d & 0x7f7f7f7fu) + 0x7f7f7f7fu) | d) & 0x80808080u;
+}
+// the top bit of each of the four bytes (nothing else set) -> a 4-bit mask (byte 0 -> bit 0)
+__device__ __forceinline__ uint32_t movemask4(uint32_t x) { return ((x >> 7) * 0x01020408u) >> 24; }
+
+struct ByteTest {   // one functor per byte class: word -> 0x80 / 0x00 per byte
+    struct Char  { uint32_t ch; __device__ __forceinline__ uint32_t operator()(uint32_t x) const { return eq4(x, ch); } };
+    struct NlCr  { __device__ __forceinline__ uint32_t operator()(uint32_t x) const { return eq4(x, '\n') | eq4(x, '\r'); } };
+    struct White { __device__ __forceinline__ uint32_t operator()(uint32_t x) const { return eq4(x, ' ') | eq4(x, '\t') | eq4(x, '\n') | eq4(x, '\r'); } };
+    // IsInAlphabet<Dna5Q> / <Iupac>: clearing bit 5 maps a lower-case letter onto its upper-case one and nothing else onto a letter
+    struct Alpha {
+        int iupac;
+        __device__ __forceinline__ uint32_t operator()(uint32_t x) const {
+            const uint32_t u = x & 0xdfdfdfdfu;
+            uint32_t ok = eq4(u, 'A') | eq4(u, 'C') | eq4(u, 'G') | eq4(u, 'T') | eq4(u, 'N');
+            if (iupac) ok |= eq4(u, 'U') | eq4(u, 'W') | eq4(u, 'Y') | eq4(u, 'M') | eq4(u, 'H') | eq4(u, 'K') | eq4(u, 'R') |
+                             eq4(u, 'D') | eq4(u, 'S') | eq4(u, 'B') | eq4(u, 'V');
+            return ok;
+        }
+    };
+};
+
+template <typename Test>
+__device__ __forceinline__ uint32_t mask_of(const Chunk& c, Test t)
+{
+    uint32_t m = 0;
+    #pragma unroll
+    for (int q = 0; q < 8; ++q) m |= movemask4(t(c.w[q])) << (4 * q);
+    return m;
+}
+
+// bits [lo, hi) of a 32-bit mask, 0 <= lo <= hi <= 32
+__device__ __forceinline__ uint32_t bit_range(uint32_t lo, uint32_t hi)
+{
+    const uint32_t upto_hi = hi >= 32 ? FULL : ((1u << hi) - 1u);
+    const uint32_t upto_lo = lo >= 32 ? FULL : ((1u << lo) - 1u);
+    return upto_hi & ~upto_lo;
+}
+
+struct OpSum  { template <typename T> __device__ __forceinline__ T operator()(T a, T b) const { return a + b; } };
+struct OpLast { template <typename T> __device__ __forceinline__ T operator()(T a, T b) const { return b ? b : a; } };   // a earlier
 
 // exclusive scan over the 256 threads of a block (identity 0); *total = combination of all
-template <typename Op>
-__device__ __forceinline__ uint64_t block_excl_scan(uint64_t v, Op op, uint64_t* sm /* [IT/32] */, uint64_t* total)
+template <typename T, typename Op>
+__device__ __forceinline__ T block_excl_scan(T v, Op op, T* sm /* [IT/32] */, T* total)
 {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint64_t x = v;
+    T x = v;
     #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        const uint64_t y = __shfl_up_sync(FULL, x, d);
+        const T y = __shfl_up_sync(FULL, x, d);
         if (lane >= (uint32_t)d) x = op(y, x);
     }
     __syncthreads();                                   // sm may still be read by a previous scan
     if (lane == 31) sm[warp] = x;
     __syncthreads();
     if (warp == 0) {
-        uint64_t w = lane < IT / 32 ? sm[lane] : 0;
+        T w = lane < IT / 32 ? sm[lane] : (T)0;
         #pragma unroll
         for (int d = 1; d < IT / 32; d <<= 1) {
-            const uint64_t y = __shfl_up_sync(FULL, w, d);
+            const T y = __shfl_up_sync(FULL, w, d);
             if (lane >= (uint32_t)d) w = op(y, w);
         }
         if (lane < IT / 32) sm[lane] = w;
     }
     __syncthreads();
-    uint64_t excl = __shfl_up_sync(FULL, x, 1);
+    T excl = __shfl_up_sync(FULL, x, 1);
     if (lane == 0) excl = 0;
-    const uint64_t prefix = warp ? sm[warp - 1] : 0;
+    const T prefix = warp ? sm[warp - 1] : (T)0;
     *total = sm[IT / 32 - 1];
     return op(prefix, excl);
+}
+
+// ---- what a thread's bytes are, once the state at its first byte is known ------------------------------------------
+struct Marks {
+    uint32_t seq;        // sequence characters
+    uint32_t qual;       // FASTQ: quality characters
+    uint32_t rec;        // record starts ('>' outside an id; '@' opening a line 0 mod 4)
+    uint32_t bad;        // FASTQ: a line 0 mod 4 that does not open with '@', a line 2 mod 4 that does not open with '+'
+    uint32_t qual_eol;   // FASTQ: the '\n' that ends a quality line
+    uint32_t late;       // FASTQ: bytes of lines 2 and 3 mod 4 (where a text may end)
+};
+
+// FASTA.  gt / nl: '>' and newline masks; in_id: state at byte 0; bytes before `begin` (the first '>') are skipped.
+__device__ __forceinline__ Marks mark_fasta(const Chunk& c, uint32_t gt, uint32_t nl, uint32_t ws, bool in_id, uint64_t i0, uint64_t begin)
+{
+    uint32_t id = 0, rec = 0, cur = 0, rem = (gt | nl) & c.valid;
+    bool st = in_id;
+    for (;;) {                                               // one round per delimiter held: usually none or one
+        const uint32_t nxt = rem ? (uint32_t)__ffs(rem) - 1u : 32u;
+        if (st) id |= bit_range(cur, nxt);
+        if (!rem) break;
+        const uint32_t bit = 1u << nxt;
+        if (gt & bit) { if (st) id |= bit; else rec |= bit; st = true; }   // a '>' inside an id is text
+        else          { if (st) id |= bit; st = false; }                   // the newline that ends the id
+        rem &= rem - 1; cur = nxt + 1;
+    }
+    const uint32_t after = i0 >= begin ? FULL : (begin - i0 >= 32 ? 0u : ~((1u << (uint32_t)(begin - i0)) - 1u));
+    Marks m; m.qual = m.bad = m.qual_eol = m.late = 0;
+    m.rec = rec;
+    m.seq = c.valid & after & ~id & ~gt & ~ws;
+    return m;
+}
+
+// FASTQ, four-line layout.  nl: '\n' mask; line0: newlines before byte 0; prev_nl: byte -1 is a '\n' (or the text starts here)
+__device__ __forceinline__ Marks mark_fastq(const Chunk& c, uint32_t nl, uint32_t ws, uint32_t at, uint32_t plus, uint64_t line0, bool prev_nl)
+{
+    uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0, cur = 0, rem = nl & c.valid;
+    uint32_t p = (uint32_t)line0 & 3u;
+    for (;;) {                                               // one round per line end held
+        const uint32_t nxt = rem ? (uint32_t)__ffs(rem) : 32u;       // one past the newline: it belongs to the line it ends
+        const uint32_t seg = bit_range(cur, nxt);
+        p0 |= p == 0 ? seg : 0u; p1 |= p == 1 ? seg : 0u; p2 |= p == 2 ? seg : 0u; p3 |= p == 3 ? seg : 0u;
+        if (!rem) break;
+        rem &= rem - 1; cur = nxt; p = (p + 1) & 3u;
+    }
+    const uint32_t first = (nl << 1) | (prev_nl ? 1u : 0u);
+    Marks m;
+    m.seq = p1 & ~ws & c.valid;
+    m.qual = p3 & ~ws & c.valid;
+    m.rec = p0 & first & at;
+    m.bad = ((p0 & first & ~at) | (p2 & first & ~plus)) & c.valid;
+    m.qual_eol = p3 & nl & c.valid;
+    m.late = (p2 | p3) & c.valid;
+    return m;
+}
+
+__device__ __forceinline__ void report(unsigned long long* g, uint64_t pos, uint32_t code)
+{
+    atomicMin(&g[G_ERR], (unsigned long long)((pos << 8) | code));
 }
 
 // ---- pass 1 ----------------------------------------------------------------------------------------------------------
@@ -116,42 +215,26 @@ template <int FMT>
 __global__ void __launch_bounds__(IT) ingest_summary_kernel(const uint8_t* __restrict__ text, uint64_t n, bool aligned,
                                                             uint64_t* __restrict__ summary, unsigned long long* __restrict__ g)
 {
-    __shared__ uint64_t sm[IT / 32];
+    __shared__ uint32_t sm[IT / 32];
     const uint64_t i0 = (uint64_t)blockIdx.x * TILE + (uint64_t)threadIdx.x * IB;
     const Chunk c = load_chunk(text, i0, n, aligned);
-    uint64_t v = 0, total;
+    uint32_t total;
     if (FMT == DYIBF_FMT_FASTA) {
-        uint32_t last = D_NONE, first_gt = IB;
-        #pragma unroll
-        for (int j = 0; j < IB; ++j) {
-            if ((uint32_t)j >= c.m) break;
-            const uint32_t ch = c.at(j);
-            if (ch == '>') { last = D_GT; if (first_gt == IB) first_gt = j; }
-            else if (is_nl(ch)) last = D_NL;
-        }
-        // the block's first '>' is the one of the lowest thread that saw any
-        const uint32_t any = __ballot_sync(FULL, first_gt != IB);
-        if (any && (threadIdx.x & 31) == (uint32_t)(__ffs(any) - 1)) atomicMin(&g[G_BEGIN], (unsigned long long)(i0 + first_gt));
-        block_excl_scan(last, OpLast(), sm, &total);
-        v = total;
+        const uint32_t gt = mask_of(c, ByteTest::Char{'>'}), nl = mask_of(c, ByteTest::NlCr());
+        const uint32_t mine = (gt | nl) ? (gt > nl ? D_GT : D_NL) : D_NONE;      // the higher mask holds the later byte
+        const uint32_t any = __ballot_sync(FULL, gt != 0);                         // the warp's first '>' is its lowest lane's
+        if (any && (threadIdx.x & 31) == (uint32_t)(__ffs(any) - 1)) atomicMin(&g[G_BEGIN], (unsigned long long)(i0 + __ffs(gt) - 1));
+        block_excl_scan<uint32_t>(mine, OpLast(), sm, &total);
     } else {
-        uint32_t nl = 0, last_graph = 0;
-        #pragma unroll
-        for (int j = 0; j < IB; ++j) {
-            if ((uint32_t)j >= c.m) break;
-            const uint32_t ch = c.at(j);
-            nl += ch == '\n';
-            if (!is_ws(ch)) last_graph = j + 1;
-        }
-        const uint64_t e = last_graph ? i0 + last_graph : 0;            // one past this thread's last non-whitespace byte
+        const uint32_t nl = mask_of(c, ByteTest::Char{'\n'}), graph = c.valid & ~mask_of(c, ByteTest::White());
+        const uint64_t e = graph ? i0 + 32 - __clz(graph) : 0;                     // one past this thread's last non-whitespace byte
         uint64_t emax = e;
         #pragma unroll
         for (int d = 16; d; d >>= 1) { const uint64_t o = __shfl_xor_sync(FULL, emax, d); emax = o > emax ? o : emax; }
         if ((threadIdx.x & 31) == 0 && emax) atomicMax(&g[G_END], (unsigned long long)emax);
-        block_excl_scan(nl, OpSum(), sm, &total);
-        v = total;
+        block_excl_scan<uint32_t>(__popc(nl), OpSum(), sm, &total);
     }
-    if (threadIdx.x == 0) summary[blockIdx.x] = v;
+    if (threadIdx.x == 0) summary[blockIdx.x] = total;
 }
 
 // ---- pass 2 (FASTA): entry[t] = kind of the last delimiter in tiles [0, t), single block ------------------------------
@@ -182,105 +265,85 @@ struct WalkArgs {
     unsigned long long* g;
 };
 
-__device__ __forceinline__ void report(unsigned long long* g, uint64_t pos, uint32_t code)
-{
-    atomicMin(&g[G_ERR], (unsigned long long)((pos << 8) | code));
-}
-
-struct Run { uint64_t rec, seq, qual; };   // running totals (pass 3: this thread's; pass 5: global)
-
-template <bool EMIT>
-__device__ __forceinline__ void walk_fasta(const WalkArgs& a, const Chunk& c, uint64_t i0, uint64_t begin, bool in_id, Run& r)
-{
-    #pragma unroll
-    for (int j = 0; j < IB; ++j) {
-        if ((uint32_t)j >= c.m) break;
-        const uint64_t i = i0 + j;
-        const uint32_t ch = c.at(j);
-        if (i < begin) continue;                           // skipUntil(iter, '>') in front of the first record
-        if (in_id) { if (is_nl(ch)) in_id = false; }
-        else if (ch == '>') { if (EMIT) a.out_limits[r.rec] = a.limit_base + r.seq; ++r.rec; in_id = true; }
-        else if (!is_ws(ch)) {
-            if (!EMIT && !in_alphabet(ch, a.iupac)) report(a.g, i, E_ALPHABET);
-            if (EMIT) a.out_seqs[r.seq] = (uint8_t)ch;
-            ++r.seq;
-        }
-    }
-}
-
-template <bool EMIT>
-__device__ __forceinline__ void walk_fastq(const WalkArgs& a, const Chunk& c, uint64_t i0, uint64_t end, uint64_t line, uint32_t prev, Run& r)
-{
-    #pragma unroll
-    for (int j = 0; j < IB; ++j) {
-        if ((uint32_t)j >= c.m) break;
-        const uint64_t i = i0 + j;
-        const uint32_t ch = c.at(j);
-        const uint32_t p = (uint32_t)line & 3u;
-        const bool first = prev == '\n';
-        if (p == 0) {
-            if (first) {
-                if (ch == '@') { if (EMIT) a.out_limits[r.rec] = a.limit_base + r.seq; ++r.rec; }
-                else if (!EMIT) report(a.g, i, E_FQ_LAYOUT);
-            }
-        } else if (p == 1) {
-            if (!is_ws(ch)) {
-                if (!EMIT && !in_alphabet(ch, a.iupac)) report(a.g, i, E_ALPHABET);
-                if (EMIT) a.out_seqs[r.seq] = (uint8_t)ch;
-                ++r.seq;
-            }
-        } else if (p == 2) {
-            if (first && ch != '+' && !EMIT) report(a.g, i, E_FQ_LAYOUT);
-        } else if (!is_ws(ch)) ++r.qual;
-        if (ch == '\n') {
-            if (EMIT && p == 3 && r.seq != r.qual) report(a.g, i, E_FQ_QUAL);
-            ++line;
-        }
-        if (EMIT && i + 1 == end && !((p == 3 || p == 2) && r.seq == r.qual)) report(a.g, i, p >= 2 ? E_FQ_QUAL : E_FQ_TRUNC);
-        prev = ch;
-    }
-}
-
 template <int FMT, bool EMIT>
 __global__ void __launch_bounds__(IT) ingest_walk_kernel(const WalkArgs a)
 {
     __shared__ uint64_t sm[IT / 32];
+    __shared__ __align__(16) uint8_t stage[EMIT ? TILE + 16 : 16];
     const uint64_t begin = FMT == DYIBF_FMT_FASTA ? a.g[G_BEGIN] : 0;
     const uint64_t end = FMT == DYIBF_FMT_FASTA ? a.n : a.g[G_END];
     const uint64_t i0 = (uint64_t)blockIdx.x * TILE + (uint64_t)threadIdx.x * IB;
     const Chunk c = load_chunk(a.text, i0, end, a.aligned);
-    uint64_t total;
-    // state at this thread's first byte
-    uint64_t mine = 0;
-    #pragma unroll
-    for (int j = 0; j < IB; ++j) {
-        if ((uint32_t)j >= c.m) break;
-        const uint32_t ch = c.at(j);
-        if (FMT == DYIBF_FMT_FASTA) { if (ch == '>') mine = D_GT; else if (is_nl(ch)) mine = D_NL; }
-        else mine += ch == '\n';
-    }
-    const uint64_t tile_entry = a.entry[blockIdx.x];
-    uint64_t state;
-    if (FMT == DYIBF_FMT_FASTA) { state = block_excl_scan(mine, OpLast(), sm, &total); if (!state) state = tile_entry; }
-    else state = tile_entry + block_excl_scan(mine, OpSum(), sm, &total);
-    const uint32_t prev = FMT == DYIBF_FMT_FASTQ ? (i0 == 0 || c.m == 0 ? (uint32_t)'\n' : (uint32_t)__ldg(a.text + i0 - 1)) : 0u;
+    const uint32_t ws = mask_of(c, ByteTest::White());
 
-    Run r; r.rec = r.seq = r.qual = 0;
-    if (FMT == DYIBF_FMT_FASTA) walk_fasta<false>(a, c, i0, begin, state == D_GT, r);
-    else                        walk_fastq<false>(a, c, i0, end, state, prev, r);
-    const uint64_t packed = r.rec | (r.seq << 16) | (r.qual << 32);       // each at most 16 per thread, 4096 per tile
-    const uint64_t excl = block_excl_scan(packed, OpSum(), sm, &total);
+    // state at this thread's first byte, then what its bytes are
+    Marks m;
+    uint64_t total;
+    if (FMT == DYIBF_FMT_FASTA) {
+        const uint32_t gt = mask_of(c, ByteTest::Char{'>'}), nl = mask_of(c, ByteTest::NlCr());
+        const uint64_t mine = (gt | nl) ? (gt > nl ? D_GT : D_NL) : D_NONE;
+        uint64_t state = block_excl_scan<uint64_t>(mine, OpLast(), sm, &total);
+        if (!state) state = a.entry[blockIdx.x];
+        m = mark_fasta(c, gt, nl, ws, state == D_GT, i0, begin);
+    } else {
+        const uint32_t nl = mask_of(c, ByteTest::Char{'\n'});
+        const uint64_t line0 = a.entry[blockIdx.x] + block_excl_scan<uint64_t>(__popc(nl), OpSum(), sm, &total);
+        const bool prev_nl = i0 == 0 || (c.valid && __ldg(a.text + i0 - 1) == '\n');
+        m = mark_fastq(c, nl, ws, mask_of(c, ByteTest::Char{'@'}), mask_of(c, ByteTest::Char{'+'}), line0, prev_nl);
+    }
+    if (!EMIT) {                                            // SeqAn's ParseErrors, reported once (the counting pass)
+        const uint32_t foreign = m.seq & ~mask_of(c, ByteTest::Alpha{a.iupac});
+        if (foreign) report(a.g, i0 + __ffs(foreign) - 1, E_ALPHABET);
+        if (m.bad)   report(a.g, i0 + __ffs(m.bad) - 1, E_FQ_LAYOUT);
+    }
+    const uint64_t packed = (uint64_t)__popc(m.rec) | ((uint64_t)__popc(m.seq) << 16) | ((uint64_t)__popc(m.qual) << 32);
+    const uint64_t excl = block_excl_scan<uint64_t>(packed, OpSum(), sm, &total);   // each field at most 8192 per tile
     if (!EMIT) {
         if (threadIdx.x == 0) {
             a.rec[blockIdx.x] = total & 0xffffu; a.seq[blockIdx.x] = (total >> 16) & 0xffffu; a.qual[blockIdx.x] = (total >> 32) & 0xffffu;
         }
         return;
     }
-    r.rec  = a.rec[blockIdx.x]  + (excl & 0xffffu);
-    r.seq  = a.seq[blockIdx.x]  + ((excl >> 16) & 0xffffu);
-    r.qual = a.qual[blockIdx.x] + ((excl >> 32) & 0xffffu);
-    if (FMT == DYIBF_FMT_FASTA) walk_fasta<true>(a, c, i0, begin, state == D_GT, r);
-    else                        walk_fastq<true>(a, c, i0, end, state, prev, r);
+    const uint64_t tile_seq = a.seq[blockIdx.x];
+    const uint32_t my_seq = (uint32_t)(excl >> 16) & 0xffffu, tile_cnt = (uint32_t)(total >> 16) & 0xffffu;
+    uint64_t rec_at = a.rec[blockIdx.x] + (excl & 0xffffu);
+    const uint64_t seq_at = tile_seq + my_seq, qual_at = a.qual[blockIdx.x] + ((excl >> 32) & 0xffffu);
+
+    // limits[r] at every record start
+    for (uint32_t r = m.rec; r; r &= r - 1) {
+        const uint32_t below = (1u << (__ffs(r) - 1)) - 1u;
+        a.out_limits[rec_at++] = a.limit_base + seq_at + __popc(m.seq & below);
+    }
+    if (FMT == DYIBF_FMT_FASTQ) {
+        // SeqAn consumes exactly length(seq) quality characters: at the end of every quality line the totals must agree
+        for (uint32_t q = m.qual_eol; q; q &= q - 1) {
+            const uint32_t j = __ffs(q) - 1, below = (1u << j) - 1u;
+            if (seq_at + __popc(m.seq & below) != qual_at + __popc(m.qual & below)) report(a.g, i0 + j, E_FQ_QUAL);
+        }
+        if (c.valid && i0 + 32 - __clz(c.valid) == end) {   // this thread holds the last byte of the text
+            const uint32_t last = 1u << (31 - __clz(c.valid));
+            if (!(m.late & last) || seq_at + __popc(m.seq) != qual_at + __popc(m.qual))
+                report(a.g, end - 1, (m.late & last) ? E_FQ_QUAL : E_FQ_TRUNC);
+        }
+    }
+    // the tile's sequence characters: staged so that 16-byte chunks of shared memory are 16-byte chunks of the output
+    uint8_t* dst = a.out_seqs + tile_seq;
+    const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    uint32_t k = shift + my_seq;
+    #pragma unroll
+    for (int j = 0; j < IB; ++j) {
+        const bool on = (m.seq >> j) & 1u;
+        if (on) stage[k] = (uint8_t)(c.w[j >> 2] >> (8 * (j & 3)));
+        k += on;
+    }
+    __syncthreads();
+    const uint32_t lo = shift, hi = shift + tile_cnt;
+    uint8_t* dst_al = dst - shift;
+    for (uint32_t b = threadIdx.x * 16u; b < hi; b += IT * 16u) {
+        if (b >= lo && b + 16 <= hi) *reinterpret_cast<uint4*>(dst_al + b) = *reinterpret_cast<const uint4*>(stage + b);
+        else
+            for (uint32_t x = b < lo ? lo : b; x < b + 16 && x < hi; ++x) dst_al[x] = stage[x];
+    }
 }
 
 __global__ void ingest_init_globals(unsigned long long* g)
