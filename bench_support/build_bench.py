@@ -266,6 +266,52 @@ def run_b200(args, B):
         if not torch.equal(words_dev, words_host):
             raise AssertionError("direct-atomics filter != bucketed filter")
 
+    # ---- extra, N > 1 (SURVEY §8(e) "Build"): ONE filter built by all GPUs — rank r adds only its own bin range to its own
+    #      column slice of every block (a self-contained IBF with bins/N bins, same P), then the slices are interleaved into
+    #      the replicated layout with NCCL all-gathers; no OR-reduction anywhere
+    sharded = None
+    if world > 1 and W % world == 0:
+        from dream_yara_b200 import dist as D
+        first, sb, snbits, Wr, _ = D.bin_shard_params(bins, nbits, rank, world)
+        f_host.close()                                                   # frees its scratch; its table becomes the assembly target
+        f_sh = dy.SeqAnBloomFilter(sb, H, K, snbits, device=local)
+        d_bin_sh = torch.arange(sb, dtype=torch.int32, device=dev)
+        def shard_step(c):
+            check(L.dyibf_add_sequences(f_sh._h, C.c_void_p(d_chunks[c].data_ptr() + first * glen), C.c_void_p(d_off.data_ptr()), sb,
+                                        C.c_void_p(d_bin_sh.data_ptr()), ENC_DNA5, MEM_DEVICE, C.c_void_p(stream)))
+        shard_step(order[0])
+        shard_view = D._tensor_from_ptr(L.dyibf_device_words(f_sh._h), P * Wr, dev)
+        D.assemble_replicated(shard_view, bins, nbits, out=words_host)   # warm-up of the collective
+        barrier()
+        e0.record()
+        for s in range(args.warmup, args.warmup + args.steps):
+            shard_step(order[s])
+        e1.record()
+        barrier()
+        e2 = torch.cuda.Event(enable_timing=True)
+        D.assemble_replicated(shard_view, bins, nbits, out=words_host)
+        e2.record()
+        barrier()
+        # every rank must hold the same table, and its own slice of it must be its shard
+        own = words_host.view(P, W)[:, rank * Wr:(rank + 1) * Wr]
+        ok_own = bool(torch.equal(own, shard_view.view(P, Wr)))
+        chk = torch.stack([words_host.sum(), words_host[::4097].sum()]).to(torch.int64)
+        allc = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        ok_same = all(bool(torch.equal(c_, allc[0])) for c_ in allc)
+        t3 = torch.tensor([e0.elapsed_time(e1), e1.elapsed_time(e2)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+        tot_kmers = bins * (glen - K + 1) * args.steps                   # all ranks together add `bins` contigs per step
+        sharded = {"value": tot_kmers / ((float(t3[0]) + float(t3[1])) / 1e3), "unit": args.unit, "scaling": "strong",
+                   "build_ms_per_step": float(t3[0]) / args.steps, "assemble_ms": float(t3[1]),
+                   "assemble_gbs_per_gpu": (world - 1) * P * Wr * 8 / (float(t3[1]) / 1e3) / 1e9,
+                   "bins_per_gpu": sb, "shard_gib": P * Wr * 8 / 2**30, "own_slice_equals_shard": ok_own, "replicas_identical": ok_same,
+                   "note": "one %d-bin filter built by %d GPUs: bin-sharded add (%d bins each) for %d steps, then one "
+                           "all-gather interleave of the %d GiB table; value counts the assembly" % (bins, world, sb, args.steps, args.filter_gib)}
+        if not (ok_own and ok_same):
+            raise AssertionError("assembled filter differs between ranks or from the rank's shard")
+        f_sh.close()
+
     # ---- roofline of the build kernels (scatter + apply, or the direct kernel) against the measured HBM peak.
     # h x (32 B sector read + 32 B sector write) per k-mer for random single-word RMW.  The bucketed
     # build replaces that traffic by h x (4 B record written + 4 B read) + one streaming pass over the table per apply
@@ -286,9 +332,9 @@ def run_b200(args, B):
                 "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": _config(args, world), "clocks": clocks,
                 "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "direct_atomics": direct,
-                "distinct_chunks": n_chunks, "impl": "b200"}
+                "sharded_build": sharded, "distinct_chunks": n_chunks, "impl": "b200"}
         print(json.dumps(line), flush=True)
-    f_dev.close(); f_host.close()
+    f_dev.close(); f_host.close()                                       # close() is idempotent
     for p_ in pinned:
         L.dyibf_host_free(p_)
     if world > 1:

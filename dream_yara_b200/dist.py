@@ -152,3 +152,34 @@ def merge_bin_lists_bin_sharded(offs_local, ids_local, bins_total):
     offs = np.concatenate(offs)
     assert offs.size == bins_total + 1, (offs.size, bins_total)
     return offs, (np.concatenate(ids) if ids else np.zeros(0, dtype=np.uint32))
+
+
+# ---- multi-GPU build (SURVEY §8(e) "Build") ----------------------------------------------------------------------------
+# A bitwise OR over partial 16 GiB tables is not an NCCL reduction.  The exact alternative needs none: bins are
+# independent columns, so rank r builds only its own bin range into its own column slice of every block — a self-contained
+# IBF with bins/G bins and the same P (bin_shard_params) — and the slices are then interleaved into the replicated layout
+# with all-gathers (assemble_replicated), or simply stay where they are when the filter is queried bin-sharded.
+def shard_bin_ids(bin_ids, first_bin):
+    """bin ids of a rank's sequences relative to its shard (bin - first_bin)"""
+    return (np.asarray(bin_ids, dtype=np.int64) - int(first_bin)).astype(np.uint32)
+
+
+def assemble_replicated(shard_words, bins, nbits, out=None, piece_bytes=1 << 30):
+    """Every rank holds its column slice [P, W/G] (flat int64 tensor, P*W/G words); returns the full table [P*W] on every
+    rank, block p = [slice_0[p] | slice_1[p] | ...] — the reference's layout.  All-gathers of about piece_bytes of the
+    full table at a time; no reduction."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    _, _, _, Wr, P = bin_shard_params(bins, nbits, rank, world)
+    W = Wr * world
+    shard = shard_words.view(-1)[: P * Wr].view(P, Wr)
+    full = out if out is not None else torch.empty(P * W, dtype=shard.dtype, device=shard.device)
+    fv = full.view(-1)[: P * W].view(P, W)
+    step = max(1, int(piece_bytes) // (8 * W))
+    for a in range(0, P, step):
+        b = min(P, a + step)
+        mine = shard[a:b].contiguous()
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine)
+        for r, part in enumerate(parts):
+            fv[a:b, r * Wr:(r + 1) * Wr] = part
+    return full

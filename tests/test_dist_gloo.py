@@ -84,6 +84,17 @@ def _worker(rank, world, port, paired, q):
         so, si = o.compact(rows_slice, sb)
         offs2, ids2 = D.merge_bin_lists_bin_sharded(so, si, p.bins)
         assert np.array_equal(offs2, want_offs) and np.array_equal(ids2, want_ids)
+
+        # ---- sharded build: every rank adds only its own bins to its own column slice, slices are interleaved
+        bw = o.new_words(sp)
+        rng = np.random.default_rng(42)
+        contigs = [rng.integers(0, 4, 1500).astype(np.uint8) for _ in range(p.bins)]       # the contigs of _workload
+        mine_bins = np.arange(first, first + sb)
+        for b_, lb in zip(mine_bins, D.shard_bin_ids(mine_bins, first)):
+            o.add_kmers(bw, sp, contigs[int(b_)], int(lb))
+        assert np.array_equal(bw[: shard.size], shard)                                   # = the slice of the one-process build
+        full = D.assemble_replicated(torch.from_numpy(bw[: sp.P * sp.W].view(np.int64).copy()), p.bins, p.nbits, piece_bytes=4096)
+        assert np.array_equal(full.numpy().view(np.uint64), words[: p.P * p.W])
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
         import traceback

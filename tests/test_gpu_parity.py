@@ -418,3 +418,30 @@ def test_bucketed_build_wide_records_equals_direct(dy):
         tables.append(words)
     assert int(torch.count_nonzero(tables[0])) > 100_000_000
     assert torch.equal(tables[0], tables[1])
+
+
+def test_bin_sharded_build_equals_column_slices(dy, oracle):
+    """SURVEY §8(e) "Build": what rank r of G builds — its own bin range into a self-contained filter with bins/G bins and
+    the same P — is exactly its column slice of the one-process filter (here the G shards are built one after the other on
+    one GPU; the all-gather interleave is covered by tests/test_dist_gloo.py)."""
+    from dream_yara_b200 import dist as D
+    rng = np.random.default_rng(77)
+    bins, h, k, nbits, G = 512, 3, 18, (1 << 25) + 256, 4
+    contigs = [rng.integers(0, 5 if b % 9 == 0 else 4, 3000).astype(np.uint8) for b in range(bins)]
+    full = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    full.addSequences(contigs, np.arange(bins))
+    words = full.download_words()
+    p = oracle.params(bins, h, k, nbits)
+    want = oracle.new_words(p)
+    for b, c in enumerate(contigs):
+        oracle.add_kmers(want, p, c, b)
+    assert np.array_equal(words[: p.P * p.W], want[: p.P * p.W])
+    for r in range(G):
+        first, sb, snbits, Wr, P = D.bin_shard_params(bins, nbits, r, G)
+        f = dy.SeqAnBloomFilter(sb, h, k, snbits)
+        assert f._noOfHashPos == P == full._noOfHashPos
+        mine = np.arange(first, first + sb)
+        f.addSequences([contigs[int(b)] for b in mine], D.shard_bin_ids(mine, first))
+        assert np.array_equal(f.download_words()[: P * Wr], D.extract_bin_shard(words, bins, nbits, r, G))
+        f.close()
+    full.close()
