@@ -121,3 +121,50 @@ def test_build_cli_kmer_direct(tools, golden, oracle, dy, tmp_path):
     codes = [oracle.encode_ascii(x) for x in reads[:200]]
     assert np.array_equal(g2.whichBinsBatch(reads[:200], 45, group=2, derive_rc=True), oracle.kdx_rows(words, p, codes, 45))
     f.close(); g2.close()
+
+
+@pytest.mark.gpu
+def test_filter_reads_cli_vs_reference_mapper_output(tools, dy, golden, tmp_path):
+    """tools/dyibf_filter_reads = the filtering stage of dream_yara_mapper: the `-vv` per-bin sizes, "Avg reads per bin"
+    and the per-bin lists of the reference's own mapper run on its test data, single- and
+    paired-end, FASTA and gzipped FASTQ input, one batch and several."""
+    exe = os.path.join(TOOLS, "bin", "dyibf_filter_reads")
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    f = dy.SeqAnBloomFilter(64, 2, 19, ka.GIB_BITS)
+    f.addSequences(genomes, np.arange(64))
+    filt = tmp_path / "ka1.filter"
+    assert f.save(filt)
+    f.close()
+    _write_fasta(tmp_path / "reads.fa", [("r%d" % i, r) for i, r in enumerate(reads)], width=60)
+    out = tmp_path / "se.txt"
+    r = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-vv", "-o", str(out), str(tmp_path / "reads.fa")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    sizes = [int(l.split("\t")[1]) for l in r.stderr.splitlines() if l.startswith("bin ")]
+    bo, ids = golden["ka5_se_bin_offsets"], golden["ka5_se_read_ids"]
+    assert sizes == [int(bo[b + 1] - bo[b]) for b in range(64)] and sizes[0] == 173 and sum(sizes) == 6538
+    assert "Avg reads per bin:\t\t102.156" in r.stderr                  # the reference mapper's own line
+    lines = [l.split() for l in open(out)]
+    assert [int(l[2]) for l in lines] == sorted(sizes, reverse=True)      # sortedBins order
+    for l in lines:
+        b = int(l[1])
+        assert [int(x) for x in l[3:]] == list(ids[int(bo[b]):int(bo[b + 1])])
+    # paired-end, gzipped FASTQ mates (KA5: pair j = reads j and j + 3200)
+    for name, part, q in (("m1.fq.gz", reads[:3200], b"I"), ("m2.fq.gz", reads[3200:], b"@")):
+        with gzip.open(tmp_path / name, "wb") as fh:
+            for i, s in enumerate(part):
+                fh.write(b"@p%d\n%s\n+\n%s\n" % (i, s, q * len(s)))
+    r = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-vv", str(tmp_path / "m1.fq.gz"), str(tmp_path / "m2.fq.gz")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    sizes = [int(l.split("\t")[1]) for l in r.stderr.splitlines() if l.startswith("bin ")]
+    bo = golden["ka5_pe_bin_offsets"]
+    assert sizes == [int(bo[b + 1] - bo[b]) for b in range(64)]
+    assert "Avg reads per bin:\t\t204.312" in r.stderr
+    # several batches (-rb 1000): ids are batch-local, sizes add up
+    r = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-rb", "1000", "-vv", str(tmp_path / "reads.fa")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    sizes = np.array([int(l.split("\t")[1]) for l in r.stderr.splitlines() if l.startswith("bin ")]).reshape(7, 64)
+    assert int(sizes.sum()) == 6538
+    want = ka.bits_from_rows(golden["ka1_rows"], 64)
+    assert np.array_equal(sizes[2], want[2000:3000].sum(axis=0))
+    r = subprocess.run([exe, "-fi", str(tmp_path / "nope.filter"), str(tmp_path / "reads.fa")], capture_output=True, text=True)
+    assert r.returncode == 1 and "could not be read" in r.stderr

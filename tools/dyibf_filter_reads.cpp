@@ -1,0 +1,203 @@
+// tools/dyibf_filter_reads.cpp — the filtering stage of dream_yara_mapper as a standalone program on top of the C ABI
+// (include/dyibf.h): what runDisMapper does between loading the filter and handing read sets to the per-bin mappers
+// (temehi/dream_yara src/d_mapper.h:900-959, :308-387, :843-854), and nothing of the mapping itself.
+//
+//   dyibf_filter_reads -fi <FILTER> [-e 5] [-rb 100000] [-v|-vv] [-o lists.txt] [--device 0] <READS> [<MATES>]
+//
+// Per batch of -rb reads (pairs), as the mapper loads them (src/mapper.h:109, d_mapper.h:870-896): the records are
+// tokenised ON THE DEVICE (dyibf_parse_records = SeqAn's readRecords; the host only reads / inflates the file), the
+// threshold comes from the batch's average read length (d_mapper.h:313-315), dyibf_classify fills origReadIdMap.
+// -vv prints "bin <b>\t<size>" per batch (:380-386); -v the timers and "Avg reads per bin" (:947-958); -o writes, per
+// batch, one line per bin in sortedBins order (:843-854): "<batch> <bin> <n> id id ...".
+#include <zlib.h>
+
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "dyibf.h"
+
+namespace {
+
+double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+[[noreturn]] void usage(const char * msg)
+{
+    if (msg) std::cerr << "dyibf_filter_reads: " << msg << "\n";
+    std::cerr << "usage: dyibf_filter_reads -fi FILTER [OPTIONS] <READS FILE> [<MATES FILE>]\n"
+                 "  -fi, --bloom-filter FILE   *.filter (bloom or kmer_direct; the kind is in the file)\n"
+                 "  -e,  --error-rate INT      percent, 0..10 (default 5)\n"
+                 "  -rb, --reads-batch INT     reads (pairs) per batch, 1000..5000000 (default 100000)\n"
+                 "  -o,  --output-file FILE    per-bin read id lists\n"
+                 "  -v / -vv                   statistics / per-bin list sizes\n"
+                 "       --device INT          CUDA device (default 0)\n";
+    exit(msg ? 1 : 0);
+}
+
+bool endsWith(const std::string & s, const char * suf)
+{
+    const std::string t = suf;
+    return s.size() >= t.size() && s.compare(s.size() - t.size(), t.size(), t) == 0;
+}
+
+// SeqFileIn picks the format from the extension; the content decides when it says nothing
+int formatOf(std::string path, const std::vector<char> & data)
+{
+    if (endsWith(path, ".gz")) path.resize(path.size() - 3);
+    if (endsWith(path, ".fq") || endsWith(path, ".fastq")) return DYIBF_FMT_FASTQ;
+    if (endsWith(path, ".fa") || endsWith(path, ".fasta") || endsWith(path, ".fna")) return DYIBF_FMT_FASTA;
+    return !data.empty() && data[0] == '@' ? DYIBF_FMT_FASTQ : DYIBF_FMT_FASTA;
+}
+
+void readAll(const std::string & path, std::vector<char> & out)
+{
+    gzFile gz = gzopen(path.c_str(), "rb");                       // plain files pass through
+    if (!gz) { std::cerr << "Unable to open reads file: " << path << std::endl; exit(1); }
+    gzbuffer(gz, 1 << 20);
+    out.clear();
+    std::vector<char> buf(8 << 20);
+    int n;
+    while ((n = gzread(gz, buf.data(), (unsigned)buf.size())) > 0) out.insert(out.end(), buf.begin(), buf.begin() + n);
+    gzclose(gz);
+    if (n < 0) { std::cerr << "Error while reading: " << path << std::endl; exit(1); }
+}
+
+struct Records { std::vector<uint8_t> seqs; std::vector<uint64_t> limits; };
+
+void parse(int device, const std::string & path, Records & r)
+{
+    std::vector<char> text;
+    readAll(path, text);
+    uint64_t n = 0, nb = 0;
+    const int fmt = formatOf(path, text);
+    int rc = dyibf_parse_records(device, text.data(), text.size(), fmt, DYIBF_ALPHA_DNA5, nullptr, 0, nullptr, 0, 0, &n, &nb, DYIBF_MEM_HOST, nullptr);
+    if (rc == DYIBF_OK)
+    {
+        r.seqs.resize(nb + 1); r.limits.resize(n + 1);
+        rc = dyibf_parse_records(device, text.data(), text.size(), fmt, DYIBF_ALPHA_DNA5, r.seqs.data(), nb, r.limits.data(), n, 0, &n, &nb,
+                                 DYIBF_MEM_HOST, nullptr);
+    }
+    if (rc != DYIBF_OK) { std::cerr << path << ": " << dyibf_last_error() << std::endl; exit(1); }
+}
+
+} // namespace
+
+int main(int argc, char ** argv)
+{
+    std::string filterFile, outFile;
+    std::vector<std::string> inputs;
+    int e = 5, verbose = 0, device = 0;
+    uint64_t readsBatch = 100000;
+    for (int i = 1; i < argc; ++i)
+    {
+        const std::string a = argv[i];
+        auto value = [&](const char * name) -> std::string { if (i + 1 >= argc) usage((std::string("missing value for ") + name).c_str()); return argv[++i]; };
+        if (a == "-h" || a == "--help") usage(nullptr);
+        else if (a == "-v" || a == "--verbose") verbose = std::max(verbose, 1);
+        else if (a == "-vv" || a == "--very-verbose") verbose = 2;
+        else if (a == "-fi" || a == "--bloom-filter") filterFile = value("-fi");
+        else if (a == "-o" || a == "--output-file") outFile = value("-o");
+        else if (a == "-e" || a == "--error-rate") { e = atoi(value("-e").c_str()); if (e < 0 || e > 10) usage("-e out of range 0..10"); }
+        else if (a == "-rb" || a == "--reads-batch") { readsBatch = strtoull(value("-rb").c_str(), nullptr, 10); if (readsBatch < 1000 || readsBatch > 5000000) usage("-rb out of range"); }
+        else if (a == "--device") device = atoi(value("--device").c_str());
+        else if (!a.empty() && a[0] == '-') usage(("unknown option " + a).c_str());
+        else inputs.push_back(a);
+    }
+    if (filterFile.empty() || inputs.empty() || inputs.size() > 2) usage("need -fi FILTER and one or two reads files");
+    const bool paired = inputs.size() == 2;
+
+    const double t0 = now();
+    dyibf_filter * filter = nullptr;
+    if (dyibf_load_file(filterFile.c_str(), device, &filter) != DYIBF_OK)
+    {
+        std::cerr << dyibf_last_error() << std::endl;                     // d_bloom_filter.h:81-85: message, exit(1)
+        return 1;
+    }
+    dyibf_params prm;
+    dyibf_get_params(filter, &prm);
+    const double loadFilter = now() - t0;
+
+    const double t1 = now();
+    Records m1, m2;
+    parse(device, inputs[0], m1);
+    if (paired)
+    {
+        parse(device, inputs[1], m2);
+        if (m2.limits.size() != m1.limits.size()) { std::cerr << "The two reads files hold different numbers of records." << std::endl; return 1; }
+    }
+    const uint64_t nReads = m1.limits.size() - 1;                        // reads, or pairs
+    const double loadReads = now() - t1;
+
+    std::ofstream out;
+    if (!outFile.empty()) { out.open(outFile); if (!out) { std::cerr << "Unable to open " << outFile << std::endl; return 1; } }
+    double filterReads = 0;
+    uint64_t filteredReads = 0, batchNo = 0;
+    std::vector<uint8_t> seqs; std::vector<uint64_t> limits, binOffsets(prm.bins + 1); std::vector<uint32_t> ids, order(prm.bins);
+    for (uint64_t first = 0; first < nReads; first += readsBatch, ++batchNo)
+    {
+        const double tb = now();
+        const uint64_t n = std::min(readsBatch, nReads - first);
+        // the batch's forward read set: [reads] or [mates 1 | mates 2] (src/file_pair.h:82-88)
+        seqs.clear(); limits.assign(1, 0);
+        for (const Records * r : {(const Records *)&m1, paired ? (const Records *)&m2 : (const Records *)nullptr})
+        {
+            if (!r) continue;
+            const uint64_t b0 = r->limits[first], b1 = r->limits[first + n];
+            const uint64_t base = seqs.size();
+            seqs.insert(seqs.end(), r->seqs.begin() + b0, r->seqs.begin() + b1);
+            for (uint64_t i = 1; i <= n; ++i) limits.push_back(base + r->limits[first + i] - b0);
+        }
+        // clasifyLoadedReads, d_mapper.h:308-375
+        const uint64_t nSeqs = limits.size() - 1;                        // forward sequences; the set the reference sees is twice that
+        const uint16_t avgReadLen = (uint16_t)(nSeqs ? limits.back() / nSeqs : 0);   // lengthSum / (2 numReads), both doubled by the rc half
+        const uint16_t threshold = dyibf_threshold(e, prm.kmer, avgReadLen);
+        if (threshold == 0)
+            std::cerr << "[WARNING!] 0 k-mer is required to filter a read!\nAll reads will pass filteration and be mapped everywhere.\n "
+                         "This will be extremly slow.\n Choose an approprate error rate based on kmer size and read length\n";
+        if (seqs.empty()) seqs.push_back(0);
+        uint64_t total = 0;
+        ids.resize(std::max<uint64_t>(ids.size(), 4 * n));
+        int rc = dyibf_classify(filter, seqs.data(), limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, threshold,
+                                binOffsets.data(), ids.data(), ids.size(), &total);
+        if (rc == DYIBF_ERR_CAPACITY)
+        {
+            ids.resize(total);
+            rc = dyibf_classify_fetch(filter, binOffsets.data(), ids.data(), ids.size(), &total);
+        }
+        if (rc != DYIBF_OK) { std::cerr << dyibf_last_error() << std::endl; return 1; }
+        filterReads += now() - tb;
+        // threshold 0: the reference pushes every read id (of the SE numbering) to every bin first and then still runs the loop (:320-333)
+        const uint64_t pre = threshold == 0 ? (paired ? 2 * n : n) : 0;
+        if (verbose > 1)
+            for (uint32_t b = 0; b < prm.bins; ++b)
+                std::cerr << "bin " << b << "\t" << pre + binOffsets[b + 1] - binOffsets[b] << std::endl;
+        for (uint32_t b = 0; b < prm.bins; ++b) filteredReads += (pre + binOffsets[b + 1] - binOffsets[b]) * (paired ? 2 : 1);   // :442
+        if (out.is_open())
+        {
+            dyibf_sorted_bins(binOffsets.data(), prm.bins, order.data());
+            for (uint32_t b : order)
+            {
+                out << batchNo << ' ' << b << ' ' << pre + binOffsets[b + 1] - binOffsets[b];
+                for (uint64_t i = 0; i < pre; ++i) out << ' ' << i;
+                for (uint64_t i = binOffsets[b]; i < binOffsets[b + 1]; ++i) out << ' ' << ids[i];
+                out << '\n';
+            }
+        }
+    }
+    if (verbose > 0)
+    {
+        const double total = (now() - t0) / 100.0;
+        std::cerr << "\nFilter loading time:\t\t" << loadFilter << " sec\t\t" << loadFilter / total << " %" << std::endl;
+        std::cerr << "Reads loading time:\t\t" << loadReads << " sec\t\t" << loadReads / total << " %" << std::endl;
+        std::cerr << "Reads filtering time:\t\t" << filterReads << " sec\t\t" << filterReads / total << " %" << std::endl;
+        std::cerr << "Reads count:\t\t\t" << nReads * (paired ? 2 : 1) << std::endl;
+        std::cerr << "Avg reads per bin:\t\t" << (double)filteredReads / prm.bins << std::endl;
+    }
+    dyibf_destroy(filter);
+    return 0;
+}
