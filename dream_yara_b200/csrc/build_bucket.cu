@@ -29,6 +29,8 @@
 #include "dyibf_internal.h"
 #include "ibf_hash.cuh"
 
+#include <cstdlib>
+
 namespace dyibf {
 
 static const uint32_t FULL          = 0xffffffffu;
@@ -141,12 +143,14 @@ __device__ __forceinline__ uint64_t load_cg(const uint64_t* p) { return (uint64_
 //            unused lines of the last chunk are filled with copies of a record of the same bucket — OR is idempotent,
 //            so a duplicate update is harmless and the consumer can read [0, cursor) without holes.
 // A bucket whose cursor passed its capacity is full: its lines are OR-ed straight into the filter, 32 atomics per line.
-static const uint32_t CHUNK_LINES = 8;                 // lines (of 32 records) per reservation
+static const uint32_t CHUNK_LINES = 8;                 // lines (of 32 records) per reservation; a power of two
 static const uint32_t LINE_NONE   = 0xffffffffu;
+static const uint32_t WARP_STAGE  = 1024 + 32;        // records of shared memory per warp: 32 lines of 32 + the 32 fill counts
 
-template <typename Rec>
+template <typename Rec, bool MATCH = false>
 struct Splitter {
     Rec* stage;                   // this warp's [32 buckets][32 records]
+    uint32_t* sfill;              // MATCH: this warp's 32 fill counts in shared memory (instead of lane b's `fill`)
     Rec* out;                     // bucket 0; bucket b starts at out + b * cap
     unsigned long long* cursors;  // bucket b's fill count in records (a multiple of 32 * CHUNK_LINES)
     uint64_t* filter;
@@ -154,14 +158,16 @@ struct Splitter {
     uint32_t cap, shift;          // records per bucket; log2(words per bucket range): record = word-in-range << 6 | bit
     uint32_t lane, lt_mask;
     LaneBits lb;
-    uint32_t fill, line, left;    // lane b: bucket b
+    uint32_t fill, line;          // lane b: bucket b.  line = next line of the WHOLE out array (b * cap / 32 + line in bucket)
 
     __device__ __forceinline__ void init(Rec* stage_, Rec* out_, unsigned long long* cursors_, uint32_t cap_, uint64_t* filter_,
                                          uint32_t shift_, uint64_t word0_, uint32_t lane_)
     {
         stage = stage_; out = out_; cursors = cursors_; cap = cap_; filter = filter_; shift = shift_; word0 = word0_;
         lane = lane_; lt_mask = (1u << lane_) - 1u; lb = lane_bits(lane_);
-        fill = 0; line = 0; left = 0;
+        fill = 0; line = 0;
+        sfill = reinterpret_cast<uint32_t*>(stage_ + 1024);          // the tail of this warp's WARP_STAGE records
+        if (MATCH) { sfill[lane_] = 0; __syncwarp(); }
     }
 
     __device__ __forceinline__ void direct(uint32_t b, Rec rec) const
@@ -173,23 +179,48 @@ struct Splitter {
     // write bucket b's staged line (all 32 lanes call this together)
     __device__ __forceinline__ void flush(uint32_t b)
     {
-        if (__shfl_sync(FULL, left, b) == 0 && __shfl_sync(FULL, line, b) != LINE_NONE) {
+        // chunks are CHUNK_LINES lines long and aligned (cap / 32 is a multiple of CHUNK_LINES), so "the chunk is used up"
+        // (or none was reserved yet) is line % CHUNK_LINES == 0; LINE_NONE (all ones) never looks like that
+        uint32_t ln = __shfl_sync(FULL, line, b);
+        if ((ln & (CHUNK_LINES - 1)) == 0) {
             if (lane == b) {
                 const unsigned long long c = atomicAdd(&cursors[b], (unsigned long long)(32 * CHUNK_LINES));
-                if (c >= cap) line = LINE_NONE; else { line = (uint32_t)(c >> 5); left = CHUNK_LINES; }
+                line = c >= cap ? LINE_NONE : b * (cap >> 5) + (uint32_t)(c >> 5);
             }
+            ln = __shfl_sync(FULL, line, b);
         }
-        const uint32_t ln = __shfl_sync(FULL, line, b);
         const Rec v = stage[b * 32 + lane];
-        if (ln != LINE_NONE) out[(uint64_t)b * cap + (uint64_t)ln * 32 + lane] = v;
+        if (ln != LINE_NONE) out[(uint64_t)ln * 32 + lane] = v;         // 32 buckets x cap / 32 lines fit 32 bits
         else direct(b, v);
-        if (lane == b && ln != LINE_NONE) { ++line; --left; }
+        if (lane == b && ln != LINE_NONE) ++line;
     }
 
     __device__ __forceinline__ void push(bool valid, uint32_t key, Rec rec)
     {
-        uint32_t peers;
-        const uint32_t mine = match_both(key, valid, lb, &peers);
+        if (MATCH) {
+            // one MATCH instead of five votes: my peers are the valid lanes with my key; the lowest of them keeps the
+            // bucket's fill count (shared memory, one word per bucket)
+            const uint32_t peers = __match_any_sync(FULL, valid ? key : 32u + lane);
+            const uint32_t base = valid ? sfill[key] : 0u;
+            const uint32_t cnt = __popc(peers), at = base + __popc(peers & lt_mask);          // at: 0 .. 62
+            const bool leader = valid && (peers & lt_mask) == 0;
+            __syncwarp();
+            if (leader) sfill[key] = (base + cnt) & 31u;
+            if (valid && at < 32) stage[key * 32 + at] = rec;
+            __syncwarp();
+            uint32_t m = __ballot_sync(FULL, leader && base + cnt >= 32);
+            while (m) {
+                const uint32_t b = __shfl_sync(FULL, key, __ffs(m) - 1);
+                m &= m - 1;
+                flush(b);
+            }
+            __syncwarp();
+            if (valid && at >= 32) stage[key * 32 + at - 32] = rec;
+            return;
+        }
+        // lane b learns which valid lanes hold key b (five votes); my peers are what the lane named by my key learned
+        const uint32_t mine = match_mine(key, valid, lb);
+        const uint32_t peers = __shfl_sync(FULL, mine, key);
         const uint32_t at = __shfl_sync(FULL, fill, key) + __popc(peers & lt_mask);      // 0 .. 62
         const uint32_t total = fill + __popc(mine);                                      // lane b: bucket b after this push
         if (valid && at < 32) stage[key * 32 + at] = rec;
@@ -210,17 +241,19 @@ struct Splitter {
         __syncwarp();
         #pragma unroll 1
         for (uint32_t b = 0; b < 32; ++b) {
-            const uint32_t f = __shfl_sync(FULL, fill, b);
+            const uint32_t f = MATCH ? sfill[b] : __shfl_sync(FULL, fill, b);
             if (lane < f) direct(b, stage[b * 32 + lane]);
-            const uint32_t lf = __shfl_sync(FULL, left, b), ln = __shfl_sync(FULL, line, b);
-            if (lf > 0 && ln != LINE_NONE) {
+            const uint32_t ln = __shfl_sync(FULL, line, b);
+            const uint32_t lf = ln == LINE_NONE ? 0u : (CHUNK_LINES - (ln & (CHUNK_LINES - 1))) & (CHUNK_LINES - 1);   // lines left of the chunk
+            if (lf > 0) {
                 // the chunk was reserved for a line that was then written, so line ln-1 exists and belongs to this warp
-                Rec* bucket = out + (uint64_t)b * cap;
-                const Rec pad = load_cg(bucket + (uint64_t)(ln - 1) * 32);
-                for (uint32_t j = 0; j < lf; ++j) bucket[(uint64_t)(ln + j) * 32 + lane] = pad;
+                const Rec pad = load_cg(out + (uint64_t)(ln - 1) * 32);
+                for (uint32_t j = 0; j < lf; ++j) out[(uint64_t)(ln + j) * 32 + lane] = pad;
+                if (lane == b) line += lf;
             }
         }
-        fill = 0; left = 0;
+        fill = 0;
+        if (MATCH) { __syncwarp(); sfill[lane] = 0; __syncwarp(); }
     }
 };
 
@@ -229,7 +262,7 @@ struct Splitter {
 // Two-level plans call it with shift = R + 5 (super-buckets), single-level plans with shift = R (final buckets).
 // A warp claims items of SPLIT1_ITEM / 32 groups of 32 packed words; the loads of the next group (sequence table,
 // packed words, bin) are issued before the current group's 96 x 32 updates are pushed.
-template <int H, typename Rec>
+template <int H, typename Rec, bool MATCH>
 __global__ void __launch_bounds__(256) split1_kernel(const HashParams hp, uint64_t* __restrict__ filter,
         const uint64_t* __restrict__ packed, const SeqMeta* __restrict__ meta, const uint32_t* __restrict__ bin_ids,
         uint32_t n_seqs, uint64_t word_begin, uint64_t total_words, uint32_t shift, uint32_t cap1,
@@ -238,8 +271,8 @@ __global__ void __launch_bounds__(256) split1_kernel(const HashParams hp, uint64
     // packed words [word_begin, total_words) of the batch; word_begin is a multiple of SPLIT1_ITEM
     extern __shared__ __align__(16) unsigned char split_smem[];
     const uint32_t lane = threadIdx.x & 31;
-    Splitter<Rec> sp;
-    sp.init(reinterpret_cast<Rec*>(split_smem) + (threadIdx.x >> 5) * 1024, out, cursors1, cap1, filter, shift, 0, lane);
+    Splitter<Rec, MATCH> sp;
+    sp.init(reinterpret_cast<Rec*>(split_smem) + (threadIdx.x >> 5) * WARP_STAGE, out, cursors1, cap1, filter, shift, 0, lane);
     const uint32_t h = H ? H : hp.h;
     const uint64_t low_mask = (1ull << shift) - 1;
     const uint64_t n_items = (total_words - word_begin + SPLIT1_ITEM - 1) / SPLIT1_ITEM;
@@ -308,14 +341,13 @@ __device__ __forceinline__ void load_batch(RecBatch<Rec>& b, const Rec* __restri
         } else {
             b.r[v * 2 + 0] = ((uint64_t)x.y << 32) | x.x; b.r[v * 2 + 1] = ((uint64_t)x.w << 32) | x.z;
         }
-        #pragma unroll
-        for (int e = 0; e < RecBatch<Rec>::PER_VEC; ++e)
-            if (first + e < end) vm |= 1u << (v * RecBatch<Rec>::PER_VEC + e);
+        // `end` is a multiple of 32 records, a vector never straddles it
+        if (first < end) vm |= ((1u << RecBatch<Rec>::PER_VEC) - 1u) << (v * RecBatch<Rec>::PER_VEC);
     }
     *valid_mask = vm;
 }
 
-template <typename Rec>
+template <typename Rec, bool MATCH>
 __global__ void __launch_bounds__(256) split2_kernel(uint64_t* __restrict__ filter, const Rec* __restrict__ in,
         const unsigned long long* __restrict__ cursors1, uint64_t cap1, uint32_t n_super, uint32_t R, uint32_t cap,
         uint32_t* __restrict__ out, unsigned long long* __restrict__ cursors, unsigned long long* __restrict__ work_counters)
@@ -323,8 +355,8 @@ __global__ void __launch_bounds__(256) split2_kernel(uint64_t* __restrict__ filt
     extern __shared__ __align__(16) unsigned char split_smem[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t sb = (uint32_t)((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) % n_super);
-    Splitter<uint32_t> sp;
-    sp.init(reinterpret_cast<uint32_t*>(split_smem) + (threadIdx.x >> 5) * 1024, out + (uint64_t)sb * 32 * cap, cursors + sb * 32,
+    Splitter<uint32_t, MATCH> sp;
+    sp.init(reinterpret_cast<uint32_t*>(split_smem) + (threadIdx.x >> 5) * WARP_STAGE, out + (uint64_t)sb * 32 * cap, cursors + sb * 32,
             cap, filter, R, (uint64_t)sb << (R + 5), lane);
     unsigned long long n = cursors1[sb];
     if (n > cap1) n = cap1;
@@ -391,6 +423,14 @@ __global__ void __launch_bounds__(256) bucket_apply_kernel(uint64_t* __restrict_
 }
 
 // ---- geometry and launchers --------------------------------------------------------------------------------------
+// DYIBF_SPLIT_MATCH=1 selects the MATCH.ANY ranking of the Splitter instead of the five votes (measured slower on B200:
+// split2 67.5 ms vs 55.1 ms per 12.3 G records — kept as a switch for the next architecture); read once
+static bool split_use_match()
+{
+    static const bool v = [] { const char* e = getenv("DYIBF_SPLIT_MATCH"); return e && e[0] == '1'; }();
+    return v;
+}
+
 bool bucket_plan(uint64_t data_words, uint64_t budget_bytes, BucketPlan* p)
 {
     uint32_t R = 21;                                              // 2^21 words = 16 MiB regions
@@ -420,13 +460,16 @@ static cudaError_t split1_launch(const HashParams& hp, uint64_t* filter, const u
                                  unsigned long long* work_counter, unsigned blocks, cudaStream_t st)
 {
     dim3 grid(blocks), block(256);
-    const size_t smem = 8 * 1024 * sizeof(Rec);
+    const size_t smem = 8 * WARP_STAGE * sizeof(Rec);
+    const bool match = split_use_match();
 #define DYIBF_S1(HH) do { \
         if (smem > 48 * 1024) { \
-            cudaError_t ea = cudaFuncSetAttribute(split1_kernel<HH, Rec>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            cudaError_t ea = cudaFuncSetAttribute(split1_kernel<HH, Rec, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            if (ea == cudaSuccess) ea = cudaFuncSetAttribute(split1_kernel<HH, Rec, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
             if (ea != cudaSuccess) return ea; \
         } \
-        split1_kernel<HH, Rec><<<grid, block, smem, st>>>(hp, filter, packed, meta, bin_ids, n_seqs, word_begin, total_words, shift, cap1, out, cursors1, work_counter); \
+        if (match) split1_kernel<HH, Rec, true><<<grid, block, smem, st>>>(hp, filter, packed, meta, bin_ids, n_seqs, word_begin, total_words, shift, cap1, out, cursors1, work_counter); \
+        else       split1_kernel<HH, Rec, false><<<grid, block, smem, st>>>(hp, filter, packed, meta, bin_ids, n_seqs, word_begin, total_words, shift, cap1, out, cursors1, work_counter); \
     } while (0)
     switch (hp.h) {
         case 2: DYIBF_S1(2); break;
@@ -477,13 +520,13 @@ cudaError_t launch_bucket_split2(uint64_t* filter, const BucketPlan& p, void* re
     uint64_t blocks = (((fill1 + SPLIT2_ITEM - 1) / SPLIT2_ITEM) * p.n_super + 7) / 8;
     if (blocks > 148ull * 6) blocks = 148ull * 6;
     if (blocks < 4) blocks = 4;                                    // 32 warps: every super-bucket has at least one
-    const size_t smem = 8 * 1024 * sizeof(uint32_t);
-    if (p.rec1_bytes == 8)
-        split2_kernel<uint64_t><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const uint64_t*>(base + p.bytes_final),
-            cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters);
-    else
-        split2_kernel<uint32_t><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const uint32_t*>(base + p.bytes_final),
-            cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters);
+    const size_t smem = 8 * WARP_STAGE * sizeof(uint32_t);
+    const bool match = split_use_match();
+#define DYIBF_S2(REC, M) split2_kernel<REC, M><<<(unsigned)blocks, 256, smem, st>>>(filter, reinterpret_cast<const REC*>(base + p.bytes_final), \
+            cursors + p.n_regions, p.cap1, p.n_super, p.R, (uint32_t)p.cap, reinterpret_cast<uint32_t*>(base), cursors, work_counters)
+    if (p.rec1_bytes == 8) { if (match) DYIBF_S2(uint64_t, true); else DYIBF_S2(uint64_t, false); }
+    else                   { if (match) DYIBF_S2(uint32_t, true); else DYIBF_S2(uint32_t, false); }
+#undef DYIBF_S2
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     return cudaMemsetAsync(cursors + p.n_regions, 0, 32 * sizeof(unsigned long long), st);
