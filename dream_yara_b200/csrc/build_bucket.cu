@@ -407,18 +407,20 @@ __global__ void __launch_bounds__(256) bucket_apply_kernel(uint64_t* __restrict_
             asm volatile("prefetch.global.L2 [%0];" :: "l"(region + line * 16));
     }
     const uint32_t* rec = records + (uint64_t)r * cap;
+    // a record (64-bit word << 6 | bit) is also (32-bit word << 5 | bit) of the same little-endian table: 32-bit REDs
+    unsigned int* region32 = reinterpret_cast<unsigned int*>(region);
     // four records per load (buckets are 128-byte aligned), streaming: the records are read once
     const uint64_t end4 = begin + ((end - begin) & ~3ull);
     for (uint64_t i = begin + 4ull * threadIdx.x; i < end4; i += 4 * 256) {
         const uint4 v = __ldcs(reinterpret_cast<const uint4*>(rec + i));
-        atomicOr(region + (v.x >> 6), 1ull << (v.x & 63u));
-        atomicOr(region + (v.y >> 6), 1ull << (v.y & 63u));
-        atomicOr(region + (v.z >> 6), 1ull << (v.z & 63u));
-        atomicOr(region + (v.w >> 6), 1ull << (v.w & 63u));
+        atomicOr(region32 + (v.x >> 5), 1u << (v.x & 31u));
+        atomicOr(region32 + (v.y >> 5), 1u << (v.y & 31u));
+        atomicOr(region32 + (v.z >> 5), 1u << (v.z & 31u));
+        atomicOr(region32 + (v.w >> 5), 1u << (v.w & 31u));
     }
     for (uint64_t i = end4 + threadIdx.x; i < end; i += 256) {
         const uint32_t v = __ldcs(rec + i);
-        atomicOr(region + (v >> 6), 1ull << (v & 63u));
+        atomicOr(region32 + (v >> 5), 1u << (v & 31u));
     }
 }
 
