@@ -4,7 +4,7 @@
 Workload (BASELINE.json configs[1], "cfg2"): synthetic 1024-bin, 16 GiB IBF (k=18, h=3) built from 1024 x 4 Mbp
 synthetic genomes; 10 M single-end 150 bp reads per GPU at e=3 (threshold 61).  One "step" = the whole hot path
 over one batch of 10 M reads: pack (2-bit + reverse complement on the device) + IBF query kernel -> per-read bin
-bitmasks.  N > 1 is read-sharded (filter replicated by an NCCL broadcast over NVLink, every rank gets its own
+bitmasks + compaction of the bitmasks into per-bin read-id lists.  N > 1 is read-sharded (filter replicated by an NCCL broadcast over NVLink, every rank gets its own
 10 M reads: weak scaling, no data-path collective).
 
     python bench.py --gpus 1 --steps 5 --warmup 3
@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--read-len", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-compact", action="store_true", help="leave the per-bin list compaction out of the timed step")
     ap.add_argument("--no-ingest", action="store_true", help="skip the extra device FASTQ-reader measurement (cfg2)")
     ap.add_argument("--no-early-exit", action="store_true", help="skip the extra DYIBF_OPT_EARLY_EXIT measurement")
     a = ap.parse_args()
@@ -273,7 +274,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     import dream_yara_b200 as dy
-    from dream_yara_b200._lib import ENC_DNA5, MEM_HOST, check
+    from dream_yara_b200._lib import ENC_DNA5, MEM_DEVICE, MEM_HOST, check
     from bench_support import synth
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -335,9 +336,20 @@ def run_b200(args):
     stream = torch.cuda.current_stream().cuda_stream
     cur_thr = [thr]
 
+    # north_star (c): the rows are compacted into per-bin read-id lists (origReadIdMap, d_mapper.h:360-368) inside the step
+    ids_cap = 4 * n
+    d_boff = torch.zeros(bins + 1, dtype=torch.int64, device=dev)
+    d_ids = torch.zeros(ids_cap, dtype=torch.int32, device=dev)
+    n_pairs = C.c_uint64(0)
+
     def device_step():
         f.query_device(d_reads.data_ptr(), d_off.data_ptr(), n_seq, cur_thr[0], d_rows.data_ptr(), group=group, derive_rc=True,
                        encoding=ENC_DNA5, max_seq_len=RL, stream=stream)
+        if not args.no_compact:
+            rc = L.dyibf_compact(f._h, C.c_void_p(d_rows.data_ptr()), n, C.c_void_p(d_boff.data_ptr()), C.c_void_p(d_ids.data_ptr()),
+                                 ids_cap, C.byref(n_pairs), MEM_DEVICE, C.c_void_p(stream))
+            if rc not in (0, -6):                                      # -6: more pairs than ids_cap (tiny thresholds); offsets are complete
+                check(rc)
 
     def barrier():
         if world > 1:
@@ -361,11 +373,11 @@ def run_b200(args):
     clocks = sampler.stop() if rank == 0 else None
     ms = e0.elapsed_time(e1)
     prof = f.profile(reset=True); f.profile_enable(False)
-    t = torch.tensor([ms, prof["query_ms"] / max(prof["query_launches"], 1), prof["pack_ms"] / max(prof["pack_launches"], 1)],
-                     dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, prof["query_ms"] / max(prof["query_launches"], 1), prof["pack_ms"] / max(prof["pack_launches"], 1),
+                      prof["compact_ms"] / args.steps], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, query_ms, pack_ms = (float(x) for x in t.tolist())
+    ms_total, query_ms, pack_ms, compact_ms = (float(x) for x in t.tolist())
     value = units_world * n * args.steps / (ms_total / 1e3)
 
     # ---- e2e: the public host-buffer call; pinned reads in, bitmask rows out, copies inside the timed region
@@ -476,7 +488,8 @@ def run_b200(args):
     peak, peak_src = measured_peak()
     achieved = n * bytes_per_read / (query_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "query_kernel<16,3,3,8>", "kernel_ms": query_ms, "pack_kernel_ms": pack_ms,
+                "traffic": None, "kernel": "query_kernel<16,3,3,8>", "kernel_ms": query_ms, "pack_kernel_ms": pack_ms, "compact_kernels_ms": compact_ms,
+                "read_bin_pairs_per_step": int(n_pairs.value),
                 "algorithmic_bytes_per_launch": n * bytes_per_read, "peak_source": peak_src,
                 "frac_of_nominal_8000": achieved / 8000.0}
     traffic_file = os.path.join(ROOT, "profiles", "query_kernel_traffic.json")
@@ -542,7 +555,7 @@ def run_b200(args):
         line = {"metric": args.metric, "value": value, "unit": args.unit, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-                "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
+                "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": (2 if args.no_compact else 8) * args.steps,
                 "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "ingest": ingest, "impl": "b200"}
         if sweep is not None:
             line["e_sweep"] = sweep

@@ -6,9 +6,9 @@
 // deterministically and without atomics.
 //
 // Scheme: the rows are cut into chunks of `chunk_rows` consecutive rows and the bins into column tiles of
-// 32 u32 columns (1024 bins).  A warp owns one (chunk, column tile): it walks its rows 32 at a time, turns
-// each 32x32 bit tile around with ballots (only for bit positions that are set anywhere in the tile — the
-// matrix is sparse when the filter works) and keeps 1024 running counters in shared memory.
+// 32 u32 columns (1024 bins).  A warp owns one (chunk, column tile): lane c owns column word c — it reads that word of
+// every row of the chunk (a row = one coalesced 128-byte request of the warp) and keeps the running counters of its 32
+// bins in shared memory, so no votes, atomics or synchronisation are needed and ids come out ascending.
 //   pass 1 (count): counters -> ws[bin * n_chunks + chunk]
 //   scan          : exclusive prefix sum over ws in that bin-major order = where (bin, chunk) starts
 //   pass 2 (fill) : same walk, lanes whose row has the bit write their row id at base + rank.
@@ -60,49 +60,48 @@ __global__ void __launch_bounds__(CW * 32) compact_walk(const uint32_t* __restri
     const uint32_t col0 = ctile * 32;
     const uint32_t ncol = g.ncols - col0 < 32 ? g.ncols - col0 : 32;
 
+    // counter of bin (col0 + c) * 32 + b lives at cnt[b * 32 + c]: lane c only ever touches column c, conflict-free
     for (uint32_t i = lane; i < 1024; i += 32) {
         uint64_t v = 0;
         if (FILL) {
-            const uint32_t bin = col0 * 32 + i;
+            const uint32_t bin = (col0 + (i & 31u)) * 32 + (i >> 5);
             if (bin < bins) v = ws[(uint64_t)bin * g.n_chunks + chunk];
         }
         cnt[i] = v;
     }
     __syncwarp();
 
+    // lane c reads word c of every row: a row is one coalesced 128-byte request, 32 of them in flight; the set bits of the
+    // lane's words (the matrix is sparse when the filter works) bump the lane's own counters — rows in ascending order,
+    // no votes, no atomics, nothing shared between lanes
+    const uint32_t first_bin = (col0 + lane) * 32;
+    uint32_t lane_mask = 0;                                            // bins beyond `bins` never select
+    if (lane < ncol && first_bin < bins) lane_mask = bins - first_bin < 32 ? (1u << (bins - first_bin)) - 1u : 0xffffffffu;
     const uint32_t row_begin = chunk * g.chunk_rows;
     const uint32_t row_end = (row_begin + g.chunk_rows < n_rows) ? row_begin + g.chunk_rows : n_rows;
     for (uint32_t r0 = row_begin; r0 < row_end; r0 += 32) {
-        const uint32_t r = r0 + lane;
-        const uint32_t* rowp = rows32 + (uint64_t)r * g.ncols + col0;
-        for (uint32_t c = 0; c < ncol; ++c) {
-            uint32_t x = (r < row_end) ? rowp[c] : 0u;
-            const uint32_t first_bin = (col0 + c) * 32;
-            if (first_bin >= bins) x = 0;
-            else if (bins - first_bin < 32) x &= (1u << (bins - first_bin)) - 1u;
-            uint32_t any = __reduce_or_sync(0xffffffffu, x);
-            while (any) {
-                const uint32_t b = __ffs(any) - 1;
-                any &= any - 1;
-                const uint32_t mine = (x >> b) & 1u;
-                const uint32_t m = __ballot_sync(0xffffffffu, mine);
-                if (FILL) {
-                    const uint64_t base = cnt[c * 32 + b];
-                    if (mine) {
-                        const uint64_t pos = base + __popc(m & ((1u << lane) - 1u));
-                        if (pos < capacity) read_ids[pos] = r;
-                    }
-                    __syncwarp();
-                }
-                if (lane == 0) cnt[c * 32 + b] += __popc(m);
-                __syncwarp();
+        uint32_t x[32];
+        #pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const uint32_t r = r0 + i;
+            x[i] = (lane_mask && r < row_end) ? __ldg(rows32 + (uint64_t)r * g.ncols + col0 + lane) : 0u;
+        }
+        #pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            uint32_t v = x[i] & lane_mask;
+            while (v) {
+                const uint32_t b = __ffs(v) - 1;
+                v &= v - 1;
+                const uint64_t c = cnt[b * 32 + lane];
+                if (FILL && c < capacity) read_ids[c] = r0 + i;
+                cnt[b * 32 + lane] = c + 1;
             }
         }
     }
     if (!FILL) {
         __syncwarp();
         for (uint32_t i = lane; i < 1024; i += 32) {
-            const uint32_t bin = col0 * 32 + i;
+            const uint32_t bin = (col0 + (i & 31u)) * 32 + (i >> 5);
             if (bin < bins) ws[(uint64_t)bin * g.n_chunks + chunk] = cnt[i];
         }
     }

@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r6_launches.csv python bench.py --reads 2000000 --steps 2 --warmup 3 --no-cpu-baseline --no-e2e --no-early-exit --no-ingest > gpurun_out/r6_ncu.log 2>&1
+tail -n 3 gpurun_out/r6_ncu.log | cut -c1-300
+exit 0
