@@ -111,21 +111,6 @@ __device__ __forceinline__ uint32_t match_mine(uint32_t key, bool valid, const L
     return mine;
 }
 
-// the same plus peers: the valid lanes whose key equals my key (my rank among them = popc(peers below me))
-__device__ __forceinline__ uint32_t match_both(uint32_t key, bool valid, const LaneBits& lb, uint32_t* peers_out)
-{
-    const uint32_t vm = __ballot_sync(FULL, valid);
-    uint32_t mine = vm, peers = vm;
-    #pragma unroll
-    for (int i = 0; i < 5; ++i) {
-        const uint32_t b = __ballot_sync(FULL, (key >> i) & 1u);
-        mine &= b ^ lb.x[i];
-        peers &= b ^ (((key >> i) & 1u) - 1u);
-    }
-    *peers_out = peers;
-    return mine;
-}
-
 // load through the L2 (a line another lane of this warp has just written)
 __device__ __forceinline__ uint32_t load_cg(const uint32_t* p) { return __ldcg(p); }
 __device__ __forceinline__ uint64_t load_cg(const uint64_t* p) { return (uint64_t)__ldcg(reinterpret_cast<const unsigned long long*>(p)); }

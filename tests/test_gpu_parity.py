@@ -4,12 +4,15 @@ Bit-exact bar: identical .filter bytes, identical per-read bin sets, identical p
 identical per-bin read-id lists.
 """
 import hashlib
+import os
 
 import numpy as np
 import pytest
 
 import ka
 from oracle_py import full_layout
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
 
@@ -445,3 +448,33 @@ def test_bin_sharded_build_equals_column_slices(dy, oracle):
         assert np.array_equal(f.download_words()[: P * Wr], D.extract_bin_shard(words, bins, nbits, r, G))
         f.close()
     full.close()
+
+
+def test_bucketed_build_match_any_variant_in_subprocess(dy):
+    """DYIBF_SPLIT_MATCH=1 (MATCH.ANY ranking of the radix split, read once per process) builds the same table as the
+    direct atomic kernel: two split levels, overflow fallback included."""
+    import subprocess
+    import sys
+    code = r'''
+import hashlib, sys
+import numpy as np
+sys.path.insert(0, %r)
+import dream_yara_b200 as dy
+from bench_support import synth
+bins, h, k, nbits, glen = 1000, 3, 18, (1 << 33) + 256, 13000
+g = synth.genomes(bins, glen)
+off = np.arange(bins + 1, dtype=np.uint64) * glen
+out = []
+for mib in (0, -1, 32):
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.set_build_bucket_mib(mib)
+    f.addSequences((g.reshape(-1), off), np.arange(bins, dtype=np.uint32))
+    out.append(hashlib.md5(f.download_words().tobytes()).hexdigest())
+    f.close()
+print("MD5S", *out)
+''' % ROOT
+    env = dict(os.environ, DYIBF_SPLIT_MATCH="1")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    md5s = [l for l in r.stdout.splitlines() if l.startswith("MD5S")][0].split()[1:]
+    assert len(md5s) == 3 and md5s[0] == md5s[1] == md5s[2]
