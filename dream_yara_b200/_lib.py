@@ -64,6 +64,8 @@ SYMBOLS = {
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "dyibf_parse_records": (C.c_int, [C.c_int, _P, C.c_uint64, C.c_int, C.c_int, _U8P, C.c_uint64, _U64P, C.c_uint64, C.c_uint64,
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int, _P]),
+    "dyibf_classify_text": (C.c_int, [_P, _P, C.c_uint64, _P, C.c_uint64, C.c_int, C.c_int, _U64P, _U32P, C.c_uint64,
+                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "dyibf_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
     "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),

@@ -353,6 +353,19 @@ __global__ void ingest_init_globals(unsigned long long* g)
 
 __global__ void ingest_set_u64(uint64_t* p, uint64_t v) { *p = v; }
 
+// longest sequence of a limits array (n + 1 entries)
+__global__ void __launch_bounds__(256) ingest_max_len_kernel(const uint64_t* __restrict__ limits, uint64_t n, unsigned long long* __restrict__ out)
+{
+    uint64_t m = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t l = limits[i + 1] - limits[i];
+        m = l > m ? l : m;
+    }
+    #pragma unroll
+    for (int d = 16; d; d >>= 1) { const uint64_t o = __shfl_xor_sync(FULL, m, d); m = o > m ? o : m; }
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, (unsigned long long)m);
+}
+
 } // namespace
 
 size_t ingest_workspace_bytes(uint64_t n_bytes)
@@ -419,6 +432,16 @@ cudaError_t launch_ingest_emit(const uint8_t* text, uint64_t n, int format, int 
     if (format == DYIBF_FMT_FASTA) ingest_walk_kernel<DYIBF_FMT_FASTA, true><<<(unsigned)n_tiles, IT, 0, st>>>(a);
     else                           ingest_walk_kernel<DYIBF_FMT_FASTQ, true><<<(unsigned)n_tiles, IT, 0, st>>>(a);
     ingest_set_u64<<<1, 1, 0, st>>>(out_limits + n_records, limit_base + n_bases);
+    return cudaGetLastError();
+}
+
+// *out (device, zeroed by the caller) = max over i of limits[i+1] - limits[i]
+cudaError_t launch_max_len(const uint64_t* limits, uint64_t n, unsigned long long* out, cudaStream_t st)
+{
+    if (n == 0) return cudaSuccess;
+    uint64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    ingest_max_len_kernel<<<(unsigned)blocks, 256, 0, st>>>(limits, n, out);
     return cudaGetLastError();
 }
 

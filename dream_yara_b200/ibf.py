@@ -225,6 +225,26 @@ class SeqAnBloomFilter:
         check(rc)
         return offs, ids[: total.value]
 
+    def classifyText(self, reads_text, mates_text=None, fmt=1, e_percent=5, capacity=None):
+        """loadReads + clasifyLoadedReads from the text of the reads file(s) (bytes; fmt 0 FASTA / 1 FASTQ): only text goes up,
+        only the lists come back.  Returns (bin_offsets, read_ids, n_reads, threshold)."""
+        t1 = np.frombuffer(bytes(reads_text), dtype=np.uint8)
+        t2 = np.frombuffer(bytes(mates_text), dtype=np.uint8) if mates_text is not None else None
+        offs = np.zeros(self._noOfBins + 1, dtype=np.uint64)
+        total, n_reads, thr = C.c_uint64(0), C.c_uint32(0), C.c_uint32(0)
+        cap = int(capacity) if capacity is not None else max(len(t1) // 16, 1024)
+        ids = np.zeros(cap, dtype=np.uint32)
+        L = lib()
+        p2 = None if t2 is None else C.c_void_p(t2.ctypes.data if t2.size else np.zeros(1, np.uint8).ctypes.data)
+        rc = L.dyibf_classify_text(self._h, C.c_void_p(t1.ctypes.data) if t1.size else None, t1.size, p2, 0 if t2 is None else t2.size,
+                                   int(fmt), int(e_percent), _ptr(offs), _ptr(ids), cap, C.byref(total), C.byref(n_reads), C.byref(thr))
+        if rc == _lib.ERR_CAPACITY and capacity is None:
+            cap = int(total.value)
+            ids = np.zeros(cap, dtype=np.uint32)
+            rc = L.dyibf_classify_fetch(self._h, _ptr(offs), _ptr(ids), cap, C.byref(total))
+        check(rc)
+        return offs, ids[: total.value], n_reads.value, thr.value
+
     def gatherReads(self, binNo):
         """loadFilteredReads (d_mapper.h:393-443) for one bin of the last classify(derive_rc=True):
         (bytes u8, limits u64[n+1], ids u32[n]) — fwd reads, [second mates,] then all reverse complements."""

@@ -194,6 +194,16 @@ int  dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int for
                          uint8_t* out_seqs, uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs,
                          uint64_t limit_base, uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream);
 
+/* loadReads (src/mapper.h:444-469) + clasifyLoadedReads (d_mapper.h:308-375) from the TEXT of the reads file(s), in one
+ * call: the text (host memory; mates_text NULL for single-end) is copied to the device once, tokenised there
+ * (dyibf_parse_records), the threshold is taken from the batch's average read length and e_percent as the reference does
+ * (d_mapper.h:313-315), and only the per-bin lists come back (as dyibf_classify).  The parsed batch stays resident for
+ * dyibf_gather_reads (ASCII sequences).  *n_reads receives the number of reads (pairs), *threshold the threshold used
+ * (0: the caller applies the reference's "everything everywhere" rule, d_mapper.h:320-333). */
+int  dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads_bytes, const char* mates_text, uint64_t mates_bytes,
+                         int format, int e_percent, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total,
+                         uint32_t* n_reads, uint32_t* threshold);
+
 /* ---- options ------------------------------------------------------------------------------- */
 
 /* DYIBF_OPT_EARLY_EXIT (default 0).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it

@@ -113,3 +113,36 @@ def test_text_to_bins_end_to_end(dy, golden, tmp_path):
     assert np.array_equal(rows_pe, golden["ka1_rows"][:3200] | golden["ka1_rows"][3200:])
     assert dy.read_fasta(rp, iupac=False)[:2] == reads[:2]
     f.close()
+
+
+def test_classify_text_equals_parse_then_classify(dy, golden, gather_golden):
+    """dyibf_classify_text (text up, lists back) against the reference's own clasifyLoadedReads lists (KA5, SE and PE) and
+    against dyibf_classify on the parsed reads; the batch it leaves resident serves dyibf_gather_reads."""
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    f = dy.SeqAnBloomFilter(64, 2, 19, ka.GIB_BITS)
+    f.addSequences(genomes, np.arange(64))
+    fa = b"".join(b">r%d some text\n%s\n%s\n" % (i, r[:61], r[61:]) for i, r in enumerate(reads))
+    offs, ids, n, thr = f.classifyText(fa, fmt=0, e_percent=3)
+    assert (n, thr) == (6400, int(golden["ka5_se_threshold"]))
+    assert np.array_equal(offs, golden["ka5_se_bin_offsets"]) and np.array_equal(ids, golden["ka5_se_read_ids"])
+    q1 = b"".join(b"@p%d/1\n%s\n+\n%s\n" % (i, r, b"I" * len(r)) for i, r in enumerate(reads[:3200]))
+    q2 = b"".join(b"@p%d/2\n%s\n+\n%s\n" % (i, r, b"+" * len(r)) for i, r in enumerate(reads[3200:]))
+    offs, ids, n, thr = f.classifyText(q1, q2, fmt=1, e_percent=3)
+    assert (n, thr) == (3200, int(golden["ka5_pe_threshold"]))
+    assert np.array_equal(offs, golden["ka5_pe_bin_offsets"]) and np.array_equal(ids, golden["ka5_pe_read_ids"])
+    o2, i2 = f.classify(reads, thr, group=4, derive_rc=True)
+    assert np.array_equal(offs, o2) and np.array_equal(ids, i2)
+    # the resident batch (ASCII) feeds loadFilteredReads: forward mates, then reverse complements
+    b = int(np.argmax(np.diff(offs.astype(np.int64))))
+    seq_bytes, limits, gids = f.gatherReads(b)
+    m = int(offs[b + 1] - offs[b])
+    assert limits.size - 1 == 4 * m and list(gids[:m]) == list(ids[int(offs[b]):int(offs[b + 1])])
+    first = int(gids[0])
+    assert seq_bytes[int(limits[0]):int(limits[1])].tobytes() == reads[first]
+    comp = bytes.maketrans(b"ACGTN", b"TGCAN")
+    assert seq_bytes[int(limits[2 * m]):int(limits[2 * m + 1])].tobytes() == reads[first][::-1].translate(comp)
+    with pytest.raises(dy.DyibfError):
+        f.classifyText(q1, q2[: len(q2) // 2 + 3], fmt=1, e_percent=3)
+    offs, ids, n, thr = f.classifyText(b"", fmt=1, e_percent=3)
+    assert n == 0 and ids.size == 0
+    f.close()
