@@ -74,3 +74,24 @@ def test_host_mirror_helpers(dy):
     assert enc == dy.ENC_DNA5 and list(off) == [0, 3, 3]
     rs = dy.ReadSet(["ACGT", "TTTT"], paired=True)
     assert len(rs) == 4 and rs.getReadsCount() == 2 and rs.getPairsCount() == 1 and rs.lengthSum() == 16
+
+
+def test_cmake_project_configures_for_sm100a(tmp_path):
+    """The CMake build (the reference's build system, src/CMakeLists.txt) configures here, compiles every csrc/*.cu the
+    in-tree build compiles, and targets sm_100a only.  Configure step only; the compile is build.py's job."""
+    import shutil
+    import subprocess
+    cmake = shutil.which("cmake")
+    if cmake is None or shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
+        pytest.skip("cmake / nvcc not on this machine")
+    env = dict(os.environ, CUDACXX=shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc")
+    r = subprocess.run([cmake, "-S", ROOT, "-B", str(tmp_path), "-G", "Ninja"], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ninja = open(tmp_path / "build.ninja").read()
+    from dream_yara_b200 import build as b
+    for src in b.SOURCES:
+        assert os.path.basename(src) in ninja, src + " missing from the CMake build"
+    assert "arch=compute_100a,code=[compute_100a,sm_100a]" in ninja or "compute_100a" in ninja
+    assert not re.search(r"compute_(?!100a)\d+", ninja)
+    for tool in ("dyibf_build_filter", "dyibf_update_filter", "dyibf_filter_reads"):
+        assert tool in ninja
