@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-compact", action="store_true", help="leave the per-bin list compaction out of the timed step")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the extra 100 000-reads-per-call dyibf_classify measurement")
+    ap.add_argument("--dropin-batch", type=int, default=100_000, help="reads (pairs) per drop-in call; the reference's -rb default")
     ap.add_argument("--no-ingest", action="store_true", help="skip the extra device FASTQ-reader measurement (cfg2)")
     ap.add_argument("--no-early-exit", action="store_true", help="skip the extra DYIBF_OPT_EARLY_EXIT measurement")
     a = ap.parse_args()
@@ -401,6 +403,62 @@ def run_b200(args):
         # device-resident and host paths must agree bit for bit
         assert np.array_equal(h_rows.reshape(-1).view(np.int64), d_rows.cpu().numpy()), "host-mode rows != device-mode rows"
 
+    # ---- extra: drop-in batching: one dyibf_classify call per 100 000 reads, as clasifyLoadedReads is called
+    # (src/mapper.h:109), pageable host buffers in, per-bin id lists out — what the patched reference mapper would see
+    dropin = None
+    if not args.no_dropin and not sharded:
+        rb = min(args.dropin_batch, n)
+        n_calls = max(1, min(n // rb, 20))
+        per_call = rb * (2 if paired else 1)
+        offs_b = np.arange(per_call + 1, dtype=np.uint64) * RL
+        boff = np.zeros(bins + 1, dtype=np.uint64); ids_b = np.zeros(4 * rb, dtype=np.uint32); tot_b = C.c_uint64(0)
+        def batch_of(i):                                                   # [reads] or [mates 1 | mates 2] of batch i, pageable
+            if paired:
+                return np.ascontiguousarray(h_reads[:, i * rb:(i + 1) * rb]).reshape(-1)
+            return np.array(h_reads[i * rb:(i + 1) * rb]).reshape(-1)
+        batches = [batch_of(i) for i in range(n_calls)]
+        def dropin_call_on(srcs, i):
+            rc = L.dyibf_classify(f._h, C.c_void_p(srcs[i].ctypes.data), C.c_void_p(offs_b.ctypes.data), per_call, ENC_DNA5, group, 1, thr,
+                                  C.c_void_p(boff.ctypes.data), C.c_void_p(ids_b.ctypes.data), ids_b.size, C.byref(tot_b))
+            check(rc)
+        def dropin_run(srcs):
+            dropin_call_on(srcs, 0); dropin_call_on(srcs, 0)
+            barrier()
+            t0 = time.perf_counter()
+            pairs = 0
+            for i in range(n_calls):
+                dropin_call_on(srcs, i)
+                pairs += tot_b.value
+            dt_b = time.perf_counter() - t0
+            barrier()
+            dtt = torch.tensor([dt_b], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dtt, op=dist.ReduceOp.MAX)
+            return float(dtt.item()), pairs
+        dt_auto, pairs_b = dropin_run(batches)
+        # the lists of the last batch must be the rows of the device pass, transposed
+        lastrows = d_rows.view(n, W)[(n_calls - 1) * rb:n_calls * rb].cpu().numpy().view(np.uint64)
+        bits = np.unpackbits(lastrows.view(np.uint8), axis=1, bitorder="little")[:, :bins]
+        assert int(bits.sum()) == int(boff[bins]) and np.array_equal(bits.sum(axis=0).astype(np.uint64), np.diff(boff)), \
+            "drop-in lists differ from the device rows"
+        f.profile_enable(True); f.profile(reset=True)                      # a separate, untimed pass: kernel time inside one call
+        for i in range(n_calls):
+            dropin_call_on(batches, i)
+        pb = f.profile(reset=True); f.profile_enable(False)
+        kern_ms = {k: pb[k + "_ms"] / n_calls for k in ("pack", "query", "compact")}
+        f.set_query_chunk_mib(1024)                                        # A/B: the whole batch as one chunk (no overlap inside a call)
+        dt_one, _ = dropin_run(batches)
+        f.set_query_chunk_mib(0)
+        dt_pin = None
+        if not paired:                                                     # A/B: the same calls on pinned host memory
+            dt_pin, _ = dropin_run([h_reads[i * rb:(i + 1) * rb].reshape(-1) for i in range(n_calls)])
+        rate = lambda dt: units_world * rb * n_calls / dt
+        dropin = {"value": rate(dt_auto), "unit": args.unit, "reads_per_call": rb, "calls": n_calls,
+                  "ms_per_call": dt_auto / n_calls * 1e3, "kernel_ms_per_call": kern_ms, "read_bin_pairs": int(pairs_b),
+                  "one_chunk_per_call": rate(dt_one), "pinned_input": rate(dt_pin) if dt_pin else None,
+                  "note": "dyibf_classify per batch of the reference's default size: pageable host reads in, per-bin read-id lists "
+                          "out, synchronous calls, host wall clock, max over ranks; not part of value/e2e"}
+
     # ---- extra (not the headline): the same step with DYIBF_OPT_EARLY_EXIT — identical rows, fewer lookups
     early = None
     if not args.no_early_exit:
@@ -556,7 +614,7 @@ def run_b200(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
                 "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": (2 if args.no_compact else 8) * args.steps,
-                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "ingest": ingest, "impl": "b200"}
+                "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "dropin_batches": dropin, "ingest": ingest, "impl": "b200"}
         if sweep is not None:
             line["e_sweep"] = sweep
         print(json.dumps(line), flush=True)

@@ -15,6 +15,7 @@ MAX_HASH = 8
 OPT_EARLY_EXIT = 1
 OPT_BUILD_BUCKET_MIB = 2
 OPT_BUILD_CHUNK_MIB = 3
+OPT_QUERY_CHUNK_MIB = 4
 
 
 class Params(C.Structure):

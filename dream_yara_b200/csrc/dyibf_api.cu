@@ -78,6 +78,7 @@ struct dyibf_filter {
     std::vector<uint64_t> h_csr_off;
     uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
     int64_t      bucket_mib = -1;         // DYIBF_OPT_BUILD_BUCKET_MIB: -1 auto, 0 direct atomics only
+    int64_t      query_chunk_mib = 0;     // DYIBF_OPT_QUERY_CHUNK_MIB: 0 = auto
     int64_t      build_chunk_mib = 256;   // DYIBF_OPT_BUILD_CHUNK_MIB: bases per host-mode build chunk
     DevBuf       bucket_records, bucket_cursors;
     void*        stage[2] = {nullptr, nullptr};   // pinned
@@ -519,12 +520,9 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
     if (n_rows == 0) return DYIBF_OK;
     const uint32_t W = f->prm.words_per_block, k = f->hp.k;
     if (!max_seq_len) {
-        uint64_t mx = 0;
-        for (uint32_t s = 0; s < n_seqs; ++s) {
-            if (offsets[s + 1] < offsets[s]) return fail(DYIBF_ERR_ARG, "offsets not monotone at %u", s);
-            mx = std::max(mx, offsets[s + 1] - offsets[s]);
-        }
-        if (mx > 0xffffffffull) return fail(DYIBF_ERR_ARG, "sequence longer than 2^32");
+        uint64_t mx = 0;                                                // branch-free (vectorises): a decreasing pair wraps to > 2^32
+        for (uint32_t s = 0; s < n_seqs; ++s) mx = std::max(mx, offsets[s + 1] - offsets[s]);
+        if (mx > 0xffffffffull) return fail(DYIBF_ERR_ARG, "offsets not monotone, or a sequence longer than 2^32");
         max_seq_len = (uint32_t)std::max<uint64_t>(mx, 1);
     }
     if (max_seq_len >= k && max_seq_len - k + 1 > 65535)
@@ -532,7 +530,12 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
 
     const uint64_t total_bytes = offsets[n_seqs] - offsets[0];
     const uint64_t per_row = total_bytes / n_rows + 8ull * group_in + 8ull * W + 1;
-    uint64_t chunk_rows = (48ull << 20) / per_row;
+    uint64_t chunk_rows = ((uint64_t)(f->query_chunk_mib > 0 ? f->query_chunk_mib : 48) << 20) / per_row;
+    if (f->query_chunk_mib <= 0 && n_rows <= chunk_rows) {           // small batch: overlap its own upload with its own query
+        static const int cuts = getenv("DYIBF_QUERY_CUTS") ? atoi(getenv("DYIBF_QUERY_CUTS")) : 4;
+        static const int min_rows = getenv("DYIBF_QUERY_MIN_ROWS") ? atoi(getenv("DYIBF_QUERY_MIN_ROWS")) : 16384;
+        chunk_rows = std::max<uint64_t>(((uint64_t)n_rows + cuts - 1) / cuts, min_rows);
+    }
     if (h_counts) chunk_rows = std::min<uint64_t>(chunk_rows, (256ull << 20) / ((uint64_t)group * f->prm.bins * 2 + 1));
     chunk_rows = std::max<uint64_t>(chunk_rows, 1024);
     chunk_rows = std::min<uint64_t>(chunk_rows, n_rows);
@@ -1228,6 +1231,10 @@ int dyibf_set_option(dyibf_filter* f, int option, int64_t value)
             if (value < -1) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_BUCKET_MIB must be -1 (auto), 0 (off) or a size in MiB");
             f->bucket_mib = value;
             return DYIBF_OK;
+        case DYIBF_OPT_QUERY_CHUNK_MIB:
+            if (value < 0 || value > 4096) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_QUERY_CHUNK_MIB must be 0 (auto) or 1..4096");
+            f->query_chunk_mib = value;
+            return DYIBF_OK;
         case DYIBF_OPT_BUILD_CHUNK_MIB:
             if (value < 1 || value > 4096) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_CHUNK_MIB must be 1..4096");
             f->build_chunk_mib = value;
@@ -1244,6 +1251,7 @@ int dyibf_get_option(const dyibf_filter* f, int option, int64_t* value)
         case DYIBF_OPT_EARLY_EXIT: *value = (f->query_flags & QUERY_EARLY_EXIT) ? 1 : 0; return DYIBF_OK;
         case DYIBF_OPT_BUILD_BUCKET_MIB: *value = f->bucket_mib; return DYIBF_OK;
         case DYIBF_OPT_BUILD_CHUNK_MIB: *value = f->build_chunk_mib; return DYIBF_OK;
+        case DYIBF_OPT_QUERY_CHUNK_MIB: *value = f->query_chunk_mib; return DYIBF_OK;
         default: return fail(DYIBF_ERR_ARG, "unknown option %d", option);
     }
 }

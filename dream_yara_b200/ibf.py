@@ -295,6 +295,10 @@ class SeqAnBloomFilter:
         """DYIBF_OPT_BUILD_CHUNK_MIB: bases per staged chunk of addSequences on host buffers."""
         check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_CHUNK_MIB, int(mib)))
 
+    def set_query_chunk_mib(self, mib):
+        """DYIBF_OPT_QUERY_CHUNK_MIB: staged bytes per chunk of the host-buffer query (0 = auto)."""
+        check(lib().dyibf_set_option(self._h, _lib.OPT_QUERY_CHUNK_MIB, int(mib)))
+
     def profile_enable(self, on=True):
         check(lib().dyibf_profile_enable(self._h, int(on)))
 

@@ -478,3 +478,29 @@ print("MD5S", *out)
     assert r.returncode == 0, r.stderr[-2000:]
     md5s = [l for l in r.stdout.splitlines() if l.startswith("MD5S")][0].split()[1:]
     assert len(md5s) == 3 and md5s[0] == md5s[1] == md5s[2]
+
+
+@pytest.mark.parametrize("paired", [False, True])
+def test_query_chunking_does_not_change_results(dy, golden, reads, ka1_filter, paired):
+    """DYIBF_OPT_QUERY_CHUNK_MIB only moves the chunk boundaries of the host-buffer pipeline: rows and per-bin lists are the
+    same for the auto rule (6400 reads < 4 x 16384: one chunk), 1 MiB chunks (several chunks over both streams) and one
+    large chunk — and equal to the reference's clasifyLoadedReads lists where the fixture holds them."""
+    f = ka1_filter
+    group = 4 if paired else 2
+    many = reads * 6 if not paired else reads * 5                       # 38 400 / 32 000 sequences, [m1 | m2] halves for pairs
+    out = []
+    for mib in (0, 1, 512):
+        f.set_query_chunk_mib(mib)
+        rows = f.whichBinsBatch(many, 25, group=group, derive_rc=True)
+        bo, ids = f.classify(many, 25, group=group, derive_rc=True)
+        out.append((rows, bo, ids))
+    f.set_query_chunk_mib(0)
+    for rows, bo, ids in out[1:]:
+        assert np.array_equal(rows, out[0][0]) and np.array_equal(bo, out[0][1]) and np.array_equal(ids, out[0][2])
+    rows, bo, ids = out[0]
+    bits = np.unpackbits(rows.view(np.uint8), axis=1, bitorder="little")[:, :64]
+    assert np.array_equal(bits.sum(axis=0), np.diff(bo.astype(np.int64)))
+    for b in (0, 7, 38, 63):
+        assert np.array_equal(np.nonzero(bits[:, b])[0], ids[int(bo[b]):int(bo[b + 1])])
+    if not paired:                                                      # six copies of KA1's reads: row r == KA1 row r % 6400
+        assert np.array_equal(rows, np.tile(golden["ka1_rows"], (6, 1)))
