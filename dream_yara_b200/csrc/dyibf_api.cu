@@ -531,11 +531,9 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
     const uint64_t total_bytes = offsets[n_seqs] - offsets[0];
     const uint64_t per_row = total_bytes / n_rows + 8ull * group_in + 8ull * W + 1;
     uint64_t chunk_rows = ((uint64_t)(f->query_chunk_mib > 0 ? f->query_chunk_mib : 48) << 20) / per_row;
-    if (f->query_chunk_mib <= 0 && n_rows <= chunk_rows) {           // small batch: overlap its own upload with its own query
-        static const int cuts = getenv("DYIBF_QUERY_CUTS") ? atoi(getenv("DYIBF_QUERY_CUTS")) : 4;
-        static const int min_rows = getenv("DYIBF_QUERY_MIN_ROWS") ? atoi(getenv("DYIBF_QUERY_MIN_ROWS")) : 16384;
-        chunk_rows = std::max<uint64_t>(((uint64_t)n_rows + cuts - 1) / cuts, min_rows);
-    }
+    if (f->query_chunk_mib <= 0 && n_rows <= chunk_rows)             // small batch: overlap its own upload with its own query
+        chunk_rows = std::max<uint64_t>(((uint64_t)n_rows + 5) / 6, 8192);   // measured on 100 000-read calls: 2/4/6/8/16 cuts
+                                                                             // -> 35.1/39.4/41.9/38.6/35.6 M reads/s (one chunk 28.5)
     if (h_counts) chunk_rows = std::min<uint64_t>(chunk_rows, (256ull << 20) / ((uint64_t)group * f->prm.bins * 2 + 1));
     chunk_rows = std::max<uint64_t>(chunk_rows, 1024);
     chunk_rows = std::min<uint64_t>(chunk_rows, n_rows);

@@ -225,8 +225,8 @@ int  dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads
 /* DYIBF_OPT_QUERY_CHUNK_MIB (default 0 = auto): dyibf_query_batch(host) / dyibf_classify stage the batch in chunks of rows,
  * alternating between two streams so that the upload of one chunk overlaps the kernels of the other.  Auto: chunks of about
  * 48 MiB of staged data, and a batch that would fit one chunk (the reference's 100 000-read batches, src/mapper.h:109) is
- * still cut into four (at least 16 384 rows each) so that its own upload and query overlap.  A value > 0 fixes the chunk
- * size in MiB and switches the four-way cut off. */
+ * still cut into six (at least 8192 rows each) so that its own upload and query overlap.  A value > 0 fixes the chunk
+ * size in MiB and switches the six-way cut off. */
 #define DYIBF_OPT_QUERY_CHUNK_MIB 4
 int  dyibf_set_option(dyibf_filter* f, int option, int64_t value);
 int  dyibf_get_option(const dyibf_filter* f, int option, int64_t* value);

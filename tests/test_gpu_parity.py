@@ -483,8 +483,8 @@ print("MD5S", *out)
 @pytest.mark.parametrize("paired", [False, True])
 def test_query_chunking_does_not_change_results(dy, golden, reads, ka1_filter, paired):
     """DYIBF_OPT_QUERY_CHUNK_MIB only moves the chunk boundaries of the host-buffer pipeline: rows and per-bin lists are the
-    same for the auto rule (6400 reads < 4 x 16384: one chunk), 1 MiB chunks (several chunks over both streams) and one
-    large chunk — and equal to the reference's clasifyLoadedReads lists where the fixture holds them."""
+    same for the auto rule (a small batch is cut into chunks of at least 8192 rows), 1 MiB chunks (many chunks over both
+    streams) and one large chunk — and equal to the reference's clasifyLoadedReads lists where the fixture holds them."""
     f = ka1_filter
     group = 4 if paired else 2
     many = reads * 6 if not paired else reads * 5                       # 38 400 / 32 000 sequences, [m1 | m2] halves for pairs
