@@ -13,8 +13,8 @@ bitmasks + compaction of the bitmasks into per-bin read-id lists.  N > 1 is read
     python bench.py --impl reference ...      # the reference's own CPU whichBins path on the host cores
 
 Prints ONE JSON line (rank 0).  `value`: reads/s with the read bytes resident in HBM (CUDA events, max over
-ranks).  `e2e`: the same through the public host-buffer call (pinned host memory in, bitmask rows out, copies
-inside the timed region).  `roofline`: the query kernel against the measured HBM peak.  `cpu_baseline`: the
+ranks).  `e2e`: the same through the reference-facing host-buffer call dyibf_classify (pinned host reads in, per-bin
+read-id lists out, copies inside the timed region); `e2e.rows_call` times dyibf_query_batch (bitmask rows out) beside it.  `roofline`: the query kernel against the measured HBM peak.  `cpu_baseline`: the
 reference's own code (oracle/_ref) on a bounded sample of the same reads, all host cores.
 """
 import argparse
@@ -382,26 +382,45 @@ def run_b200(args):
     ms_total, query_ms, pack_ms, compact_ms = (float(x) for x in t.tolist())
     value = units_world * n * args.steps / (ms_total / 1e3)
 
-    # ---- e2e: the public host-buffer call; pinned reads in, bitmask rows out, copies inside the timed region
+    # ---- e2e: the reference-facing host-buffer call (clasifyLoadedReads = dyibf_classify): pinned reads in, per-bin read-id lists
+    # out, copies inside the timed region.  The bitmask-rows call (dyibf_query_batch, 1.28 GB of rows back) is timed beside it.
     e2e = None
+    ip = C.c_void_p()
     if not args.no_e2e:
+        check(L.dyibf_host_alloc(C.byref(ip), ids_cap * 4))
+        h_ids = np.ctypeslib.as_array(C.cast(ip, C.POINTER(C.c_uint32)), shape=(ids_cap,))
+        h_boff = np.zeros(bins + 1, dtype=np.uint64)
+        tot_h = C.c_uint64(0)
         def host_step():
             check(L.dyibf_query_batch(f._h, hp, op, n_seq, ENC_DNA5, group, 1, thr, RL, rp, None, MEM_HOST, None))
-        for _ in range(max(1, min(args.warmup, 2))):
-            host_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            host_step()
-        barrier()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": units_world * n * args.steps / float(dt.item()), "unit": args.unit,
-               "h2d_bytes_per_step": world * (n_seq * RL + (n_seq + 1) * 8), "d2h_bytes_per_step": world * n * W * 8,
-               "timing": "host wall clock around K synchronous dyibf_query_batch(host) calls, max over ranks"}
+        def classify_step():
+            check(L.dyibf_classify(f._h, hp, op, n_seq, ENC_DNA5, group, 1, thr, C.c_void_p(h_boff.ctypes.data), ip, ids_cap, C.byref(tot_h)))
+        def host_timed(fn):
+            for _ in range(max(1, min(args.warmup, 2))):
+                fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                fn()
+            barrier()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            return float(dt.item())
+        dt_rows = host_timed(host_step)
+        dt_cls = host_timed(classify_step)
+        h2d = world * (n_seq * RL + (n_seq + 1) * 8)
+        e2e = {"value": units_world * n * args.steps / dt_cls, "unit": args.unit,
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": world * ((bins + 1) * 8 + int(tot_h.value) * 4),
+               "timing": "host wall clock around K synchronous dyibf_classify(host) calls (reads in, per-bin read-id lists out), max over ranks",
+               "rows_call": {"value": units_world * n * args.steps / dt_rows, "unit": args.unit, "h2d_bytes_per_step": h2d,
+                             "d2h_bytes_per_step": world * n * W * 8, "call": "dyibf_query_batch(host): bitmask rows out"}}
         # device-resident and host paths must agree bit for bit
         assert np.array_equal(h_rows.reshape(-1).view(np.int64), d_rows.cpu().numpy()), "host-mode rows != device-mode rows"
+        if not args.no_compact:
+            tot = int(tot_h.value)
+            assert tot == int(n_pairs.value) and np.array_equal(h_boff.view(np.int64), d_boff.cpu().numpy()) and \
+                np.array_equal(h_ids[:tot].view(np.int32), d_ids[:tot].cpu().numpy()), "host-mode lists != device-mode lists"
 
     # ---- extra: drop-in batching: one dyibf_classify call per 100 000 reads, as clasifyLoadedReads is called
     # (src/mapper.h:109), pageable host buffers in, per-bin id lists out — what the patched reference mapper would see
@@ -619,7 +638,7 @@ def run_b200(args):
             line["e_sweep"] = sweep
         print(json.dumps(line), flush=True)
     f.close()
-    for p_ in (hp, op, rp):
+    for p_ in (hp, op, rp, ip):
         L.dyibf_host_free(p_)
     if world > 1:
         dist.destroy_process_group()
