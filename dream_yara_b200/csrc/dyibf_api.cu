@@ -519,13 +519,12 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
     const uint32_t n_rows = (uint32_t)(n_total / group);
     if (n_rows == 0) return DYIBF_OK;
     const uint32_t W = f->prm.words_per_block, k = f->hp.k;
-    if (!max_seq_len) {
-        uint64_t mx = 0;                                                // branch-free (vectorises): a decreasing pair wraps to > 2^32
-        for (uint32_t s = 0; s < n_seqs; ++s) mx = std::max(mx, offsets[s + 1] - offsets[s]);
-        if (mx > 0xffffffffull) return fail(DYIBF_ERR_ARG, "offsets not monotone, or a sequence longer than 2^32");
-        max_seq_len = (uint32_t)std::max<uint64_t>(mx, 1);
-    }
-    if (max_seq_len >= k && max_seq_len - k + 1 > 65535)
+    // Without a caller-supplied bound the longest sequence is found chunk by chunk below, just before the chunk's copies are
+    // issued: the scan of one chunk's limits then runs while the device works on the chunk before (a scan of all limits up
+    // front costs ~8 ms per 10 M reads with the device idle).
+    const bool scan_len = max_seq_len == 0;
+    if (offsets[n_seqs] < offsets[0]) return fail(DYIBF_ERR_ARG, "offsets not monotone");
+    if (!scan_len && max_seq_len >= k && max_seq_len - k + 1 > 65535)
         return fail(DYIBF_ERR_ARG, "a sequence of %u bases has more than 65535 k-mers (uint16 counts in the reference)", max_seq_len);
 
     const uint64_t total_bytes = offsets[n_seqs] - offsets[0];
@@ -549,6 +548,26 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
         Slot& sl = f->slot[c & 1];
         PackSource src; memset(&src, 0, sizeof src);
         src.n_ranges = group_in; src.cnt = cnt;
+        uint32_t chunk_max = max_seq_len;
+        bool inside = true;                                             // every copy below stays inside [offsets[0], offsets[n_seqs]]
+        for (uint32_t g = 0; g < group_in; ++g) {
+            const uint64_t s0 = (uint64_t)g * n_rows + a;
+            inside = inside && offsets[0] <= offsets[s0] && offsets[s0] <= offsets[s0 + cnt] && offsets[s0 + cnt] <= offsets[n_seqs];
+        }
+        if (!inside) { rc = fail(DYIBF_ERR_ARG, "offsets not monotone"); break; }
+        if (scan_len) {
+            uint64_t mx = 0;                                            // branch-free (vectorises): a decreasing pair wraps to > 2^32
+            for (uint32_t g = 0; g < group_in; ++g) {
+                const uint64_t* o = offsets + (uint64_t)g * n_rows + a;
+                for (uint32_t s = 0; s < cnt; ++s) mx = std::max(mx, o[s + 1] - o[s]);
+            }
+            if (mx > 0xffffffffull) { rc = fail(DYIBF_ERR_ARG, "offsets not monotone, or a sequence longer than 2^32"); break; }
+            chunk_max = (uint32_t)std::max<uint64_t>(mx, 1);
+            if (chunk_max >= k && chunk_max - k + 1 > 65535) {
+                rc = fail(DYIBF_ERR_ARG, "a sequence of %u bases has more than 65535 k-mers (uint16 counts in the reference)", chunk_max);
+                break;
+            }
+        }
         uint64_t bytes = 0;
         for (uint32_t g = 0; g < group_in; ++g) {
             const uint64_t s0 = (uint64_t)g * n_rows + a;
@@ -575,7 +594,7 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
             src.offsets[g] = doff;
         }
         uint64_t* d_rows = d_rows_all ? d_rows_all + a * W : (uint64_t*)sl.rows.p;
-        rc = query_on_device(f, sl, src, bytes, encoding, (uint32_t)group, derive_rc, threshold, max_seq_len, d_rows, d_counts, sl.st);
+        rc = query_on_device(f, sl, src, bytes, encoding, (uint32_t)group, derive_rc, threshold, chunk_max, d_rows, d_counts, sl.st);
         if (rc) break;
         if (h_rows) CU(cudaMemcpyAsync(h_rows + a * W, d_rows, (uint64_t)cnt * W * 8, cudaMemcpyDeviceToHost, sl.st));
         if (h_counts)

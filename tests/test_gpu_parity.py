@@ -504,3 +504,39 @@ def test_query_chunking_does_not_change_results(dy, golden, reads, ka1_filter, p
         assert np.array_equal(np.nonzero(bits[:, b])[0], ids[int(bo[b]):int(bo[b + 1])])
     if not paired:                                                      # six copies of KA1's reads: row r == KA1 row r % 6400
         assert np.array_equal(rows, np.tile(golden["ka1_rows"], (6, 1)))
+
+
+def test_host_batch_argument_errors(dy):
+    """Bad limits and over-long sequences are refused by the host-buffer calls (the length scan runs chunk by chunk inside the
+    pipeline): DYIBF_ERR_ARG, and the handle stays usable afterwards."""
+    import ctypes as C
+    from dream_yara_b200._lib import ENC_DNA5, MEM_HOST
+    L = dy.lib()
+    f = dy.SeqAnBloomFilter(64, 2, 16, (1 << 24) + 256)
+    rng = np.random.default_rng(3)
+    n = 40_000                                                            # > 4 x 8192 rows: several chunks
+    codes = rng.integers(0, 4, size=n * 50, dtype=np.uint8)
+    off = np.arange(n + 1, dtype=np.uint64) * 50
+    rows = np.zeros((n, 1), dtype=np.uint64)
+    bo = np.zeros(65, dtype=np.uint64); ids = np.zeros(4 * n, dtype=np.uint32); tot = C.c_uint64(0)
+    ptr = lambda a: C.c_void_p(a.ctypes.data)
+    def query(o, max_len=0):
+        return L.dyibf_query_batch(f._h, ptr(codes), ptr(o), n, ENC_DNA5, 2, 1, 3, max_len, ptr(rows), None, MEM_HOST, None)
+    def classify(o):
+        return L.dyibf_classify(f._h, ptr(codes), ptr(o), n, ENC_DNA5, 2, 1, 3, ptr(bo), ptr(ids), ids.size, C.byref(tot))
+    assert query(off) == 0
+    good = rows.copy()
+    bad = off.copy(); bad[n - 5] = bad[n - 4] + 7                         # a decreasing pair in the last chunk
+    assert query(bad) == -1 and "monotone" in L.dyibf_last_error().decode()
+    assert classify(bad) == -1
+    bad = off.copy(); bad[-1] = 0                                         # ends before it starts
+    assert query(bad) == -1 and classify(bad) == -1
+    assert query(off, max_len=70_000) == -1 and "65535" in L.dyibf_last_error().decode()
+    long_codes = rng.integers(0, 4, size=70_000, dtype=np.uint8)          # one sequence with more than 65535 k-mers
+    loff = np.array([0, 70_000], dtype=np.uint64)
+    one = np.zeros((1, 1), dtype=np.uint64)
+    rc = L.dyibf_query_batch(f._h, ptr(long_codes), ptr(loff), 1, ENC_DNA5, 1, 0, 3, 0, ptr(one), None, MEM_HOST, None)
+    assert rc == -1 and "65535" in L.dyibf_last_error().decode()
+    assert query(off) == 0 and np.array_equal(rows, good)                 # the handle still works
+    assert classify(off) == 0 and int(bo[64]) == tot.value
+    f.close()
