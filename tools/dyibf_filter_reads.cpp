@@ -11,10 +11,12 @@
 // batch, one line per bin in sortedBins order (:843-854): "<batch> <bin> <n> id id ...".
 #include <zlib.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <iostream>
 #include <string>
@@ -68,6 +70,28 @@ void readAll(const std::string & path, std::vector<char> & out)
 }
 
 struct Records { std::vector<uint8_t> seqs; std::vector<uint64_t> limits; };
+
+// the batch handed to dyibf_classify lives in pinned host memory (its upload then runs at PCIe speed), grown on demand
+struct PinnedBytes
+{
+    uint8_t * p = nullptr; size_t cap = 0, n = 0;
+    ~PinnedBytes() { dyibf_host_free(p); }
+    void clear() { n = 0; }
+    void append(const uint8_t * src, size_t len)
+    {
+        if (n + len > cap)
+        {
+            size_t want = std::max<size_t>(2 * cap, n + len + 4096);
+            void * q = nullptr;
+            if (dyibf_host_alloc(&q, want) != DYIBF_OK) { std::cerr << dyibf_last_error() << std::endl; exit(1); }
+            if (n) memcpy(q, p, n);
+            dyibf_host_free(p);
+            p = (uint8_t *)q; cap = want;
+        }
+        memcpy(p + n, src, len);
+        n += len;
+    }
+};
 
 void parse(int device, const std::string & path, Records & r)
 {
@@ -137,7 +161,7 @@ int main(int argc, char ** argv)
     if (!outFile.empty()) { out.open(outFile); if (!out) { std::cerr << "Unable to open " << outFile << std::endl; return 1; } }
     double filterReads = 0;
     uint64_t filteredReads = 0, batchNo = 0;
-    std::vector<uint8_t> seqs; std::vector<uint64_t> limits, binOffsets(prm.bins + 1); std::vector<uint32_t> ids, order(prm.bins);
+    PinnedBytes seqs; std::vector<uint64_t> limits, binOffsets(prm.bins + 1); std::vector<uint32_t> ids, order(prm.bins);
     for (uint64_t first = 0; first < nReads; first += readsBatch, ++batchNo)
     {
         const double tb = now();
@@ -148,8 +172,8 @@ int main(int argc, char ** argv)
         {
             if (!r) continue;
             const uint64_t b0 = r->limits[first], b1 = r->limits[first + n];
-            const uint64_t base = seqs.size();
-            seqs.insert(seqs.end(), r->seqs.begin() + b0, r->seqs.begin() + b1);
+            const uint64_t base = seqs.n;
+            seqs.append(r->seqs.data() + b0, b1 - b0);
             for (uint64_t i = 1; i <= n; ++i) limits.push_back(base + r->limits[first + i] - b0);
         }
         // clasifyLoadedReads, d_mapper.h:308-375
@@ -159,10 +183,10 @@ int main(int argc, char ** argv)
         if (threshold == 0)
             std::cerr << "[WARNING!] 0 k-mer is required to filter a read!\nAll reads will pass filteration and be mapped everywhere.\n "
                          "This will be extremly slow.\n Choose an approprate error rate based on kmer size and read length\n";
-        if (seqs.empty()) seqs.push_back(0);
+        if (seqs.n == 0) { const uint8_t zero = 0; seqs.append(&zero, 1); }
         uint64_t total = 0;
         ids.resize(std::max<uint64_t>(ids.size(), 4 * n));
-        int rc = dyibf_classify(filter, seqs.data(), limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, threshold,
+        int rc = dyibf_classify(filter, seqs.p, limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, threshold,
                                 binOffsets.data(), ids.data(), ids.size(), &total);
         if (rc == DYIBF_ERR_CAPACITY)
         {

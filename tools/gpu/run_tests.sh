@@ -1,5 +1,12 @@
-set -x
+#!/bin/bash
+# the round-end check as the driver runs it: GPU tests, smoke, one short bench line
 mkdir -p gpurun_out
-( time python -m pytest tests -m gpu -x -q ) > gpurun_out/gpu_tests.log 2>&1; echo "pytest rc=$?" >> gpurun_out/gpu_tests.log
-tail -n 30 gpurun_out/gpu_tests.log
-exit 0
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/final_tests.log 2>&1; echo "tests rc=$?" | tee -a gpurun_out/final_tests.log
+tail -n 3 gpurun_out/final_tests.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/final_smoke.log 2>&1; echo "smoke rc=$?"; tail -n 2 gpurun_out/final_smoke.log
+timeout 600 python bench.py > gpurun_out/final_bench.json 2> gpurun_out/final_bench.err; echo "bench rc=$?"; tail -n 3 gpurun_out/final_bench.err
+python - <<'PY'
+import json
+d = json.loads(open("gpurun_out/final_bench.json").read().strip().splitlines()[-1])
+print(d["value"], d["ms_per_step"], d["e2e"]["value"], d["roofline"]["frac"], d["dropin_batches"]["value"], d["clocks"])
+PY
