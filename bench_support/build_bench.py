@@ -242,6 +242,20 @@ def run_b200(args, B):
         if not torch.equal(chk, words_host[: 1 << 24]):
             raise AssertionError("downloaded words differ from the table in HBM")
         del out_words, chk
+        # optional A/B of DYIBF_OPT_BUILD_CHUNK_MIB (re-adding the same contigs leaves the table as it is)
+        if os.environ.get("DYIBF_BENCH_BUILD_CHUNKS"):
+            by_chunk = {}
+            for mib in [int(x) for x in os.environ["DYIBF_BENCH_BUILD_CHUNKS"].split(",")]:
+                check(L.dyibf_set_option(f_host._h, 3, mib))
+                host_step(f_host, order[0])
+                barrier()
+                t0 = time.perf_counter()
+                for s in range(2):
+                    host_step(f_host, order[s])
+                barrier()
+                by_chunk[str(mib)] = world * kmers_step * 2 / (time.perf_counter() - t0)
+            check(L.dyibf_set_option(f_host._h, 3, 256))
+            e2e["add_only_by_chunk_mib"] = by_chunk
 
     # ---- extra (not the headline): the same steps with the bucketed build off = one atomic OR per (k-mer, hash) straight
     #      into the table (DYIBF_OPT_BUILD_BUCKET_MIB = 0); ORs of bits that are already set cost the same traffic

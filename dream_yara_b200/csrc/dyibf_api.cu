@@ -1166,8 +1166,10 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
     BucketRun br;
     int brc = buckets_begin(f, (offsets[n_seqs] - offsets[0]) * f->hp.h, &br);
     if (brc) return brc;
-    uint32_t a = 0, c = 0;
-    while (a < n_seqs) {
+    // Software-pipelined by one chunk: the copies of chunk c+1 are issued (on the other slot's stream) before chunk c's
+    // kernels, so that they also run while buckets_scatter blocks the host to empty a full record buffer (level 2 / apply).
+    struct Chunk { uint32_t a, cnt; uint64_t bytes, words; };
+    auto stage = [&](uint32_t a, uint32_t c, Chunk* out) -> int {
         uint32_t b = a + 1;
         while (b < n_seqs && offsets[b + 1] - offsets[a] <= target) ++b;
         const uint32_t cnt = b - a;
@@ -1182,21 +1184,32 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         if (bytes) CU(cudaMemcpyAsync(sl.in_bytes.p, seqs + offsets[a], bytes, cudaMemcpyHostToDevice, sl.st));
         CU(cudaMemcpyAsync(sl.in_offsets.p, offsets + a, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
         CU(cudaMemcpyAsync(sl.counts.p, bin_ids + a, (uint64_t)cnt * 4, cudaMemcpyHostToDevice, sl.st));
+        *out = Chunk{a, cnt, bytes, words};
+        return DYIBF_OK;
+    };
+    Chunk cur, next;
+    int src_rc = stage(0, 0, &cur);
+    if (src_rc) return src_rc;
+    for (uint32_t c = 0;; ++c) {
+        const bool more = cur.a + cur.cnt < n_seqs;
+        if (more) { src_rc = stage(cur.a + cur.cnt, c + 1, &next); if (src_rc) return src_rc; }
+        Slot& sl = f->slot[c & 1];
         PackSource src; memset(&src, 0, sizeof src);
-        src.n_ranges = 1; src.cnt = cnt; src.first_off[0] = offsets[a];
-        src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[a]; src.offsets[0] = (const uint64_t*)sl.in_offsets.p;
+        src.n_ranges = 1; src.cnt = cur.cnt; src.first_off[0] = offsets[cur.a];
+        src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[cur.a]; src.offsets[0] = (const uint64_t*)sl.in_offsets.p;
         { Scope sc(f, sl.st, K_PACK);
-          CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, sl.st)); }
+          CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, cur.words, cur.words, sl.st)); }
         if (br.active) {
             brc = buckets_scatter(f, &br, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, (const uint32_t*)sl.counts.p,
-                                  cnt, words, c & 1, true, sl.st);
+                                  cur.cnt, cur.words, c & 1, true, sl.st);
             if (brc) return brc;
         } else {
             Scope sc(f, sl.st, K_BUILD);
             CU(launch_build(build_params(f), f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
-                            (const uint32_t*)sl.counts.p, cnt, words, sl.st));
+                            (const uint32_t*)sl.counts.p, cur.cnt, cur.words, sl.st));
         }
-        a = b; ++c;
+        if (!more) break;
+        cur = next;
     }
     CU(cudaStreamSynchronize(f->slot[0].st));
     CU(cudaStreamSynchronize(f->slot[1].st));
