@@ -1166,39 +1166,67 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
     BucketRun br;
     int brc = buckets_begin(f, (offsets[n_seqs] - offsets[0]) * f->hp.h, &br);
     if (brc) return brc;
-    // Software-pipelined by one chunk: the copies of chunk c+1 are issued (on the other slot's stream) before chunk c's
-    // kernels, so that they also run while buckets_scatter blocks the host to empty a full record buffer (level 2 / apply).
+    // The bases go up on a copy stream of their own, two chunks ahead of the kernels: the upload of chunk c+2 into slot c&1
+    // starts as soon as pack(c) has consumed that slot's bytes, and keeps running while buckets_scatter blocks the host on
+    // the two kernel streams to empty a full record buffer (level 2 / apply).  pack(c) waits for its own upload by event.
     struct Chunk { uint32_t a, cnt; uint64_t bytes, words; };
-    auto stage = [&](uint32_t a, uint32_t c, Chunk* out) -> int {
+    std::vector<Chunk> chunks;
+    uint64_t max_bytes = 0, max_words = 0; uint32_t max_cnt = 0;
+    for (uint32_t a = 0; a < n_seqs;) {
         uint32_t b = a + 1;
         while (b < n_seqs && offsets[b + 1] - offsets[a] <= target) ++b;
-        const uint32_t cnt = b - a;
-        const uint64_t bytes = offsets[b] - offsets[a];
-        Slot& sl = f->slot[c & 1];
-        CU(sl.in_bytes.reserve(bytes + 16));
-        CU(sl.in_offsets.reserve((uint64_t)(cnt + 1) * 8));
-        CU(sl.counts.reserve((uint64_t)cnt * 4));
-        const uint64_t words = packed_words_for(bytes, cnt);
-        CU(sl.packed.reserve(words * 8));
-        CU(sl.meta.reserve((uint64_t)cnt * sizeof(SeqMeta)));
-        if (bytes) CU(cudaMemcpyAsync(sl.in_bytes.p, seqs + offsets[a], bytes, cudaMemcpyHostToDevice, sl.st));
-        CU(cudaMemcpyAsync(sl.in_offsets.p, offsets + a, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
-        CU(cudaMemcpyAsync(sl.counts.p, bin_ids + a, (uint64_t)cnt * 4, cudaMemcpyHostToDevice, sl.st));
-        *out = Chunk{a, cnt, bytes, words};
+        const Chunk ch{a, b - a, offsets[b] - offsets[a], packed_words_for(offsets[b] - offsets[a], b - a)};
+        chunks.push_back(ch);
+        max_bytes = std::max(max_bytes, ch.bytes); max_words = std::max(max_words, ch.words); max_cnt = std::max(max_cnt, ch.cnt);
+        a = b;
+    }
+    for (int i = 0; i < 2 && i < (int)chunks.size(); ++i) {        // sized once: no reallocation under the pipeline
+        Slot& sl = f->slot[i];
+        CU(sl.in_bytes.reserve(max_bytes + 16));
+        CU(sl.in_offsets.reserve((uint64_t)(max_cnt + 1) * 8));
+        CU(sl.counts.reserve((uint64_t)max_cnt * 4));
+        CU(sl.packed.reserve(max_words * 8));
+        CU(sl.meta.reserve((uint64_t)max_cnt * sizeof(SeqMeta)));
+    }
+    struct Upload {                                                  // copy stream + per-slot events, released on every exit path
+        cudaStream_t st = nullptr; cudaEvent_t copied[2] = {nullptr, nullptr}, packed[2] = {nullptr, nullptr};
+        ~Upload() {
+            if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+            for (int i = 0; i < 2; ++i) { if (copied[i]) cudaEventDestroy(copied[i]); if (packed[i]) cudaEventDestroy(packed[i]); }
+        }
+    } up;
+    CU(cudaStreamCreateWithFlags(&up.st, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaEventCreateWithFlags(&up.copied[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&up.packed[i], cudaEventDisableTiming));
+    }
+    auto upload = [&](uint32_t c) -> int {                           // bases + limits of chunk c into slot c&1, on the copy stream
+        const Chunk& ch = chunks[c]; Slot& sl = f->slot[c & 1];
+        if (ch.bytes) CU(cudaMemcpyAsync(sl.in_bytes.p, seqs + offsets[ch.a], ch.bytes, cudaMemcpyHostToDevice, up.st));
+        CU(cudaMemcpyAsync(sl.in_offsets.p, offsets + ch.a, (uint64_t)(ch.cnt + 1) * 8, cudaMemcpyHostToDevice, up.st));
+        CU(cudaEventRecord(up.copied[c & 1], up.st));
         return DYIBF_OK;
     };
-    Chunk cur, next;
-    int src_rc = stage(0, 0, &cur);
-    if (src_rc) return src_rc;
-    for (uint32_t c = 0;; ++c) {
-        const bool more = cur.a + cur.cnt < n_seqs;
-        if (more) { src_rc = stage(cur.a + cur.cnt, c + 1, &next); if (src_rc) return src_rc; }
+    int urc = upload(0);
+    if (!urc && chunks.size() > 1) urc = upload(1);
+    if (urc) return urc;
+    for (uint32_t c = 0; c < chunks.size(); ++c) {
+        const Chunk& cur = chunks[c];
         Slot& sl = f->slot[c & 1];
+        // bin ids: small, and read by this chunk's split kernels to the end, so they travel on the kernel stream
+        CU(cudaMemcpyAsync(sl.counts.p, bin_ids + cur.a, (uint64_t)cur.cnt * 4, cudaMemcpyHostToDevice, sl.st));
+        CU(cudaStreamWaitEvent(sl.st, up.copied[c & 1], 0));
         PackSource src; memset(&src, 0, sizeof src);
         src.n_ranges = 1; src.cnt = cur.cnt; src.first_off[0] = offsets[cur.a];
         src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[cur.a]; src.offsets[0] = (const uint64_t*)sl.in_offsets.p;
         { Scope sc(f, sl.st, K_PACK);
           CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, cur.words, cur.words, sl.st)); }
+        if (c + 2 < chunks.size()) {                                 // the slot's bytes are free once this pack has run
+            CU(cudaEventRecord(up.packed[c & 1], sl.st));
+            CU(cudaStreamWaitEvent(up.st, up.packed[c & 1], 0));
+            urc = upload(c + 2);
+            if (urc) return urc;
+        }
         if (br.active) {
             brc = buckets_scatter(f, &br, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, (const uint32_t*)sl.counts.p,
                                   cur.cnt, cur.words, c & 1, true, sl.st);
@@ -1208,8 +1236,6 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
             CU(launch_build(build_params(f), f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
                             (const uint32_t*)sl.counts.p, cur.cnt, cur.words, sl.st));
         }
-        if (!more) break;
-        cur = next;
     }
     CU(cudaStreamSynchronize(f->slot[0].st));
     CU(cudaStreamSynchronize(f->slot[1].st));
