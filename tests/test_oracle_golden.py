@@ -204,3 +204,40 @@ def test_load_filtered_reads_vs_reference(oracle, golden, gather_golden, tag, pa
     sizes = np.diff(bo.astype(np.int64))
     sb = g[tag + "_sorted_bins"]
     assert sorted(sb.tolist()) == list(range(64)) and np.all(np.diff(sizes[sb]) <= 0)
+
+
+@pytest.mark.skipif(not Ref.available(), reason="oracle/_ref/libref_ibf.so not built")
+@pytest.mark.parametrize("bins,h,k,nbits", [
+    (1, 1, 4, 64 * 50 + 256),                 # one bin, one hash, tiny k
+    (63, 2, 12, (1 << 16) + 256),             # W = 1, last word bit unused
+    (64, 3, 18, (1 << 18) + 256),             # W = 1 exactly (BASELINE configs[0] shape)
+    (65, 4, 19, 128 * 1001 + 256),            # W = 2, P = 1001 (odd)
+    (130, 5, 31, 192 * 777 + 256 + 64),       # W = 3, (N - 256) % S != 0: unused words in front of the trailer
+    (1024, 3, 32, 1024 * 257 + 256),          # k = 32: the leading-N term is gone from the first k-mer on
+    (200, 2, 25, 256 * 4096 + 256),           # power-of-two P with W = 4
+])
+def test_oracle_vs_compiled_reference_shapes(oracle, bins, h, k, nbits):
+    """The restatement against the compiled reference over the corners of the parameter space: W = 1..16, odd and power-of-two P,
+    unaligned trailers, k from 4 to 32, 1..5 hash functions; sequences with N runs, leading N, length k exactly."""
+    ref = Ref()
+    rng = np.random.default_rng(bins * 131 + k)
+    f = ref.new(bins, h, k, nbits)
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    seqs = []
+    for i in range(40):
+        n = k if i % 7 == 0 else int(rng.integers(k, 300))
+        c = rng.integers(0, 4, n).astype(np.uint8)
+        if i % 3 == 0:
+            c[: int(rng.integers(1, min(n, 6) + 1))] = 4              # leading N (the hashInit quirk)
+        if i % 4 == 0:
+            a = int(rng.integers(0, n)); c[a:a + int(rng.integers(1, 20))] = 4
+        b = int(rng.integers(0, bins))
+        ref.add_kmers(f, c, b); oracle.add_kmers(words, p, c, b); seqs.append(c)
+    assert np.array_equal(ref.words(f)[: p.P * p.W], words[: p.P * p.W])
+    for c in seqs[:25]:
+        q = c[: max(k, min(c.size, 150))]
+        assert np.array_equal(ref.kmer_hashes(q, k), oracle.kmer_hashes(q, k))
+        for thr in (1, 2, max(1, (q.size - k + 1) // 2), q.size - k + 1):
+            assert np.array_equal(ref.which_bins(f, q, thr, bins), oracle.which_bins(words, p, q, thr)), (thr, q.size)
+    ref.free(f)
