@@ -301,6 +301,7 @@ def run_b200(args):
     units_world = 1 if sharded else world                                # cfg4: every GPU sees every read
     genomes = synth.genomes(bins, args.genome_len, first_bin=rank * bins if sharded else 0)
     words = torch.zeros(P * W, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()          # the fill runs on torch's stream; the library's streams are not ordered behind it
     f = dy.SeqAnBloomFilter.attach(bins, H, K, nbits, words.data_ptr(), device=local, keep=words)
     t_build = time.perf_counter()
     if rank == 0 or sharded:                                             # cfg4: every rank builds its own bin shard

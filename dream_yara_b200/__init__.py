@@ -5,7 +5,7 @@ the reference's SeqAnBloomFilter class (ibf.py) and of the mapper's filtering st
 multi-GPU shardings (dist.py).  Nothing in this package has a CPU implementation of the filter.
 """
 from ._lib import ENC_ASCII, ENC_DNA5, ENC_DNA5Q, DyibfError, lib          # noqa: F401
-from .ibf import SeqAnBloomFilter, SeqAnKDXFilter, as_batch, read_fasta                    # noqa: F401
+from .ibf import ClassifyTicket, FilterGroup, SeqAnBloomFilter, SeqAnKDXFilter, as_batch, read_fasta                    # noqa: F401
 from .ingest import parseRecords, readRecords                               # noqa: F401
 from .mapper import (DisOptions, ReadSet, clasifyLoadedReads, loadFilteredReads, readFilterMetadata,  # noqa: F401
                      sortedBins, loadReads)

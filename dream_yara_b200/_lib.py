@@ -6,7 +6,9 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libdyibf.so")
 
-OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_FORMAT, ERR_SIZE_MISMATCH, ERR_CAPACITY, ERR_NOMEM = 0, -1, -2, -3, -4, -5, -6, -7
+OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_FORMAT, ERR_SIZE_MISMATCH, ERR_CAPACITY, ERR_NOMEM, ERR_BUSY = 0, -1, -2, -3, -4, -5, -6, -7, -8
+DEVERR_BIN_RANGE, DEVERR_SEQ_TOO_LONG = 1, 2
+GROUP_READ_SHARDED, GROUP_BIN_SHARDED = 0, 1
 ENC_DNA5, ENC_DNA5Q, ENC_ASCII = 0, 1, 2
 MEM_HOST, MEM_DEVICE = 0, 1
 FMT_FASTA, FMT_FASTQ = 0, 1
@@ -30,6 +32,11 @@ class Profile(C.Structure):
                 ("build_launches", C.c_uint64), ("clear_launches", C.c_uint64), ("query_lookups", C.c_uint64),
                 ("build_apply_ms", C.c_double), ("build_apply_launches", C.c_uint64),
                 ("build_split2_ms", C.c_double), ("build_split2_launches", C.c_uint64)]
+
+
+class IoStats(C.Structure):
+    _fields_ = [("bytes", C.c_uint64), ("seconds", C.c_double), ("file_seconds", C.c_double),
+                ("copy_wait_seconds", C.c_double), ("threads", C.c_int), ("devices", C.c_int)]
 
 
 # every symbol include/dyibf.h declares: name -> (restype, argtypes)
@@ -71,6 +78,30 @@ SYMBOLS = {
     "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),
     "dyibf_profile_get": (C.c_int, [_P, C.POINTER(Profile), C.c_int]),
+    "dyibf_launch_count": (C.c_uint64, [_P]),
+    "dyibf_device_errors": (C.c_int, [_P, C.POINTER(C.c_uint32), C.c_int]),
+    "dyibf_set_io_threads": (C.c_int, [C.c_int]),
+    "dyibf_last_io_stats": (C.c_int, [C.POINTER(IoStats)]),
+    "dyibf_classify_begin": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(_P)]),
+    "dyibf_classify_poll": (C.c_int, [_P, C.POINTER(C.c_int)]),
+    "dyibf_classify_end": (C.c_int, [_P, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dyibf_classify_cancel": (None, [_P]),
+    "dyibf_shard_bins": (C.c_int, [C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "dyibf_shard_reads": (C.c_int, [C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "dyibf_group_create": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(_P)]),
+    "dyibf_group_load_file": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(_P)]),
+    "dyibf_group_destroy": (None, [_P]),
+    "dyibf_group_get_params": (C.c_int, [_P, C.POINTER(Params), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "dyibf_group_member": (C.c_int, [_P, C.c_int, C.POINTER(_P), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "dyibf_group_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
+    "dyibf_group_save_file": (C.c_int, [_P, C.c_char_p]),
+    "dyibf_broadcast_filter": (C.c_int, [_P, C.c_int]),
+    "dyibf_group_classify": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32,
+                                       _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dyibf_group_classify_fetch": (C.c_int, [_P, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "dyibf_group_classify_begin": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(_P)]),
+    "dyibf_group_add_sequences": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, _U32P, C.c_int]),
+    "dyibf_group_clear_bins": (C.c_int, [_P, _U32P, C.c_uint32]),
     "dyibf_host_alloc": (C.c_int, [C.POINTER(_P), C.c_size_t]),
     "dyibf_host_free": (None, [_P]),
 }

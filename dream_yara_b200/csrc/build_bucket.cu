@@ -86,6 +86,11 @@ __device__ __forceinline__ LaneWord load_lane_word(const HashParams& hp, const u
     w.hi_w = __ldg(packed + t); w.lo_w = __ldg(packed + t + 1);
     w.firstN = flags & 1u;
     const uint32_t bin = __ldg(bin_ids + s);
+    if (bin >= hp.bins) {                          // device-resident bin ids the host could not check: flag, add nothing
+        if (hp.err) atomicOr(hp.err, DYIBF_DEVERR_BIN_RANGE);
+        w.cnt = 0;
+        return w;
+    }
     w.bit = bin & 63u; w.col = bin >> 6;
     w.i0_hi = i0 >= 32 ? 32u : 0u;
     return w;

@@ -45,6 +45,10 @@ __device__ __forceinline__ void for_each_update(const HashParams& hp, const uint
     const uint64_t hi_w = packed[t], lo_w = packed[t + 1];
     const uint32_t firstN = m.flags & 1u;
     const uint32_t bin = bin_ids[s];
+    if (bin >= hp.bins) {                          // device-resident bin ids the host could not check: flag, add nothing
+        if (hp.err) atomicOr(hp.err, DYIBF_DEVERR_BIN_RANGE);
+        return;
+    }
     const uint32_t bit = bin & 63u;
     const uint64_t col = bin >> 6;
     #pragma unroll 4

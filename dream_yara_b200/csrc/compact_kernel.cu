@@ -48,7 +48,7 @@ size_t compact_workspace_bytes(uint32_t bins, uint32_t n_rows)
 template <bool FILL>
 __global__ void __launch_bounds__(CW * 32) compact_walk(const uint32_t* __restrict__ rows32, uint32_t n_rows, uint32_t bins,
                                                         CompactGeom g, uint64_t* __restrict__ ws,
-                                                        uint32_t* __restrict__ read_ids, uint64_t capacity)
+                                                        uint32_t* __restrict__ read_ids, uint64_t capacity, uint32_t id_base)
 {
     __shared__ uint64_t counters[CW][1024];
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(CW * 32) compact_walk(const uint32_t* __restri
                 const uint32_t b = __ffs(v) - 1;
                 v &= v - 1;
                 const uint64_t c = cnt[b * 32 + lane];
-                if (FILL && c < capacity) read_ids[c] = r0 + i;
+                if (FILL && c < capacity) read_ids[c] = id_base + r0 + i;
                 cnt[b * 32 + lane] = c + 1;
             }
         }
@@ -187,7 +187,7 @@ cudaError_t launch_compact_count(const uint64_t* rows, uint32_t n_rows, uint32_t
     uint64_t units = (uint64_t)g.n_chunks * g.n_ctiles;
     if (units == 0) return cudaSuccess;
     compact_walk<false><<<(unsigned)((units + CW - 1) / CW), CW * 32, 0, st>>>(
-        reinterpret_cast<const uint32_t*>(rows), n_rows, bins, g, ws, nullptr, 0);
+        reinterpret_cast<const uint32_t*>(rows), n_rows, bins, g, ws, nullptr, 0, 0);
     return cudaGetLastError();
 }
 
@@ -219,13 +219,13 @@ cudaError_t launch_compact_scan(uint64_t* ws, uint32_t bins, uint32_t n_rows, ui
 }
 
 cudaError_t launch_compact_fill(const uint64_t* rows, uint32_t n_rows, uint32_t bins, const uint64_t* ws,
-                                uint32_t* read_ids, uint64_t capacity, cudaStream_t st)
+                                uint32_t* read_ids, uint64_t capacity, uint32_t id_base, cudaStream_t st)
 {
     CompactGeom g = compact_geom(bins, n_rows);
     uint64_t units = (uint64_t)g.n_chunks * g.n_ctiles;
     if (units == 0) return cudaSuccess;
     compact_walk<true><<<(unsigned)((units + CW - 1) / CW), CW * 32, 0, st>>>(
-        reinterpret_cast<const uint32_t*>(rows), n_rows, bins, g, const_cast<uint64_t*>(ws), read_ids, capacity);
+        reinterpret_cast<const uint32_t*>(rows), n_rows, bins, g, const_cast<uint64_t*>(ws), read_ids, capacity, id_base);
     return cudaGetLastError();
 }
 

@@ -7,23 +7,15 @@
 //   u64 (1<<56 | nbits) ; ceil(nbits/64) little-endian u64 words ; the last four words are [bins, h, k, 0].
 // In HBM only the P*W data words are kept; the (all-zero) gap before the trailer and the trailer itself are
 // synthesised when the filter is downloaded or saved.
-#include "dyibf_internal.h"
+#include "dyibf_handle.h"
 
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <cstdarg>
 #include <cmath>
-#include <mutex>
-#include <string>
-#include <vector>
-#include <algorithm>
 
 using namespace dyibf;
 
-namespace {
+namespace dyibf {
 
-thread_local std::string g_err;
+static thread_local std::string g_err;
 
 int fail(int code, const char* fmt, ...)
 {
@@ -32,71 +24,8 @@ int fail(int code, const char* fmt, ...)
     g_err = buf;
     return code;
 }
-#define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) \
-    return fail(DYIBF_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
-
-const uint64_t SEED = 0x90b45d39fb6da1faULL;      // _seedValue, d_bloom_filter.h:329
-const uint64_t META_BITS = 256;                    // filterMetadataSize, d_misc_options.h:40
-const size_t   STAGE_BYTES = 32u << 20;            // pinned staging buffers for file / word transfers
-
-struct DevBuf {
-    void* p = nullptr; size_t cap = 0;
-    cudaError_t reserve(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-};
-
-struct Slot {                     // one stage of the host-mode pipeline
-    cudaStream_t st = nullptr;
-    DevBuf in_bytes, in_offsets, packed, meta, rows, counts, ctr;
-};
-
-enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_APPLY, K_SPLIT2, K_N };
-
-struct Pending { cudaEvent_t a, b; int kind; };
-
-} // namespace
-
-struct dyibf_filter {
-    dyibf_params prm;
-    HashParams   hp;
-    int          sm_count = 148;
-    uint64_t*    d_words = nullptr;       // P*W data words
-    uint64_t     data_words = 0;
-    bool         owns_words = true;
-    Slot         slot[2];
-    DevBuf       misc, compact_ws, build_bins, rows_all, stats;
-    // the read batch and the per-bin lists of the last dyibf_classify stay resident for dyibf_gather_reads
-    DevBuf       batch_bytes, batch_offsets, csr_off, csr_ids, gather_ws, gather_out, gather_ids;
-    struct { bool valid = false; uint32_t n_fwd = 0, group = 0, encoding = 0; uint64_t first_off = 0; } batch;
-    std::vector<uint64_t> h_csr_off;
-    uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
-    int64_t      bucket_mib = -1;         // DYIBF_OPT_BUILD_BUCKET_MIB: -1 auto, 0 direct atomics only
-    int64_t      query_chunk_mib = 0;     // DYIBF_OPT_QUERY_CHUNK_MIB: 0 = auto
-    int64_t      build_chunk_mib = 256;   // DYIBF_OPT_BUILD_CHUNK_MIB: bases per host-mode build chunk
-    DevBuf       bucket_records, bucket_cursors;
-    void*        stage[2] = {nullptr, nullptr};   // pinned
-    cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
-    bool         profiling = false;
-    std::vector<Pending> pending;
-    std::vector<cudaEvent_t> ev_pool;
-    double       ms[K_N] = {0, 0, 0, 0, 0, 0, 0};
-    uint64_t     launches[K_N] = {0, 0, 0, 0, 0, 0, 0};
-};
-
-namespace {
-
-struct DeviceGuard {
-    int prev = -1; bool ok = true;
-    explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; ok = cudaSetDevice(dev) == cudaSuccess; }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
+const std::string& last_error_string() { return g_err; }
+void set_last_error(const std::string& s) { g_err = s; }
 
 int init_params(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, dyibf_params* prm, HashParams* hp)
 {
@@ -154,6 +83,20 @@ int new_handle(uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, int device
         if (e != cudaSuccess) { cudaFree(f->d_words); delete f; return fail(DYIBF_ERR_CUDA, "cudaMemset: %s", cudaGetErrorString(e)); }
         if (zero) { e = cudaMemset(f->d_words, 0, f->data_words * 8); if (e != cudaSuccess) { cudaFree(f->d_words); delete f; return fail(DYIBF_ERR_CUDA, "cudaMemset: %s", cudaGetErrorString(e)); } }
     }
+    // sticky device-side error word (DYIBF_DEVERR_*): kernels OR into it, dyibf_device_errors reads it
+    {
+        cudaError_t e = f->dev_err.reserve(8);
+        if (e == cudaSuccess) e = cudaMemset(f->dev_err.p, 0, 8);
+        if (e != cudaSuccess) { if (f->owns_words) cudaFree(f->d_words); delete f; return fail(DYIBF_ERR_CUDA, "device error word: %s", cudaGetErrorString(e)); }
+        f->hp.err = static_cast<uint32_t*>(f->dev_err.p);
+    }
+    // The fills above run on the legacy default stream and are asynchronous to the host; every later operation of this
+    // handle runs on non-blocking streams that are NOT ordered behind it.  Wait here, once, so that no upload, build or
+    // caller-stream kernel can reach words the zero fill has not written yet.
+    {
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { if (f->owns_words) cudaFree(f->d_words); f->dev_err.release(); delete f; return fail(DYIBF_ERR_CUDA, "zero fill: %s", cudaGetErrorString(e)); }
+    }
     for (int i = 0; i < 2; ++i) {
         if (cudaStreamCreateWithFlags(&f->slot[i].st, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreateWithFlags(&f->stage_ev[i], cudaEventDisableTiming) != cudaSuccess) {
@@ -171,19 +114,6 @@ int ensure_stage(dyibf_filter* f)
     return DYIBF_OK;
 }
 
-// profiling: bracket a launch with events on its stream
-struct Scope {
-    dyibf_filter* f; cudaStream_t st; int kind; cudaEvent_t a = nullptr, b = nullptr;
-    static cudaEvent_t get(dyibf_filter* f) {
-        if (!f->ev_pool.empty()) { cudaEvent_t e = f->ev_pool.back(); f->ev_pool.pop_back(); return e; }
-        cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
-    }
-    Scope(dyibf_filter* f_, cudaStream_t st_, int kind_) : f(f_), st(st_), kind(kind_) {
-        if (f->profiling) { a = get(f); b = get(f); cudaEventRecord(a, st); }
-    }
-    ~Scope() { if (a) { cudaEventRecord(b, st); f->pending.push_back({a, b, kind}); } }
-};
-
 void drain_profile(dyibf_filter* f)
 {
     for (auto& p : f->pending) {
@@ -194,35 +124,6 @@ void drain_profile(dyibf_filter* f)
         f->ev_pool.push_back(p.a); f->ev_pool.push_back(p.b);
     }
     f->pending.clear();
-}
-
-struct FileHeader { uint64_t nbits; uint32_t bins, h, k; uint64_t file_size; };
-
-int read_file_header(FILE* fp, const char* path, FileHeader* fh)
-{
-    uint64_t header = 0;
-    if (fread(&header, 8, 1, fp) != 1) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
-    if ((header >> 56) != 1) return fail(DYIBF_ERR_FORMAT, "File \"%s\" is not an sdsl bit_vector (width byte %u)", path, (unsigned)(header >> 56));
-    fh->nbits = header & ((1ULL << 56) - 1);
-    if (fh->nbits < META_BITS + 64) return fail(DYIBF_ERR_FORMAT, "File \"%s\": %llu bits is too small for a filter", path, (unsigned long long)fh->nbits);
-    if (fseeko(fp, 0, SEEK_END) != 0) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
-    fh->file_size = (uint64_t)ftello(fp);
-    uint64_t n_words = (fh->nbits + 63) >> 6;
-    if (fh->file_size < 8 + n_words * 8) return fail(DYIBF_ERR_FORMAT, "File \"%s\" is truncated: %llu bytes for %llu bits", path,
-                                                     (unsigned long long)fh->file_size, (unsigned long long)fh->nbits);
-    // _getMetadata, d_bloom_filter.h:255-265: three 64-bit reads at bit nbits-256 (+64, +128); they are
-    // word-aligned iff nbits is a multiple of 64, otherwise they straddle words (sdsl bits::read_int)
-    uint64_t m = fh->nbits - META_BITS;
-    uint64_t w0 = m >> 6, sh = m & 63;
-    uint64_t buf[5] = {0, 0, 0, 0, 0};
-    size_t want = (size_t)std::min<uint64_t>(5, n_words - w0);
-    if (fseeko(fp, (off_t)(8 + w0 * 8), SEEK_SET) != 0 || fread(buf, 8, want, fp) != want)
-        return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
-    auto get = [&](int i) { return sh ? (buf[i] >> sh) | (buf[i + 1] << (64 - sh)) : buf[i]; };
-    fh->bins = (uint32_t)get(0);           // truncation as the members have it (u32, u8, u8)
-    fh->h = (uint8_t)get(1);
-    fh->k = (uint8_t)get(2);
-    return DYIBF_OK;
 }
 
 // trailer + gap words for download/save: word index `w` of the sdsl array, w >= data_words
@@ -238,7 +139,7 @@ void synth_tail(const dyibf_filter* f, uint64_t first, uint64_t n, uint64_t* out
     }
 }
 
-} // namespace
+} // namespace dyibf
 
 extern "C" {
 
@@ -278,7 +179,8 @@ void dyibf_destroy(dyibf_filter* f)
         if (f->stage[i]) cudaFreeHost(f->stage[i]);
         if (f->stage_ev[i]) cudaEventDestroy(f->stage_ev[i]);
     }
-    f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release(); f->stats.release();
+    free_tickets(f);
+    f->misc.release(); f->compact_ws.release(); f->build_bins.release(); f->rows_all.release(); f->stats.release(); f->dev_err.release();
     f->batch_bytes.release(); f->batch_offsets.release(); f->csr_off.release(); f->csr_ids.release();
     f->gather_ws.release(); f->gather_out.release(); f->gather_ids.release();
     f->bucket_records.release(); f->bucket_cursors.release();
@@ -311,55 +213,6 @@ int dyibf_peek_file(const char* path, uint32_t* bins, uint32_t* n_hash, uint32_t
     if (rc) return rc;
     if (bins) *bins = fh.bins; if (n_hash) *n_hash = fh.h; if (kmer) *kmer = fh.k; if (nbits) *nbits = fh.nbits;
     return DYIBF_OK;
-}
-
-static int load_impl(const char* path, bool expect, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits,
-                     int device, dyibf_filter** out)
-{
-    if (!path || !out) return fail(DYIBF_ERR_ARG, "NULL argument");
-    *out = nullptr;
-    FILE* fp = fopen(path, "rb");
-    if (!fp) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
-    FileHeader fh; int rc = read_file_header(fp, path, &fh);
-    if (rc) { fclose(fp); return rc; }
-    if (expect) {
-        if (fh.nbits != nbits) { fclose(fp); return fail(DYIBF_ERR_SIZE_MISMATCH, "Size mismatch: \n\t Loaded file \t%llu bits\n\t expected\t%llu",
-                                                          (unsigned long long)fh.nbits, (unsigned long long)nbits); }
-    } else { bins = fh.bins; n_hash = fh.h; kmer = fh.k; nbits = fh.nbits; }
-    dyibf_filter* f = nullptr;
-    rc = new_handle(bins, n_hash, kmer, nbits, device, nullptr, false, &f);
-    if (rc) { fclose(fp); return rc; }
-    DeviceGuard guard(device);
-    rc = ensure_stage(f);
-    // stream the data words: disk -> pinned (alternating) -> HBM
-    uint64_t left = f->data_words * 8, done = 0;
-    int cur = 0;
-    if (!rc && fseeko(fp, 8, SEEK_SET) != 0) rc = fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
-    while (!rc && left) {
-        size_t n = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
-        cudaEventSynchronize(f->stage_ev[cur]);                      // previous copy out of this buffer finished
-        if (fread(f->stage[cur], 1, n, fp) != n) { rc = fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path); break; }
-        cudaError_t e = cudaMemcpyAsync((char*)f->d_words + done, f->stage[cur], n, cudaMemcpyHostToDevice, f->slot[0].st);
-        if (e == cudaSuccess) e = cudaEventRecord(f->stage_ev[cur], f->slot[0].st);
-        if (e != cudaSuccess) { rc = fail(DYIBF_ERR_CUDA, "filter upload: %s", cudaGetErrorString(e)); break; }
-        done += n; left -= n; cur ^= 1;
-    }
-    fclose(fp);
-    if (!rc && cudaStreamSynchronize(f->slot[0].st) != cudaSuccess) rc = fail(DYIBF_ERR_CUDA, "filter upload failed");
-    if (rc) { std::string keep = g_err; dyibf_destroy(f); g_err = keep; return rc; }
-    *out = f;
-    return DYIBF_OK;
-}
-
-int dyibf_load_file(const char* path, int device, dyibf_filter** out)
-{
-    return load_impl(path, false, 0, 0, 0, 0, device, out);
-}
-
-int dyibf_load_file_expect(const char* path, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device,
-                           dyibf_filter** out)
-{
-    return load_impl(path, true, bins, n_hash, kmer, nbits, device, out);
 }
 
 int dyibf_upload_words(dyibf_filter* f, const uint64_t* host_words, uint64_t first, uint64_t n)
@@ -417,52 +270,12 @@ int dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first, 
     return DYIBF_OK;
 }
 
-int dyibf_save_file(dyibf_filter* f, const char* path)
-{
-    if (!f || !path) return fail(DYIBF_ERR_ARG, "NULL argument");
-    DeviceGuard guard(f->prm.device);
-    int rc = ensure_stage(f); if (rc) return rc;
-    FILE* fp = fopen(path, "wb");
-    if (!fp) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
-    uint64_t header = (1ULL << 56) | f->prm.nbits;
-    bool ok = fwrite(&header, 8, 1, fp) == 1;
-    uint64_t left = f->data_words * 8, done = 0; int cur = 0;
-    size_t c[2] = {0, 0};
-    // HBM -> pinned (alternating) -> disk; the next D2H is in flight while the previous buffer is written
-    if (ok && left) {
-        c[cur] = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
-        ok = cudaMemcpyAsync(f->stage[cur], (const char*)f->d_words + done, c[cur], cudaMemcpyDeviceToHost, f->slot[0].st) == cudaSuccess &&
-             cudaEventRecord(f->stage_ev[cur], f->slot[0].st) == cudaSuccess;
-        done += c[cur]; left -= c[cur];
-    }
-    while (ok && c[cur]) {
-        int nx = cur ^ 1; c[nx] = 0;
-        if (left) {
-            c[nx] = (size_t)std::min<uint64_t>(left, STAGE_BYTES);
-            ok = cudaMemcpyAsync(f->stage[nx], (const char*)f->d_words + done, c[nx], cudaMemcpyDeviceToHost, f->slot[0].st) == cudaSuccess &&
-                 cudaEventRecord(f->stage_ev[nx], f->slot[0].st) == cudaSuccess;
-            done += c[nx]; left -= c[nx];
-        }
-        ok = ok && cudaEventSynchronize(f->stage_ev[cur]) == cudaSuccess && fwrite(f->stage[cur], 1, c[cur], fp) == c[cur];
-        cur = nx;
-    }
-    if (ok) {
-        uint64_t tail_n = f->prm.n_words - f->data_words;
-        std::vector<uint64_t> tail(tail_n);
-        synth_tail(f, f->data_words, tail_n, tail.data());
-        ok = fwrite(tail.data(), 8, tail_n, fp) == tail_n;
-    }
-    ok = (fclose(fp) == 0) && ok;
-    if (!ok) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
-    return DYIBF_OK;
-}
-
 } // extern "C"
 
 // ============================================================================================================
 // query / compaction / build drivers
 // ============================================================================================================
-namespace {
+namespace dyibf {
 
 // pack + query of one device-resident batch on stream st, using the workspace of slot sl
 int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t total_bytes, int encoding, uint32_t group,
@@ -512,12 +325,14 @@ int check_query_args(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offse
 // Destination: h_rows (host, per-chunk D2H) and/or d_rows_all (device, whole batch).
 int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding, int group,
                int derive_rc, uint32_t threshold, uint32_t max_seq_len, uint64_t* h_rows, uint64_t* d_rows_all,
-               uint16_t* h_counts, bool keep_batch = false)
+               uint16_t* h_counts, bool keep_batch, uint32_t row0, uint32_t row1)
 {
     const uint32_t group_in = derive_rc ? group / 2 : group;
     const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
     const uint32_t n_rows = (uint32_t)(n_total / group);
-    if (n_rows == 0) return DYIBF_OK;
+    if (row1 > n_rows) row1 = n_rows;
+    if (n_rows == 0 || row0 >= row1) return DYIBF_OK;
+    const uint32_t n_mine = row1 - row0;                               // rows this call produces
     const uint32_t W = f->prm.words_per_block, k = f->hp.k;
     // Without a caller-supplied bound the longest sequence is found chunk by chunk below, just before the chunk's copies are
     // issued: the scan of one chunk's limits then runs while the device works on the chunk before (a scan of all limits up
@@ -530,12 +345,12 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
     const uint64_t total_bytes = offsets[n_seqs] - offsets[0];
     const uint64_t per_row = total_bytes / n_rows + 8ull * group_in + 8ull * W + 1;
     uint64_t chunk_rows = ((uint64_t)(f->query_chunk_mib > 0 ? f->query_chunk_mib : 48) << 20) / per_row;
-    if (f->query_chunk_mib <= 0 && n_rows <= chunk_rows)             // small batch: overlap its own upload with its own query
-        chunk_rows = std::max<uint64_t>(((uint64_t)n_rows + 5) / 6, 8192);   // measured on 100 000-read calls: 2/4/6/8/16 cuts
+    if (f->query_chunk_mib <= 0 && n_mine <= chunk_rows)             // small batch: overlap its own upload with its own query
+        chunk_rows = std::max<uint64_t>(((uint64_t)n_mine + 5) / 6, 8192);   // measured on 100 000-read calls: 2/4/6/8/16 cuts
                                                                              // -> 35.1/39.4/41.9/38.6/35.6 M reads/s (one chunk 28.5)
     if (h_counts) chunk_rows = std::min<uint64_t>(chunk_rows, (256ull << 20) / ((uint64_t)group * f->prm.bins * 2 + 1));
     chunk_rows = std::max<uint64_t>(chunk_rows, 1024);
-    chunk_rows = std::min<uint64_t>(chunk_rows, n_rows);
+    chunk_rows = std::min<uint64_t>(chunk_rows, n_mine);
 
     if (keep_batch) {                     // the whole forward set stays in HBM, laid out like the caller's buffer
         f->batch.valid = false;
@@ -543,8 +358,8 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
         CU(f->batch_offsets.reserve((uint64_t)(n_seqs + 1) * 8));
     }
     int rc = DYIBF_OK; uint32_t c = 0;
-    for (uint64_t a = 0; a < n_rows && !rc; a += chunk_rows, ++c) {
-        const uint32_t cnt = (uint32_t)std::min<uint64_t>(chunk_rows, n_rows - a);
+    for (uint64_t a = row0; a < row1 && !rc; a += chunk_rows, ++c) {
+        const uint32_t cnt = (uint32_t)std::min<uint64_t>(chunk_rows, row1 - a);
         Slot& sl = f->slot[c & 1];
         PackSource src; memset(&src, 0, sizeof src);
         src.n_ranges = group_in; src.cnt = cnt;
@@ -593,13 +408,13 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
             src.bytes[g] = dst - src.first_off[g];
             src.offsets[g] = doff;
         }
-        uint64_t* d_rows = d_rows_all ? d_rows_all + a * W : (uint64_t*)sl.rows.p;
+        uint64_t* d_rows = d_rows_all ? d_rows_all + (a - row0) * W : (uint64_t*)sl.rows.p;
         rc = query_on_device(f, sl, src, bytes, encoding, (uint32_t)group, derive_rc, threshold, chunk_max, d_rows, d_counts, sl.st);
         if (rc) break;
-        if (h_rows) CU(cudaMemcpyAsync(h_rows + a * W, d_rows, (uint64_t)cnt * W * 8, cudaMemcpyDeviceToHost, sl.st));
+        if (h_rows) CU(cudaMemcpyAsync(h_rows + (a - row0) * W, d_rows, (uint64_t)cnt * W * 8, cudaMemcpyDeviceToHost, sl.st));
         if (h_counts)
             for (uint32_t g = 0; g < (uint32_t)group; ++g)
-                CU(cudaMemcpyAsync(h_counts + ((uint64_t)g * n_rows + a) * f->prm.bins, d_counts + (uint64_t)g * cnt * f->prm.bins,
+                CU(cudaMemcpyAsync(h_counts + ((uint64_t)g * n_mine + (a - row0)) * f->prm.bins, d_counts + (uint64_t)g * cnt * f->prm.bins,
                                    (uint64_t)cnt * f->prm.bins * 2, cudaMemcpyDeviceToHost, sl.st));
     }
     cudaError_t e0 = cudaStreamSynchronize(f->slot[0].st), e1 = cudaStreamSynchronize(f->slot[1].st);
@@ -614,7 +429,7 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
 }
 
 // compaction of device rows; bin_offsets/read_ids are device pointers; *total on the host (synchronises st)
-int compact_on_device(dyibf_filter* f, const uint64_t* d_rows, uint32_t n_rows, uint64_t* d_bin_offsets,
+int compact_on_device(dyibf_filter* f, const uint64_t* d_rows, uint32_t n_rows, uint32_t id_base, uint64_t* d_bin_offsets,
                       uint32_t* d_read_ids, uint64_t capacity, uint64_t* total, cudaStream_t st)
 {
     const uint32_t bins = f->prm.bins;
@@ -623,7 +438,7 @@ int compact_on_device(dyibf_filter* f, const uint64_t* d_rows, uint32_t n_rows, 
     CU(cudaMemsetAsync(ws, 0, compact_workspace_bytes(bins, n_rows), st));
     uint64_t tot = 0;
     {
-        Scope sc(f, st, K_COMPACT);
+        Scope sc(f, st, K_COMPACT, 5);                               // count walk, three scan kernels, offsets gather
         CU(launch_compact_count(d_rows, n_rows, bins, ws, st));
         CU(launch_compact_scan(ws, bins, n_rows, d_bin_offsets, st));
     }
@@ -634,12 +449,12 @@ int compact_on_device(dyibf_filter* f, const uint64_t* d_rows, uint32_t n_rows, 
                                     (unsigned long long)tot, (unsigned long long)capacity);
     {
         Scope sc(f, st, K_COMPACT);
-        CU(launch_compact_fill(d_rows, n_rows, bins, ws, d_read_ids, capacity, st));
+        CU(launch_compact_fill(d_rows, n_rows, bins, ws, d_read_ids, capacity, id_base, st));
     }
     return DYIBF_OK;
 }
 
-} // namespace
+} // namespace dyibf
 
 extern "C" {
 
@@ -666,7 +481,7 @@ int dyibf_query_batch(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offs
     if (n_seqs == 0) return DYIBF_OK;
     DeviceGuard guard(f->prm.device);
     if (mem == DYIBF_MEM_HOST)
-        return query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, max_seq_len, out_rows, nullptr, out_counts);
+        return query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, max_seq_len, out_rows, nullptr, out_counts, false, 0, 0xffffffffu);
     if (mem != DYIBF_MEM_DEVICE) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
     // device mode: one range, whole batch, caller's stream; total bytes are not known on the host without a
     // read-back, so the two offsets that bound the batch are fetched (16 bytes, synchronises the stream)
@@ -692,7 +507,7 @@ int dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64
     DeviceGuard guard(f->prm.device);
     const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
     if (mem == DYIBF_MEM_DEVICE)
-        return compact_on_device(f, rows, n_rows, bin_offsets, read_ids, capacity, total, (cudaStream_t)stream);
+        return compact_on_device(f, rows, n_rows, 0, bin_offsets, read_ids, capacity, total, (cudaStream_t)stream);
     if (mem != DYIBF_MEM_HOST) return fail(DYIBF_ERR_ARG, "unknown memory space %d", mem);
     Slot& sl = f->slot[0];
     CU(sl.rows.reserve((uint64_t)n_rows * W * 8 + 8));
@@ -700,7 +515,7 @@ int dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64
     if (n_rows) CU(cudaMemcpyAsync(sl.rows.p, rows, (uint64_t)n_rows * W * 8, cudaMemcpyHostToDevice, sl.st));
     // pass 1 + scan give the total; the id buffer is sized from it
     uint64_t tot = 0;
-    int rc = compact_on_device(f, (const uint64_t*)sl.rows.p, n_rows, (uint64_t*)f->misc.p, nullptr, 0, &tot, sl.st);
+    int rc = compact_on_device(f, (const uint64_t*)sl.rows.p, n_rows, 0, (uint64_t*)f->misc.p, nullptr, 0, &tot, sl.st);
     if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
     CU(cudaMemcpyAsync(bin_offsets, f->misc.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
     CU(cudaStreamSynchronize(sl.st));
@@ -711,15 +526,19 @@ int dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64
     CU(sl.counts.reserve(tot * 4));
     {
         Scope sc(f, sl.st, K_COMPACT);
-        CU(launch_compact_fill((const uint64_t*)sl.rows.p, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)sl.counts.p, tot, sl.st));
+        CU(launch_compact_fill((const uint64_t*)sl.rows.p, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)sl.counts.p, tot, 0, sl.st));
     }
     CU(cudaMemcpyAsync(read_ids, sl.counts.p, tot * 4, cudaMemcpyDeviceToHost, sl.st));
     CU(cudaStreamSynchronize(sl.st));
     return DYIBF_OK;
 }
 
-// copy the per-bin lists of the last dyibf_classify to the host
-static int classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total)
+} // extern "C"
+
+namespace dyibf {
+
+// copy the per-bin lists of the last classify to the host
+int classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total)
 {
     const uint32_t bins = f->prm.bins;
     if (f->h_csr_off.size() != (size_t)bins + 1) return fail(DYIBF_ERR_ARG, "no dyibf_classify result is resident");
@@ -735,6 +554,47 @@ static int classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read
     return DYIBF_OK;
 }
 
+// rows [row0, row1) of the batch: query with the rows kept in HBM, compaction into the handle's resident CSR with the
+// row numbers of the WHOLE batch as ids (a device of a read-sharded group filters a contiguous row range)
+int classify_range(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding, int group,
+                   int derive_rc, uint32_t threshold, uint32_t row0, uint32_t row1)
+{
+    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
+    const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
+    const uint32_t n_rows = (uint32_t)(n_total / group);
+    if (row1 > n_rows) row1 = n_rows;
+    if (row0 > row1) row0 = row1;
+    const uint32_t n_mine = row1 - row0;
+    f->h_csr_off.clear(); f->batch.valid = false;
+    // rows of the whole range stay in HBM; only the CSR lists cross PCIe.  With derive_rc (and the whole batch on this
+    // device) the forward read set stays resident as well, so that dyibf_gather_reads needs no second upload.
+    CU(f->rows_all.reserve((uint64_t)n_mine * W * 8 + 8));
+    uint64_t* d_rows = (uint64_t*)f->rows_all.p;
+    if (n_mine) {
+        int rc = query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, 0, nullptr, d_rows, nullptr,
+                            derive_rc != 0 && n_mine == n_rows, row0, row1);
+        if (rc) return rc;
+    }
+    Slot& sl = f->slot[0];
+    CU(f->csr_off.reserve((uint64_t)(bins + 1) * 8));
+    uint64_t tot = 0;
+    int rc = compact_on_device(f, d_rows, n_mine, row0, (uint64_t*)f->csr_off.p, nullptr, 0, &tot, sl.st);
+    if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
+    f->h_csr_off.resize((size_t)bins + 1);
+    CU(cudaMemcpyAsync(f->h_csr_off.data(), f->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
+    if (tot) {
+        CU(f->csr_ids.reserve(tot * 4));
+        Scope sc(f, sl.st, K_COMPACT);
+        CU(launch_compact_fill(d_rows, n_mine, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)f->csr_ids.p, tot, row0, sl.st));
+    }
+    CU(cudaStreamSynchronize(sl.st));
+    return DYIBF_OK;
+}
+
+} // namespace dyibf
+
+extern "C" {
+
 int dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
                    int group, int derive_rc, uint32_t threshold, uint64_t* bin_offsets, uint32_t* read_ids,
                    uint64_t capacity, uint64_t* total)
@@ -743,32 +603,8 @@ int dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets
     if (rc) return rc;
     if (!bin_offsets || (capacity && !read_ids)) return fail(DYIBF_ERR_ARG, "NULL argument");
     DeviceGuard guard(f->prm.device);
-    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
-    const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
-    const uint32_t n_rows = (uint32_t)(n_total / group);
-    f->h_csr_off.clear(); f->batch.valid = false;
-    // rows of the whole batch stay in HBM; only the CSR lists cross PCIe.  With derive_rc the forward read set stays
-    // resident as well, so that dyibf_gather_reads can build the per-bin read sets without a second upload.
-    CU(f->rows_all.reserve((uint64_t)n_rows * W * 8 + 8));
-    uint64_t* d_rows = (uint64_t*)f->rows_all.p;
-    if (n_rows) {
-        rc = query_host(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, 0, nullptr, d_rows, nullptr,
-                        derive_rc != 0);
-        if (rc) return rc;
-    }
-    Slot& sl = f->slot[0];
-    CU(f->csr_off.reserve((uint64_t)(bins + 1) * 8));
-    uint64_t tot = 0;
-    rc = compact_on_device(f, d_rows, n_rows, (uint64_t*)f->csr_off.p, nullptr, 0, &tot, sl.st);
-    if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
-    f->h_csr_off.resize((size_t)bins + 1);
-    CU(cudaMemcpyAsync(f->h_csr_off.data(), f->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, sl.st));
-    if (tot) {
-        CU(f->csr_ids.reserve(tot * 4));
-        Scope sc(f, sl.st, K_COMPACT);
-        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)f->csr_ids.p, tot, sl.st));
-    }
-    CU(cudaStreamSynchronize(sl.st));
+    rc = classify_range(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold, 0, 0xffffffffu);
+    if (rc) return rc;
     return classify_fetch(f, bin_offsets, read_ids, capacity, total);
 }
 
@@ -972,14 +808,14 @@ int dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads_
     }
     CU(f->csr_off.reserve((uint64_t)(bins + 1) * 8));
     uint64_t tot = 0;
-    rc = compact_on_device(f, d_rows, n_rows, (uint64_t*)f->csr_off.p, nullptr, 0, &tot, st);
+    rc = compact_on_device(f, d_rows, n_rows, 0, (uint64_t*)f->csr_off.p, nullptr, 0, &tot, st);
     if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
     f->h_csr_off.resize((size_t)bins + 1);
     CU(cudaMemcpyAsync(f->h_csr_off.data(), f->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, st));
     if (tot) {
         CU(f->csr_ids.reserve(tot * 4));
         Scope sc(f, st, K_COMPACT);
-        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)f->csr_ids.p, tot, st));
+        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)f->csr_ids.p, tot, 0, st));
     }
     CU(cudaStreamSynchronize(st));
     f->batch.valid = true; f->batch.n_fwd = (uint32_t)n_fwd; f->batch.group = group; f->batch.encoding = DYIBF_ENC_ASCII;
@@ -1029,7 +865,10 @@ int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
         return DYIBF_OK;
     }
     CU(f->bucket_cursors.reserve(bucket_cursor_slots(br->plan) * 8));
-    CU(cudaMemset(f->bucket_cursors.p, 0, bucket_cursor_slots(br->plan) * 8));
+    // zeroed on a stream of the handle and waited for: the split kernels run on non-blocking streams (and, in device
+    // mode, on the caller's), none of which is ordered behind the legacy default stream a plain cudaMemset uses
+    CU(cudaMemsetAsync(f->bucket_cursors.p, 0, bucket_cursor_slots(br->plan) * 8, f->slot[0].st));
+    CU(cudaStreamSynchronize(f->slot[0].st));
     // 10 % slack per bucket: the hash is uniform; every writing warp may leave a chunk of padding lines per bucket
     br->limit = (uint64_t)((double)br->plan.n_regions * (double)br->plan.cap / 1.10);
     br->limit1 = br->plan.n_super > 1 ? (uint64_t)((double)br->plan.n_super * (double)br->plan.cap1 / 1.10) : br->limit;
@@ -1319,6 +1158,7 @@ int dyibf_profile_enable(dyibf_filter* f, int on)
     if (on && !f->stats.p) {
         CU(f->stats.reserve(64));
         CU(cudaMemset(f->stats.p, 0, 64));
+        CU(cudaDeviceSynchronize());
     }
     f->profiling = on != 0;
     return DYIBF_OK;
@@ -1345,6 +1185,19 @@ int dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset)
     if (reset) for (int i = 0; i < K_N; ++i) { f->ms[i] = 0; f->launches[i] = 0; }
     return DYIBF_OK;
 }
+
+int dyibf_device_errors(dyibf_filter* f, uint32_t* flags, int reset)
+{
+    if (!f || !flags) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    CU(cudaDeviceSynchronize());                                       // everything that could still set a bit has run
+    CU(cudaMemcpy(flags, f->dev_err.p, 4, cudaMemcpyDeviceToHost));
+    if (reset && *flags) CU(cudaMemset(f->dev_err.p, 0, 4));
+    if (reset) CU(cudaDeviceSynchronize());
+    return DYIBF_OK;
+}
+
+uint64_t dyibf_launch_count(const dyibf_filter* f) { return f ? f->kernel_launches : 0; }
 
 int dyibf_host_alloc(void** ptr, size_t bytes)
 {

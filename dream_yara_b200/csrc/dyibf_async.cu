@@ -1,0 +1,203 @@
+// dyibf_async.cu — ticketed (asynchronous) classify: dyibf_classify_begin / dyibf_classify_end.
+//
+// Why: the reference's mapper calls the filtering stage once per batch of 100 000 reads (src/mapper.h:109) while a
+// prefetch thread already loads the next batch (src/file_prefetched.h:137-205).  A synchronous dyibf_classify of such a
+// batch cannot hide its own upload, list download and the query kernel's ramp-up / drain behind anything.  A ticket owns
+// a stream and a private set of buffers, so batch i+1 uploads and starts while batch i is still in the query kernel and
+// batch i-1's lists travel back: the GPU sees a continuous stream of work at the reference's batch size.
+//
+// begin: H2D of the batch (straight from the caller's memory: truly asynchronous when it is pinned, staged by the driver
+//        when it is pageable), pack, query, compaction count + scan + fill, D2H of the bin offsets — all enqueued, nothing
+//        waited for.  The caller's seqs / offsets must stay valid until dyibf_classify_end.
+// end:   waits for the ticket, copies the lists out (the only copy whose size is not known before), and makes the
+//        ticket's batch the handle's resident batch (dyibf_gather_reads / dyibf_classify_fetch work on it).
+#include "dyibf_handle.h"
+
+using namespace dyibf;
+
+namespace dyibf {
+
+struct Ticket {
+    dyibf_filter* f = nullptr;
+    int           index = 0;
+    bool          busy = false;
+    Slot          sl;                         // stream + pack / query workspace
+    DevBuf        bytes, offsets, rows, compact_ws, csr_off, csr_ids;
+    uint64_t*     h_off = nullptr;            // pinned: bins + 1 bin offsets
+    cudaEvent_t   done = nullptr;
+    uint32_t      n_rows = 0;
+    uint64_t      ids_cap = 0;                // entries the fill kernel was allowed to write
+    ResidentBatch batch;
+};
+
+void free_tickets(dyibf_filter* f)
+{
+    for (int i = 0; i < DYIBF_MAX_TICKETS; ++i) {
+        Ticket* t = f->tickets[i];
+        if (!t) continue;
+        if (t->sl.st) { cudaStreamSynchronize(t->sl.st); cudaStreamDestroy(t->sl.st); }
+        if (t->done) cudaEventDestroy(t->done);
+        if (t->h_off) cudaFreeHost(t->h_off);
+        t->sl.in_bytes.release(); t->sl.in_offsets.release(); t->sl.packed.release(); t->sl.meta.release();
+        t->sl.rows.release(); t->sl.counts.release(); t->sl.ctr.release();
+        t->bytes.release(); t->offsets.release(); t->rows.release(); t->compact_ws.release(); t->csr_off.release(); t->csr_ids.release();
+        delete t;
+        f->tickets[i] = nullptr;
+    }
+}
+
+static int acquire_ticket(dyibf_filter* f, Ticket** out)
+{
+    for (int i = 0; i < DYIBF_MAX_TICKETS; ++i) {
+        Ticket* t = f->tickets[i];
+        if (t && t->busy) continue;
+        if (!t) {
+            t = new Ticket();
+            t->f = f; t->index = i;
+            if (cudaStreamCreateWithFlags(&t->sl.st, cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&t->done, cudaEventDisableTiming) != cudaSuccess ||
+                cudaMallocHost((void**)&t->h_off, ((size_t)f->prm.bins + 2) * 8) != cudaSuccess) {
+                if (t->sl.st) cudaStreamDestroy(t->sl.st);
+                if (t->done) cudaEventDestroy(t->done);
+                delete t;
+                return fail(DYIBF_ERR_CUDA, "dyibf_classify_begin: ticket resources could not be created");
+            }
+            f->tickets[i] = t;
+        }
+        *out = t;
+        return DYIBF_OK;
+    }
+    return fail(DYIBF_ERR_BUSY, "dyibf_classify_begin: all %d tickets of this handle are in flight", DYIBF_MAX_TICKETS);
+}
+
+} // namespace dyibf
+
+extern "C" {
+
+int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
+                         int group, int derive_rc, uint32_t threshold, dyibf_ticket** ticket)
+{
+    if (!ticket) return fail(DYIBF_ERR_ARG, "ticket is NULL");
+    *ticket = nullptr;
+    int rc = check_query_args(f, seqs, offsets, n_seqs, encoding, group, derive_rc, threshold);
+    if (rc) return rc;
+    DeviceGuard guard(f->prm.device);
+    Ticket* t = nullptr;
+    rc = acquire_ticket(f, &t);
+    if (rc) return rc;
+    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block, k = f->hp.k;
+    const uint32_t group_in = derive_rc ? group / 2 : group;
+    const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
+    const uint32_t n_rows = (uint32_t)(n_total / group);
+    cudaStream_t st = t->sl.st;
+    t->n_rows = n_rows; t->batch.valid = false; t->ids_cap = 0;
+    CU(t->csr_off.reserve((uint64_t)(bins + 1) * 8));
+    if (n_rows == 0) {
+        CU(cudaMemsetAsync(t->csr_off.p, 0, (uint64_t)(bins + 1) * 8, st));
+    } else {
+        // the longest sequence picks the counter width of the query kernel; one pass over the limits (~30 us per 100 000)
+        uint64_t mx = 0;
+        for (uint32_t s = 0; s < n_seqs; ++s) mx = std::max(mx, offsets[s + 1] - offsets[s]);
+        if (offsets[n_seqs] < offsets[0] || mx > 0xffffffffull) return fail(DYIBF_ERR_ARG, "offsets not monotone, or a sequence longer than 2^32");
+        const uint32_t max_len = (uint32_t)std::max<uint64_t>(mx, 1);
+        if (max_len >= k && max_len - k + 1 > 65535)
+            return fail(DYIBF_ERR_ARG, "a sequence of %u bases has more than 65535 k-mers (uint16 counts in the reference)", max_len);
+        const uint64_t total_bytes = offsets[n_seqs] - offsets[0];
+        CU(t->bytes.reserve(total_bytes + 16));
+        CU(t->offsets.reserve((uint64_t)(n_seqs + 1) * 8));
+        CU(t->rows.reserve((uint64_t)n_rows * W * 8 + 8));
+        if (total_bytes) CU(cudaMemcpyAsync(t->bytes.p, seqs + offsets[0], total_bytes, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(t->offsets.p, offsets, (uint64_t)(n_seqs + 1) * 8, cudaMemcpyHostToDevice, st));
+        // the batch as the pack kernel sees it: group_in ranges of n_rows sequences each, laid out as the caller's buffer
+        PackSource src; memset(&src, 0, sizeof src);
+        src.n_ranges = group_in; src.cnt = n_rows;
+        for (uint32_t g = 0; g < group_in; ++g) {
+            const uint64_t s0 = (uint64_t)g * n_rows;
+            src.first_off[g] = offsets[s0]; src.pack_base[g] = offsets[s0] - offsets[0];
+            src.bytes[g] = (const uint8_t*)t->bytes.p - offsets[0];
+            src.offsets[g] = (const uint64_t*)t->offsets.p + s0;
+        }
+        uint64_t* d_rows = (uint64_t*)t->rows.p;
+        rc = query_on_device(f, t->sl, src, total_bytes, encoding, (uint32_t)group, derive_rc, threshold, max_len, d_rows, nullptr, st);
+        if (rc) return rc;
+        // compaction: count + scan, then the fill into a buffer sized for the usual case (<= 4 lists per row); a batch
+        // that needs more is re-filled in dyibf_classify_end
+        const size_t ws_bytes = compact_workspace_bytes(bins, n_rows);
+        CU(t->compact_ws.reserve(ws_bytes));
+        t->ids_cap = std::max<uint64_t>(4ull * n_rows, 1024);
+        CU(t->csr_ids.reserve(t->ids_cap * 4));
+        t->ids_cap = t->csr_ids.cap / 4;
+        uint64_t* ws = (uint64_t*)t->compact_ws.p;
+        CU(cudaMemsetAsync(ws, 0, ws_bytes, st));
+        {
+            Scope sc(f, st, K_COMPACT, 6);
+            CU(launch_compact_count(d_rows, n_rows, bins, ws, st));
+            CU(launch_compact_scan(ws, bins, n_rows, (uint64_t*)t->csr_off.p, st));
+            CU(launch_compact_fill(d_rows, n_rows, bins, ws, (uint32_t*)t->csr_ids.p, t->ids_cap, 0, st));
+        }
+        if (derive_rc) {
+            t->batch.valid = true; t->batch.n_fwd = n_seqs; t->batch.group = (uint32_t)group; t->batch.encoding = (uint32_t)encoding;
+            t->batch.first_off = offsets[0];
+        }
+    }
+    CU(cudaMemcpyAsync(t->h_off, t->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(t->done, st));
+    t->busy = true;
+    *ticket = reinterpret_cast<dyibf_ticket*>(t);
+    return DYIBF_OK;
+}
+
+int dyibf_classify_poll(dyibf_ticket* ticket, int* ready)
+{
+    Ticket* t = reinterpret_cast<Ticket*>(ticket);
+    if (!t || !t->busy || !ready) return fail(DYIBF_ERR_ARG, "dyibf_classify_poll: not a ticket in flight");
+    cudaError_t e = cudaEventQuery(t->done);
+    if (e != cudaSuccess && e != cudaErrorNotReady) return fail(DYIBF_ERR_CUDA, "dyibf_classify_poll: %s", cudaGetErrorString(e));
+    *ready = e == cudaSuccess;
+    return DYIBF_OK;
+}
+
+int dyibf_classify_end(dyibf_ticket* ticket, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total)
+{
+    Ticket* t = reinterpret_cast<Ticket*>(ticket);
+    if (!t || !t->busy) return fail(DYIBF_ERR_ARG, "dyibf_classify_end: not a ticket in flight");
+    if (!bin_offsets || (capacity && !read_ids)) return fail(DYIBF_ERR_ARG, "NULL argument");
+    dyibf_filter* f = t->f;
+    DeviceGuard guard(f->prm.device);
+    const uint32_t bins = f->prm.bins;
+    cudaStream_t st = t->sl.st;
+    cudaError_t e = cudaEventSynchronize(t->done);
+    if (e != cudaSuccess) { t->busy = false; return fail(DYIBF_ERR_CUDA, "dyibf_classify_end: %s", cudaGetErrorString(e)); }
+    memcpy(bin_offsets, t->h_off, (size_t)(bins + 1) * 8);
+    const uint64_t tot = t->h_off[bins];
+    if (total) *total = tot;
+    if (tot > capacity)                                               // the ticket stays in flight: call again with room
+        return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu", (unsigned long long)tot, (unsigned long long)capacity);
+    if (tot > t->ids_cap) {                                           // rare: more lists than the first fill had room for
+        CU(t->csr_ids.reserve(tot * 4));
+        t->ids_cap = t->csr_ids.cap / 4;
+        Scope sc(f, st, K_COMPACT);
+        CU(launch_compact_fill((const uint64_t*)t->rows.p, t->n_rows, bins, (const uint64_t*)t->compact_ws.p,
+                               (uint32_t*)t->csr_ids.p, t->ids_cap, 0, st));
+    }
+    if (tot) CU(cudaMemcpyAsync(read_ids, t->csr_ids.p, tot * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    // the ticket's batch becomes the handle's resident batch (buffers change hands, nothing is copied)
+    f->h_csr_off.assign(t->h_off, t->h_off + bins + 1);
+    f->csr_off.swap(t->csr_off); f->csr_ids.swap(t->csr_ids);
+    f->batch_bytes.swap(t->bytes); f->batch_offsets.swap(t->offsets);
+    f->batch = t->batch;
+    t->busy = false;
+    return DYIBF_OK;
+}
+
+void dyibf_classify_cancel(dyibf_ticket* ticket)
+{
+    Ticket* t = reinterpret_cast<Ticket*>(ticket);
+    if (!t || !t->busy) return;
+    DeviceGuard guard(t->f->prm.device);
+    cudaStreamSynchronize(t->sl.st);
+    t->busy = false;
+}
+
+} // extern "C"

@@ -21,6 +21,10 @@ struct HashParams {
     // is not a block of the table go to block `sink` (query: an all-zero block behind the data, build: a scratch block)
     uint32_t direct;
     uint64_t sink;
+    // sticky device-side error word of the handle (DYIBF_DEVERR_* bits, include/dyibf.h): a kernel that meets input the
+    // host could not validate (device-resident bin ids, a sequence longer than the caller's bound) ORs a bit in and
+    // skips the offending work instead of writing out of bounds
+    uint32_t* err;
 };
 
 // One packed sequence: 2 bits per base, first base in the two top bits of word 0 (so that a k-mer is a
@@ -104,8 +108,9 @@ static const uint32_t COMPACT_CHUNK_ROWS = 2048;
 size_t      compact_workspace_bytes(uint32_t bins, uint32_t n_rows);
 cudaError_t launch_compact_count(const uint64_t* rows, uint32_t n_rows, uint32_t bins, uint64_t* ws, cudaStream_t st);
 cudaError_t launch_compact_scan(uint64_t* ws, uint32_t bins, uint32_t n_rows, uint64_t* bin_offsets, cudaStream_t st);
+// id_base: added to the row numbers written (a device that filters rows [id_base, id_base + n_rows) of a batch)
 cudaError_t launch_compact_fill(const uint64_t* rows, uint32_t n_rows, uint32_t bins, const uint64_t* ws,
-                                uint32_t* read_ids, uint64_t capacity, cudaStream_t st);
+                                uint32_t* read_ids, uint64_t capacity, uint32_t id_base, cudaStream_t st);
 
 // exclusive scan of u64 a[0..n) in place, total in a[n]; `a` must hold scan_workspace_elems(n) elements
 size_t      scan_workspace_elems(uint64_t n);

@@ -1,0 +1,315 @@
+// dyibf_io.cu — the .filter loader and writer: disk <-> pinned host memory <-> HBM, several reader threads.
+//
+// Reference code replaced: the file constructors of SeqAnBloomFilter (src/d_bloom_filter.h:59-89: sdsl::load_from_file
+// into host RAM, then _getMetadata) and save (:150-154: _setMetadata + sdsl::store_to_file).  The mapper times this stage
+// as "Filter loading time" (src/d_mapper.h:913-921) and it is half of the reference's own test run.
+//
+// On-disk format (sdsl::int_vector<1>::serialize, include/sdsl-lite/include/sdsl/int_vector.hpp:1463-1472,
+// write_header :534-544; trailer d_bloom_filter.h:255-277):
+//   u64 (1<<56 | nbits) ; ceil(nbits/64) little-endian u64 words ; the last four words are [bins, h, k, 0].
+// In HBM only the P*W data words are kept; the (all-zero) gap before the trailer and the trailer itself are
+// synthesised when the filter is downloaded or saved, so a saved file is byte-identical to the reference's.
+//
+// Pipeline: T reader threads (default 4); thread t owns chunks t, t+T, ... of the data words, two pinned buffers and one
+// stream per target device.  pread -> cudaMemcpyAsync(H2D) -> (replicas: cudaMemcpyPeerAsync device 0 -> the others over
+// NVLink, on the same stream) so that file reads, PCIe and NVLink all overlap.  A bin shard (device r of G owns word
+// columns [r W/G, (r+1) W/G) of every block) is a pitched copy out of the same pinned chunk.  Saving runs the pipeline
+// backwards with pwrite.
+#include "dyibf_handle.h"
+
+#include <atomic>
+#include <chrono>
+#include <thread>
+
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+using namespace dyibf;
+
+namespace dyibf {
+
+static std::atomic<int> g_io_threads{4};
+static thread_local dyibf_io_stats g_last_io = {0, 0.0, 0.0, 0.0, 0, 0};
+
+static double now_s()
+{
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+int read_file_header(FILE* fp, const char* path, FileHeader* fh)
+{
+    uint64_t header = 0;
+    if (fread(&header, 8, 1, fp) != 1) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    if ((header >> 56) != 1) return fail(DYIBF_ERR_FORMAT, "File \"%s\" is not an sdsl bit_vector (width byte %u)", path, (unsigned)(header >> 56));
+    fh->nbits = header & ((1ULL << 56) - 1);
+    if (fh->nbits < META_BITS + 64) return fail(DYIBF_ERR_FORMAT, "File \"%s\": %llu bits is too small for a filter", path, (unsigned long long)fh->nbits);
+    if (fseeko(fp, 0, SEEK_END) != 0) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    fh->file_size = (uint64_t)ftello(fp);
+    uint64_t n_words = (fh->nbits + 63) >> 6;
+    if (fh->file_size < 8 + n_words * 8) return fail(DYIBF_ERR_FORMAT, "File \"%s\" is truncated: %llu bytes for %llu bits", path,
+                                                     (unsigned long long)fh->file_size, (unsigned long long)fh->nbits);
+    // _getMetadata, d_bloom_filter.h:255-265: three 64-bit reads at bit nbits-256 (+64, +128); they are
+    // word-aligned iff nbits is a multiple of 64, otherwise they straddle words (sdsl bits::read_int)
+    uint64_t m = fh->nbits - META_BITS;
+    uint64_t w0 = m >> 6, sh = m & 63;
+    uint64_t buf[5] = {0, 0, 0, 0, 0};
+    size_t want = (size_t)std::min<uint64_t>(5, n_words - w0);
+    if (fseeko(fp, (off_t)(8 + w0 * 8), SEEK_SET) != 0 || fread(buf, 8, want, fp) != want)
+        return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    auto get = [&](int i) { return sh ? (buf[i] >> sh) | (buf[i + 1] << (64 - sh)) : buf[i]; };
+    fh->bins = (uint32_t)get(0);           // truncation as the members have it (u32, u8, u8)
+    fh->h = (uint8_t)get(1);
+    fh->k = (uint8_t)get(2);
+    return DYIBF_OK;
+}
+
+// One destination (or source) of the word stream: the words [col0, col0 + Wr) of every W-word block of the file live
+// contiguously (Wr words per block) at d_words on `device`.  Wr == W: the whole table.
+struct IoTarget { int device; uint64_t* d_words; uint32_t col0, Wr; };
+
+struct IoResult { int rc = DYIBF_OK; std::string err; double file_s = 0, wait_s = 0; };
+
+// blocks per chunk so that a chunk is about `want` bytes and holds whole blocks
+static uint64_t blocks_per_chunk(uint32_t W, uint64_t want) { return std::max<uint64_t>(1, want / ((uint64_t)W * 8)); }
+
+static const uint64_t IO_CHUNK_BYTES = 64ull << 20;
+
+// file bytes [8, 8 + n_blocks * W * 8) <-> the targets.  to_device: load; otherwise save (exactly one whole-table target
+// per column range: every word of the file is written once).
+static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blocks, uint32_t W,
+                        const std::vector<IoTarget>& targets, bool replicas, dyibf_io_stats* stats)
+{
+    const double t_begin = now_s();
+    const uint64_t bpc = blocks_per_chunk(W, IO_CHUNK_BYTES);
+    const uint64_t n_chunks = (n_blocks + bpc - 1) / bpc;
+    int T = g_io_threads.load();
+    if (T < 1) T = 1;
+    if ((uint64_t)T > n_chunks) T = (int)std::max<uint64_t>(n_chunks, 1);
+    std::vector<IoResult> res(T);
+    const size_t buf_bytes = (size_t)(bpc * W * 8);
+    auto worker = [&](int t) {
+        IoResult& r = res[t];
+        auto bad = [&](int code, const std::string& what) { if (!r.rc) { r.rc = code; r.err = what; } };
+        const size_t nt = targets.size();
+        void* buf[2] = {nullptr, nullptr};
+        std::vector<cudaStream_t> st(nt, nullptr);
+        std::vector<cudaEvent_t> ev(2 * nt, nullptr);                // ev[b * nt + i]: buffer b is free again for target i
+        // replicas: one stream on the first device drives the H2D and the peer copies; shards: one stream per device
+        const size_t n_streams = replicas ? 1 : nt;
+        for (size_t i = 0; i < n_streams && !r.rc; ++i) {
+            if (cudaSetDevice(targets[i].device) != cudaSuccess ||
+                cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&ev[nt + i], cudaEventDisableTiming) != cudaSuccess)
+                bad(DYIBF_ERR_CUDA, "filter I/O: stream / event creation failed");
+        }
+        for (int b = 0; b < 2 && !r.rc; ++b)
+            if (cudaMallocHost(&buf[b], buf_bytes) != cudaSuccess) bad(DYIBF_ERR_NOMEM, "filter I/O: pinned staging allocation failed");
+        int cur = 0;
+        for (uint64_t c = (uint64_t)t; c < n_chunks && !r.rc; c += (uint64_t)T, cur ^= 1) {
+            const uint64_t blk0 = c * bpc, nb = std::min(bpc, n_blocks - blk0);
+            const size_t bytes = (size_t)(nb * W * 8);
+            const off_t file_off = (off_t)(8 + blk0 * W * 8);
+            double t0 = now_s();
+            for (size_t i = 0; i < n_streams; ++i) cudaEventSynchronize(ev[cur * nt + i]);       // buffer free again
+            r.wait_s += now_s() - t0;
+            if (to_device) {
+                t0 = now_s();
+                size_t got = 0;
+                while (got < bytes) {
+                    ssize_t n = pread(fd, (char*)buf[cur] + got, bytes - got, file_off + (off_t)got);
+                    if (n <= 0) { bad(DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be read."); break; }
+                    got += (size_t)n;
+                }
+                r.file_s += now_s() - t0;
+                if (r.rc) break;
+                cudaError_t e = cudaSuccess;
+                if (replicas) {
+                    const IoTarget& a = targets[0];
+                    e = cudaSetDevice(a.device);
+                    char* dst0 = (char*)a.d_words + blk0 * W * 8;
+                    if (e == cudaSuccess) e = cudaMemcpyAsync(dst0, buf[cur], bytes, cudaMemcpyHostToDevice, st[0]);
+                    if (e == cudaSuccess) e = cudaEventRecord(ev[cur * nt], st[0]);
+                    for (size_t i = 1; i < nt && e == cudaSuccess; ++i)                     // NVLink fan-out of the chunk
+                        e = cudaMemcpyPeerAsync((char*)targets[i].d_words + blk0 * W * 8, targets[i].device, dst0, a.device, bytes, st[0]);
+                } else {
+                    for (size_t i = 0; i < nt && e == cudaSuccess; ++i) {
+                        const IoTarget& a = targets[i];
+                        e = cudaSetDevice(a.device);
+                        if (e != cudaSuccess) break;
+                        if (a.Wr == W)
+                            e = cudaMemcpyAsync((char*)a.d_words + blk0 * W * 8, buf[cur], bytes, cudaMemcpyHostToDevice, st[i]);
+                        else
+                            e = cudaMemcpy2DAsync((char*)a.d_words + blk0 * a.Wr * 8, (size_t)a.Wr * 8, (char*)buf[cur] + (size_t)a.col0 * 8,
+                                                  (size_t)W * 8, (size_t)a.Wr * 8, (size_t)nb, cudaMemcpyHostToDevice, st[i]);
+                        if (e == cudaSuccess) e = cudaEventRecord(ev[cur * nt + i], st[i]);
+                    }
+                }
+                if (e != cudaSuccess) bad(DYIBF_ERR_CUDA, std::string("filter upload: ") + cudaGetErrorString(e));
+            } else {
+                cudaError_t e = cudaSuccess;
+                for (size_t i = 0; i < nt && e == cudaSuccess; ++i) {
+                    const IoTarget& a = targets[i];
+                    e = cudaSetDevice(a.device);
+                    if (e != cudaSuccess) break;
+                    if (a.Wr == W)
+                        e = cudaMemcpyAsync(buf[cur], (char*)a.d_words + blk0 * W * 8, bytes, cudaMemcpyDeviceToHost, st[i]);
+                    else
+                        e = cudaMemcpy2DAsync((char*)buf[cur] + (size_t)a.col0 * 8, (size_t)W * 8, (char*)a.d_words + blk0 * a.Wr * 8,
+                                              (size_t)a.Wr * 8, (size_t)a.Wr * 8, (size_t)nb, cudaMemcpyDeviceToHost, st[i]);
+                    if (e == cudaSuccess) e = cudaEventRecord(ev[cur * nt + i], st[i]);
+                }
+                if (e != cudaSuccess) { bad(DYIBF_ERR_CUDA, std::string("filter download: ") + cudaGetErrorString(e)); break; }
+                // the previous chunk of this thread is written while this one downloads
+                t0 = now_s();
+                for (size_t i = 0; i < n_streams; ++i) cudaEventSynchronize(ev[cur * nt + i]);
+                r.wait_s += now_s() - t0;
+                t0 = now_s();
+                size_t put = 0;
+                while (put < bytes) {
+                    ssize_t n = pwrite(fd, (char*)buf[cur] + put, bytes - put, file_off + (off_t)put);
+                    if (n <= 0) { bad(DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be written."); break; }
+                    put += (size_t)n;
+                }
+                r.file_s += now_s() - t0;
+            }
+        }
+        for (size_t i = 0; i < n_streams; ++i)
+            if (st[i]) {
+                cudaSetDevice(targets[i].device);
+                if (cudaStreamSynchronize(st[i]) != cudaSuccess) bad(DYIBF_ERR_CUDA, "filter I/O: copy failed");
+                cudaStreamDestroy(st[i]);
+            }
+        for (cudaEvent_t e : ev) if (e) cudaEventDestroy(e);
+        for (int b = 0; b < 2; ++b) if (buf[b]) cudaFreeHost(buf[b]);
+    };
+    int prev = -1; cudaGetDevice(&prev);
+    if (T == 1) worker(0);
+    else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; ++t) th.emplace_back(worker, t);
+        for (auto& x : th) x.join();
+    }
+    if (prev >= 0) cudaSetDevice(prev);
+    double file_s = 0, wait_s = 0;
+    for (auto& r : res) { file_s = std::max(file_s, r.file_s); wait_s = std::max(wait_s, r.wait_s); }
+    if (stats) {
+        stats->bytes = n_blocks * W * 8; stats->seconds = now_s() - t_begin; stats->file_seconds = file_s;
+        stats->copy_wait_seconds = wait_s; stats->threads = T; stats->devices = (int)targets.size();
+    }
+    for (auto& r : res) if (r.rc) return fail(r.rc, "%s", r.err.c_str());
+    return DYIBF_OK;
+}
+
+// load the data words of an open, validated .filter file into the targets
+int io_load_words(const char* path, uint64_t n_blocks, uint32_t W, const int* devices, uint64_t* const* d_words, int n,
+                  bool bin_sharded)
+{
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+#ifdef POSIX_FADV_SEQUENTIAL
+    posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+#endif
+    std::vector<IoTarget> tg;
+    const uint32_t Wr = bin_sharded ? W / (uint32_t)n : W;
+    for (int i = 0; i < n; ++i) tg.push_back({devices[i], d_words[i], bin_sharded ? (uint32_t)i * Wr : 0u, Wr});
+    dyibf_io_stats st; memset(&st, 0, sizeof st);
+    int rc = stream_words(fd, path, true, n_blocks, W, tg, !bin_sharded, &st);
+    close(fd);
+    g_last_io = st;
+    return rc;
+}
+
+// write a complete .filter file: header, data words gathered from the sources, zero gap + trailer
+int io_save_words(const char* path, const dyibf_filter* whole_params, uint64_t n_blocks, uint32_t W, const int* devices,
+                  uint64_t* const* d_words, int n, bool bin_sharded)
+{
+    int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
+    const uint64_t header = (1ULL << 56) | whole_params->prm.nbits;
+    const uint64_t data_words = n_blocks * W;
+    const uint64_t tail_n = whole_params->prm.n_words - data_words;
+    std::vector<uint64_t> tail(tail_n);
+    synth_tail(whole_params, data_words, tail_n, tail.data());
+    bool ok = pwrite(fd, &header, 8, 0) == 8;
+    ok = ok && (tail_n == 0 || pwrite(fd, tail.data(), tail_n * 8, (off_t)(8 + data_words * 8)) == (ssize_t)(tail_n * 8));
+    int rc = DYIBF_OK;
+    dyibf_io_stats st; memset(&st, 0, sizeof st);
+    if (ok && data_words) {
+        std::vector<IoTarget> tg;
+        const uint32_t Wr = bin_sharded ? W / (uint32_t)n : W;
+        const int n_src = bin_sharded ? n : 1;                       // replicas: every device holds the same words
+        for (int i = 0; i < n_src; ++i) tg.push_back({devices[i], d_words[i], bin_sharded ? (uint32_t)i * Wr : 0u, Wr});
+        rc = stream_words(fd, path, false, n_blocks, W, tg, false, &st);
+    }
+    ok = (close(fd) == 0) && ok;
+    g_last_io = st;
+    if (rc) return rc;
+    if (!ok) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
+    return DYIBF_OK;
+}
+
+static int load_impl(const char* path, bool expect, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits,
+                     int device, dyibf_filter** out)
+{
+    if (!path || !out) return fail(DYIBF_ERR_ARG, "NULL argument");
+    *out = nullptr;
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return fail(DYIBF_ERR_IO, "File \"%s\" could not be read.", path);
+    FileHeader fh; int rc = read_file_header(fp, path, &fh);
+    fclose(fp);
+    if (rc) return rc;
+    if (expect) {
+        if (fh.nbits != nbits) return fail(DYIBF_ERR_SIZE_MISMATCH, "Size mismatch: \n\t Loaded file \t%llu bits\n\t expected\t%llu",
+                                           (unsigned long long)fh.nbits, (unsigned long long)nbits);
+    } else { bins = fh.bins; n_hash = fh.h; kmer = fh.k; nbits = fh.nbits; }
+    dyibf_filter* f = nullptr;
+    rc = new_handle(bins, n_hash, kmer, nbits, device, nullptr, false, &f);
+    if (rc) return rc;
+    uint64_t* dw = f->d_words;
+    rc = io_load_words(path, f->prm.n_blocks, f->prm.words_per_block, &device, &dw, 1, false);
+    if (rc) { std::string keep = last_error_string(); dyibf_destroy(f); set_last_error(keep); return rc; }
+    *out = f;
+    return DYIBF_OK;
+}
+
+} // namespace dyibf
+
+extern "C" {
+
+int dyibf_load_file(const char* path, int device, dyibf_filter** out)
+{
+    return load_impl(path, false, 0, 0, 0, 0, device, out);
+}
+
+int dyibf_load_file_expect(const char* path, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, int device,
+                           dyibf_filter** out)
+{
+    return load_impl(path, true, bins, n_hash, kmer, nbits, device, out);
+}
+
+int dyibf_save_file(dyibf_filter* f, const char* path)
+{
+    if (!f || !path) return fail(DYIBF_ERR_ARG, "NULL argument");
+    DeviceGuard guard(f->prm.device);
+    CU(cudaDeviceSynchronize());                                      // builds still in flight on caller streams
+    uint64_t* dw = f->d_words; int dev = f->prm.device;
+    return io_save_words(path, f, f->prm.n_blocks, f->prm.words_per_block, &dev, &dw, 1, false);
+}
+
+int dyibf_set_io_threads(int n)
+{
+    if (n < 1 || n > 64) return fail(DYIBF_ERR_ARG, "I/O threads must be 1..64");
+    g_io_threads.store(n);
+    return DYIBF_OK;
+}
+
+int dyibf_last_io_stats(dyibf_io_stats* out)
+{
+    if (!out) return fail(DYIBF_ERR_ARG, "NULL argument");
+    *out = g_last_io;
+    return DYIBF_OK;
+}
+
+} // extern "C"

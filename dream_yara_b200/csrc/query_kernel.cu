@@ -129,6 +129,12 @@ query_kernel(const HashParams hp, const uint8_t* __restrict__ filter, const uint
                     wp = packed + m.word_off;
                     firstN = m.flags & 1u;
                     nk = m.len >= k ? m.len - k + 1 : 0;
+                    if (PLANES < 16 && nk >= (1u << PLANES)) {
+                        // the caller's max_seq_len did not bound this sequence (device mode: nothing could check it): its
+                        // counts would wrap in the 8-plane counters.  Flag it and let it select nothing.
+                        if (li == 0 && tile == 0 && hp.err) atomicOr(hp.err, DYIBF_DEVERR_SEQ_TOO_LONG);
+                        nk = 0;
+                    }
                 }
                 const uint32_t nk_max = __reduce_max_sync(0xffffffffu, nk);
 

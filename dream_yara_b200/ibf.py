@@ -225,6 +225,42 @@ class SeqAnBloomFilter:
         check(rc)
         return offs, ids[: total.value]
 
+    def classifyBegin(self, seqs, threshold, group=2, derive_rc=True, encoding=None):
+        """dyibf_classify_begin: enqueue one batch and return a ticket at once (up to four in flight per filter).  The ticket
+        keeps the host arrays alive until classifyEnd."""
+        concat, offsets, enc = as_batch(seqs, encoding)
+        n = offsets.size - 1
+        t = C.c_void_p()
+        check(self._begin(_ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)), int(threshold), C.byref(t)))
+        return ClassifyTicket(t, (concat, offsets), (2 * n if derive_rc else n) // group, self._noOfBins)
+
+    def _begin(self, *a):
+        return lib().dyibf_classify_begin(self._h, *a)
+
+    def classifyEnd(self, ticket, capacity=None):
+        """dyibf_classify_end: wait for the ticket, (bin_offsets, read_ids) exactly as classify returns them."""
+        offs = np.zeros(ticket.bins + 1, dtype=np.uint64)
+        total = C.c_uint64(0)
+        cap = int(capacity) if capacity is not None else max(4 * ticket.n_rows, 1024)
+        ids = np.zeros(cap, dtype=np.uint32)
+        L = lib()
+        rc = L.dyibf_classify_end(ticket.handle, _ptr(offs), _ptr(ids), cap, C.byref(total))
+        if rc == _lib.ERR_CAPACITY and capacity is None:          # the ticket stays in flight: again, with room
+            cap = int(total.value)
+            ids = np.zeros(cap, dtype=np.uint32)
+            rc = L.dyibf_classify_end(ticket.handle, _ptr(offs), _ptr(ids), cap, C.byref(total))
+        check(rc)
+        ticket.keep = None
+        return offs, ids[: total.value]
+
+    def launch_count(self):
+        return int(lib().dyibf_launch_count(self._h))
+
+    def device_errors(self, reset=True):
+        fl = C.c_uint32(0)
+        check(lib().dyibf_device_errors(self._h, C.byref(fl), int(reset)))
+        return int(fl.value)
+
     def classifyText(self, reads_text, mates_text=None, fmt=1, e_percent=5, capacity=None):
         """loadReads + clasifyLoadedReads from the text of the reads file(s) (bytes; fmt 0 FASTA / 1 FASTQ): only text goes up,
         only the lists come back.  Returns (bin_offsets, read_ids, n_reads, threshold)."""
@@ -314,6 +350,120 @@ class SeqAnBloomFilter:
                                       int(bool(derive_rc)), int(threshold), int(max_seq_len), C.c_void_p(rows_ptr),
                                       C.c_void_p(counts_ptr) if counts_ptr else None, MEM_DEVICE,
                                       C.c_void_p(stream) if stream else None))
+
+
+class ClassifyTicket:
+    """One asynchronous classify in flight (dyibf_ticket)."""
+
+    def __init__(self, handle, keep, n_rows, bins):
+        self.handle, self.keep, self.n_rows, self.bins = handle, keep, n_rows, bins
+
+    def ready(self):
+        r = C.c_int(0)
+        check(lib().dyibf_classify_poll(self.handle, C.byref(r)))
+        return bool(r.value)
+
+
+class FilterGroup:
+    """One filter over several GPUs of ONE process (dyibf_group, include/dyibf.h): mode "read" = a replica per device, the
+    rows of every batch split over the devices; mode "bin" = device r owns the bins dyibf_shard_bins(r) of a filter larger
+    than one GPU's HBM.  What spawnDisMapper's single filter object (src/d_mapper.h:911-922) becomes on an 8-GPU box.
+
+        FilterGroup(n_bins, n_hash_func, kmer_size, vec_size, devices=[0, 1], mode="read")
+        FilterGroup(fileName, devices=[...], mode=...)
+    """
+
+    def __init__(self, *args, devices=(0,), mode="read"):
+        L = lib()
+        self._g = C.c_void_p()
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        m = {"read": _lib.GROUP_READ_SHARDED, "bin": _lib.GROUP_BIN_SHARDED}[mode]
+        if len(args) == 4:
+            check(L.dyibf_group_create(args[0], args[1], args[2], args[3], devs, len(devices), m, C.byref(self._g)))
+        elif len(args) == 1:
+            rc = L.dyibf_group_load_file(str(args[0]).encode(), devs, len(devices), m, C.byref(self._g))
+            SeqAnBloomFilter._exit_like_reference(rc)
+        else:
+            raise TypeError("FilterGroup(n_bins, n_hash_func, kmer_size, vec_size) | (fileName)")
+        p = _lib.Params(); nd, md = C.c_int(0), C.c_int(0)
+        check(L.dyibf_group_get_params(self._g, C.byref(p), C.byref(nd), C.byref(md)))
+        self._noOfBins, self._noOfHashFunc, self._kmerSize = p.bins, p.n_hash, p.kmer
+        self._binIntWidth, self._noOfBits, self._noOfHashPos = p.words_per_block, p.nbits, p.n_blocks
+        self.n_words, self.n_devices, self.mode = p.n_words, nd.value, mode
+        self.devices = list(devices)
+
+    def close(self):
+        if getattr(self, "_g", None) is not None and self._g:
+            lib().dyibf_group_destroy(self._g)
+            self._g = C.c_void_p()
+
+    __del__ = close
+
+    def getNumberOfBins(self):
+        return self._noOfBins
+
+    def getKmerSize(self):
+        return self._kmerSize
+
+    def member(self, i):
+        """(SeqAnBloomFilter view of device i's handle — not owning —, first_bin, n_bins)"""
+        h = C.c_void_p(); fb, nb = C.c_uint32(0), C.c_uint32(0)
+        check(lib().dyibf_group_member(self._g, int(i), C.byref(h), C.byref(fb), C.byref(nb)))
+        f = SeqAnBloomFilter(_handle=h)
+        f.close = lambda: None                                    # the group owns the handle
+        f._owner = self
+        return f, fb.value, nb.value
+
+    def addSequences(self, seqs, bin_ids, encoding=None):
+        concat, offsets, enc = as_batch(seqs, encoding)
+        bins = np.ascontiguousarray(bin_ids, dtype=np.uint32)
+        n = offsets.size - 1
+        if bins.size != n:
+            raise ValueError("bin_ids must have one entry per sequence")
+        check(lib().dyibf_group_add_sequences(self._g, _ptr(concat), _ptr(offsets), n, _ptr(bins), enc))
+
+    def clearBins(self, bins2clear, threadsCount=1):
+        b = np.ascontiguousarray(bins2clear, dtype=np.uint32)
+        check(lib().dyibf_group_clear_bins(self._g, _ptr(b), b.size))
+
+    def save(self, fileName):
+        return lib().dyibf_group_save_file(self._g, str(fileName).encode()) == _lib.OK
+
+    def broadcast(self, src_member=0):
+        check(lib().dyibf_broadcast_filter(self._g, int(src_member)))
+
+    def set_early_exit(self, on=True):
+        check(lib().dyibf_group_set_option(self._g, _lib.OPT_EARLY_EXIT, int(bool(on))))
+
+    def classify(self, seqs, threshold, group=2, derive_rc=True, encoding=None, capacity=None):
+        """clasifyLoadedReads over all devices of the group: (bin_offsets, read_ids), identical to one device's."""
+        concat, offsets, enc = as_batch(seqs, encoding)
+        n = offsets.size - 1
+        n_rows = (2 * n if derive_rc else n) // group
+        offs = np.zeros(self._noOfBins + 1, dtype=np.uint64)
+        total = C.c_uint64(0)
+        cap = int(capacity) if capacity is not None else max(4 * n_rows, 1024)
+        ids = np.zeros(cap, dtype=np.uint32)
+        L = lib()
+        rc = L.dyibf_group_classify(self._g, _ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)), int(threshold),
+                                    _ptr(offs), _ptr(ids), cap, C.byref(total))
+        if rc == _lib.ERR_CAPACITY and capacity is None:
+            cap = int(total.value)
+            ids = np.zeros(cap, dtype=np.uint32)
+            rc = L.dyibf_group_classify_fetch(self._g, _ptr(offs), _ptr(ids), cap, C.byref(total))
+        check(rc)
+        return offs, ids[: total.value]
+
+    def classifyBegin(self, seqs, threshold, group=2, derive_rc=True, encoding=None):
+        """whole batches to successive replicas (read-sharded groups); end with classifyEnd"""
+        concat, offsets, enc = as_batch(seqs, encoding)
+        n = offsets.size - 1
+        t = C.c_void_p()
+        check(lib().dyibf_group_classify_begin(self._g, _ptr(concat), _ptr(offsets), n, enc, group, int(bool(derive_rc)),
+                                               int(threshold), C.byref(t)))
+        return ClassifyTicket(t, (concat, offsets), (2 * n if derive_rc else n) // group, self._noOfBins)
+
+    classifyEnd = SeqAnBloomFilter.classifyEnd
 
 
 class SeqAnKDXFilter(SeqAnBloomFilter):

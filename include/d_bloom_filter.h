@@ -31,6 +31,17 @@
 
 #include "dyibf.h"
 
+// src/d_mapper.cpp:537 (readFilterMetadata) uses sdsl::int_vector<64> and gets it through the reference header's
+// #include <sdsl/bit_vectors.hpp> (src/d_bloom_filter.h:35); keep that TU compiling unchanged where sdsl is on the path.
+// This class itself does not use sdsl.
+#if defined(__has_include)
+#  if __has_include(<sdsl/bit_vectors.hpp>)
+#    include <sdsl/bit_vectors.hpp>
+#  endif
+#endif
+#include <valarray>
+#include <algorithm>
+
 namespace seqan
 {
     template<typename TString = Dna5String>
@@ -39,34 +50,74 @@ namespace seqan
     public:
         typedef Shape<Dna, SimpleShape> TShape;     // kept for source compatibility; hashing happens on the GPU
 
+        // Which GPUs: the reference's call sites construct the filter without saying (src/d_mapper.h:913, src/d_build_filter.cpp:298,
+        // src/d_update_filter.cpp:276), so the unmodified programs pick the devices up from the environment:
+        //   DYIBF_DEVICES = "all" | "0,1,2,3"   (default: device 0 only)
+        //   DYIBF_GROUP_MODE = "read" (default: a replica per GPU, every read batch split over them) | "bin" (the GPUs own
+        //                      contiguous bin ranges of a filter larger than one GPU's HBM)
+        // or a caller passes them: SeqAnBloomFilter(fileName, devices, mode).  More than one device makes the object a
+        // dyibf_group (include/dyibf.h); every member below works on either.
+
         // d_bloom_filter.h:48
-        SeqAnBloomFilter(uint32_t n_bins, uint8_t n_hash_func, uint8_t kmer_size, uint64_t vec_size, int device = 0)
+        SeqAnBloomFilter(uint32_t n_bins, uint8_t n_hash_func, uint8_t kmer_size, uint64_t vec_size, int device = -1)
         {
-            _check(dyibf_create(n_bins, n_hash_func, kmer_size, vec_size, device, &_h));
+            // spawnDisMapper's placeholder for `-ft none` (src/d_mapper.h:941: SeqAnBloomFilter<> filter(64, 3, 20, 1)) is
+            // never queried: a vector too small for one hash block makes an empty object instead of an error
+            if (vec_size < 256 + 64ull * ((n_bins + 63) / 64)) { _prm = dyibf_params(); _prm.bins = n_bins; _prm.n_hash = n_hash_func; _prm.kmer = kmer_size; return; }
+            std::vector<int> devs = _devicesFor(device);
+            if (devs.size() > 1) _check(dyibf_group_create(n_bins, n_hash_func, kmer_size, vec_size, devs.data(), (int)devs.size(), _envMode(), &_g));
+            else                 _check(dyibf_create(n_bins, n_hash_func, kmer_size, vec_size, devs[0], &_h));
             _cacheParams();
         }
 
         // d_bloom_filter.h:59 — load failure / size mismatch: message on std::cerr, exit(1)
         SeqAnBloomFilter(const char *fileName, uint32_t n_bins, uint8_t n_hash_func, uint8_t kmer_size, uint64_t vec_size,
-                         int device = 0)
+                         int device = -1)
         {
-            _exitOnLoadFailure(dyibf_load_file_expect(fileName, n_bins, n_hash_func, kmer_size, vec_size, device, &_h));
+            std::vector<int> devs = _devicesFor(device);
+            if (devs.size() > 1)
+            {
+                uint64_t nbits = 0;
+                _exitOnLoadFailure(dyibf_peek_file(fileName, nullptr, nullptr, nullptr, &nbits));
+                if (nbits != vec_size)
+                {
+                    std::cerr << "Size mismatch: \n\t Loaded file \t" << nbits << " bits\n\t expected\t" << vec_size << std::endl;
+                    exit(1);
+                }
+                _exitOnLoadFailure(dyibf_group_load_file(fileName, devs.data(), (int)devs.size(), _envMode(), &_g));
+            }
+            else
+                _exitOnLoadFailure(dyibf_load_file_expect(fileName, n_bins, n_hash_func, kmer_size, vec_size, devs[0], &_h));
             _cacheParams();
         }
 
         // d_bloom_filter.h:79 — parameters from the file's trailer
-        explicit SeqAnBloomFilter(const char *fileName, int device = 0)
+        explicit SeqAnBloomFilter(const char *fileName, int device = -1)
         {
-            _exitOnLoadFailure(dyibf_load_file(fileName, device, &_h));
+            std::vector<int> devs = _devicesFor(device);
+            if (devs.size() > 1) _exitOnLoadFailure(dyibf_group_load_file(fileName, devs.data(), (int)devs.size(), _envMode(), &_g));
+            else                 _exitOnLoadFailure(dyibf_load_file(fileName, devs[0], &_h));
             _cacheParams();
         }
 
-        ~SeqAnBloomFilter() { dyibf_destroy(_h); }
+        // explicit device lists (mode: DYIBF_GROUP_READ_SHARDED / DYIBF_GROUP_BIN_SHARDED)
+        SeqAnBloomFilter(const char *fileName, std::vector<int> const & devices, int mode)
+        {
+            _exitOnLoadFailure(dyibf_group_load_file(fileName, devices.data(), (int)devices.size(), mode, &_g));
+            _cacheParams();
+        }
+        SeqAnBloomFilter(uint32_t n_bins, uint8_t n_hash_func, uint8_t kmer_size, uint64_t vec_size, std::vector<int> const & devices, int mode)
+        {
+            _check(dyibf_group_create(n_bins, n_hash_func, kmer_size, vec_size, devices.data(), (int)devices.size(), mode, &_g));
+            _cacheParams();
+        }
+
+        ~SeqAnBloomFilter() { dyibf_destroy(_h); dyibf_group_destroy(_g); }
 
         // the object owns a device handle: movable, not copyable (the reference object was never copied either)
         SeqAnBloomFilter(SeqAnBloomFilter const &) = delete;
         SeqAnBloomFilter & operator=(SeqAnBloomFilter const &) = delete;
-        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _prm(o._prm), _mtx(std::move(o._mtx)) { o._h = nullptr; }
+        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _g(o._g), _prm(o._prm), _mtx(std::move(o._mtx)) { o._h = nullptr; o._g = nullptr; }
 
         // d_bloom_filter.h:91
         void addKmers(TString const & text, uint32_t const & binNo)
@@ -74,14 +125,15 @@ namespace seqan
             if (length(text) < _prm.kmer) return;               // reference: out-of-bounds hashing; here: nothing
             uint64_t offsets[2] = {0, (uint64_t)length(text)};
             std::lock_guard<std::mutex> lock(*_mtx);
-            _check(dyibf_add_sequences(_h, _bytes(text), offsets, 1, &binNo, _encoding(text), DYIBF_MEM_HOST, nullptr));
+            _add(_bytes(text), offsets, 1, &binNo, _encoding(text));
         }
 
         // d_bloom_filter.h:99 — threadsCount is accepted for source compatibility; the GPU does the pass
         void clearBins(std::vector<uint32_t> & bins2clear, uint32_t & /*threadsCount*/)
         {
             std::lock_guard<std::mutex> lock(*_mtx);
-            _check(dyibf_clear_bins(_h, bins2clear.data(), (uint32_t)bins2clear.size()));
+            if (_g) _check(dyibf_group_clear_bins(_g, bins2clear.data(), (uint32_t)bins2clear.size()));
+            else    _check(dyibf_clear_bins(_need(), bins2clear.data(), (uint32_t)bins2clear.size()));
         }
 
         // d_bloom_filter.h:127 — same reader, same Iupac -> TString conversion, one kernel batch per file
@@ -113,8 +165,7 @@ namespace seqan
             {
                 std::vector<uint32_t> bins(offsets.size() - 1, binNo);
                 std::lock_guard<std::mutex> lock(*_mtx);     // the reference calls this from several threads (one per bin range)
-                _check(dyibf_add_sequences(_h, concat.data(), offsets.data(), (uint32_t)bins.size(), bins.data(),
-                                           _encodingOf((typename Value<TString>::Type *)nullptr), DYIBF_MEM_HOST, nullptr));
+                _add(concat.data(), offsets.data(), (uint32_t)bins.size(), bins.data(), _encodingOf((typename Value<TString>::Type *)nullptr));
             }
         }
 
@@ -122,13 +173,15 @@ namespace seqan
         bool save(const char *fileName)
         {
             std::lock_guard<std::mutex> lock(*_mtx);
-            return dyibf_save_file(_h, fileName) == DYIBF_OK;
+            if (_g) return dyibf_group_save_file(_g, fileName) == DYIBF_OK;
+            return _h && dyibf_save_file(_h, fileName) == DYIBF_OK;
         }
 
         // d_bloom_filter.h:156
         double size_mb()
         {
-            return dyibf_size_mb(_h);
+            // sdsl::size_in_mega_bytes = serialized bytes / 2^20: 8-byte header + words
+            return (double)(8 + _prm.n_words * 8) / (1024.0 * 1024.0);
         }
 
         // d_bloom_filter.h:161 — OR-accumulates into `selected`, never clears
@@ -136,10 +189,9 @@ namespace seqan
         {
             if (length(text) < _prm.kmer) return;               // reference: uint16 wrap + out-of-bounds reads
             uint64_t offsets[2] = {0, (uint64_t)length(text)};
-            std::vector<uint64_t> row(_prm.words_per_block, 0);
+            std::vector<uint64_t> row;
             std::lock_guard<std::mutex> lock(*_mtx);             // called from threadsCount std::async tasks (d_mapper.h:338-375)
-            _check(dyibf_query_batch(_h, _bytes(text), offsets, 1, _encoding(text), 1, 0, threshold, 0, row.data(), nullptr,
-                                     DYIBF_MEM_HOST, nullptr));
+            _rows(row, _bytes(text), offsets, 1, _encoding(text), 1, 0, threshold);
             for (uint32_t binNo = 0; binNo < _prm.bins; ++binNo)
                 if ((row[binNo >> 6] >> (binNo & 63)) & 1)
                     selected[binNo] = true;
@@ -165,11 +217,8 @@ namespace seqan
         void whichBinsBatch(std::vector<uint64_t> & rows, const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs,
                             int encoding, int group, bool derive_rc, uint16_t threshold) const
         {
-            uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
-            rows.assign((n_total / group) * _prm.words_per_block, 0);
             std::lock_guard<std::mutex> lock(*_mtx);
-            _check(dyibf_query_batch(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold, 0,
-                                     rows.data(), nullptr, DYIBF_MEM_HOST, nullptr));
+            _rows(rows, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold);
         }
 
         // Query + compaction: per bin the ascending ids of the reads (pairs) that select it.
@@ -181,12 +230,50 @@ namespace seqan
             std::vector<uint32_t> ids(std::max<uint64_t>(4 * n_rows, 1024));
             uint64_t total = 0;
             std::lock_guard<std::mutex> lock(*_mtx);
-            int rc = dyibf_classify(_h, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
-                                    binOffsets.data(), ids.data(), ids.size(), &total);
+            int rc = _g ? dyibf_group_classify(_g, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
+                                               binOffsets.data(), ids.data(), ids.size(), &total)
+                        : dyibf_classify(_need(), concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold,
+                                         binOffsets.data(), ids.data(), ids.size(), &total);
             if (rc == DYIBF_ERR_CAPACITY)                        // the lists are still in HBM: fetch, no second pass
             {
                 ids.resize(total);
-                rc = dyibf_classify_fetch(_h, binOffsets.data(), ids.data(), ids.size(), &total);
+                rc = _g ? dyibf_group_classify_fetch(_g, binOffsets.data(), ids.data(), ids.size(), &total)
+                        : dyibf_classify_fetch(_h, binOffsets.data(), ids.data(), ids.size(), &total);
+            }
+            _check(rc);
+            readIdsPerBin.assign(_prm.bins, std::vector<uint32_t>());
+            for (uint32_t b = 0; b < _prm.bins; ++b)
+                readIdsPerBin[b].assign(ids.begin() + binOffsets[b], ids.begin() + binOffsets[b + 1]);
+        }
+
+        // Asynchronous classify for the reference's batching (one clasifyLoadedReads call per 100 000 reads, src/mapper.h:109,
+        // while file_prefetched.h:137-205 already loads the next batch): classifyBegin returns at once, up to four batches per
+        // GPU in flight; concat / limits must stay valid until classifyEnd, which returns what classify returns.
+        dyibf_ticket * classifyBegin(const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs, int encoding, int group,
+                                     bool derive_rc, uint16_t threshold) const
+        {
+            dyibf_ticket * t = nullptr;
+            std::lock_guard<std::mutex> lock(*_mtx);
+            if (_g && _mode == DYIBF_GROUP_READ_SHARDED)
+                _check(dyibf_group_classify_begin(_g, concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold, &t));
+            else if (_g)
+                throw std::runtime_error("dyibf: classifyBegin hands whole batches to replicas; a bin-sharded filter uses classify()");
+            else
+                _check(dyibf_classify_begin(_need(), concat, limits, n_seqs, encoding, group, derive_rc ? 1 : 0, threshold, &t));
+            return t;
+        }
+
+        void classifyEnd(dyibf_ticket * ticket, std::vector<std::vector<uint32_t> > & readIdsPerBin, uint32_t n_rows) const
+        {
+            std::vector<uint64_t> binOffsets(_prm.bins + 1, 0);
+            std::vector<uint32_t> ids(std::max<uint64_t>(4ull * n_rows, 1024));
+            uint64_t total = 0;
+            std::lock_guard<std::mutex> lock(*_mtx);
+            int rc = dyibf_classify_end(ticket, binOffsets.data(), ids.data(), ids.size(), &total);
+            if (rc == DYIBF_ERR_CAPACITY)                        // the ticket stays in flight: again, with room
+            {
+                ids.resize(total);
+                rc = dyibf_classify_end(ticket, binOffsets.data(), ids.data(), ids.size(), &total);
             }
             _check(rc);
             readIdsPerBin.assign(_prm.bins, std::vector<uint32_t>());
@@ -201,7 +288,8 @@ namespace seqan
         {
             uint64_t ns = 0, nb = 0;
             std::lock_guard<std::mutex> lock(*_mtx);
-            int rc = dyibf_gather_reads(_h, binNo, nullptr, 0, nullptr, nullptr, 0, &ns, &nb);
+            if (_g) throw std::runtime_error("dyibf: gatherReads needs the batch on one GPU (the batch of a multi-GPU filter is split)");
+            int rc = dyibf_gather_reads(_need(), binNo, nullptr, 0, nullptr, nullptr, 0, &ns, &nb);
             if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) _check(rc);
             bytes.resize(nb); limits.assign(ns + 1, 0); ids.resize(ns);
             if (ns)
@@ -219,16 +307,22 @@ namespace seqan
         }
 
         // DYIBF_OPT_EARLY_EXIT (see dyibf.h): identical bin sets from fewer lookups
-        void setEarlyExit(bool on) { _check(dyibf_set_option(_h, DYIBF_OPT_EARLY_EXIT, on ? 1 : 0)); }
+        void setEarlyExit(bool on)
+        {
+            if (_g) _check(dyibf_group_set_option(_g, DYIBF_OPT_EARLY_EXIT, on ? 1 : 0));
+            else    _check(dyibf_set_option(_need(), DYIBF_OPT_EARLY_EXIT, on ? 1 : 0));
+        }
 
         void addSequences(const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs, const uint32_t * binIds, int encoding)
         {
             std::lock_guard<std::mutex> lock(*_mtx);
-            _check(dyibf_add_sequences(_h, concat, limits, n_seqs, binIds, encoding, DYIBF_MEM_HOST, nullptr));
+            _add(concat, limits, n_seqs, binIds, encoding);
         }
 
         uint32_t getBinWidth() const { return _prm.words_per_block; }
-        dyibf_filter * handle() const { return _h; }
+        dyibf_filter * handle() const { return _h; }           // single-GPU objects
+        dyibf_group * group() const { return _g; }             // multi-GPU objects
+        int deviceCount() const { return _nDevices; }
 
     private:
         static void _check(int rc)
@@ -244,7 +338,86 @@ namespace seqan
             exit(1);
         }
 
-        void _cacheParams() { _check(dyibf_get_params(_h, &_prm)); }
+        void _cacheParams()
+        {
+            if (_g) _check(dyibf_group_get_params(_g, &_prm, &_nDevices, &_mode));
+            else    _check(dyibf_get_params(_h, &_prm));
+        }
+
+        dyibf_filter * _need() const
+        {
+            if (!_h) throw std::runtime_error("dyibf: this filter object is empty (vector size too small for one hash block)");
+            return _h;
+        }
+
+        // DYIBF_DEVICES / DYIBF_GROUP_MODE (see the constructors)
+        static std::vector<int> _devicesFor(int device)
+        {
+            if (device >= 0) return std::vector<int>(1, device);
+            std::vector<int> devs;
+            const char * env = std::getenv("DYIBF_DEVICES");
+            if (env && std::string(env) == "all")
+            {
+                int n = 0;
+                _check(dyibf_device_count(&n));
+                for (int i = 0; i < n; ++i) devs.push_back(i);
+            }
+            else if (env && *env)
+            {
+                std::string s(env);
+                size_t at = 0;
+                while (at <= s.size())
+                {
+                    size_t comma = s.find(',', at);
+                    if (comma == std::string::npos) comma = s.size();
+                    if (comma > at) devs.push_back(std::atoi(s.substr(at, comma - at).c_str()));
+                    at = comma + 1;
+                }
+            }
+            if (devs.empty()) devs.push_back(0);
+            return devs;
+        }
+        static int _envMode()
+        {
+            const char * env = std::getenv("DYIBF_GROUP_MODE");
+            return (env && std::string(env) == "bin") ? DYIBF_GROUP_BIN_SHARDED : DYIBF_GROUP_READ_SHARDED;
+        }
+
+        void _add(const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs, const uint32_t * binIds, int encoding)
+        {
+            if (_g) _check(dyibf_group_add_sequences(_g, concat, limits, n_seqs, binIds, encoding));
+            else    _check(dyibf_add_sequences(_need(), concat, limits, n_seqs, binIds, encoding, DYIBF_MEM_HOST, nullptr));
+        }
+
+        // selection rows of a batch; on a multi-GPU object through the member handles (a compatibility path: the fast
+        // multi-GPU entry is classify): replicas -> member 0, bin shards -> every member's column slice side by side
+        void _rows(std::vector<uint64_t> & rows, const uint8_t * concat, const uint64_t * limits, uint32_t n_seqs, int encoding,
+                   int group, int derive_rc, uint16_t threshold) const
+        {
+            const uint64_t n_rows = (derive_rc ? 2ull * n_seqs : n_seqs) / group;
+            const uint32_t W = _prm.words_per_block;
+            rows.assign(n_rows * W, 0);
+            if (!_g)
+            {
+                _check(dyibf_query_batch(_need(), concat, limits, n_seqs, encoding, group, derive_rc, threshold, 0, rows.data(), nullptr,
+                                         DYIBF_MEM_HOST, nullptr));
+                return;
+            }
+            const int members = _mode == DYIBF_GROUP_BIN_SHARDED ? _nDevices : 1;
+            std::vector<uint64_t> part;
+            for (int m = 0; m < members; ++m)
+            {
+                dyibf_filter * f = nullptr; uint32_t firstBin = 0, nBins = 0;
+                _check(dyibf_group_member(_g, m, &f, &firstBin, &nBins));
+                dyibf_params p; _check(dyibf_get_params(f, &p));
+                part.assign(n_rows * p.words_per_block, 0);
+                _check(dyibf_query_batch(f, concat, limits, n_seqs, encoding, group, derive_rc, threshold, 0, part.data(), nullptr,
+                                         DYIBF_MEM_HOST, nullptr));
+                for (uint64_t r = 0; r < n_rows; ++r)
+                    for (uint32_t w = 0; w < p.words_per_block; ++w)
+                        rows[r * W + firstBin / 64 + w] = part[r * p.words_per_block + w];
+            }
+        }
 
         // SeqAn alphabets are SimpleType<unsigned char, ...>: one byte per character, contiguous in Alloc strings
         static int _encodingOf(Dna5 *)  { return DYIBF_ENC_DNA5; }
@@ -258,7 +431,9 @@ namespace seqan
             return reinterpret_cast<const uint8_t *>(&*begin(s, Standard()));
         }
 
-        dyibf_filter *  _h = nullptr;
+        dyibf_filter *  _h = nullptr;          // one GPU ...
+        dyibf_group *   _g = nullptr;          // ... or several (exactly one of the two is set; neither: the empty object)
+        int             _nDevices = 1, _mode = DYIBF_GROUP_READ_SHARDED;
         dyibf_params    _prm;
         // a handle is stream-ordered: calls are serialised here, as the reference's callers use one object from many threads
         std::unique_ptr<std::mutex> _mtx{new std::mutex()};

@@ -9,7 +9,8 @@
  * include/d_bloom_filter.h in this repo re-creates the class on top of these calls.
  *
  * Rules: plain pointers and sizes only; no CPU fallback anywhere (a missing GPU is an error);
- * one handle = one filter (or one bin-shard of a filter) resident in the HBM of one GPU.
+ * one handle = one filter (or one bin-shard of a filter) resident in the HBM of one GPU; a dyibf_group is one filter
+ * over several GPUs of one process (replicated and read-sharded, or bin-sharded).
  * Calls on one handle must be serialised by the caller.  All functions return DYIBF_OK (0) or a
  * negative error code; dyibf_last_error() gives the message of the calling thread's last failure.
  *
@@ -35,6 +36,11 @@ extern "C" {
 #define DYIBF_ERR_SIZE_MISMATCH -5   /* file bit count != expected (d_bloom_filter.h:71-76)       */
 #define DYIBF_ERR_CAPACITY      -6   /* caller's output buffer too small                          */
 #define DYIBF_ERR_NOMEM         -7
+#define DYIBF_ERR_BUSY          -8   /* every asynchronous ticket of the handle is in flight          */
+
+/* sticky device-side error bits (dyibf_device_errors): input that only the kernels could see was invalid */
+#define DYIBF_DEVERR_BIN_RANGE     1u  /* a device-resident bin id >= bins: the sequence was skipped             */
+#define DYIBF_DEVERR_SEQ_TOO_LONG  2u  /* a sequence had more k-mers than the caller's max_seq_len allows: it selected nothing */
 
 #define DYIBF_MAX_HASH           8
 
@@ -48,6 +54,8 @@ extern "C" {
 #define DYIBF_MEM_DEVICE 1
 
 typedef struct dyibf_filter dyibf_filter;
+typedef struct dyibf_ticket dyibf_ticket;   /* one asynchronous classify in flight (dyibf_classify_begin)         */
+typedef struct dyibf_group  dyibf_group;    /* one filter over several GPUs of one process (dyibf_group_create)   */
 
 typedef struct dyibf_params {
     uint32_t bins;        /* _noOfBins      */
@@ -108,11 +116,26 @@ int  dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first,
 /* save(fileName), d_bloom_filter.h:150-154 -> sdsl::store_to_file: byte-identical file */
 int  dyibf_save_file(dyibf_filter* f, const char* path);
 
+/* The loader / writer behind dyibf_load_file* / dyibf_save_file (and their group forms) streams the file through pinned
+ * host buffers with several threads (pread / pwrite + asynchronous copies); this is the stage the mapper prints as
+ * "Filter loading time" (src/d_mapper.h:913-921).  dyibf_set_io_threads: 1..64, default 4, process-wide.
+ * dyibf_last_io_stats: the calling thread's last load or save. */
+typedef struct dyibf_io_stats {
+    uint64_t bytes;               /* data-word bytes moved between the file and HBM                         */
+    double   seconds;             /* wall time of the transfer                                              */
+    double   file_seconds;        /* longest time any one thread spent inside pread / pwrite                */
+    double   copy_wait_seconds;   /* longest time any one thread waited for its copies                      */
+    int      threads, devices;
+} dyibf_io_stats;
+int  dyibf_set_io_threads(int n);
+int  dyibf_last_io_stats(dyibf_io_stats* out);
+
 /* ---- build --------------------------------------------------------------------------------- */
 
 /* addKmers(text, binNo), d_bloom_filter.h:91-94,293-315, for n_seqs sequences at once (atomic-OR kernel).
  * seqs: concatenated sequence bytes; offsets[n_seqs+1]; bin_ids[n_seqs].  Sequences shorter than k are
- * skipped (:142).  mem says where seqs/offsets/bin_ids live. */
+ * skipped (:142).  mem says where seqs/offsets/bin_ids live.  Host mode validates bin_ids (DYIBF_ERR_ARG); device mode
+ * cannot: a device-resident bin id >= bins adds nothing and sets DYIBF_DEVERR_BIN_RANGE (dyibf_device_errors). */
 int  dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
                          const uint32_t* bin_ids, int encoding, int mem, void* stream);
 /* clearBins(bins2clear, threads), d_bloom_filter.h:99-123 */
@@ -136,6 +159,8 @@ uint16_t dyibf_threshold_rate(float error_rate, uint32_t kmer, uint16_t read_len
  *   out_counts   : optional (NULL to skip) n_total x bins u16: the per-bin k-mer counts (`counts`, :165).
  *   max_seq_len  : longest sequence, 0 = unknown (host mode computes it; device mode then uses the
  *                  16-bit counters).  Sequences with more than 65535 k-mers are rejected (u16 in the reference).
+ *                  A non-zero bound is trusted: a sequence with more than 255 k-mers under a bound that promised at most
+ *                  255 selects nothing and sets DYIBF_DEVERR_SEQ_TOO_LONG (dyibf_device_errors).
  */
 int  dyibf_query_batch(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
                        int encoding, int group, int derive_rc, uint32_t threshold, uint32_t max_seq_len,
@@ -156,6 +181,21 @@ int  dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offset
 /* The per-bin lists of the last dyibf_classify again (they stay in HBM): for a caller whose first buffer was too
  * small (DYIBF_ERR_CAPACITY) — no second pass over the reads. */
 int  dyibf_classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
+
+/* Asynchronous form of dyibf_classify for the reference's real batching: clasifyLoadedReads is called once per 100 000
+ * reads (src/mapper.h:109) while a prefetch thread already loads the next batch (src/file_prefetched.h:137-205).
+ * dyibf_classify_begin enqueues upload, pack, query and compaction of one batch on a stream and buffers of its own and
+ * returns a ticket at once; up to four tickets per handle may be in flight (DYIBF_ERR_BUSY beyond), so batch i+1 uploads
+ * and starts while batch i is in the query kernel.  seqs / offsets must stay valid until dyibf_classify_end, which waits
+ * for the ticket and copies the lists out exactly as dyibf_classify returns them.  On DYIBF_ERR_CAPACITY (bin_offsets and
+ * *total are filled) the ticket stays in flight: call dyibf_classify_end again with a larger buffer.  After a successful
+ * end the ticket's batch is the handle's resident batch (dyibf_gather_reads, dyibf_classify_fetch).  dyibf_classify_poll:
+ * *ready = 1 once dyibf_classify_end would not block.  dyibf_classify_cancel abandons a ticket. */
+int  dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
+                          int encoding, int group, int derive_rc, uint32_t threshold, dyibf_ticket** ticket);
+int  dyibf_classify_poll(dyibf_ticket* ticket, int* ready);
+int  dyibf_classify_end(dyibf_ticket* ticket, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
+void dyibf_classify_cancel(dyibf_ticket* ticket);
 
 /* sortedBins, d_mapper.h:843-854: bin numbers by descending list size (std::sort, same comparator). bin_offsets[bins+1]
  * as dyibf_classify / dyibf_compact return them. */
@@ -204,6 +244,47 @@ int  dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads
                          int format, int e_percent, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total,
                          uint32_t* n_reads, uint32_t* threshold);
 
+/* ---- several GPUs, one process ----------------------------------------------------------------
+ *
+ * The reference's callers are single processes: spawnDisMapper constructs ONE filter (src/d_mapper.h:911-922),
+ * clasifyLoadedReads splits ONE read batch over its worker threads (:338-375), build_filter splits the bins over its
+ * threads (src/d_build_filter.cpp:227-260).  A group is the same with GPUs as the workers (dyibf_comm_init
+ * = dyibf_group_create / dyibf_group_load_file, dyibf_broadcast_filter, dyibf_shard_bins; §8(e)):
+ *   DYIBF_GROUP_READ_SHARDED  every device holds a replica (loaded once, fanned out over NVLink peer copies); device r
+ *                             filters rows [r n/G, (r+1) n/G) (dyibf_shard_reads) of the caller's one host batch; per-bin lists
+ *                             concatenate in device order = ascending ids.
+ *   DYIBF_GROUP_BIN_SHARDED   for filters larger than one GPU's HBM: device r owns the word columns [r W/G, (r+1) W/G) of
+ *                             every hash block = bins dyibf_shard_bins(r) as a self-contained filter with the same number of
+ *                             blocks; every device sees every read; lists of the bin ranges concatenate.  Needs G | W.
+ * Neither needs a reduction (the threshold is per bin and per read).  Results are identical to one device's.
+ * dyibf_group_add_sequences routes every sequence to the device owning its bin's word column (no two devices OR into the
+ * same word) and, for replicas, then exchanges the columns between the devices' HBM over NVLink so that all replicas are
+ * identical again.  dyibf_group_member gives the per-device handle (options, profiling, device pointers).
+ * dyibf_group_classify_begin hands whole batches to successive replicas (tickets end with dyibf_classify_end). */
+#define DYIBF_GROUP_READ_SHARDED 0
+#define DYIBF_GROUP_BIN_SHARDED  1
+int  dyibf_shard_bins(uint32_t bins, int rank, int nranks, uint32_t* first_bin, uint32_t* n_bins);
+int  dyibf_shard_reads(uint32_t n_reads, int rank, int nranks, uint32_t* first, uint32_t* last);
+int  dyibf_group_create(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, const int* devices, int n_devices,
+                        int mode, dyibf_group** out);
+int  dyibf_group_load_file(const char* path, const int* devices, int n_devices, int mode, dyibf_group** out);
+void dyibf_group_destroy(dyibf_group* g);
+int  dyibf_group_get_params(const dyibf_group* g, dyibf_params* whole, int* n_devices, int* mode);
+int  dyibf_group_member(dyibf_group* g, int index, dyibf_filter** member, uint32_t* first_bin, uint32_t* n_bins);
+int  dyibf_group_set_option(dyibf_group* g, int option, int64_t value);
+int  dyibf_group_save_file(dyibf_group* g, const char* path);
+/* replicate member src_member's words to every other replica (after a build through that member's own handle) */
+int  dyibf_broadcast_filter(dyibf_group* g, int src_member);
+int  dyibf_group_classify(dyibf_group* g, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
+                          int group, int derive_rc, uint32_t threshold, uint64_t* bin_offsets, uint32_t* read_ids,
+                          uint64_t capacity, uint64_t* total);
+int  dyibf_group_classify_fetch(dyibf_group* g, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
+int  dyibf_group_classify_begin(dyibf_group* g, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs, int encoding,
+                                int group, int derive_rc, uint32_t threshold, dyibf_ticket** ticket);
+int  dyibf_group_add_sequences(dyibf_group* g, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
+                               const uint32_t* bin_ids, int encoding);
+int  dyibf_group_clear_bins(dyibf_group* g, const uint32_t* bins, uint32_t n);
+
 /* ---- options ------------------------------------------------------------------------------- */
 
 /* DYIBF_OPT_EARLY_EXIT (default 0).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it
@@ -234,6 +315,10 @@ int  dyibf_get_option(const dyibf_filter* f, int option, int64_t* value);
 /* ---- instrumentation ----------------------------------------------------------------------- */
 int  dyibf_profile_enable(dyibf_filter* f, int on);
 int  dyibf_profile_get(dyibf_filter* f, dyibf_profile* out, int reset);
+/* kernels this handle has launched since it was created (always counted, no profiling needed) */
+uint64_t dyibf_launch_count(const dyibf_filter* f);
+/* the sticky DYIBF_DEVERR_* bits of the handle; waits for the device first */
+int  dyibf_device_errors(dyibf_filter* f, uint32_t* flags, int reset);
 
 /* pinned host memory helpers (callers that want full PCIe rate allocate their buffers here) */
 int  dyibf_host_alloc(void** ptr, size_t bytes);
