@@ -119,7 +119,8 @@ class SeqAnBloomFilter:
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
-            lib().dyibf_destroy(self._h)
+            if getattr(self, "_owned", True):                    # a FilterGroup member view does not own its handle
+                lib().dyibf_destroy(self._h)
             self._h = C.c_void_p()
 
     __del__ = close
@@ -410,7 +411,7 @@ class FilterGroup:
         h = C.c_void_p(); fb, nb = C.c_uint32(0), C.c_uint32(0)
         check(lib().dyibf_group_member(self._g, int(i), C.byref(h), C.byref(fb), C.byref(nb)))
         f = SeqAnBloomFilter(_handle=h)
-        f.close = lambda: None                                    # the group owns the handle
+        f._owned = False                                          # the group owns the handle
         f._owner = self
         return f, fb.value, nb.value
 
