@@ -58,6 +58,10 @@ def parse():
     ap.add_argument("--dropin-batch", type=int, default=100_000, help="reads (pairs) per drop-in call; the reference's -rb default")
     ap.add_argument("--no-ingest", action="store_true", help="skip the extra device FASTQ-reader measurement (cfg2)")
     ap.add_argument("--no-early-exit", action="store_true", help="skip the extra DYIBF_OPT_EARLY_EXIT measurement")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the extras that ride in the cfg2 line: filter load/save, cfg3 sweep, cfg5 build (N=1); multi-GPU "
+                         "parity, cfg4 bin-sharded, one-process group (N>1)")
+    ap.add_argument("--extras", default="all", help="comma list out of io,cfg3,cfg5,parity,cfg4,single,async (default all)")
     a = ap.parse_args()
     a.paired = a.workload == "cfg3"
     a.bin_sharded = a.workload == "cfg4"
@@ -309,11 +313,21 @@ def run_b200(args):
         f.addSequences((genomes.reshape(-1), goff), np.arange(bins, dtype=np.uint32))
     torch.cuda.synchronize()
     t_build = time.perf_counter() - t_build
+    replication = None
     if world > 1 and not sharded:                                        # read-sharded: replicate over NVLink
         step = 1 << 27                                                   # 1 GiB pieces
+        dist.broadcast(words[:1024], src=0)                              # communicator set-up is not the transfer
+        dist.barrier(); torch.cuda.synchronize()
+        t_rep = time.perf_counter()
         for a in range(0, words.numel(), step):
             dist.broadcast(words[a:a + step], src=0)
         torch.cuda.synchronize()
+        t_rep = time.perf_counter() - t_rep
+        trep = torch.tensor([t_rep], dtype=torch.float64, device=dev)
+        dist.all_reduce(trep, op=dist.ReduceOp.MAX)
+        replication = {"seconds": float(trep.item()), "bytes": int(words.numel()) * 8, "gbs": words.numel() * 8 / float(trep.item()) / 1e9,
+                       "how": "ncclBroadcast of the P*W data words from rank 0 in 1 GiB pieces into memory every rank adopts with "
+                              "dyibf_attach (NVLink / NVSwitch); max over ranks, wall clock"}
 
     hp = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(hp), n_seq * RL))
     h_reads = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(2, n, RL) if paired else (n, RL))
@@ -345,6 +359,33 @@ def run_b200(args):
     d_ids = torch.zeros(ids_cap, dtype=torch.int32, device=dev)
     n_pairs = C.c_uint64(0)
 
+    enabled = set(args.extras.split(",")) if args.extras != "all" else {"io", "cfg3", "cfg5", "parity", "cfg4", "single", "async"}
+
+    def want(name):
+        return not args.no_extras and name in enabled and args.workload == "cfg2"
+
+    _cpu = {}
+
+    def cpu_filter():
+        """the reference's filter object on the host with the words of THIS GPU's table (one 16 GiB download, cached)"""
+        if "cf" not in _cpu:
+            cf_ = CpuFilter(bins, H, K, nbits)
+            check(L.dyibf_download_words(f._h, C.c_void_p(cf_.words.ctypes.data), 0, P * W))
+            _cpu["cf"] = cf_
+        return _cpu["cf"]
+
+    def mk_ctx():
+        from types import SimpleNamespace
+        return SimpleNamespace(L=L, dy=dy, f=f, words=words, dev=dev, local=local, rank=rank, world=world, args=args, genomes=genomes,
+                               h_reads=h_reads, d_reads=d_reads, d_off=d_off, d_rows=d_rows, n=n, RL=RL, bins=bins, W=W, P=P, thr=thr,
+                               nbits=nbits, stream=stream, barrier=barrier, torch=torch, dist=dist, units_world=units_world,
+                               peak=measured_peak()[0], cpu_filter=cpu_filter)
+
+    def mk_ctx_light():
+        from types import SimpleNamespace
+        return SimpleNamespace(L=L, dy=dy, dev=dev, local=local, rank=rank, world=world, args=args, stream=stream, barrier=barrier,
+                               torch=torch, dist=dist, peak=measured_peak()[0])
+
     def device_step():
         f.query_device(d_reads.data_ptr(), d_off.data_ptr(), n_seq, cur_thr[0], d_rows.data_ptr(), group=group, derive_rc=True,
                        encoding=ENC_DNA5, max_seq_len=RL, stream=stream)
@@ -368,11 +409,13 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = f.launch_count()
     e0.record()
     for _ in range(args.steps):
         device_step()
     e1.record()
     barrier()
+    gpu_launches = f.launch_count() - launches0                          # counted by the library at every kernel launch
     clocks = sampler.stop() if rank == 0 else None
     ms = e0.elapsed_time(e1)
     prof = f.profile(reset=True); f.profile_enable(False)
@@ -474,10 +517,16 @@ def run_b200(args):
             dt_pin, _ = dropin_run([h_reads[i * rb:(i + 1) * rb].reshape(-1) for i in range(n_calls)])
         rate = lambda dt: units_world * rb * n_calls / dt
         dropin = {"value": rate(dt_auto), "unit": args.unit, "reads_per_call": rb, "calls": n_calls,
-                  "ms_per_call": dt_auto / n_calls * 1e3, "kernel_ms_per_call": kern_ms, "read_bin_pairs": int(pairs_b),
+                  "ms_per_call": dt_auto / n_calls * 1e3, "kernel_ms_per_call": kern_ms,
+                  "kernel_ms_note": "summed over the two stream slots of a call (their kernels overlap), so the sum may exceed ms_per_call",
+                  "read_bin_pairs": int(pairs_b),
                   "one_chunk_per_call": rate(dt_one), "pinned_input": rate(dt_pin) if dt_pin else None,
                   "note": "dyibf_classify per batch of the reference's default size: pageable host reads in, per-bin read-id lists "
                           "out, synchronous calls, host wall clock, max over ranks; not part of value/e2e"}
+        if want("async"):
+            from bench_support import extras as X
+            pinned_b = None if paired else [h_reads[i * rb:(i + 1) * rb].reshape(-1) for i in range(n_calls)]
+            dropin["asynchronous"] = X.dropin_async(mk_ctx(), batches, pinned_b, per_call, rb, group)
 
     # ---- extra (not the headline): the same step with DYIBF_OPT_EARLY_EXIT — identical rows, fewer lookups
     early = None
@@ -502,22 +551,32 @@ def run_b200(args):
         early = {"value": units_world * n * args.steps / (float(t2[0]) / 1e3), "unit": args.unit, "kernel_ms": float(t2[1]),
                  "lookups_frac": (p2["query_lookups"] / max(p2["query_launches"], 1)) / max(full_lookups, 1),
                  "rows_equal_full": same,
+                 "roofline": {"bound": "hbm", "unit": "GB/s", "peak": measured_peak()[0],
+                              "achieved": (p2["query_lookups"] / max(p2["query_launches"], 1)) * algorithmic_bytes_per_read(bins, RL, paired)
+                                          / ((RL - K + 1) * (4 if paired else 2)) / (float(t2[1]) / 1e3) / 1e9,
+                              "definition": "bytes touched in 32 B sectors (lookups performed x h x sector bytes per lookup) / kernel time"},
                  "note": "DYIBF_OPT_EARLY_EXIT=1: a sequence stops once no remaining k-mer can change its bin set; "
                          "off by default, not used for value/e2e/roofline"}
+        early["roofline"]["frac"] = early["roofline"]["achieved"] / early["roofline"]["peak"]
         if not same:
             raise AssertionError("early-exit rows differ from the full pass")
         if not args.no_e2e:
-            host_step()
+            # e2e of the early-exit mode through the mapper-facing call (lists out, 36 MB back instead of 1.28 GB of rows)
+            classify_step()
             barrier()
             t0 = time.perf_counter()
             for _ in range(args.steps):
-                host_step()
+                classify_step()
             barrier()
             dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
             if world > 1:
                 dist.all_reduce(dt, op=dist.ReduceOp.MAX)
             early["e2e"] = units_world * n * args.steps / float(dt.item())
-            assert np.array_equal(h_rows.reshape(-1).view(np.int64), full_rows.cpu().numpy()), "early-exit host rows differ"
+            early["e2e_over_value"] = early["e2e"] / early["value"]
+            early["e2e_h2d_gbs_per_gpu"] = (n_seq * RL + (n_seq + 1) * 8) * args.steps / float(dt.item()) / 1e9
+            early["e2e_call"] = "dyibf_classify(host): pinned reads in, per-bin lists out"
+            tot = int(tot_h.value)
+            assert tot == int(n_pairs.value) and np.array_equal(h_ids[:tot].view(np.int32), d_ids[:tot].cpu().numpy()), "early-exit host lists differ"
         f.set_early_exit(False)
         del full_rows
 
@@ -565,8 +624,14 @@ def run_b200(args):
     bytes_per_read = algorithmic_bytes_per_read(bins, RL, paired)
     peak, peak_src = measured_peak()
     achieved = n * bytes_per_read / (query_ms / 1e3) / 1e9
+    vec = 16 if W % 2 == 0 else 8
+    tl2 = 0
+    while tl2 < 5 and (1 << tl2) < (W * 8) // vec:
+        tl2 += 1
+    planes = 8 if (RL - K + 1) <= 255 else 16
+    kernel_name = "query_kernel<%d,%d,%d,%d>" % (vec, tl2, H if planes == 8 else 0, planes)       # launch_query's dispatch
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "query_kernel<16,3,3,8>", "kernel_ms": query_ms, "pack_kernel_ms": pack_ms, "compact_kernels_ms": compact_ms,
+                "traffic": None, "kernel": kernel_name, "kernel_ms": query_ms, "pack_kernel_ms": pack_ms, "compact_kernels_ms": compact_ms,
                 "read_bin_pairs_per_step": int(n_pairs.value),
                 "algorithmic_bytes_per_launch": n * bytes_per_read, "peak_source": peak_src,
                 "frac_of_nominal_8000": achieved / 8000.0}
@@ -574,18 +639,17 @@ def run_b200(args):
     if os.path.exists(traffic_file) and args.workload == "cfg2" and bins == 1024 and RL == 150:
         try:
             tj = json.load(open(traffic_file))
-            if tj.get("reads_per_launch"):
+            if tj.get("reads_per_launch") and tj.get("kernel") == kernel_name:
                 roofline["traffic"] = tj["dram_bytes_per_launch"] * (n / tj["reads_per_launch"])
-                roofline["traffic_source"] = tj.get("source")
+                roofline["traffic_source"] = "DERIVED, not measured in this run: " + str(tj.get("source")) + \
+                    "; scaled by reads per launch; query_kernel.cu commit of the capture: " + str(tj.get("kernel_commit"))
         except Exception:
             pass
 
     # ---- CPU baseline: the reference's own code on a bounded sample of the same reads (rank 0, N = 1)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cf = CpuFilter(bins, H, K, nbits)
-        nd = P * W
-        check(L.dyibf_download_words(f._h, C.c_void_p(cf.words.ctypes.data), 0, nd))   # same filter words as the GPU
+        cf = cpu_filter()                                                  # same filter words as the GPU (downloaded from HBM)
         prefix = (lambda m: h_reads[:, :m]) if paired else (lambda m: h_reads[:m])
         if paired:
             # the GPU rows of a prefix of pairs need that prefix queried on its own ([m1 | m2] halves move with n)
@@ -602,6 +666,7 @@ def run_b200(args):
         cpu = {"value": rate, "unit": args.unit, "cores": cf.cores, "kind": cf.kind,
                "sample": "first %d %s of the workload, %.1f s, same filter words (downloaded from HBM)"
                          % (n_s, "pairs" if paired else "reads", dt_s),
+               "build": "oracle/Makefile: g++ -O3 -march=x86-64-v3 (built in the CPU container, run here; not -march=native)",
                "rows_equal_gpu": same}
         if not same:
             raise AssertionError("GPU rows differ from the CPU reference on the sampled prefix")
@@ -629,16 +694,45 @@ def run_b200(args):
             sweep["e%d" % e] = res
         f.set_early_exit(False); cur_thr[0] = thr
 
+    # ---- extras that ride in the cfg2 line (bench_support/extras.py): the other BASELINE configs, multi-GPU parity against the
+    # reference's CPU code, the stages either side of the kernel.  Order matters: cfg3 overwrites the read buffer, cfg4 needs
+    # the cfg2 filter's memory.
+    extras = {}
+    if args.workload == "cfg2" and not args.no_extras:
+        from bench_support import extras as X
+        ctx = mk_ctx()
+        if world > 1 and want("parity"):
+            extras["multi_gpu_parity"] = X.multi_gpu_parity(ctx)
+        if world > 1 and want("single"):
+            extras["single_process"] = X.single_process(ctx)
+        if world == 1 and want("io"):
+            extras["filter_io"] = X.filter_io(ctx)
+        if want("cfg3"):
+            extras["cfg3"] = X.cfg3(ctx)
+        _cpu.clear()
+        if world == 1 and want("cfg5"):
+            extras["cfg5"] = X.cfg5(ctx)
+        if world > 1 and want("cfg4"):
+            f.close(); f = None
+            del words, d_reads, d_rows, d_ids, ctx
+            torch.cuda.empty_cache()
+            ctx4 = mk_ctx_light()
+            extras["cfg4"] = X.cfg4(ctx4)
+
     if rank == 0:
         line = {"metric": args.metric, "value": value, "unit": args.unit, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-                "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": (2 if args.no_compact else 8) * args.steps,
+                "config": workload_config(args, thr, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches),
                 "roofline": roofline, "cpu_baseline": cpu, "filter_build_s": t_build, "early_exit": early, "dropin_batches": dropin, "ingest": ingest, "impl": "b200"}
+        if replication is not None:
+            line["filter_replication"] = replication
+        line.update(extras)
         if sweep is not None:
             line["e_sweep"] = sweep
         print(json.dumps(line), flush=True)
-    f.close()
+    if f is not None:
+        f.close()
     for p_ in (hp, op, rp, ip):
         L.dyibf_host_free(p_)
     if world > 1:

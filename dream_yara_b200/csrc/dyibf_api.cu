@@ -223,6 +223,14 @@ int dyibf_upload_words(dyibf_filter* f, const uint64_t* host_words, uint64_t fir
     DeviceGuard guard(f->prm.device);
     if (first >= f->data_words) return DYIBF_OK;                      // gap / trailer: synthesised
     n = std::min<uint64_t>(n, f->data_words - first);
+    const uint32_t Wb = f->prm.words_per_block;
+    if (first % Wb == 0 && n >= (uint64_t)Wb * 1024) {                // bulk: whole blocks through the threaded pinned pipeline
+        const uint64_t nb = n / Wb;
+        int brc = io_copy_words(f, const_cast<uint64_t*>(host_words), first / Wb, nb, true);
+        if (brc) return brc;
+        host_words += nb * Wb; first += nb * Wb; n -= nb * Wb;
+        if (n == 0) return DYIBF_OK;
+    }
     int rc = ensure_stage(f); if (rc) return rc;
     uint64_t left = n * 8, done = 0; int cur = 0;
     while (left) {
@@ -244,9 +252,20 @@ int dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first, 
                                                 (unsigned long long)first, (unsigned long long)n, (unsigned long long)f->prm.n_words);
     DeviceGuard guard(f->prm.device);
     uint64_t nd = first < f->data_words ? std::min<uint64_t>(n, f->data_words - first) : 0;
-    if (nd) {
+    CU(cudaDeviceSynchronize());                                      // builds still in flight on other streams
+    const uint32_t Wb = f->prm.words_per_block;
+    uint64_t bulk = 0;
+    if (nd && first % Wb == 0 && nd >= (uint64_t)Wb * 1024) {         // bulk: whole blocks through the threaded pinned pipeline
+        const uint64_t nb = nd / Wb;
+        int brc = io_copy_words(f, host_words, first / Wb, nb, false);
+        if (brc) return brc;
+        bulk = nb * Wb;
+    }
+    if (nd > bulk) {
         int rc = ensure_stage(f); if (rc) return rc;
-        uint64_t left = nd * 8, done = 0;
+        const uint64_t first0 = first; (void)first0;
+        host_words += bulk; first += bulk;
+        uint64_t left = (nd - bulk) * 8, done = 0;
         // two pinned buffers: the next D2H is in flight while the previous buffer is copied to the caller
         size_t c[2] = {0, 0}; uint64_t at[2] = {0, 0}; int cur = 0;
         auto issue = [&](int b) -> cudaError_t {

@@ -134,6 +134,9 @@ int classify_range(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets
 int classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
 void free_tickets(dyibf_filter* f);
 
+// bulk word transfer between one table and host memory through the threaded pinned pipeline of dyibf_io.cu
+int io_copy_words(dyibf_filter* f, uint64_t* host_words, uint64_t first_block, uint64_t n_blocks, bool to_device);
+
 struct FileHeader { uint64_t nbits; uint32_t bins, h, k; uint64_t file_size; };
 int read_file_header(FILE* fp, const char* path, FileHeader* fh);
 

@@ -10,7 +10,8 @@
 // In HBM only the P*W data words are kept; the (all-zero) gap before the trailer and the trailer itself are
 // synthesised when the filter is downloaded or saved, so a saved file is byte-identical to the reference's.
 //
-// Pipeline: T reader threads (default 4); thread t owns chunks t, t+T, ... of the data words, two pinned buffers and one
+// Pipeline: T reader threads (default 8); thread t owns chunks t, t+T, ... (8 MiB each) of the data words, two pinned buffers
+// (from a pool that is allocated once per process) and one
 // stream per target device.  pread -> cudaMemcpyAsync(H2D) -> (replicas: cudaMemcpyPeerAsync device 0 -> the others over
 // NVLink, on the same stream) so that file reads, PCIe and NVLink all overlap.  A bin shard (device r of G owns word
 // columns [r W/G, (r+1) W/G) of every block) is a pitched copy out of the same pinned chunk.  Saving runs the pipeline
@@ -29,7 +30,33 @@ using namespace dyibf;
 
 namespace dyibf {
 
-static std::atomic<int> g_io_threads{4};
+static std::atomic<int> g_io_threads{8};
+
+// Pinned staging for the transfer threads: allocated once per process and kept (cudaMallocHost costs ~0.6 s per GiB, as
+// much as the transfer of several GiB).  2 buffers x IO_CHUNK_BYTES per thread slot.
+struct StagePool {
+    std::mutex m;
+    std::vector<void*> buf;       // 2 per slot
+    size_t each = 0;
+    ~StagePool() {}               // process exit frees it; the CUDA runtime may already be gone
+    // buffers [2 t, 2 t + 1] of thread slot t, at least `bytes` each
+    int get(int slots, size_t bytes, std::vector<void*>* out) {
+        std::lock_guard<std::mutex> l(m);
+        if (bytes > each) {
+            for (void* p : buf) cudaFreeHost(p);
+            buf.clear(); each = bytes;
+        }
+        while ((int)buf.size() < 2 * slots) {
+            void* p = nullptr;
+            if (cudaMallocHost(&p, each) != cudaSuccess) return DYIBF_ERR_NOMEM;
+            buf.push_back(p);
+        }
+        out->assign(buf.begin(), buf.begin() + 2 * slots);
+        return DYIBF_OK;
+    }
+};
+static StagePool g_stage;
+static std::mutex g_io_mutex;     // one transfer at a time uses the pool
 static thread_local dyibf_io_stats g_last_io = {0, 0.0, 0.0, 0.0, 0, 0};
 
 static double now_s()
@@ -73,13 +100,15 @@ struct IoResult { int rc = DYIBF_OK; std::string err; double file_s = 0, wait_s 
 // blocks per chunk so that a chunk is about `want` bytes and holds whole blocks
 static uint64_t blocks_per_chunk(uint32_t W, uint64_t want) { return std::max<uint64_t>(1, want / ((uint64_t)W * 8)); }
 
-static const uint64_t IO_CHUNK_BYTES = 64ull << 20;
+static const uint64_t IO_CHUNK_BYTES = 8ull << 20;
 
 // file bytes [8, 8 + n_blocks * W * 8) <-> the targets.  to_device: load; otherwise save (exactly one whole-table target
 // per column range: every word of the file is written once).
-static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blocks, uint32_t W,
+// fd < 0: the other end is host memory (`host`, laid out like the file's data words) instead of a file.
+static int stream_words(int fd, const char* path, char* host, bool to_device, uint64_t n_blocks, uint32_t W,
                         const std::vector<IoTarget>& targets, bool replicas, dyibf_io_stats* stats)
 {
+    std::lock_guard<std::mutex> io_lock(g_io_mutex);
     const double t_begin = now_s();
     const uint64_t bpc = blocks_per_chunk(W, IO_CHUNK_BYTES);
     const uint64_t n_chunks = (n_blocks + bpc - 1) / bpc;
@@ -88,11 +117,13 @@ static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blo
     if ((uint64_t)T > n_chunks) T = (int)std::max<uint64_t>(n_chunks, 1);
     std::vector<IoResult> res(T);
     const size_t buf_bytes = (size_t)(bpc * W * 8);
+    std::vector<void*> pool;
+    if (g_stage.get(T, std::max<size_t>(buf_bytes, (size_t)IO_CHUNK_BYTES), &pool) != DYIBF_OK) return fail(DYIBF_ERR_NOMEM, "filter I/O: pinned staging allocation failed");
     auto worker = [&](int t) {
         IoResult& r = res[t];
         auto bad = [&](int code, const std::string& what) { if (!r.rc) { r.rc = code; r.err = what; } };
         const size_t nt = targets.size();
-        void* buf[2] = {nullptr, nullptr};
+        void* buf[2] = {pool[2 * t], pool[2 * t + 1]};
         std::vector<cudaStream_t> st(nt, nullptr);
         std::vector<cudaEvent_t> ev(2 * nt, nullptr);                // ev[b * nt + i]: buffer b is free again for target i
         // replicas: one stream on the first device drives the H2D and the peer copies; shards: one stream per device
@@ -104,8 +135,6 @@ static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blo
                 cudaEventCreateWithFlags(&ev[nt + i], cudaEventDisableTiming) != cudaSuccess)
                 bad(DYIBF_ERR_CUDA, "filter I/O: stream / event creation failed");
         }
-        for (int b = 0; b < 2 && !r.rc; ++b)
-            if (cudaMallocHost(&buf[b], buf_bytes) != cudaSuccess) bad(DYIBF_ERR_NOMEM, "filter I/O: pinned staging allocation failed");
         int cur = 0;
         for (uint64_t c = (uint64_t)t; c < n_chunks && !r.rc; c += (uint64_t)T, cur ^= 1) {
             const uint64_t blk0 = c * bpc, nb = std::min(bpc, n_blocks - blk0);
@@ -117,6 +146,7 @@ static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blo
             if (to_device) {
                 t0 = now_s();
                 size_t got = 0;
+                if (fd < 0) { memcpy(buf[cur], host + blk0 * W * 8, bytes); got = bytes; }
                 while (got < bytes) {
                     ssize_t n = pread(fd, (char*)buf[cur] + got, bytes - got, file_off + (off_t)got);
                     if (n <= 0) { bad(DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be read."); break; }
@@ -167,6 +197,7 @@ static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blo
                 r.wait_s += now_s() - t0;
                 t0 = now_s();
                 size_t put = 0;
+                if (fd < 0) { memcpy(host + blk0 * W * 8, buf[cur], bytes); put = bytes; }
                 while (put < bytes) {
                     ssize_t n = pwrite(fd, (char*)buf[cur] + put, bytes - put, file_off + (off_t)put);
                     if (n <= 0) { bad(DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be written."); break; }
@@ -182,7 +213,6 @@ static int stream_words(int fd, const char* path, bool to_device, uint64_t n_blo
                 cudaStreamDestroy(st[i]);
             }
         for (cudaEvent_t e : ev) if (e) cudaEventDestroy(e);
-        for (int b = 0; b < 2; ++b) if (buf[b]) cudaFreeHost(buf[b]);
     };
     int prev = -1; cudaGetDevice(&prev);
     if (T == 1) worker(0);
@@ -215,7 +245,7 @@ int io_load_words(const char* path, uint64_t n_blocks, uint32_t W, const int* de
     const uint32_t Wr = bin_sharded ? W / (uint32_t)n : W;
     for (int i = 0; i < n; ++i) tg.push_back({devices[i], d_words[i], bin_sharded ? (uint32_t)i * Wr : 0u, Wr});
     dyibf_io_stats st; memset(&st, 0, sizeof st);
-    int rc = stream_words(fd, path, true, n_blocks, W, tg, !bin_sharded, &st);
+    int rc = stream_words(fd, path, nullptr, true, n_blocks, W, tg, !bin_sharded, &st);
     close(fd);
     g_last_io = st;
     return rc;
@@ -241,13 +271,25 @@ int io_save_words(const char* path, const dyibf_filter* whole_params, uint64_t n
         const uint32_t Wr = bin_sharded ? W / (uint32_t)n : W;
         const int n_src = bin_sharded ? n : 1;                       // replicas: every device holds the same words
         for (int i = 0; i < n_src; ++i) tg.push_back({devices[i], d_words[i], bin_sharded ? (uint32_t)i * Wr : 0u, Wr});
-        rc = stream_words(fd, path, false, n_blocks, W, tg, false, &st);
+        rc = stream_words(fd, path, nullptr, false, n_blocks, W, tg, false, &st);
     }
     ok = (close(fd) == 0) && ok;
     g_last_io = st;
     if (rc) return rc;
     if (!ok) return fail(DYIBF_ERR_IO, "File \"%s\" could not be written.", path);
     return DYIBF_OK;
+}
+
+// words [first_block * W, (first_block + n_blocks) * W) of one table <-> host memory, through the threaded pinned pipeline
+int io_copy_words(dyibf_filter* f, uint64_t* host_words, uint64_t first_block, uint64_t n_blocks, bool to_device)
+{
+    const uint32_t W = f->prm.words_per_block;
+    std::vector<IoTarget> tg;
+    tg.push_back({f->prm.device, f->d_words + first_block * W, 0u, W});
+    dyibf_io_stats st; memset(&st, 0, sizeof st);
+    int rc = stream_words(-1, "", reinterpret_cast<char*>(host_words), to_device, n_blocks, W, tg, false, &st);
+    g_last_io = st;
+    return rc;
 }
 
 static int load_impl(const char* path, bool expect, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits,

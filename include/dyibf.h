@@ -118,7 +118,8 @@ int  dyibf_save_file(dyibf_filter* f, const char* path);
 
 /* The loader / writer behind dyibf_load_file* / dyibf_save_file (and their group forms) streams the file through pinned
  * host buffers with several threads (pread / pwrite + asynchronous copies); this is the stage the mapper prints as
- * "Filter loading time" (src/d_mapper.h:913-921).  dyibf_set_io_threads: 1..64, default 4, process-wide.
+ * "Filter loading time" (src/d_mapper.h:913-921); dyibf_upload_words / dyibf_download_words of whole blocks use the same
+ * pipeline.  dyibf_set_io_threads: 1..64, default 8, process-wide.
  * dyibf_last_io_stats: the calling thread's last load or save. */
 typedef struct dyibf_io_stats {
     uint64_t bytes;               /* data-word bytes moved between the file and HBM                         */
