@@ -18,6 +18,9 @@ OPT_EARLY_EXIT = 1
 OPT_BUILD_BUCKET_MIB = 2
 OPT_BUILD_CHUNK_MIB = 3
 OPT_QUERY_CHUNK_MIB = 4
+OPT_BUILD_MODE = 5
+OPT_LAST_BUILD_MODE = 6
+BUILD_AUTO, BUILD_DIRECT, BUILD_BUCKETED, BUILD_SLICED = 0, 1, 2, 3
 
 
 class Params(C.Structure):

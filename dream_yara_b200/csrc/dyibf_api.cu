@@ -296,6 +296,13 @@ int dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first, 
 // ============================================================================================================
 namespace dyibf {
 
+// a build leaves its record buffer (up to tens of GiB) allocated for the next dyibf_add_sequences; a handle that goes on
+// to answer queries or is saved gives it back here
+void trim_build_scratch(dyibf_filter* f)
+{
+    if (f->bucket_records.cap > (1ull << 30)) { cudaDeviceSynchronize(); f->bucket_records.release(); }
+}
+
 // pack + query of one device-resident batch on stream st, using the workspace of slot sl
 int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t total_bytes, int encoding, uint32_t group,
                     int derive_rc, uint32_t threshold, uint32_t max_seq_len, uint64_t* d_rows, uint16_t* d_counts,
@@ -304,6 +311,7 @@ int query_on_device(dyibf_filter* f, Slot& sl, const PackSource& src, uint64_t t
     const uint64_t n_in = (uint64_t)src.n_ranges * src.cnt;
     const uint64_t n_total = derive_rc ? 2 * n_in : n_in;
     if (n_total == 0) return DYIBF_OK;
+    trim_build_scratch(f);
     if (n_total > 0xffffffffull) return fail(DYIBF_ERR_ARG, "too many sequences in one batch");
     const uint32_t n_rows = (uint32_t)(n_total / group);
     const uint64_t words_one = packed_words_for(total_bytes, n_in);
@@ -376,6 +384,10 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
         CU(f->batch_bytes.reserve(total_bytes + 16));
         CU(f->batch_offsets.reserve((uint64_t)(n_seqs + 1) * 8));
     }
+    // pageable caller memory goes through pinned pieces filled by helper threads (dyibf_hostcopy.cu); the driver's own
+    // pageable path moves ~10 GB/s and drains the stream first
+    const bool big = offsets[n_seqs] - offsets[0] >= (1u << 20);
+    const bool pageable = big && is_pageable(seqs + offsets[0]), pageable_off = big && is_pageable(offsets);
     int rc = DYIBF_OK; uint32_t c = 0;
     for (uint64_t a = row0; a < row1 && !rc; a += chunk_rows, ++c) {
         const uint32_t cnt = (uint32_t)std::min<uint64_t>(chunk_rows, row1 - a);
@@ -420,13 +432,16 @@ int query_host(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, ui
             const uint64_t nb = offsets[s0 + cnt] - offsets[s0];
             uint8_t* dst = keep_batch ? (uint8_t*)f->batch_bytes.p + (offsets[s0] - offsets[0])
                                       : (uint8_t*)sl.in_bytes.p + src.pack_base[g];
-            if (nb) CU(cudaMemcpyAsync(dst, seqs + offsets[s0], nb, cudaMemcpyHostToDevice, sl.st));
+            if (nb && pageable) { rc = staged_h2d(dst, seqs + offsets[s0], nb, sl.st); if (rc) break; }
+            else if (nb) CU(cudaMemcpyAsync(dst, seqs + offsets[s0], nb, cudaMemcpyHostToDevice, sl.st));
             uint64_t* doff = keep_batch ? (uint64_t*)f->batch_offsets.p + s0
                                         : (uint64_t*)sl.in_offsets.p + (uint64_t)g * (cnt + 1);
-            CU(cudaMemcpyAsync(doff, offsets + s0, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
+            if (pageable_off) { rc = staged_h2d(doff, offsets + s0, (uint64_t)(cnt + 1) * 8, sl.st); if (rc) break; }
+            else CU(cudaMemcpyAsync(doff, offsets + s0, (uint64_t)(cnt + 1) * 8, cudaMemcpyHostToDevice, sl.st));
             src.bytes[g] = dst - src.first_off[g];
             src.offsets[g] = doff;
         }
+        if (rc) break;
         uint64_t* d_rows = d_rows_all ? d_rows_all + (a - row0) * W : (uint64_t*)sl.rows.p;
         rc = query_on_device(f, sl, src, bytes, encoding, (uint32_t)group, derive_rc, threshold, chunk_max, d_rows, d_counts, sl.st);
         if (rc) break;
@@ -923,8 +938,28 @@ int buckets_apply(dyibf_filter* f, BucketRun* br, cudaStream_t st)
 }
 
 // Split the updates of packed words [0, words) of one pack buffer into the buckets, in word ranges that fit the buffers;
-// makes room first (level 2, apply) where needed.  sync_all: the call uses both stream slots (host mode), so everything
+// makes room first (level 2, apply) where needed.  sync_all: the call uses both stream slots (host mode), so a buffer is
+// emptied only after everything in flight on EITHER stream, and later splits on either stream wait for the emptying —
+// ordered with events between the two streams (join_streams / fork_streams), never by blocking the host, so the host keeps
+// enqueueing chunks and the uploads keep running.  [round 1 blocked the host here: 17.6 instead of 22 G k-mers/s]
 // in flight is waited for before a buffer is emptied; otherwise the work is stream-ordered on st.
+// st waits for everything enqueued so far on the other slot's stream
+int join_streams(dyibf_filter* f, cudaStream_t st)
+{
+    cudaStream_t ot = f->slot[0].st == st ? f->slot[1].st : f->slot[0].st;
+    CU(cudaEventRecord(f->stage_ev[0], ot));
+    CU(cudaStreamWaitEvent(st, f->stage_ev[0], 0));
+    return DYIBF_OK;
+}
+// the other slot's stream waits for everything enqueued so far on st
+int fork_streams(dyibf_filter* f, cudaStream_t st)
+{
+    cudaStream_t ot = f->slot[0].st == st ? f->slot[1].st : f->slot[0].st;
+    CU(cudaEventRecord(f->stage_ev[1], st));
+    CU(cudaStreamWaitEvent(ot, f->stage_ev[1], 0));
+    return DYIBF_OK;
+}
+
 int buckets_scatter(dyibf_filter* f, BucketRun* br, const uint64_t* packed, const SeqMeta* meta, const uint32_t* bin_ids,
                     uint32_t n_seqs, uint64_t words, uint32_t counter_slot, bool sync_all, cudaStream_t st)
 {
@@ -940,21 +975,21 @@ int buckets_scatter(dyibf_filter* f, BucketRun* br, const uint64_t* packed, cons
         if (room < left && room < max_words) {
             // not enough room for a full-sized range: empty the level-1 buffer, and the final buckets if they could not
             // take what level 1 may still hold plus a full range
-            if (sync_all) { CU(cudaStreamSynchronize(f->slot[0].st)); CU(cudaStreamSynchronize(f->slot[1].st)); }
+            if (sync_all) { int jrc = join_streams(f, st); if (jrc) return jrc; }
             int rc = buckets_flush_level1(f, br, st);
             if (rc) return rc;
             const uint64_t next = std::min(left, max_words) * per_word;
             if (br->pending && br->pending + next > br->limit) { rc = buckets_apply(f, br, st); if (rc) return rc; }
-            if (sync_all) CU(cudaStreamSynchronize(st));
+            if (sync_all) { int frc = fork_streams(f, st); if (frc) return frc; }
             continue;
         }
         const uint64_t n = std::min(left, std::min(room, max_words));
         const uint64_t add = n * per_word;
         if (two && br->pending + br->pending1 + add > br->limit) {   // the final buckets must be able to take level 1's content
-            if (sync_all) { CU(cudaStreamSynchronize(f->slot[0].st)); CU(cudaStreamSynchronize(f->slot[1].st)); }
+            if (sync_all) { int jrc = join_streams(f, st); if (jrc) return jrc; }
             int rc = buckets_apply(f, br, st);
             if (rc) return rc;
-            if (sync_all) CU(cudaStreamSynchronize(st));
+            if (sync_all) { int frc = fork_streams(f, st); if (frc) return frc; }
         }
         { Scope sc(f, st, K_BUILD);
           CU(launch_bucket_split(f->hp, f->d_words, packed, meta, bin_ids, n_seqs, w0, w0 + n, br->plan, f->bucket_records.p,
@@ -967,8 +1002,82 @@ int buckets_scatter(dyibf_filter* f, BucketRun* br, const uint64_t* packed, cons
 
 void buckets_end(dyibf_filter* f, BucketRun* br)
 {
+    // The record buffer stays allocated for the next dyibf_add_sequences call: a cudaMalloc / cudaFree pair of tens of GiB
+    // costs more than the build of a 4 Gbp batch.  trim_build_scratch (first query after a build, dyibf_save_file) frees it.
+    (void)f;
     br->active = false;
-    if (f->bucket_records.cap > (1ull << 30)) f->bucket_records.release();   // do not sit on gigabytes between calls
+}
+
+// ---- the bit-sliced build (build_sliced.cu): per-bin bit vectors in the L2, then interleaved --------------------------
+struct SlicedRun {
+    bool active = false;
+    SlicedPlan plan;
+    int cur = -1;                                   // group whose updates the shadow holds (-1: none)
+};
+
+// may this call use the sliced build at all (mode, table size, call size) — and with which plan
+bool sliced_candidate(dyibf_filter* f, uint64_t expected_records, SlicedPlan* plan)
+{
+    const int64_t mode = f->build_mode;
+    if (mode == DYIBF_BUILD_DIRECT || mode == DYIBF_BUILD_BUCKETED || f->hp.direct) return false;
+    if (mode == DYIBF_BUILD_AUTO) {
+        if (f->data_words * 8 <= (256ull << 20)) return false;     // table (nearly) fits the L2: direct atomics are L2 hits
+        if (expected_records < (32ull << 20)) return false;         // too few updates to pay for the zero / interleave passes
+    }
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return false;
+    free_b += f->bucket_records.cap;
+    const uint64_t budget = std::min<uint64_t>(free_b / 2, 16ull << 30);
+    return sliced_plan(f->hp, budget, plan);
+}
+
+// bin changes along the batch decide whether the vectors of the bins in flight fit the L2
+int sliced_begin(dyibf_filter* f, const SlicedPlan& plan, uint64_t total_bases, uint64_t switches, SlicedRun* sr)
+{
+    sr->active = false; sr->plan = plan; sr->cur = -1;
+    if (f->build_mode == DYIBF_BUILD_AUTO) {
+        const uint64_t avg_run = std::max<uint64_t>(total_bases / (switches + 1), 1);
+        const uint64_t bins_in_flight = SLICED_WINDOW_BASES / avg_run + 2;
+        if (bins_in_flight * plan.pw * 4 > (80ull << 20)) return DYIBF_OK;   // not clustered by bin: bucketed / direct
+    }
+    if (f->bucket_records.reserve(plan.shadow_bytes) != cudaSuccess) {
+        cudaGetLastError();                                          // not enough memory: the other builds
+        return DYIBF_OK;
+    }
+    CU(f->bucket_cursors.reserve(256));
+    sr->active = true;
+    return DYIBF_OK;
+}
+
+// the shadow's group goes into the table (stream-ordered on st)
+int sliced_finish_group(dyibf_filter* f, SlicedRun* sr, cudaStream_t st)
+{
+    if (!sr->active || sr->cur < 0) return DYIBF_OK;
+    Scope sc(f, st, K_APPLY);
+    CU(launch_sliced_interleave(f->hp, f->d_words, f->bucket_records.p, sr->plan, (uint32_t)sr->cur, st));
+    sr->cur = -1;
+    return DYIBF_OK;
+}
+
+// the updates of group g's sequences of one packed batch -> the shadow; switches the shadow to g first where needed.
+// both_streams: the call alternates between the two slot streams (host mode) — emptying / zeroing the shadow is ordered
+// against the other stream with events; scatters of different chunks may overlap (atomics).
+int sliced_scatter_group(dyibf_filter* f, SlicedRun* sr, uint32_t g, const uint64_t* packed, const SeqMeta* meta,
+                         const uint32_t* bin_ids, uint32_t n_seqs, uint64_t words, bool both_streams, cudaStream_t st)
+{
+    if (sr->cur != (int)g) {
+        if (both_streams) { int rc = join_streams(f, st); if (rc) return rc; }
+        int rc = sliced_finish_group(f, sr, st);
+        if (rc) return rc;
+        CU(launch_sliced_zero(f->bucket_records.p, sr->plan, st));
+        if (both_streams) { rc = fork_streams(f, st); if (rc) return rc; }
+        sr->cur = (int)g;
+    }
+    Scope sc(f, st, K_BUILD);
+    // one work counter per slot stream: scatters of successive chunks may overlap
+    unsigned long long* ctr = static_cast<unsigned long long*>(f->bucket_cursors.p) + (st == f->slot[1].st ? 8 : 0);
+    CU(launch_sliced_scatter(f->hp, f->bucket_records.p, sr->plan, g, packed, meta, bin_ids, n_seqs, words, ctr, st));
+    return DYIBF_OK;
 }
 
 } // namespace
@@ -988,8 +1097,28 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         uint64_t first = 0, last = 0;
         CU(cudaMemcpyAsync(&first, offsets, 8, cudaMemcpyDeviceToHost, st));
         CU(cudaMemcpyAsync(&last, offsets + n_seqs, 8, cudaMemcpyDeviceToHost, st));
+        // sliced build: which column groups occur and how clustered the bins are — asked of the device-resident bin ids
+        // here, answered by the synchronisation that fetches the offsets anyway
+        SlicedPlan splan; SlicedRun sr;
+        std::vector<uint32_t> group_mask; unsigned long long switches = 0;
+        // the call's size is not known before the sync: plan for a large one, decide after
+        const bool s_cand = sliced_candidate(f, ~0ull, &splan) && splan.n_groups <= 4096;
+        if (s_cand) {
+            CU(f->build_bins.reserve((size_t)splan.n_groups * 4 + 16));
+            uint32_t* d_mask = static_cast<uint32_t*>(f->build_bins.p);
+            unsigned long long* d_sw = reinterpret_cast<unsigned long long*>(d_mask + ((splan.n_groups + 1) & ~1u));
+            CU(launch_sliced_presence(bin_ids, n_seqs, f->prm.bins, splan, d_mask, d_sw, st));
+            f->kernel_launches += 1;
+            group_mask.resize(splan.n_groups);
+            CU(cudaMemcpyAsync(group_mask.data(), d_mask, (size_t)splan.n_groups * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(&switches, d_sw, 8, cudaMemcpyDeviceToHost, st));
+        }
         CU(cudaStreamSynchronize(st));
         if (last < first) return fail(DYIBF_ERR_ARG, "offsets not monotone");
+        if (s_cand && (f->build_mode != DYIBF_BUILD_AUTO || (last - first) * f->hp.h >= (32ull << 20))) {
+            int src_ = sliced_begin(f, splan, last - first, switches, &sr);
+            if (src_) return src_;
+        }
         Slot& sl = f->slot[0];
         PackSource src; memset(&src, 0, sizeof src);
         src.n_ranges = 1; src.cnt = n_seqs; src.bytes[0] = seqs; src.offsets[0] = offsets; src.first_off[0] = first;
@@ -998,9 +1127,19 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         CU(sl.meta.reserve((uint64_t)n_seqs * sizeof(SeqMeta)));
         { Scope sc(f, st, K_PACK);
           CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, words, words, st)); }
+        if (sr.active) {
+            f->last_build_mode = DYIBF_BUILD_SLICED;
+            for (uint32_t g = 0; g < splan.n_groups; ++g) {
+                if (!group_mask[g]) continue;
+                int rc = sliced_scatter_group(f, &sr, g, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, false, st);
+                if (rc) return rc;
+            }
+            return sliced_finish_group(f, &sr, st);                  // the shadow stays allocated: stream-ordered call
+        }
         BucketRun br;
-        int brc = buckets_begin(f, (last - first) * f->hp.h, &br);
+        int brc = f->build_mode == DYIBF_BUILD_DIRECT ? (br.active = false, DYIBF_OK) : buckets_begin(f, (last - first) * f->hp.h, &br);
         if (brc) return brc;
+        f->last_build_mode = br.active ? DYIBF_BUILD_BUCKETED : DYIBF_BUILD_DIRECT;
         if (!br.active) {
             Scope sc(f, st, K_BUILD);
             CU(launch_build(build_params(f), f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, bin_ids, n_seqs, words, st));
@@ -1020,10 +1159,21 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
     }
     // chunks of whole sequences, ~256 MB of bases each by default (8192 scatter work items: enough warps for every SM),
     // alternating between the two stream slots
-    const uint64_t target = (uint64_t)f->build_chunk_mib << 20;
+    const uint64_t expected = (offsets[n_seqs] - offsets[0]) * f->hp.h;
+    SlicedPlan splan; SlicedRun sr;
+    if (sliced_candidate(f, expected, &splan)) {
+        uint64_t switches = 0;
+        for (uint32_t s = 1; s < n_seqs; ++s) switches += bin_ids[s] != bin_ids[s - 1];
+        int src_ = sliced_begin(f, splan, offsets[n_seqs] - offsets[0], switches, &sr);
+        if (src_) return src_;
+    }
     BucketRun br;
-    int brc = buckets_begin(f, (offsets[n_seqs] - offsets[0]) * f->hp.h, &br);
+    int brc = (sr.active || f->build_mode == DYIBF_BUILD_DIRECT) ? (br.active = false, DYIBF_OK) : buckets_begin(f, expected, &br);
     if (brc) return brc;
+    // auto chunk size: 64 MiB under the sliced build (its scatter never holds the host, so small chunks only shorten the
+    // pipeline's ramp), 256 MiB under the others (a bucket flush holds the host; larger chunks amortise it)
+    const uint64_t target = (uint64_t)(f->build_chunk_mib ? f->build_chunk_mib : sr.active ? 64 : 256) << 20;
+    f->last_build_mode = sr.active ? DYIBF_BUILD_SLICED : br.active ? DYIBF_BUILD_BUCKETED : DYIBF_BUILD_DIRECT;
     // The bases go up on a copy stream of their own, two chunks ahead of the kernels: the upload of chunk c+2 into slot c&1
     // starts as soon as pack(c) has consumed that slot's bytes, and keeps running while buckets_scatter blocks the host on
     // the two kernel streams to empty a full record buffer (level 2 / apply).  pack(c) waits for its own upload by event.
@@ -1041,8 +1191,6 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
     for (int i = 0; i < 2 && i < (int)chunks.size(); ++i) {        // sized once: no reallocation under the pipeline
         Slot& sl = f->slot[i];
         CU(sl.in_bytes.reserve(max_bytes + 16));
-        CU(sl.in_offsets.reserve((uint64_t)(max_cnt + 1) * 8));
-        CU(sl.counts.reserve((uint64_t)max_cnt * 4));
         CU(sl.packed.reserve(max_words * 8));
         CU(sl.meta.reserve((uint64_t)max_cnt * sizeof(SeqMeta)));
     }
@@ -1058,45 +1206,91 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         CU(cudaEventCreateWithFlags(&up.copied[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&up.packed[i], cudaEventDisableTiming));
     }
+    const bool pageable = offsets[n_seqs] - offsets[0] >= (8u << 20) && is_pageable(seqs + offsets[0]);
     auto upload = [&](uint32_t c) -> int {                           // bases + limits of chunk c into slot c&1, on the copy stream
         const Chunk& ch = chunks[c]; Slot& sl = f->slot[c & 1];
-        if (ch.bytes) CU(cudaMemcpyAsync(sl.in_bytes.p, seqs + offsets[ch.a], ch.bytes, cudaMemcpyHostToDevice, up.st));
-        CU(cudaMemcpyAsync(sl.in_offsets.p, offsets + ch.a, (uint64_t)(ch.cnt + 1) * 8, cudaMemcpyHostToDevice, up.st));
+        if (ch.bytes && pageable) {                                  // through pinned pieces, copied by helper threads
+            int rc = staged_h2d(sl.in_bytes.p, seqs + offsets[ch.a], ch.bytes, up.st);
+            if (rc) return rc;
+        } else if (ch.bytes) {
+            CU(cudaMemcpyAsync(sl.in_bytes.p, seqs + offsets[ch.a], ch.bytes, cudaMemcpyHostToDevice, up.st));
+        }
         CU(cudaEventRecord(up.copied[c & 1], up.st));
         return DYIBF_OK;
     };
+    // the limits and bin ids of the whole call go up once, ahead of everything (a per-chunk copy from the caller's pageable
+    // arrays would make the host wait for the chunk's stream to drain every time, serialising upload and kernels)
+    const uint64_t off_bytes = ((uint64_t)(n_seqs + 1) * 8 + 15) & ~15ull;
+    CU(f->build_bins.reserve(off_bytes + (uint64_t)n_seqs * 4 + 16));
+    const uint64_t* d_offsets_all = static_cast<const uint64_t*>(f->build_bins.p);
+    CU(cudaMemcpyAsync(f->build_bins.p, offsets, (uint64_t)(n_seqs + 1) * 8, cudaMemcpyHostToDevice, up.st));
+    CU(cudaMemcpyAsync(static_cast<char*>(f->build_bins.p) + off_bytes, bin_ids, (uint64_t)n_seqs * 4, cudaMemcpyHostToDevice, up.st));
+    cudaEvent_t bins_up = up.packed[0];                            // borrowed: recorded once here, before its per-slot use
+    CU(cudaEventRecord(bins_up, up.st));
+    CU(cudaStreamWaitEvent(f->slot[0].st, bins_up, 0));
+    CU(cudaStreamWaitEvent(f->slot[1].st, bins_up, 0));
+    const uint32_t* d_bins_all = reinterpret_cast<const uint32_t*>(static_cast<const char*>(f->build_bins.p) + off_bytes);
     int urc = upload(0);
     if (!urc && chunks.size() > 1) urc = upload(1);
     if (urc) return urc;
     for (uint32_t c = 0; c < chunks.size(); ++c) {
         const Chunk& cur = chunks[c];
         Slot& sl = f->slot[c & 1];
-        // bin ids: small, and read by this chunk's split kernels to the end, so they travel on the kernel stream
-        CU(cudaMemcpyAsync(sl.counts.p, bin_ids + cur.a, (uint64_t)cur.cnt * 4, cudaMemcpyHostToDevice, sl.st));
+        const uint32_t* d_bins = d_bins_all + cur.a;
         CU(cudaStreamWaitEvent(sl.st, up.copied[c & 1], 0));
         PackSource src; memset(&src, 0, sizeof src);
         src.n_ranges = 1; src.cnt = cur.cnt; src.first_off[0] = offsets[cur.a];
-        src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[cur.a]; src.offsets[0] = (const uint64_t*)sl.in_offsets.p;
+        src.bytes[0] = (const uint8_t*)sl.in_bytes.p - offsets[cur.a]; src.offsets[0] = d_offsets_all + cur.a;
         { Scope sc(f, sl.st, K_PACK);
           CU(launch_pack(src, encoding, 0, (uint64_t*)sl.packed.p, (SeqMeta*)sl.meta.p, cur.words, cur.words, sl.st)); }
-        if (c + 2 < chunks.size()) {                                 // the slot's bytes are free once this pack has run
-            CU(cudaEventRecord(up.packed[c & 1], sl.st));
+        const bool more = c + 2 < chunks.size();
+        if (more) CU(cudaEventRecord(up.packed[c & 1], sl.st));      // the slot's bytes are free once this pack has run
+        // Bucketed: buckets_scatter may hold the host to empty a full record buffer, so the next upload is queued first.
+        // Otherwise the chunk's kernels are queued first: staging a pageable range holds the host instead.
+        if (more && br.active) {
             CU(cudaStreamWaitEvent(up.st, up.packed[c & 1], 0));
             urc = upload(c + 2);
             if (urc) return urc;
         }
-        if (br.active) {
-            brc = buckets_scatter(f, &br, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, (const uint32_t*)sl.counts.p,
+        if (sr.active) {
+            // the column groups this chunk's sequences belong to, in order of first appearance (bin-sorted input: ascending,
+            // every group once per call)
+            std::vector<uint32_t> groups;
+            for (uint32_t s = cur.a; s < cur.a + cur.cnt; ++s) {
+                const uint32_t g = bin_ids[s] / splan.group_bins;
+                if (groups.empty() || (groups.back() != g && std::find(groups.begin(), groups.end(), g) == groups.end())) groups.push_back(g);
+            }
+            if (!groups.empty() && sr.cur >= 0) {                    // keep the group that is already in the shadow first
+                auto it = std::find(groups.begin(), groups.end(), (uint32_t)sr.cur);
+                if (it != groups.end()) std::rotate(groups.begin(), it, it + 1);
+            }
+            for (uint32_t g : groups) {
+                int rc = sliced_scatter_group(f, &sr, g, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, d_bins,
+                                              cur.cnt, cur.words, true, sl.st);
+                if (rc) return rc;
+            }
+        } else if (br.active) {
+            brc = buckets_scatter(f, &br, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p, d_bins,
                                   cur.cnt, cur.words, c & 1, true, sl.st);
             if (brc) return brc;
         } else {
             Scope sc(f, sl.st, K_BUILD);
             CU(launch_build(build_params(f), f->d_words, (const uint64_t*)sl.packed.p, (const SeqMeta*)sl.meta.p,
-                            (const uint32_t*)sl.counts.p, cur.cnt, cur.words, sl.st));
+                            d_bins, cur.cnt, cur.words, sl.st));
+        }
+        if (more && !br.active) {
+            CU(cudaStreamWaitEvent(up.st, up.packed[c & 1], 0));
+            urc = upload(c + 2);
+            if (urc) return urc;
         }
     }
     CU(cudaStreamSynchronize(f->slot[0].st));
     CU(cudaStreamSynchronize(f->slot[1].st));
+    if (sr.active) {
+        int rc = sliced_finish_group(f, &sr, f->slot[0].st);
+        if (rc) return rc;
+        CU(cudaStreamSynchronize(f->slot[0].st));
+    }
     if (br.active) {
         brc = buckets_apply(f, &br, f->slot[0].st);
         if (brc) return brc;
@@ -1150,8 +1344,12 @@ int dyibf_set_option(dyibf_filter* f, int option, int64_t value)
             f->query_chunk_mib = value;
             return DYIBF_OK;
         case DYIBF_OPT_BUILD_CHUNK_MIB:
-            if (value < 1 || value > 4096) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_CHUNK_MIB must be 1..4096");
+            if (value < 0 || value > 4096) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_CHUNK_MIB must be 0 (auto) or 1..4096");
             f->build_chunk_mib = value;
+            return DYIBF_OK;
+        case DYIBF_OPT_BUILD_MODE:
+            if (value < DYIBF_BUILD_AUTO || value > DYIBF_BUILD_SLICED) return fail(DYIBF_ERR_ARG, "DYIBF_OPT_BUILD_MODE must be 0..3");
+            f->build_mode = value;
             return DYIBF_OK;
         default:
             return fail(DYIBF_ERR_ARG, "unknown option %d", option);
@@ -1166,6 +1364,8 @@ int dyibf_get_option(const dyibf_filter* f, int option, int64_t* value)
         case DYIBF_OPT_BUILD_BUCKET_MIB: *value = f->bucket_mib; return DYIBF_OK;
         case DYIBF_OPT_BUILD_CHUNK_MIB: *value = f->build_chunk_mib; return DYIBF_OK;
         case DYIBF_OPT_QUERY_CHUNK_MIB: *value = f->query_chunk_mib; return DYIBF_OK;
+        case DYIBF_OPT_BUILD_MODE: *value = f->build_mode; return DYIBF_OK;
+        case DYIBF_OPT_LAST_BUILD_MODE: *value = f->last_build_mode; return DYIBF_OK;
         default: return fail(DYIBF_ERR_ARG, "unknown option %d", option);
     }
 }

@@ -13,88 +13,9 @@
 //        ticket's batch the handle's resident batch (dyibf_gather_reads / dyibf_classify_fetch work on it).
 #include "dyibf_handle.h"
 
-#include <condition_variable>
-#include <thread>
-
-#include <emmintrin.h>
-
 using namespace dyibf;
 
 namespace dyibf {
-
-// Pageable caller memory: cudaMemcpyAsync from it is staged by the driver on the calling thread at ~10 GB/s, which for a
-// 100 000-read batch (15 MB) is most of the batch's GPU time — the host would be the bottleneck of the pipeline.  The batch
-// is instead copied into a pinned buffer of the ticket by a few helper threads (memory-bandwidth bound, several times
-// faster) and uploaded from there asynchronously.
-// memcpy with non-temporal stores: the destination is pinned staging that only the DMA engine reads next.  Lines left
-// dirty in the private caches of several cores made that DMA three times slower (17 instead of 51 GB/s, measured on the
-// B200 box: tools/debug/async_probe.py), so the stores bypass the caches.
-static void copy_streaming(void* dst, const void* src, size_t n)
-{
-    char* d = static_cast<char*>(dst); const char* s = static_cast<const char*>(src);
-    while (n && (reinterpret_cast<uintptr_t>(d) & 15)) { *d++ = *s++; --n; }
-    for (; n >= 64; n -= 64, d += 64, s += 64) {
-        const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s));
-        const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + 16));
-        const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + 32));
-        const __m128i e = _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + 48));
-        _mm_stream_si128(reinterpret_cast<__m128i*>(d), a);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(d + 16), b);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(d + 32), c);
-        _mm_stream_si128(reinterpret_cast<__m128i*>(d + 48), e);
-    }
-    while (n) { *d++ = *s++; --n; }
-    _mm_sfence();
-}
-
-class HostCopier {
-public:
-    static HostCopier& get() { static HostCopier* c = new HostCopier(); return *c; }   // never destroyed: its threads outlive main
-    void copy(void* dst, const void* src, size_t n) {
-        if (n < (1u << 20)) { copy_streaming(dst, src, n); return; }
-        std::unique_lock<std::mutex> call(call_m_);                  // one parallel copy at a time
-        const size_t part = (n / (N + 1) + 63) & ~size_t(63);
-        {
-            std::lock_guard<std::mutex> l(m_);
-            for (int i = 0; i < N; ++i) {
-                const size_t a = std::min(n, part * (i + 1)), b = std::min(n, part * (i + 2));
-                job_[i] = {static_cast<char*>(dst) + a, static_cast<const char*>(src) + a, b - a};
-            }
-            pending_ = N; ++gen_;
-        }
-        cv_.notify_all();
-        copy_streaming(dst, src, std::min(n, part));
-        std::unique_lock<std::mutex> l(m_);
-        done_.wait(l, [this] { return pending_ == 0; });
-    }
-private:
-    static const int N = 3;                                          // helpers; the caller copies a share too
-    struct Job { char* d; const char* s; size_t n; };
-    HostCopier() { for (int i = 0; i < N; ++i) th_[i] = std::thread([this, i] { loop(i); }); for (auto& t : th_) t.detach(); }
-    void loop(int i) {
-        uint64_t seen = 0;
-        for (;;) {
-            Job j;
-            {
-                std::unique_lock<std::mutex> l(m_);
-                cv_.wait(l, [&] { return gen_ != seen; });
-                seen = gen_; j = job_[i];
-            }
-            if (j.n) copy_streaming(j.d, j.s, j.n);
-            { std::lock_guard<std::mutex> l(m_); if (--pending_ == 0) done_.notify_all(); }
-        }
-    }
-    std::thread th_[N]; Job job_[N];
-    std::mutex m_, call_m_; std::condition_variable cv_, done_;
-    int pending_ = 0; uint64_t gen_ = 0;
-};
-
-static bool is_pageable(const void* p)
-{
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
-    return a.type == cudaMemoryTypeUnregistered;
-}
 
 struct Ticket {
     dyibf_filter* f = nullptr;
@@ -190,8 +111,10 @@ int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* o
         const uint8_t* src_bytes = seqs + offsets[0];
         const uint64_t* src_off = offsets;
         const size_t off_bytes = (size_t)(n_seqs + 1) * 8;
-        static const int stage_mode = getenv("DYIBF_STAGE_MODE") ? atoi(getenv("DYIBF_STAGE_MODE")) : 1;   // debug
-        if (stage_mode != 0 && total_bytes + off_bytes >= (1u << 20) && (is_pageable(src_bytes) || stage_mode >= 3)) {
+        // Pageable caller memory: cudaMemcpyAsync from it is staged by the driver on the calling thread at ~10 GB/s, which for
+        // a 100 000-read batch (15 MB) is most of the batch's GPU time.  The batch is instead copied into a pinned buffer of
+        // the ticket by a few helper threads (dyibf_hostcopy.cu) and uploaded from there asynchronously.
+        if (total_bytes + off_bytes >= (1u << 20) && is_pageable(src_bytes)) {
             // the previous use of the staging buffer was waited for by that ticket's dyibf_classify_end
             const size_t b_pad = (total_bytes + 63) & ~size_t(63);
             if (b_pad + off_bytes > t->h_in_cap) {
@@ -200,12 +123,10 @@ int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* o
                 CU(cudaMallocHost(&t->h_in, want));
                 t->h_in_cap = want;
             }
-            if (stage_mode == 2) memcpy(t->h_in, src_bytes, total_bytes); else HostCopier::get().copy(t->h_in, src_bytes, total_bytes);
-            copy_streaming(static_cast<char*>(t->h_in) + b_pad, offsets, off_bytes);
-            if (stage_mode != 3) {
+            host_copy_parallel(t->h_in, src_bytes, total_bytes, 4);
+            host_copy_streaming(static_cast<char*>(t->h_in) + b_pad, offsets, off_bytes);
             src_bytes = static_cast<const uint8_t*>(t->h_in);
             src_off = reinterpret_cast<const uint64_t*>(static_cast<char*>(t->h_in) + b_pad);
-            }
         }
         if (total_bytes) CU(cudaMemcpyAsync(t->bytes.p, src_bytes, total_bytes, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(t->offsets.p, src_off, off_bytes, cudaMemcpyHostToDevice, st));

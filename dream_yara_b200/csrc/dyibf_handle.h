@@ -74,7 +74,9 @@ struct dyibf_filter {
     uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
     int64_t      bucket_mib = -1;         // DYIBF_OPT_BUILD_BUCKET_MIB: -1 auto, 0 direct atomics only
     int64_t      query_chunk_mib = 0;     // DYIBF_OPT_QUERY_CHUNK_MIB: 0 = auto
-    int64_t      build_chunk_mib = 256;   // DYIBF_OPT_BUILD_CHUNK_MIB: bases per host-mode build chunk
+    int64_t      build_chunk_mib = 0;     // DYIBF_OPT_BUILD_CHUNK_MIB: bases per host-mode build chunk (0 = auto)
+    int64_t      build_mode = 0;          // DYIBF_OPT_BUILD_MODE
+    int          last_build_mode = 0;     // what the last dyibf_add_sequences used (DYIBF_BUILD_*)
     dyibf::DevBuf bucket_records, bucket_cursors;
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
@@ -133,6 +135,13 @@ int classify_range(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets
                    int derive_rc, uint32_t threshold, uint32_t row0, uint32_t row1);
 int classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total);
 void free_tickets(dyibf_filter* f);
+void trim_build_scratch(dyibf_filter* f);
+
+// dyibf_hostcopy.cu: pageable caller memory -> pinned staging -> device
+void host_copy_streaming(void* dst, const void* src, size_t n);              // memcpy with non-temporal stores
+void host_copy_parallel(void* dst, const void* src, size_t n, int threads);  // ... split over up to 8 threads
+bool is_pageable(const void* p);
+int staged_h2d(void* d_dst, const void* h_src, size_t n, cudaStream_t st);   // returns once the range has been staged
 
 // bulk word transfer between one table and host memory through the threaded pinned pipeline of dyibf_io.cu
 int io_copy_words(dyibf_filter* f, uint64_t* host_words, uint64_t first_block, uint64_t n_blocks, bool to_device);

@@ -99,6 +99,26 @@ cudaError_t launch_bucket_split2(uint64_t* filter, const BucketPlan& plan, void*
 cudaError_t launch_bucket_apply(uint64_t* filter, uint64_t data_words, const BucketPlan& plan, void* records,
                                 unsigned long long* cursors, uint64_t max_fill, cudaStream_t st);
 
+// bit-sliced build (build_sliced.cu): per-bin Bloom bit vectors that live in the L2, then interleaved into the table.
+struct SlicedPlan {
+    uint64_t pw;               // 32-bit words per bin vector (ceil(P / 32), rounded up to 8)
+    uint32_t cols_per_group;   // word columns (64 bins each) per pass: 4, or fewer for narrow tables / small budgets
+    uint32_t group_bins;       // 64 * cols_per_group
+    uint32_t n_groups;         // passes that cover all W columns
+    uint64_t shadow_bytes;     // group_bins * pw * 4
+};
+static const uint64_t SLICED_WINDOW_BASES = 148ull * 8 * 8 * 1024;   // bases the resident warps of the scatter kernel span
+bool        sliced_plan(const HashParams& hp, uint64_t budget_bytes, SlicedPlan* plan);
+// mask[g] = 1 for every group with a sequence; *switches = number of bin changes along the batch (device buffers)
+cudaError_t launch_sliced_presence(const uint32_t* bin_ids, uint32_t n_seqs, uint32_t bins, const SlicedPlan& plan, uint32_t* mask,
+                                   unsigned long long* switches, cudaStream_t st);
+cudaError_t launch_sliced_zero(void* shadow, const SlicedPlan& plan, cudaStream_t st);
+cudaError_t launch_sliced_scatter(const HashParams& hp, void* shadow, const SlicedPlan& plan, uint32_t group, const uint64_t* packed,
+                                  const SeqMeta* meta, const uint32_t* bin_ids, uint32_t n_seqs, uint64_t total_words,
+                                  unsigned long long* work_counter, cudaStream_t st);
+cudaError_t launch_sliced_interleave(const HashParams& hp, uint64_t* filter, const void* shadow, const SlicedPlan& plan, uint32_t group,
+                                     cudaStream_t st);
+
 // clear: for every hash block, words cols[i] &= ~masks[i]
 cudaError_t launch_clear(const HashParams& hp, uint64_t* filter, const uint32_t* cols, const uint64_t* masks, uint32_t n_cols,
                          cudaStream_t st);

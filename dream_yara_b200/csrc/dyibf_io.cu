@@ -336,6 +336,7 @@ int dyibf_save_file(dyibf_filter* f, const char* path)
     if (!f || !path) return fail(DYIBF_ERR_ARG, "NULL argument");
     DeviceGuard guard(f->prm.device);
     CU(cudaDeviceSynchronize());                                      // builds still in flight on caller streams
+    trim_build_scratch(f);
     uint64_t* dw = f->d_words; int dev = f->prm.device;
     return io_save_words(path, f, f->prm.n_blocks, f->prm.words_per_block, &dev, &dw, 1, false);
 }

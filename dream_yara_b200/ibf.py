@@ -328,6 +328,15 @@ class SeqAnBloomFilter:
         """DYIBF_OPT_BUILD_BUCKET_MIB: scratch size of the bucketed build (-1 auto, 0 = direct atomics only)."""
         check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_BUCKET_MIB, int(mib)))
 
+    def set_build_mode(self, mode):
+        """DYIBF_OPT_BUILD_MODE: 0 auto, 1 direct atomics, 2 bucketed (radix split + apply), 3 sliced (per-bin bit vectors in the L2)."""
+        check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_MODE, int(mode)))
+
+    def last_build_mode(self):
+        v = C.c_int64(0)
+        check(lib().dyibf_get_option(self._h, _lib.OPT_LAST_BUILD_MODE, C.byref(v)))
+        return int(v.value)
+
     def set_build_chunk_mib(self, mib):
         """DYIBF_OPT_BUILD_CHUNK_MIB: bases per staged chunk of addSequences on host buffers."""
         check(lib().dyibf_set_option(self._h, _lib.OPT_BUILD_CHUNK_MIB, int(mib)))

@@ -301,8 +301,26 @@ int  dyibf_group_clear_bins(dyibf_group* g, const uint32_t* bins, uint32_t n);
  * this size and then ORs them in region by region, so that DRAM sees streaming instead of random sector traffic.  The
  * filter is bit-identical either way (OR is commutative and idempotent). */
 #define DYIBF_OPT_BUILD_BUCKET_MIB 2
-/* DYIBF_OPT_BUILD_CHUNK_MIB (default 256): dyibf_add_sequences(host) stages whole sequences in chunks of about this many
- * MiB of bases, alternating between two streams so that the copy of one chunk overlaps the kernels of the other. */
+/* DYIBF_OPT_BUILD_MODE (default 0 = auto).  How dyibf_add_sequences turns _insertKmer's random single-bit ORs into memory traffic:
+ *   1 direct    one atomic OR per (k-mer, hash function) straight into the table (what small calls and L2-sized tables use);
+ *   2 bucketed  the radix-split + apply build described at DYIBF_OPT_BUILD_BUCKET_MIB;
+ *   3 sliced    per-bin Bloom bit vectors (P bits = 16 MiB at 16 GiB / 1024 bins) that stay in the L2 while a bin's genome is
+ *               hashed, then interleaved into the table with bit-matrix transposes — one L2 atomic per update and two streaming
+ *               passes; needs the batch clustered by bin (build_filter adds one FASTA file per bin) and a scratch of 256 bin
+ *               vectors (4 GiB).
+ * Auto picks sliced for bin-clustered batches of at least 32 M updates into tables larger than the L2, else bucketed / direct.
+ * The filter is bit-identical in every mode. */
+#define DYIBF_OPT_BUILD_MODE 5
+#define DYIBF_BUILD_AUTO     0
+#define DYIBF_BUILD_DIRECT   1
+#define DYIBF_BUILD_BUCKETED 2
+#define DYIBF_BUILD_SLICED   3
+/* read-only (dyibf_get_option): the DYIBF_BUILD_* path the last dyibf_add_sequences of the handle took */
+#define DYIBF_OPT_LAST_BUILD_MODE 6
+/* DYIBF_OPT_BUILD_CHUNK_MIB (default 0 = auto): dyibf_add_sequences(host) stages whole sequences in chunks of about this
+ * many MiB of bases, alternating between two streams so that the copy of one chunk overlaps the kernels of the other.  Auto:
+ * 64 MiB under the sliced build, 256 MiB under the bucketed / direct ones.  Pageable caller memory is staged through pinned
+ * pieces by helper threads (the driver's own pageable path moves ~10 GB/s and holds the calling thread). */
 #define DYIBF_OPT_BUILD_CHUNK_MIB 3
 /* DYIBF_OPT_QUERY_CHUNK_MIB (default 0 = auto): dyibf_query_batch(host) / dyibf_classify stage the batch in chunks of rows,
  * alternating between two streams so that the upload of one chunk overlaps the kernels of the other.  Auto: chunks of about

@@ -395,6 +395,85 @@ def test_bucketed_build_equals_direct_and_oracle(dy, oracle, log2_bits):
     assert np.array_equal(many, want) and p4["build_launches"] >= 14 and p4["build_apply_launches"] == 1
 
 
+@pytest.mark.parametrize("bins,nbits,h,k", [(1000, (1 << 32) + 256, 3, 18), (130, 3 * (1 << 30) + 777, 2, 19), (64, (1 << 30) + 256, 3, 12),
+                                            (200, (1 << 31) + 256, 5, 20)])
+def test_sliced_build_equals_oracle(dy, oracle, bins, nbits, h, k):
+    """The bit-sliced build (DYIBF_OPT_BUILD_MODE = 3: per-bin Bloom bit vectors in the L2, then interleaved with bit-matrix
+    transposes) against the oracle: W = 16 (four-column groups, 32-byte sector path), W = 3 (odd, non-power-of-two P,
+    unaligned trailer), W = 1, W = 4 with bins that are not a multiple of 64 and the generic hash count; sequences in bin order
+    and shuffled, host buffers in several chunks and device buffers, leading-N and short sequences, onto a table that already
+    holds other bits (the interleave ORs)."""
+    import torch
+    from bench_support import synth
+    from dream_yara_b200._lib import BUILD_SLICED, check
+    glen = 9_000
+    genomes = synth.genomes(bins, glen)
+    genomes[min(5, bins - 1), :40] = 4
+    rng = np.random.default_rng(bins)
+    seqs, ids = [], []
+    for b in range(bins):
+        cut = int(rng.integers(1, glen - 1))
+        seqs += [genomes[b, :cut], genomes[b, cut:]]; ids += [b, b]
+        if b % 17 == 0:
+            seqs.append(genomes[b, :k - 1]); ids.append(b)              # shorter than k: adds nothing
+    p = oracle.params(bins, h, k, nbits)
+    words = oracle.new_words(p)
+    pre = rng.integers(0, 4, 5000).astype(np.uint8)
+    oracle.add_kmers(words, p, pre, bins - 1)
+    for s_, b in zip(seqs, ids):
+        oracle.add_kmers(words, p, s_, b)
+    nd = p.P * p.W
+    order = rng.permutation(len(seqs))
+    for variant in ("host", "host_chunks_shuffled", "device"):
+        f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+        f.addSequences([pre], [bins - 1])                              # pre-existing content
+        f.set_build_mode(BUILD_SLICED)
+        f.profile_enable(True)
+        if variant == "host":
+            f.addSequences(seqs, ids)
+        elif variant == "host_chunks_shuffled":
+            f.set_build_chunk_mib(1)
+            f.addSequences([seqs[i] for i in order], [ids[i] for i in order])
+        else:
+            cat, off, enc = dy.as_batch(seqs)
+            d_seq = torch.from_numpy(cat).cuda(); d_off = torch.from_numpy(off.view(np.int64)).cuda()
+            d_ids = torch.from_numpy(np.asarray(ids, dtype=np.int32)).cuda()
+            check(dy.lib().dyibf_add_sequences(f._h, d_seq.data_ptr(), d_off.data_ptr(), len(seqs), d_ids.data_ptr(), enc, 1, None))
+            torch.cuda.synchronize()
+        assert f.last_build_mode() == BUILD_SLICED, variant
+        got = f.download_words()[:nd]
+        prof = f.profile()
+        assert np.array_equal(got, words[:nd]), (variant, int((got != words[:nd]).sum()))
+        assert prof["build_apply_launches"] >= (p.W + 3) // 4, variant   # one interleave per column group at least
+        assert f.device_errors() == 0
+        f.close()
+
+
+def test_sliced_build_auto_choice(dy):
+    """auto mode: bin-clustered batches of >= 32 M updates into a table larger than the L2 take the sliced build; the same
+    bases cut into 1 kbp pieces of alternating bins do not (their bins' vectors would not fit the L2 together)"""
+    from bench_support import synth
+    from dream_yara_b200._lib import BUILD_BUCKETED, BUILD_SLICED
+    bins, h, k, nbits = 64, 3, 18, (1 << 33) + 256
+    glen = 4_000_000                                                # runs of 4 Mbp: a few 16 MiB vectors in flight
+    # no N: a piece that STARTS with N hashes its first k-mer differently (raw first character, shape_base.h:479-494), so the
+    # subset property below would not hold
+    genomes = np.minimum(synth.genomes(bins, glen), 3)
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addSequences((genomes.reshape(-1), np.arange(bins + 1, dtype=np.uint64) * glen), np.arange(bins, dtype=np.uint32))
+    assert f.last_build_mode() == BUILD_SLICED
+    a = f.download_words()
+    g = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    pieces = genomes.reshape(bins, glen // 1000, 1000).transpose(1, 0, 2).reshape(-1, 1000)      # piece j of every bin, then j + 1
+    g.addSequences((pieces.reshape(-1), np.arange(pieces.shape[0] + 1, dtype=np.uint64) * 1000),
+                   np.tile(np.arange(bins, dtype=np.uint32), glen // 1000))
+    assert g.last_build_mode() == BUILD_BUCKETED
+    # the pieces lose the k-mers that span a cut: g's bits are a subset of a's
+    b = g.download_words()
+    assert np.array_equal(a | b, a) and not np.array_equal(a, b)
+    f.close(); g.close()
+
+
 def test_bucketed_build_wide_records_equals_direct(dy):
     """Tables above 16 GiB have regions of more than 2^21 words, so the level-1 records of the two-level split are 64 bit
     wide.  32 GiB table, GPU against GPU: the bucketed build must leave exactly the words the direct atomic kernel (pinned

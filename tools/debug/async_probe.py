@@ -45,8 +45,7 @@ def run(srcs, off, depth, calls=200):
     dt = time.perf_counter() - t0
     return rb * calls / dt / 1e6, dt / calls * 1e3, tb / calls * 1e3, te / calls * 1e3
 
-mode = os.environ.get("DYIBF_STAGE_MODE", "1")
-cases = (("pinned", pinned, offs_p), ("pageable", pageable, offs)) if mode != "3" else (("pinned, staged copy unused", pinned, offs_p),)
+cases = (("pinned", pinned, offs_p), ("pageable", pageable, offs))
 for name, srcs, off in cases:
     for depth in (1, 3):
         run(srcs, off, depth, 40)
@@ -55,11 +54,18 @@ for name, srcs, off in cases:
         p = f.profile(reset=True); f.profile_enable(False)
         print("%-26s depth %d: %.1f M reads/s, %.3f ms/call (begin %.3f, end %.3f)" % ((name, depth) + r),
               "kernels ms/launch: pack %.3f query %.3f compact(3 scopes) %.3f" % (p["pack_ms"] / p["pack_launches"], p["query_ms"] / p["query_launches"], 2 * p["compact_ms"] / p["compact_launches"]))
-# large batch for reference
-big = hr.reshape(-1); offb = np.arange(rb * nb + 1, dtype=np.uint64) * RL
-bo2 = np.zeros(bins + 1, dtype=np.uint64); ids2 = np.zeros(4 * rb * nb, dtype=np.uint32)
-for _ in range(2):
+# synchronous dyibf_classify per 100 000-read batch, and one call over all reads
+for name, srcs, off in cases:
     t0 = time.perf_counter()
-    check(L.dyibf_classify(f._h, vp(big), vp(offb), rb * nb, ENC_DNA5, 2, 1, thr, vp(bo2), vp(ids2), ids2.size, C.byref(tot)))
+    for i in range(100):
+        check(L.dyibf_classify(f._h, vp(srcs[i % nb]), vp(off), rb, ENC_DNA5, 2, 1, thr, vp(bo), vp(ids), cap, C.byref(tot)))
     dt = time.perf_counter() - t0
-print("one synchronous call of %d reads: %.1f M reads/s" % (rb * nb, rb * nb / dt / 1e6))
+    print("%-10s synchronous dyibf_classify per batch: %.1f M reads/s" % (name, rb * 100 / dt / 1e6))
+offb = np.arange(rb * nb + 1, dtype=np.uint64) * RL
+bo2 = np.zeros(bins + 1, dtype=np.uint64); ids2 = np.zeros(4 * rb * nb, dtype=np.uint32)
+for name, big in (("pinned", hr.reshape(-1)), ("pageable", reads.reshape(-1))):
+    for _ in range(2):
+        t0 = time.perf_counter()
+        check(L.dyibf_classify(f._h, vp(big), vp(offb), rb * nb, ENC_DNA5, 2, 1, thr, vp(bo2), vp(ids2), ids2.size, C.byref(tot)))
+        dt = time.perf_counter() - t0
+    print("%-10s one synchronous call of %d reads: %.1f M reads/s" % (name, rb * nb, rb * nb / dt / 1e6))
