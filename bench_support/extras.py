@@ -136,15 +136,19 @@ def filter_io(ctx):
         d2h = 3 * n_h2d / (e0.elapsed_time(e1) / 1e3) / 1e9
         del hp, dp
         st = IoStats()
+        ncpu = os.cpu_count() or 8
+        io_threads = max(4, min(16, ncpu))
+        check(L.dyibf_set_io_threads(io_threads))
         t0 = time.perf_counter()
         check(L.dyibf_save_file(f._h, path.encode()))
         t_save = time.perf_counter() - t0
         check(L.dyibf_last_io_stats(C.byref(st)))
-        out.update({"save_s": t_save, "save_gbs": size / t_save / 1e9, "save_file_s": st.file_seconds, "threads": st.threads,
-                    "h2d_pinned_gbs": h2d, "d2h_pinned_gbs": d2h})
-        loads = {}
-        for threads in (1, 4, 8):
+        out.update({"save_s": t_save, "save_gbs": size / t_save / 1e9, "save_pwrite_s": st.file_seconds, "save_threads": st.threads,
+                    "host_cores": ncpu, "h2d_pinned_gbs": h2d, "d2h_pinned_gbs": d2h})
+
+        def load(threads, chunk_mib):
             check(L.dyibf_set_io_threads(threads))
+            check(L.dyibf_set_io_chunk_mib(chunk_mib))
             h = C.c_void_p()
             t0 = time.perf_counter()
             check(L.dyibf_load_file(path.encode(), ctx.local, C.byref(h)))
@@ -156,15 +160,21 @@ def filter_io(ctx):
             L.dyibf_destroy(h)
             if not same:
                 raise AssertionError("filter words after save + load differ from the table in HBM")
-            loads[str(threads)] = {"load_s": t_load, "load_gbs": size / t_load / 1e9, "transfer_s": st.seconds,
-                                   "pread_s": st.file_seconds, "copy_wait_s": st.copy_wait_seconds}
-        check(L.dyibf_set_io_threads(4))
-        best = max(loads.values(), key=lambda d: d["load_gbs"])
-        out.update({"load_by_threads": loads, "load_gbs": best["load_gbs"], "load_s": best["load_s"],
+            return {"threads": st.threads, "chunk_mib": st.chunk_bytes >> 20, "load_s": t_load, "load_gbs": size / t_load / 1e9,
+                    "transfer_s": st.seconds, "pread_s_max_thread": st.file_seconds, "copy_wait_s": st.copy_wait_seconds,
+                    "submit_s": st.submit_seconds, "starved_s": st.starve_seconds, "pinned_pool_alloc_s": st.pool_seconds}
+
+        loads = [load(t, 8) for t in sorted({1, 4, 8, io_threads})]
+        loads += [load(io_threads, c) for c in (4, 16)]
+        check(L.dyibf_set_io_threads(8)); check(L.dyibf_set_io_chunk_mib(0))
+        best = max(loads, key=lambda d: d["load_gbs"])
+        out.update({"loads": loads, "load_gbs": best["load_gbs"], "load_s": best["load_s"], "load_threads": best["threads"],
+                    "load_chunk_mib": best["chunk_mib"],
                     "frac_of_h2d": best["load_gbs"] / h2d, "words_equal_after_roundtrip": True,
-                    "note": "dyibf_save_file then dyibf_load_file of the %d GiB cfg2 filter (file -> pinned staging -> HBM, N reader "
-                            "threads); load_s includes cudaMalloc of the table; h2d_pinned_gbs = this box's measured pinned "
-                            "host->HBM rate" % (size >> 30)})
+                    "note": "dyibf_save_file then dyibf_load_file of the %d GiB cfg2 filter (file -> ring of pinned chunks filled by N "
+                            "pread threads -> one thread issuing the copies -> HBM); load_s includes cudaMalloc + zero fill of the "
+                            "table; h2d_pinned_gbs = this box's measured pinned host->HBM rate; starved_s = time the copy thread "
+                            "waited for the pread threads (page cache -> pinned memcpy rate of the host)" % (size >> 30)})
     finally:
         try:
             os.unlink(path)

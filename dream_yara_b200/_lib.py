@@ -39,7 +39,9 @@ class Profile(C.Structure):
 
 class IoStats(C.Structure):
     _fields_ = [("bytes", C.c_uint64), ("seconds", C.c_double), ("file_seconds", C.c_double),
-                ("copy_wait_seconds", C.c_double), ("threads", C.c_int), ("devices", C.c_int)]
+                ("copy_wait_seconds", C.c_double), ("threads", C.c_int), ("devices", C.c_int),
+                ("submit_seconds", C.c_double), ("starve_seconds", C.c_double), ("pool_seconds", C.c_double),
+                ("chunk_bytes", C.c_uint64)]
 
 
 # every symbol include/dyibf.h declares: name -> (restype, argtypes)
@@ -84,6 +86,7 @@ SYMBOLS = {
     "dyibf_launch_count": (C.c_uint64, [_P]),
     "dyibf_device_errors": (C.c_int, [_P, C.POINTER(C.c_uint32), C.c_int]),
     "dyibf_set_io_threads": (C.c_int, [C.c_int]),
+    "dyibf_set_io_chunk_mib": (C.c_int, [C.c_int]),
     "dyibf_last_io_stats": (C.c_int, [C.POINTER(IoStats)]),
     "dyibf_classify_begin": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(_P)]),
     "dyibf_classify_poll": (C.c_int, [_P, C.POINTER(C.c_int)]),

@@ -116,14 +116,22 @@ int ensure_stage(dyibf_filter* f)
 
 void drain_profile(dyibf_filter* f)
 {
+    // debugging aid: DYIBF_TRACE=<file> appends one line per profiled scope — kind, stream, start and end in ms since
+    // profiling was switched on — i.e. a timeline of the handle's kernels across its streams
+    static const char* trace_path = getenv("DYIBF_TRACE");
+    FILE* tr = (trace_path && f->trace_base && !f->pending.empty()) ? fopen(trace_path, "a") : nullptr;
     for (auto& p : f->pending) {
         float ms = 0.f;
         if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
             f->ms[p.kind] += ms; f->launches[p.kind] += 1;
+            float t0 = 0.f;
+            if (tr && cudaEventElapsedTime(&t0, f->trace_base, p.a) == cudaSuccess)
+                fprintf(tr, "%d %p %.4f %.4f\n", p.kind, (void*)p.st, t0, t0 + ms);
         }
         f->ev_pool.push_back(p.a); f->ev_pool.push_back(p.b);
     }
     f->pending.clear();
+    if (tr) fclose(tr);
 }
 
 // trailer + gap words for download/save: word index `w` of the sdsl array, w >= data_words
@@ -172,6 +180,7 @@ void dyibf_destroy(dyibf_filter* f)
     cudaDeviceSynchronize();
     drain_profile(f);
     for (auto e : f->ev_pool) cudaEventDestroy(e);
+    if (f->trace_base) cudaEventDestroy(f->trace_base);
     for (int i = 0; i < 2; ++i) {
         Slot& s = f->slot[i];
         s.in_bytes.release(); s.in_offsets.release(); s.packed.release(); s.meta.release(); s.rows.release(); s.counts.release(); s.ctr.release();
@@ -1378,6 +1387,12 @@ int dyibf_profile_enable(dyibf_filter* f, int on)
         CU(f->stats.reserve(64));
         CU(cudaMemset(f->stats.p, 0, 64));
         CU(cudaDeviceSynchronize());
+    }
+    if (on && getenv("DYIBF_TRACE")) {                                // timeline origin (see drain_profile)
+        if (!f->trace_base) CU(cudaEventCreate(&f->trace_base));
+        CU(cudaDeviceSynchronize());
+        CU(cudaEventRecord(f->trace_base, 0));
+        CU(cudaEventSynchronize(f->trace_base));
     }
     f->profiling = on != 0;
     return DYIBF_OK;

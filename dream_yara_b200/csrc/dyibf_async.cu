@@ -128,8 +128,11 @@ int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* o
             src_bytes = static_cast<const uint8_t*>(t->h_in);
             src_off = reinterpret_cast<const uint64_t*>(static_cast<char*>(t->h_in) + b_pad);
         }
-        if (total_bytes) CU(cudaMemcpyAsync(t->bytes.p, src_bytes, total_bytes, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(t->offsets.p, src_off, off_bytes, cudaMemcpyHostToDevice, st));
+        {
+            Scope sc(f, st, K_COPY, 0);
+            if (total_bytes) CU(cudaMemcpyAsync(t->bytes.p, src_bytes, total_bytes, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(t->offsets.p, src_off, off_bytes, cudaMemcpyHostToDevice, st));
+        }
         // the batch as the pack kernel sees it: group_in ranges of n_rows sequences each, laid out as the caller's buffer
         PackSource src; memset(&src, 0, sizeof src);
         src.n_ranges = group_in; src.cnt = n_rows;

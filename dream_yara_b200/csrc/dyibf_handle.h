@@ -45,9 +45,9 @@ struct Slot {                     // one stage of the host-mode pipeline
     DevBuf in_bytes, in_offsets, packed, meta, rows, counts, ctr;
 };
 
-enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_APPLY, K_SPLIT2, K_N };
+enum Kind { K_PACK = 0, K_QUERY, K_COMPACT, K_BUILD, K_CLEAR, K_APPLY, K_SPLIT2, K_COPY /* trace only */, K_N };
 
-struct Pending { cudaEvent_t a, b; int kind; };
+struct Pending { cudaEvent_t a, b; int kind; cudaStream_t st; };
 
 struct ResidentBatch { bool valid = false; uint32_t n_fwd = 0, group = 0, encoding = 0; uint64_t first_off = 0; };
 
@@ -81,6 +81,7 @@ struct dyibf_filter {
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
     bool         profiling = false;
+    cudaEvent_t  trace_base = nullptr;    // DYIBF_TRACE=<file>: per-scope start / end times relative to this event
     std::vector<dyibf::Pending> pending;
     std::vector<cudaEvent_t> ev_pool;
     double       ms[dyibf::K_N] = {0, 0, 0, 0, 0, 0, 0};
@@ -108,7 +109,7 @@ struct Scope {
         f->kernel_launches += n_kernels;
         if (f->profiling) { a = get(f); b = get(f); cudaEventRecord(a, st); }
     }
-    ~Scope() { if (a) { cudaEventRecord(b, st); f->pending.push_back({a, b, kind}); } }
+    ~Scope() { if (a) { cudaEventRecord(b, st); f->pending.push_back({a, b, kind, st}); } }
 };
 
 void drain_profile(dyibf_filter* f);

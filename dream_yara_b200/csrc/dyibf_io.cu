@@ -10,16 +10,16 @@
 // In HBM only the P*W data words are kept; the (all-zero) gap before the trailer and the trailer itself are
 // synthesised when the filter is downloaded or saved, so a saved file is byte-identical to the reference's.
 //
-// Pipeline: T reader threads (default 8); thread t owns chunks t, t+T, ... (8 MiB each) of the data words, two pinned buffers
-// (from a pool that is allocated once per process) and one
-// stream per target device.  pread -> cudaMemcpyAsync(H2D) -> (replicas: cudaMemcpyPeerAsync device 0 -> the others over
-// NVLink, on the same stream) so that file reads, PCIe and NVLink all overlap.  A bin shard (device r of G owns word
-// columns [r W/G, (r+1) W/G) of every block) is a pitched copy out of the same pinned chunk.  Saving runs the pipeline
-// backwards with pwrite.
+// Pipeline: T file threads (default 8) pread chunks (8 MiB) of the data words into a ring of 2 T pinned buffers (allocated
+// once per process); ONE thread issues the copies in file order: cudaMemcpyAsync(H2D) -> (replicas: cudaMemcpyPeerAsync
+// device 0 -> the others over NVLink, on the same stream), so that file reads, PCIe and NVLink all overlap.  A bin shard
+// (device r of G owns word columns [r W/G, (r+1) W/G) of every block) is a pitched copy out of the same pinned chunk.
+// Saving runs the pipeline backwards: the one thread issues the downloads, the file threads wait for a chunk's event and pwrite it.
 #include "dyibf_handle.h"
 
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <thread>
 
 #include <fcntl.h>
@@ -57,7 +57,7 @@ struct StagePool {
 };
 static StagePool g_stage;
 static std::mutex g_io_mutex;     // one transfer at a time uses the pool
-static thread_local dyibf_io_stats g_last_io = {0, 0.0, 0.0, 0.0, 0, 0};
+static thread_local dyibf_io_stats g_last_io = {0, 0.0, 0.0, 0.0, 0, 0, 0.0, 0.0, 0.0, 0};
 
 static double now_s()
 {
@@ -95,12 +95,52 @@ int read_file_header(FILE* fp, const char* path, FileHeader* fh)
 // contiguously (Wr words per block) at d_words on `device`.  Wr == W: the whole table.
 struct IoTarget { int device; uint64_t* d_words; uint32_t col0, Wr; };
 
-struct IoResult { int rc = DYIBF_OK; std::string err; double file_s = 0, wait_s = 0; };
+struct IoResult { int rc = DYIBF_OK; std::string err; double file_s = 0; };
 
 // blocks per chunk so that a chunk is about `want` bytes and holds whole blocks
 static uint64_t blocks_per_chunk(uint32_t W, uint64_t want) { return std::max<uint64_t>(1, want / ((uint64_t)W * 8)); }
 
-static const uint64_t IO_CHUNK_BYTES = 8ull << 20;
+static std::atomic<int> g_io_chunk_mib{0};          // 0 = not set: DYIBF_IO_CHUNK_MIB from the environment, else 8
+static uint64_t io_chunk_bytes()
+{
+    int mib = g_io_chunk_mib.load();
+    if (mib <= 0) {
+        const char* e = getenv("DYIBF_IO_CHUNK_MIB");
+        mib = e ? atoi(e) : 0;
+        if (mib < 1 || mib > 1024) mib = 8;
+    }
+    return (uint64_t)mib << 20;
+}
+
+// The ring of pinned chunks between the file threads and the one thread that talks to CUDA.  Slot c % N serves chunk c:
+//   load:  a reader waits until the slot is free for chunk c, preads into it, marks it filled; the submitter (the calling
+//          thread) takes the chunks in order, issues the copies, and frees the slot again for chunk c + N once the copies
+//          of chunk c have finished;
+//   save:  the submitter issues the download of chunk c into the slot and marks it filled; a writer waits for the copy's
+//          event, pwrites and frees the slot.
+// One submitting thread, because copies issued from many threads at once serialise inside the driver (measured: 8 threads
+// each spent 2.7 ms per 8 MiB chunk inside cudaMemcpyAsync / cudaEventRecord, the copy engine idle most of the time).
+struct ChunkRing {
+    std::mutex m;
+    std::condition_variable cv;
+    std::vector<int64_t> filled;     // filled[slot] == c + 1: chunk c is in the slot (load: read; save: download issued)
+    std::vector<int64_t> free_for;   // the slot may be used for chunk free_for[slot]
+    bool abort = false;
+    explicit ChunkRing(int n) : filled(n, 0), free_for(n) { for (int i = 0; i < n; ++i) free_for[i] = i; }
+    bool wait_free(int slot, int64_t c) {
+        std::unique_lock<std::mutex> l(m);
+        cv.wait(l, [&] { return abort || free_for[slot] == c; });
+        return !abort;
+    }
+    bool wait_filled(int slot, int64_t c) {
+        std::unique_lock<std::mutex> l(m);
+        cv.wait(l, [&] { return abort || filled[slot] == c + 1; });
+        return !abort;
+    }
+    void set_filled(int slot, int64_t c) { { std::lock_guard<std::mutex> l(m); filled[slot] = c + 1; } cv.notify_all(); }
+    void set_free(int slot, int64_t next_chunk) { { std::lock_guard<std::mutex> l(m); free_for[slot] = next_chunk; } cv.notify_all(); }
+    void stop() { { std::lock_guard<std::mutex> l(m); abort = true; } cv.notify_all(); }
+};
 
 // file bytes [8, 8 + n_blocks * W * 8) <-> the targets.  to_device: load; otherwise save (exactly one whole-table target
 // per column range: every word of the file is written once).
@@ -110,124 +150,158 @@ static int stream_words(int fd, const char* path, char* host, bool to_device, ui
 {
     std::lock_guard<std::mutex> io_lock(g_io_mutex);
     const double t_begin = now_s();
-    const uint64_t bpc = blocks_per_chunk(W, IO_CHUNK_BYTES);
-    const uint64_t n_chunks = (n_blocks + bpc - 1) / bpc;
+    const uint64_t chunk_bytes = io_chunk_bytes();
+    const uint64_t bpc = blocks_per_chunk(W, chunk_bytes);
+    const int64_t n_chunks = (int64_t)((n_blocks + bpc - 1) / bpc);
     int T = g_io_threads.load();
     if (T < 1) T = 1;
-    if ((uint64_t)T > n_chunks) T = (int)std::max<uint64_t>(n_chunks, 1);
-    std::vector<IoResult> res(T);
+    if ((int64_t)T > n_chunks) T = (int)std::max<int64_t>(n_chunks, 1);
+    const int N = 2 * T;                                              // slots: T being read or written, T in the copy queue
     const size_t buf_bytes = (size_t)(bpc * W * 8);
     std::vector<void*> pool;
-    if (g_stage.get(T, std::max<size_t>(buf_bytes, (size_t)IO_CHUNK_BYTES), &pool) != DYIBF_OK) return fail(DYIBF_ERR_NOMEM, "filter I/O: pinned staging allocation failed");
-    auto worker = [&](int t) {
+    if (g_stage.get(T, std::max<size_t>(buf_bytes, (size_t)chunk_bytes), &pool) != DYIBF_OK) return fail(DYIBF_ERR_NOMEM, "filter I/O: pinned staging allocation failed");
+    const double t_pool = now_s();
+    const size_t nt = targets.size();
+    // replicas: one stream on the first device drives the H2D and the peer copies; shards: one stream per device
+    const size_t n_streams = replicas ? 1 : nt;
+    std::vector<cudaStream_t> st(n_streams, nullptr);
+    std::vector<cudaEvent_t> ev((size_t)N * n_streams, nullptr);       // ev[slot * n_streams + i]: the copies of the slot's chunk on stream i
+    int prev = -1; cudaGetDevice(&prev);
+    IoResult sub;                                                     // the submitter's own result
+    auto bad = [](IoResult& r, int code, const std::string& what) { if (!r.rc) { r.rc = code; r.err = what; } };
+    for (size_t i = 0; i < n_streams && !sub.rc; ++i) {
+        if (cudaSetDevice(targets[i].device) != cudaSuccess || cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking) != cudaSuccess)
+            bad(sub, DYIBF_ERR_CUDA, "filter I/O: stream creation failed");
+        for (int s = 0; s < N && !sub.rc; ++s)
+            if (cudaEventCreateWithFlags(&ev[(size_t)s * n_streams + i], cudaEventDisableTiming) != cudaSuccess)
+                bad(sub, DYIBF_ERR_CUDA, "filter I/O: event creation failed");
+    }
+    ChunkRing ring(N);
+    std::atomic<int64_t> next{0};
+    std::vector<IoResult> res(T);
+    auto chunk_geom = [&](int64_t c, uint64_t* blk0, uint64_t* nb) { *blk0 = (uint64_t)c * bpc; *nb = std::min(bpc, n_blocks - *blk0); };
+
+    // ---- file side: T threads ----
+    auto file_worker = [&](int t) {
         IoResult& r = res[t];
-        auto bad = [&](int code, const std::string& what) { if (!r.rc) { r.rc = code; r.err = what; } };
-        const size_t nt = targets.size();
-        void* buf[2] = {pool[2 * t], pool[2 * t + 1]};
-        std::vector<cudaStream_t> st(nt, nullptr);
-        std::vector<cudaEvent_t> ev(2 * nt, nullptr);                // ev[b * nt + i]: buffer b is free again for target i
-        // replicas: one stream on the first device drives the H2D and the peer copies; shards: one stream per device
-        const size_t n_streams = replicas ? 1 : nt;
-        for (size_t i = 0; i < n_streams && !r.rc; ++i) {
-            if (cudaSetDevice(targets[i].device) != cudaSuccess ||
-                cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking) != cudaSuccess ||
-                cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess ||
-                cudaEventCreateWithFlags(&ev[nt + i], cudaEventDisableTiming) != cudaSuccess)
-                bad(DYIBF_ERR_CUDA, "filter I/O: stream / event creation failed");
-        }
-        int cur = 0;
-        for (uint64_t c = (uint64_t)t; c < n_chunks && !r.rc; c += (uint64_t)T, cur ^= 1) {
-            const uint64_t blk0 = c * bpc, nb = std::min(bpc, n_blocks - blk0);
+        for (;;) {
+            const int64_t c = next.fetch_add(1);
+            if (c >= n_chunks) break;
+            const int slot = (int)(c % N);
+            uint64_t blk0, nb; chunk_geom(c, &blk0, &nb);
             const size_t bytes = (size_t)(nb * W * 8);
             const off_t file_off = (off_t)(8 + blk0 * W * 8);
-            double t0 = now_s();
-            for (size_t i = 0; i < n_streams; ++i) cudaEventSynchronize(ev[cur * nt + i]);       // buffer free again
-            r.wait_s += now_s() - t0;
+            char* buf = static_cast<char*>(pool[slot]);
             if (to_device) {
-                t0 = now_s();
+                if (!ring.wait_free(slot, c)) break;
+                const double t0 = now_s();
                 size_t got = 0;
-                if (fd < 0) { memcpy(buf[cur], host + blk0 * W * 8, bytes); got = bytes; }
+                if (fd < 0) { memcpy(buf, host + blk0 * W * 8, bytes); got = bytes; }
                 while (got < bytes) {
-                    ssize_t n = pread(fd, (char*)buf[cur] + got, bytes - got, file_off + (off_t)got);
-                    if (n <= 0) { bad(DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be read."); break; }
+                    ssize_t n = pread(fd, buf + got, bytes - got, file_off + (off_t)got);
+                    if (n <= 0) { bad(r, DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be read."); break; }
                     got += (size_t)n;
                 }
                 r.file_s += now_s() - t0;
-                if (r.rc) break;
-                cudaError_t e = cudaSuccess;
-                if (replicas) {
-                    const IoTarget& a = targets[0];
-                    e = cudaSetDevice(a.device);
-                    char* dst0 = (char*)a.d_words + blk0 * W * 8;
-                    if (e == cudaSuccess) e = cudaMemcpyAsync(dst0, buf[cur], bytes, cudaMemcpyHostToDevice, st[0]);
-                    if (e == cudaSuccess) e = cudaEventRecord(ev[cur * nt], st[0]);
-                    for (size_t i = 1; i < nt && e == cudaSuccess; ++i)                     // NVLink fan-out of the chunk
-                        e = cudaMemcpyPeerAsync((char*)targets[i].d_words + blk0 * W * 8, targets[i].device, dst0, a.device, bytes, st[0]);
-                } else {
-                    for (size_t i = 0; i < nt && e == cudaSuccess; ++i) {
-                        const IoTarget& a = targets[i];
-                        e = cudaSetDevice(a.device);
-                        if (e != cudaSuccess) break;
-                        if (a.Wr == W)
-                            e = cudaMemcpyAsync((char*)a.d_words + blk0 * W * 8, buf[cur], bytes, cudaMemcpyHostToDevice, st[i]);
-                        else
-                            e = cudaMemcpy2DAsync((char*)a.d_words + blk0 * a.Wr * 8, (size_t)a.Wr * 8, (char*)buf[cur] + (size_t)a.col0 * 8,
-                                                  (size_t)W * 8, (size_t)a.Wr * 8, (size_t)nb, cudaMemcpyHostToDevice, st[i]);
-                        if (e == cudaSuccess) e = cudaEventRecord(ev[cur * nt + i], st[i]);
-                    }
-                }
-                if (e != cudaSuccess) bad(DYIBF_ERR_CUDA, std::string("filter upload: ") + cudaGetErrorString(e));
+                if (r.rc) { ring.stop(); break; }
+                ring.set_filled(slot, c);
             } else {
-                cudaError_t e = cudaSuccess;
-                for (size_t i = 0; i < nt && e == cudaSuccess; ++i) {
-                    const IoTarget& a = targets[i];
-                    e = cudaSetDevice(a.device);
-                    if (e != cudaSuccess) break;
-                    if (a.Wr == W)
-                        e = cudaMemcpyAsync(buf[cur], (char*)a.d_words + blk0 * W * 8, bytes, cudaMemcpyDeviceToHost, st[i]);
-                    else
-                        e = cudaMemcpy2DAsync((char*)buf[cur] + (size_t)a.col0 * 8, (size_t)W * 8, (char*)a.d_words + blk0 * a.Wr * 8,
-                                              (size_t)a.Wr * 8, (size_t)a.Wr * 8, (size_t)nb, cudaMemcpyDeviceToHost, st[i]);
-                    if (e == cudaSuccess) e = cudaEventRecord(ev[cur * nt + i], st[i]);
-                }
-                if (e != cudaSuccess) { bad(DYIBF_ERR_CUDA, std::string("filter download: ") + cudaGetErrorString(e)); break; }
-                // the previous chunk of this thread is written while this one downloads
-                t0 = now_s();
-                for (size_t i = 0; i < n_streams; ++i) cudaEventSynchronize(ev[cur * nt + i]);
-                r.wait_s += now_s() - t0;
-                t0 = now_s();
+                if (!ring.wait_filled(slot, c)) break;
+                for (size_t i = 0; i < n_streams; ++i)
+                    if (cudaEventSynchronize(ev[(size_t)slot * n_streams + i]) != cudaSuccess) bad(r, DYIBF_ERR_CUDA, "filter download: copy failed");
+                const double t0 = now_s();
                 size_t put = 0;
-                if (fd < 0) { memcpy(host + blk0 * W * 8, buf[cur], bytes); put = bytes; }
-                while (put < bytes) {
-                    ssize_t n = pwrite(fd, (char*)buf[cur] + put, bytes - put, file_off + (off_t)put);
-                    if (n <= 0) { bad(DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be written."); break; }
+                if (fd < 0) { memcpy(host + blk0 * W * 8, buf, bytes); put = bytes; }
+                while (put < bytes && !r.rc) {
+                    ssize_t n = pwrite(fd, buf + put, bytes - put, file_off + (off_t)put);
+                    if (n <= 0) { bad(r, DYIBF_ERR_IO, std::string("File \"") + path + "\" could not be written."); break; }
                     put += (size_t)n;
                 }
                 r.file_s += now_s() - t0;
+                if (r.rc) { ring.stop(); break; }
+                ring.set_free(slot, c + N);
             }
         }
-        for (size_t i = 0; i < n_streams; ++i)
-            if (st[i]) {
-                cudaSetDevice(targets[i].device);
-                if (cudaStreamSynchronize(st[i]) != cudaSuccess) bad(DYIBF_ERR_CUDA, "filter I/O: copy failed");
-                cudaStreamDestroy(st[i]);
-            }
-        for (cudaEvent_t e : ev) if (e) cudaEventDestroy(e);
     };
-    int prev = -1; cudaGetDevice(&prev);
-    if (T == 1) worker(0);
-    else {
-        std::vector<std::thread> th;
-        for (int t = 0; t < T; ++t) th.emplace_back(worker, t);
-        for (auto& x : th) x.join();
+    std::vector<std::thread> th;
+    if (!sub.rc) for (int t = 0; t < T; ++t) th.emplace_back(file_worker, t);
+
+    // ---- CUDA side: this thread ----
+    double wait_s = 0, submit_s = 0, starve_s = 0;
+    auto copy_chunk = [&](int64_t c) -> cudaError_t {
+        const int slot = (int)(c % N);
+        uint64_t blk0, nb; chunk_geom(c, &blk0, &nb);
+        const size_t bytes = (size_t)(nb * W * 8);
+        char* buf = static_cast<char*>(pool[slot]);
+        cudaError_t e = cudaSuccess;
+        if (replicas) {
+            const IoTarget& a = targets[0];
+            e = cudaSetDevice(a.device);
+            char* dst0 = (char*)a.d_words + blk0 * W * 8;
+            if (e == cudaSuccess) e = cudaMemcpyAsync(dst0, buf, bytes, cudaMemcpyHostToDevice, st[0]);
+            for (size_t i = 1; i < nt && e == cudaSuccess; ++i)                         // NVLink fan-out of the chunk
+                e = cudaMemcpyPeerAsync((char*)targets[i].d_words + blk0 * W * 8, targets[i].device, dst0, a.device, bytes, st[0]);
+            // the slot is reusable once the H2D has read it, but the event also orders the end of the call: after the fan-out
+            if (e == cudaSuccess) e = cudaEventRecord(ev[(size_t)slot * n_streams], st[0]);
+            return e;
+        }
+        for (size_t i = 0; i < nt && e == cudaSuccess; ++i) {
+            const IoTarget& a = targets[i];
+            e = cudaSetDevice(a.device);
+            if (e != cudaSuccess) break;
+            const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+            char* dev_p = (char*)a.d_words + blk0 * a.Wr * 8;
+            if (a.Wr == W)
+                e = to_device ? cudaMemcpyAsync(dev_p, buf, bytes, kind, st[i]) : cudaMemcpyAsync(buf, dev_p, bytes, kind, st[i]);
+            else if (to_device)
+                e = cudaMemcpy2DAsync(dev_p, (size_t)a.Wr * 8, buf + (size_t)a.col0 * 8, (size_t)W * 8, (size_t)a.Wr * 8, (size_t)nb, kind, st[i]);
+            else
+                e = cudaMemcpy2DAsync(buf + (size_t)a.col0 * 8, (size_t)W * 8, dev_p, (size_t)a.Wr * 8, (size_t)a.Wr * 8, (size_t)nb, kind, st[i]);
+            if (e == cudaSuccess) e = cudaEventRecord(ev[(size_t)slot * n_streams + i], st[i]);
+        }
+        return e;
+    };
+    for (int64_t c = 0; c < n_chunks && !sub.rc; ++c) {
+        const int slot = (int)(c % N);
+        double t0 = now_s();
+        const bool go = to_device ? ring.wait_filled(slot, c) : ring.wait_free(slot, c);
+        starve_s += now_s() - t0;
+        if (!go) break;
+        t0 = now_s();
+        cudaError_t e = copy_chunk(c);
+        submit_s += now_s() - t0;
+        if (e != cudaSuccess) { bad(sub, DYIBF_ERR_CUDA, std::string(to_device ? "filter upload: " : "filter download: ") + cudaGetErrorString(e)); ring.stop(); break; }
+        if (!to_device) { ring.set_filled(slot, c); continue; }
+        // load: the slot of chunk c - T goes back to the readers once its copies are done
+        const int64_t done = c - T;
+        if (done >= 0) {
+            t0 = now_s();
+            for (size_t i = 0; i < n_streams; ++i) cudaEventSynchronize(ev[(size_t)(done % N) * n_streams + i]);
+            wait_s += now_s() - t0;
+            ring.set_free((int)(done % N), done + N);
+        }
     }
+    if (sub.rc) ring.stop();
+    for (auto& x : th) x.join();
+    double t0 = now_s();
+    for (size_t i = 0; i < n_streams; ++i)
+        if (st[i]) {
+            cudaSetDevice(targets[i].device);
+            if (cudaStreamSynchronize(st[i]) != cudaSuccess) bad(sub, DYIBF_ERR_CUDA, "filter I/O: copy failed");
+            cudaStreamDestroy(st[i]);
+        }
+    wait_s += now_s() - t0;
+    for (cudaEvent_t e : ev) if (e) cudaEventDestroy(e);
     if (prev >= 0) cudaSetDevice(prev);
-    double file_s = 0, wait_s = 0;
-    for (auto& r : res) { file_s = std::max(file_s, r.file_s); wait_s = std::max(wait_s, r.wait_s); }
+    double file_s = 0;
+    for (auto& r : res) file_s = std::max(file_s, r.file_s);
     if (stats) {
         stats->bytes = n_blocks * W * 8; stats->seconds = now_s() - t_begin; stats->file_seconds = file_s;
         stats->copy_wait_seconds = wait_s; stats->threads = T; stats->devices = (int)targets.size();
+        stats->submit_seconds = submit_s; stats->starve_seconds = starve_s; stats->pool_seconds = t_pool - t_begin;
+        stats->chunk_bytes = buf_bytes;
     }
+    if (sub.rc) return fail(sub.rc, "%s", sub.err.c_str());
     for (auto& r : res) if (r.rc) return fail(r.rc, "%s", r.err.c_str());
     return DYIBF_OK;
 }
@@ -345,6 +419,13 @@ int dyibf_set_io_threads(int n)
 {
     if (n < 1 || n > 64) return fail(DYIBF_ERR_ARG, "I/O threads must be 1..64");
     g_io_threads.store(n);
+    return DYIBF_OK;
+}
+
+int dyibf_set_io_chunk_mib(int mib)
+{
+    if (mib < 0 || mib > 1024) return fail(DYIBF_ERR_ARG, "I/O chunk size must be 0 (default) .. 1024 MiB");
+    g_io_chunk_mib.store(mib);
     return DYIBF_OK;
 }
 

@@ -117,7 +117,7 @@ int  dyibf_download_words(dyibf_filter* f, uint64_t* host_words, uint64_t first,
 int  dyibf_save_file(dyibf_filter* f, const char* path);
 
 /* The loader / writer behind dyibf_load_file* / dyibf_save_file (and their group forms) streams the file through pinned
- * host buffers with several threads (pread / pwrite + asynchronous copies); this is the stage the mapper prints as
+ * host buffers with several file threads (pread / pwrite) and one thread issuing the asynchronous copies; this is the stage the mapper prints as
  * "Filter loading time" (src/d_mapper.h:913-921); dyibf_upload_words / dyibf_download_words of whole blocks use the same
  * pipeline.  dyibf_set_io_threads: 1..64, default 8, process-wide.
  * dyibf_last_io_stats: the calling thread's last load or save. */
@@ -127,8 +127,13 @@ typedef struct dyibf_io_stats {
     double   file_seconds;        /* longest time any one thread spent inside pread / pwrite                */
     double   copy_wait_seconds;   /* longest time any one thread waited for its copies                      */
     int      threads, devices;
+    double   submit_seconds;      /* time the submitting thread spent inside the CUDA copy calls            */
+    double   starve_seconds;      /* time it waited for the file threads (load: data to copy; save: free buffers) */
+    double   pool_seconds;        /* pinned staging allocation (first transfer of the process only)          */
+    uint64_t chunk_bytes;         /* bytes per pinned chunk                                                  */
 } dyibf_io_stats;
 int  dyibf_set_io_threads(int n);
+int  dyibf_set_io_chunk_mib(int mib);   /* 1..1024, 0 = default (DYIBF_IO_CHUNK_MIB from the environment, else 8) */
 int  dyibf_last_io_stats(dyibf_io_stats* out);
 
 /* ---- build --------------------------------------------------------------------------------- */
