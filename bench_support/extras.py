@@ -43,7 +43,7 @@ def _lists_from_rows(rows, bins):
 # asynchronous drop-in batches: dyibf_classify_begin / _end at the reference's batch size (src/mapper.h:109), as a
 # prefetching caller (src/file_prefetched.h:137-205) feeds them
 # ---------------------------------------------------------------------------------------------------------------------
-def dropin_async(ctx, batches_pageable, batches_pinned, per_call, rb, group, depth=3):
+def dropin_async(ctx, batches_pageable, batches_pinned, per_call, rb, group, depth=4):
     L, f, bins = ctx.L, ctx.f, ctx.bins
     from dream_yara_b200._lib import ENC_DNA5, check
     offs_b = np.arange(per_call + 1, dtype=np.uint64) * ctx.RL
@@ -164,9 +164,9 @@ def filter_io(ctx):
                     "transfer_s": st.seconds, "pread_s_max_thread": st.file_seconds, "copy_wait_s": st.copy_wait_seconds,
                     "submit_s": st.submit_seconds, "starved_s": st.starve_seconds, "pinned_pool_alloc_s": st.pool_seconds}
 
-        loads = [load(t, 8) for t in sorted({1, 4, 8, io_threads})]
-        loads += [load(io_threads, c) for c in (4, 16)]
-        check(L.dyibf_set_io_threads(8)); check(L.dyibf_set_io_chunk_mib(0))
+        loads = [load(t, 4) for t in sorted({1, 4, 8, io_threads})]
+        loads += [load(io_threads, 8)]
+        check(L.dyibf_set_io_threads(0)); check(L.dyibf_set_io_chunk_mib(0))
         best = max(loads, key=lambda d: d["load_gbs"])
         out.update({"loads": loads, "load_gbs": best["load_gbs"], "load_s": best["load_s"], "load_threads": best["threads"],
                     "load_chunk_mib": best["chunk_mib"],

@@ -79,6 +79,8 @@ SYMBOLS = {
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int, _P]),
     "dyibf_classify_text": (C.c_int, [_P, _P, C.c_uint64, _P, C.c_uint64, C.c_int, C.c_int, _U64P, _U32P, C.c_uint64,
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "dyibf_classify_text_begin": (C.c_int, [_P, _P, C.c_uint64, _P, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint32),
+                                            C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]),
     "dyibf_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
     "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),

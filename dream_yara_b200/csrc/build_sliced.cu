@@ -9,19 +9,28 @@
 // one FASTA file per bin, d_build_filter.cpp:227-260), so at any moment the resident warps work on two or three bins and
 // their vectors stay in the L2 while they fill: the REDs are L2 hits, DRAM only sees each vector stream in and out once.
 //
-//   pass, for a group of up to 4 word columns (256 bins; shadow = 256 x P bits = 4 GiB at P = 2^27):
+//   pass, for a group of word columns (all W of them when the scratch fits: 16 GiB at 1024 bins / P = 2^27; else 4, 2 or 1):
 //     1. zero the shadow
-//     2. sliced_scatter_kernel: every k-mer of every sequence whose bin is in the group -> h REDs (32-bit OR) into
-//        shadow[bin - first][block / 32]
-//     3. sliced_interleave_kernel: 64 bins x 256 blocks tiles are transposed with 32 x 32 bit-matrix butterflies (shuffles)
-//        and OR-ed into the table, 4 columns = one full 32-byte sector per block and lane
+//     2. sliced_scatter_kernel: every k-mer of every sequence whose bin is in the group -> h REDs (32-bit OR) into the
+//        bin's bit vector
+//     3. sliced_interleave_kernel: 64 bins x 32 blocks bit matrices are transposed with 32 x 32 butterflies (shuffles),
+//        collected in shared memory and OR-ed into the table as whole rows of the group's columns
 //   and the next group.  Sequences may come in any order (a pass picks its own by bin); the speed-up needs them clustered
 //   by bin, which the host driver checks before it chooses this path over the bucketed one (build_bucket.cu).
 //
+// Shadow layout: [bin of the group][P / 32 words], every bin's vector contiguous (16 MiB at cfg2) and a whole number of
+// 128-byte lines.  The interleave takes tiles of 1024 blocks: one line from each bin's vector (rows 16 MiB apart, but whole
+// lines), transposed through shared memory into whole table rows.  (A tile-major layout — [tile][bin][32 words], everything
+// a tile needs contiguous — was tried and dropped: the scatter then spreads one bin's updates over the whole 16 GiB scratch
+// and ran four times slower, 258 instead of 66 ms per 4 Gbp, with an odd line stride as well: the REDs need the bin's
+// vector contiguous, i.e. few pages, not only few lines.  The first interleave read one 32-byte sector per bin and updated
+// 32 of the 128 bytes of every table row: ncu showed 26.9 GB of DRAM reads per 4-column pass where 8.6 GB were needed.)
+//
 // Against the bucketed build (two radix-split levels + apply: 58 + 49 + 69 ms per 4 Gbp step on a B200) the two split
 // levels disappear: what remains is one RED per update — the same L1TEX-bound rate as the bucketed build's apply — plus
-// ~50 GiB of streaming for the zero / interleave passes.
+// streaming passes for zero / interleave.
 #include "dyibf_internal.h"
+#include <cstdlib>
 #include "ibf_hash.cuh"
 
 namespace dyibf {
@@ -109,69 +118,102 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t x, uint32_t lane)
     return x;
 }
 
-// A warp handles one tile: `NC` word columns x 256 blocks (8 shadow words per bin).  Lane l first holds the 8 words of bins
-// c*64 + l and c*64 + 32 + l of column c (two 32-byte loads: full sectors); after the transposes lane j holds, for each of
-// the 8 sub-blocks w, the 64-bit table word of block q0*32 + w*32 + j in column c.  With NC = 4 a lane then owns 4 adjacent
-// words = one 32-byte sector of the table per block: one read, OR, one write.
-template <int NC>
-__global__ void __launch_bounds__(256) sliced_interleave_kernel(uint64_t* __restrict__ filter, const uint32_t* __restrict__ shadow,
-        uint64_t pw, uint64_t P, uint32_t W, uint32_t first_col, uint32_t n_cols, uint32_t group_bins)
+// A block handles one shadow tile (1024 blocks x the group's bins) in sub-tiles of SW * 32 blocks.  Warp w takes the word
+// columns w, w + 8, ...: lane l loads SW words (SW * 4 contiguous bytes) of bins c*64 + l and c*64 + 32 + l; after the
+// transposes lane j holds, for each of the SW words, the 64-bit table word of block (word * 32 + j) in column c, which goes to
+// shared memory [block][column].  The block then ORs the sub-tile into the table: SW * 32 consecutive rows of n_cols words —
+// whole 128-byte rows, coalesced, when the group spans all W columns.
+template <int SW>
+__global__ void __launch_bounds__(256, SW <= 8 ? 4 : 3) sliced_interleave_kernel(uint64_t* __restrict__ filter, const uint32_t* __restrict__ shadow,
+        uint64_t pw, uint64_t n_tiles, uint64_t P, uint32_t W, uint32_t first_col, uint32_t n_cols)
 {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint64_t n_tiles = (pw + 7) / 8;                          // tiles of 8 shadow words = 256 blocks
-    const uint64_t n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t tile = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; tile < n_tiles; tile += n_warps) {
-        const uint64_t q0 = tile * 8;
-        uint64_t out[NC][8];
-        bool any = false;
-        #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-            uint32_t lo[8], hi[8];
-            #pragma unroll
-            for (int w = 0; w < 8; ++w) { lo[w] = 0; hi[w] = 0; }
-            if ((uint32_t)c < n_cols) {
-                const uint32_t b_lo = c * 64 + lane, b_hi = b_lo + 32;
-                // pw is a multiple of 8, shadow rows are 32-byte aligned
-                if (b_lo < group_bins) {
-                    const uint4* p = reinterpret_cast<const uint4*>(shadow + (uint64_t)b_lo * pw + q0);
-                    const uint4 a = __ldcs(p), b = __ldcs(p + 1);
-                    lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; lo[3] = a.w; lo[4] = b.x; lo[5] = b.y; lo[6] = b.z; lo[7] = b.w;
-                }
-                if (b_hi < group_bins) {
-                    const uint4* p = reinterpret_cast<const uint4*>(shadow + (uint64_t)b_hi * pw + q0);
-                    const uint4 a = __ldcs(p), b = __ldcs(p + 1);
-                    hi[0] = a.x; hi[1] = a.y; hi[2] = a.z; hi[3] = a.w; hi[4] = b.x; hi[5] = b.y; hi[6] = b.z; hi[7] = b.w;
-                }
-            }
-            #pragma unroll
-            for (int w = 0; w < 8; ++w) {
-                // most tiles of a sparse pass are empty: skip the butterflies when nobody has a bit
-                const bool some = __any_sync(FULLW, (lo[w] | hi[w]) != 0);
-                uint64_t v = 0;
-                if (some) {
-                    v = (uint64_t)transpose32(lo[w], lane) | ((uint64_t)transpose32(hi[w], lane) << 32);
-                    any = true;
-                }
-                out[c][w] = v;
-            }
-        }
-        if (!any) continue;
-        #pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            const uint64_t blk = (q0 + w) * 32 + lane;
-            if (blk >= P) continue;
-            uint64_t* dst = filter + blk * W + first_col;
-            if (NC == 4 && ((W | first_col) & 3u) == 0) {           // one aligned 32-byte sector: two 16-byte accesses
-                if ((out[0][w] | out[1][w] | out[NC - 2][w] | out[NC - 1][w]) == 0) continue;
-                ulonglong2* d2 = reinterpret_cast<ulonglong2*>(dst);
-                ulonglong2 a = d2[0], b = d2[1];
-                a.x |= out[0][w]; a.y |= out[1][w]; b.x |= out[NC - 2][w]; b.y |= out[NC - 1][w];
-                d2[0] = a; d2[1] = b;
-            } else {
+    extern __shared__ uint64_t il_sm[];                              // [SW * 32 rows][stride]
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    const uint32_t stride = n_cols | 1u;                             // odd: the transposed stores of a warp spread over the banks
+    const uint32_t rows = SW * 32;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint32_t* base = shadow + tile * 32;                    // word 0 of the tile in bin 0's vector
+        for (uint32_t sub = 0; sub < 32 / SW; ++sub) {
+            bool any = false;
+            for (uint32_t c = warp; c < n_cols; c += n_warps) {
+                uint32_t lo[SW], hi[SW];
+                const uint4* plo = reinterpret_cast<const uint4*>(base + (uint64_t)(c * 64 + lane) * pw + sub * SW);
+                const uint4* phi = reinterpret_cast<const uint4*>(base + (uint64_t)(c * 64 + 32 + lane) * pw + sub * SW);
                 #pragma unroll
-                for (int c = 0; c < NC; ++c)
-                    if ((uint32_t)c < n_cols && out[c][w]) dst[c] |= out[c][w];
+                for (int q = 0; q < SW / 4; ++q) {
+                    const uint4 a = __ldcs(plo + q), b = __ldcs(phi + q);
+                    lo[4 * q] = a.x; lo[4 * q + 1] = a.y; lo[4 * q + 2] = a.z; lo[4 * q + 3] = a.w;
+                    hi[4 * q] = b.x; hi[4 * q + 1] = b.y; hi[4 * q + 2] = b.z; hi[4 * q + 3] = b.w;
+                }
+                #pragma unroll
+                for (int w = 0; w < SW; ++w) {
+                    // sparse passes: skip the butterflies when nobody has a bit
+                    const bool some = __any_sync(FULLW, (lo[w] | hi[w]) != 0);
+                    uint64_t v = 0;
+                    if (some) {
+                        v = (uint64_t)transpose32(lo[w], lane) | ((uint64_t)transpose32(hi[w], lane) << 32);
+                        any = true;
+                    }
+                    il_sm[(uint32_t)(w * 32 + lane) * stride + c] = v;
+                }
             }
+            const int nonzero = __syncthreads_or(any);
+            if (nonzero) {
+                const uint64_t blk0 = tile * 1024 + (uint64_t)sub * rows;
+                const uint32_t rows_here = blk0 >= P ? 0u : (uint32_t)(P - blk0 < rows ? P - blk0 : rows);
+                if (n_cols == W && (W & 1u) == 0) {
+                    // the group spans whole table rows: the sub-tile is rows_here * W consecutive words.  16 bytes per thread
+                    // and access, four accesses in flight per thread before the first store.
+                    ulonglong2* T = reinterpret_cast<ulonglong2*>(filter + blk0 * W);
+                    const uint32_t pairs = rows_here * (W >> 1), half = W >> 1;
+                    for (uint32_t i0 = threadIdx.x; i0 < pairs; i0 += 4 * blockDim.x) {
+                        ulonglong2 v[4], o[4];
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t i = i0 + j * blockDim.x;
+                            v[j] = make_ulonglong2(0, 0);
+                            if (i < pairs) {
+                                const uint32_t r = i / half, c = (i - r * half) << 1;
+                                v[j].x = il_sm[r * stride + c]; v[j].y = il_sm[r * stride + c + 1];
+                            }
+                        }
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (v[j].x | v[j].y) {
+                                const longlong2 t = __ldcs(reinterpret_cast<const longlong2*>(T + i0 + j * blockDim.x));
+                                o[j] = make_ulonglong2((unsigned long long)t.x, (unsigned long long)t.y);
+                            }
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (v[j].x | v[j].y)
+                                __stcs(reinterpret_cast<longlong2*>(T + i0 + j * blockDim.x),
+                                       make_longlong2((long long)(o[j].x | v[j].x), (long long)(o[j].y | v[j].y)));
+                    }
+                } else {
+                    // a narrower group: n_cols words of every row.  Batches of 4 words per thread, loads before stores.
+                    const uint32_t total = rows_here * n_cols;
+                    for (uint32_t i0 = threadIdx.x; i0 < total; i0 += 4 * blockDim.x) {
+                        uint64_t v[4], old[4];
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t i = i0 + j * blockDim.x;
+                            v[j] = 0;
+                            if (i < total) { const uint32_t r = i / n_cols; v[j] = il_sm[r * stride + (i - r * n_cols)]; }
+                        }
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t i = i0 + j * blockDim.x, r = i / n_cols;
+                            old[j] = v[j] ? __ldcs(filter + (blk0 + r) * W + first_col + (i - r * n_cols)) : 0;
+                        }
+                        #pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t i = i0 + j * blockDim.x, r = i / n_cols;
+                            if (v[j]) __stcs(filter + (blk0 + r) * W + first_col + (i - r * n_cols), old[j] | v[j]);
+                        }
+                    }
+                }
+            }
+            __syncthreads();
         }
     }
 }
@@ -195,15 +237,21 @@ __global__ void sliced_presence_kernel(const uint32_t* __restrict__ bin_ids, uin
 bool sliced_plan(const HashParams& hp, uint64_t budget_bytes, SlicedPlan* p)
 {
     if (hp.direct) return false;
-    const uint64_t pw = ((hp.P + 31) / 32 + 7) & ~7ull;             // 32-bit words per bin vector, 32-byte aligned rows
+    const uint64_t pw = ((hp.P + 31) / 32 + 31) & ~31ull;           // 32-bit words of one bin's vector: whole 128-byte lines
     if (pw * 4 > (32ull << 20)) return false;                       // a bin's vector must sit comfortably in the L2
     if (pw * 4 < (64ull << 10)) return false;                       // tiny tables: direct atomics are L2 hits anyway
-    uint32_t cols = hp.W >= 4 ? 4 : hp.W >= 2 ? 2 : 1;              // the interleave kernel comes in these widths
-    while (cols > 1 && (uint64_t)cols * 64 * pw * 4 > budget_bytes) cols >>= 1;
+    const uint64_t n_tiles = pw / 32;                               // tiles of 1024 blocks = one line per bin
+    // all W columns in one pass when the scratch allows (the interleave then streams whole table rows); else 4, 2 or 1
+    uint32_t cols = hp.W;
+    const char* env_cols = getenv("DYIBF_SLICED_MAX_COLS");         // tests: force the narrow groups a small scratch would get
+    const uint32_t max_cols = env_cols && atoi(env_cols) > 0 ? (uint32_t)atoi(env_cols) : 16u;
+    if (cols > max_cols || n_tiles * (cols * 64 + 1) * 128 > budget_bytes) cols = (hp.W >= 4 && max_cols >= 4) ? 4 : (hp.W >= 2 && max_cols >= 2) ? 2 : 1;
+    while (cols > 1 && n_tiles * (cols * 64 + 1) * 128 > budget_bytes) cols >>= 1;
     if ((uint64_t)cols * 64 * pw * 4 > budget_bytes) return false;
-    p->pw = pw; p->cols_per_group = cols; p->group_bins = cols * 64;
+    p->pw = pw; p->n_tiles = n_tiles; p->cols_per_group = cols; p->group_bins = cols * 64;
     p->n_groups = (hp.W + cols - 1) / cols;
-    p->shadow_bytes = (uint64_t)cols * 64 * pw * 4;
+    p->shadow_bytes = n_tiles * (cols * 64 + 1) * 128;
+    p->scatter_blocks = SLICED_MAX_BLOCKS;
     return true;
 }
 
@@ -231,7 +279,13 @@ cudaError_t launch_sliced_scatter(const HashParams& hp, void* shadow, const Slic
     if (ce != cudaSuccess) return ce;
     const uint64_t tiles = (total_words + 31) / 32;
     uint64_t blocks = (tiles + 7) / 8;
-    if (blocks > 148ull * 8) blocks = 148ull * 8;                   // 64 warps per SM: the window of bins in flight stays small
+    // The window of bins in flight must stay small (plan.scatter_blocks, set from the batch's average run per bin): measured on
+    // 1024 bins x 1 Mbp into 16 GiB, 1184 / 592 / 296 / 148 blocks scatter in 60 / 46 / 32 / 23 ms (the RED rate does not
+    // need more than 8 warps per SM, the L2 needs the vectors of the bins in flight to fit); 4 Mbp per bin: 66 / 66 / 67 / 69 ms.
+    const uint64_t max_blocks = p.scatter_blocks ? p.scatter_blocks : SLICED_MAX_BLOCKS;
+    if (blocks > max_blocks) blocks = max_blocks;
+    static const char* env_blocks = getenv("DYIBF_SLICED_BLOCKS");  // experiments
+    if (env_blocks && atoi(env_blocks) > 0 && blocks > (uint64_t)atoi(env_blocks)) blocks = (uint64_t)atoi(env_blocks);
     const uint32_t first_bin = group * p.group_bins;
     uint32_t* sh = static_cast<uint32_t*>(shadow);
     dim3 grid((unsigned)blocks), block(256);
@@ -249,15 +303,22 @@ cudaError_t launch_sliced_interleave(const HashParams& hp, uint64_t* filter, con
 {
     const uint32_t first_col = group * p.cols_per_group;
     const uint32_t n_cols = hp.W - first_col < p.cols_per_group ? hp.W - first_col : p.cols_per_group;
-    const uint32_t first_bin = group * p.group_bins;
-    const uint32_t gbins = hp.bins - first_bin < p.group_bins ? hp.bins - first_bin : p.group_bins;
-    const uint64_t tiles = (p.pw + 7) / 8;
-    uint64_t blocks = (tiles + 7) / 8;
-    if (blocks > 148ull * 8) blocks = 148ull * 8;
+    // words per lane and sub-tile: 8 (32 bytes per lane and bin, 256 table rows per sub-tile: measured 18.6 / 23.4 / 29.1 ms per 16 GiB
+    // pass for 8 / 16 / 32 — the smaller the shared-memory tile, the more blocks per SM) unless DYIBF_SLICED_SW says 16 or 32
+    static const int sw = getenv("DYIBF_SLICED_SW") ? atoi(getenv("DYIBF_SLICED_SW")) : 8;
     const uint32_t* sh = static_cast<const uint32_t*>(shadow);
-    if (p.cols_per_group == 4)      sliced_interleave_kernel<4><<<(unsigned)blocks, 256, 0, st>>>(filter, sh, p.pw, hp.P, hp.W, first_col, n_cols, gbins);
-    else if (p.cols_per_group == 2) sliced_interleave_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(filter, sh, p.pw, hp.P, hp.W, first_col, n_cols, gbins);
-    else                            sliced_interleave_kernel<1><<<(unsigned)blocks, 256, 0, st>>>(filter, sh, p.pw, hp.P, hp.W, first_col, n_cols, gbins);
+    uint64_t blocks = p.n_tiles;
+    if (blocks > 148ull * 16) blocks = 148ull * 16;
+#define DYIBF_IL(SWV) do { \
+        const size_t smem = (size_t)SWV * 32 * (n_cols | 1u) * 8; \
+        if (smem > 48 * 1024) {                                     /* per device, so per launch (a group spans several GPUs) */ \
+            cudaError_t e = cudaFuncSetAttribute(sliced_interleave_kernel<SWV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            if (e != cudaSuccess) return e; \
+        } \
+        sliced_interleave_kernel<SWV><<<(unsigned)blocks, 256, smem, st>>>(filter, sh, p.pw, p.n_tiles, hp.P, hp.W, first_col, n_cols); \
+    } while (0)
+    if (sw == 16) DYIBF_IL(16); else if (sw == 32) DYIBF_IL(32); else DYIBF_IL(8);
+#undef DYIBF_IL
     return cudaGetLastError();
 }
 

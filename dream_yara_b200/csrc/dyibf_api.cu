@@ -789,83 +789,6 @@ int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int form
     return DYIBF_OK;
 }
 
-/* loadReads + clasifyLoadedReads from the text of the reads file(s): only text goes up, only the per-bin lists come back */
-int dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads_bytes, const char* mates_text, uint64_t mates_bytes,
-                        int format, int e_percent, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total,
-                        uint32_t* n_reads, uint32_t* threshold)
-{
-    if (!f || !bin_offsets || (capacity && !read_ids) || (reads_bytes && !reads_text) || (mates_bytes && !mates_text))
-        return fail(DYIBF_ERR_ARG, "dyibf_classify_text: NULL argument");
-    if (format != DYIBF_FMT_FASTA && format != DYIBF_FMT_FASTQ) return fail(DYIBF_ERR_ARG, "dyibf_classify_text: bad format");
-    const bool paired = mates_text != nullptr;
-    DeviceGuard guard(f->prm.device);
-    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
-    Slot& sl = f->slot[0];
-    cudaStream_t st = sl.st;
-    f->h_csr_off.clear(); f->batch.valid = false;
-    // the text goes to the device once; the parsed forward read set ([reads] or [mates 1 | mates 2]) becomes the resident batch
-    const uint64_t off2 = (reads_bytes + 15) & ~15ull, all_bytes = off2 + mates_bytes;
-    CU(sl.in_bytes.reserve(all_bytes + 32));
-    char* d_text = static_cast<char*>(sl.in_bytes.p);
-    if (reads_bytes) CU(cudaMemcpyAsync(d_text, reads_text, reads_bytes, cudaMemcpyHostToDevice, st));
-    if (mates_bytes) CU(cudaMemcpyAsync(d_text + off2, mates_text, mates_bytes, cudaMemcpyHostToDevice, st));
-    const uint64_t cap_seqs = (reads_bytes + mates_bytes) / 2 + 2;           // a record is at least two bytes of text
-    CU(f->batch_bytes.reserve(reads_bytes + mates_bytes + 32));
-    CU(f->batch_offsets.reserve((cap_seqs + 2) * 8));
-    uint8_t* d_seqs = static_cast<uint8_t*>(f->batch_bytes.p);
-    uint64_t* d_lim = static_cast<uint64_t*>(f->batch_offsets.p);
-    uint64_t n1 = 0, b1 = 0, n2 = 0, b2 = 0;
-    int rc = dyibf_parse_records(f->prm.device, d_text, reads_bytes, format, DYIBF_ALPHA_DNA5, d_seqs, reads_bytes + 16, d_lim, cap_seqs, 0,
-                                 &n1, &b1, DYIBF_MEM_DEVICE, st);
-    if (rc) return rc;
-    if (paired) {
-        rc = dyibf_parse_records(f->prm.device, d_text + off2, mates_bytes, format, DYIBF_ALPHA_DNA5, d_seqs + b1, mates_bytes + 16,
-                                 d_lim + n1, cap_seqs - n1, b1, &n2, &b2, DYIBF_MEM_DEVICE, st);
-        if (rc) return rc;
-        if (n2 != n1) return fail(DYIBF_ERR_ARG, "dyibf_classify_text: %llu reads but %llu mates", (unsigned long long)n1, (unsigned long long)n2);
-    }
-    const uint64_t n_fwd = n1 + n2, total_bytes = b1 + b2;
-    if (2 * n_fwd > 0xffffffffull) return fail(DYIBF_ERR_ARG, "too many sequences in one batch");
-    // the batch's threshold, d_mapper.h:313-315: average length over the whole read set (the rc half doubles both sums)
-    const uint16_t avg = (uint16_t)(n_fwd ? total_bytes / n_fwd : 0);
-    const uint32_t thr = dyibf_threshold(e_percent, f->prm.kmer, avg);
-    const uint32_t group = paired ? 4 : 2;
-    const uint32_t n_rows = (uint32_t)(2 * n_fwd / group);
-    if (n_reads) *n_reads = n_rows;
-    if (threshold) *threshold = thr;
-    CU(f->rows_all.reserve((uint64_t)n_rows * W * 8 + 8));
-    uint64_t* d_rows = static_cast<uint64_t*>(f->rows_all.p);
-    if (n_rows) {
-        CU(f->misc.reserve(64));
-        CU(cudaMemsetAsync(f->misc.p, 0, 8, st));
-        CU(launch_max_len(d_lim, n_fwd, static_cast<unsigned long long*>(f->misc.p), st));
-        unsigned long long max_len = 0;
-        CU(cudaMemcpyAsync(&max_len, f->misc.p, 8, cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-        if (max_len >= f->hp.k && max_len - f->hp.k + 1 > 65535)
-            return fail(DYIBF_ERR_ARG, "a sequence of %llu bases has more than 65535 k-mers (uint16_t in the reference)", max_len);
-        PackSource src; memset(&src, 0, sizeof src);
-        src.n_ranges = 1; src.cnt = (uint32_t)n_fwd; src.bytes[0] = d_seqs; src.offsets[0] = d_lim;
-        rc = query_on_device(f, sl, src, total_bytes, DYIBF_ENC_ASCII, group, 1, thr, (uint32_t)max_len, d_rows, nullptr, st);
-        if (rc) return rc;
-    }
-    CU(f->csr_off.reserve((uint64_t)(bins + 1) * 8));
-    uint64_t tot = 0;
-    rc = compact_on_device(f, d_rows, n_rows, 0, (uint64_t*)f->csr_off.p, nullptr, 0, &tot, st);
-    if (rc != DYIBF_OK && rc != DYIBF_ERR_CAPACITY) return rc;
-    f->h_csr_off.resize((size_t)bins + 1);
-    CU(cudaMemcpyAsync(f->h_csr_off.data(), f->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, st));
-    if (tot) {
-        CU(f->csr_ids.reserve(tot * 4));
-        Scope sc(f, st, K_COMPACT);
-        CU(launch_compact_fill(d_rows, n_rows, bins, (const uint64_t*)f->compact_ws.p, (uint32_t*)f->csr_ids.p, tot, 0, st));
-    }
-    CU(cudaStreamSynchronize(st));
-    f->batch.valid = true; f->batch.n_fwd = (uint32_t)n_fwd; f->batch.group = group; f->batch.encoding = DYIBF_ENC_ASCII;
-    f->batch.first_off = 0;
-    return classify_fetch(f, bin_offsets, read_ids, capacity, total);
-}
-
 } // extern "C"
 
 // ============================================================================================================
@@ -1031,12 +954,14 @@ bool sliced_candidate(dyibf_filter* f, uint64_t expected_records, SlicedPlan* pl
     if (mode == DYIBF_BUILD_DIRECT || mode == DYIBF_BUILD_BUCKETED || f->hp.direct) return false;
     if (mode == DYIBF_BUILD_AUTO) {
         if (f->data_words * 8 <= (256ull << 20)) return false;     // table (nearly) fits the L2: direct atomics are L2 hits
-        if (expected_records < (32ull << 20)) return false;         // too few updates to pay for the zero / interleave passes
+        // too few updates to pay for the zero / interleave passes (~11 ms for a 16 GiB table: the break-even against direct
+        // atomics at 21 G updates/s is ~280 M updates; calls between 32 M and that go to the bucketed build)
+        if (expected_records < (256ull << 20)) return false;
     }
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return false;
     free_b += f->bucket_records.cap;
-    const uint64_t budget = std::min<uint64_t>(free_b / 2, 16ull << 30);
+    const uint64_t budget = std::min<uint64_t>(free_b / 2, 17ull << 30);   // all 1024 bins of a 16 GiB table: 16 GiB + pad lines
     return sliced_plan(f->hp, budget, plan);
 }
 
@@ -1044,9 +969,13 @@ bool sliced_candidate(dyibf_filter* f, uint64_t expected_records, SlicedPlan* pl
 int sliced_begin(dyibf_filter* f, const SlicedPlan& plan, uint64_t total_bases, uint64_t switches, SlicedRun* sr)
 {
     sr->active = false; sr->plan = plan; sr->cur = -1;
+    // the scatter kernel's window (bases its resident warps span) is cut to about 1.5 average runs of one bin, so that two
+    // or three bins' vectors are being filled at any time; the smallest useful grid still spans SLICED_MIN_BLOCKS * 8192 bases
+    const uint64_t avg_run = std::max<uint64_t>(total_bases / (switches + 1), 1);
+    const uint64_t want_blocks = (avg_run + avg_run / 2) / SLICED_BLOCK_BASES;
+    sr->plan.scatter_blocks = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want_blocks, SLICED_MIN_BLOCKS), SLICED_MAX_BLOCKS);
     if (f->build_mode == DYIBF_BUILD_AUTO) {
-        const uint64_t avg_run = std::max<uint64_t>(total_bases / (switches + 1), 1);
-        const uint64_t bins_in_flight = SLICED_WINDOW_BASES / avg_run + 2;
+        const uint64_t bins_in_flight = sr->plan.scatter_blocks * SLICED_BLOCK_BASES / avg_run + 2;
         if (bins_in_flight * plan.pw * 4 > (80ull << 20)) return DYIBF_OK;   // not clustered by bin: bucketed / direct
     }
     if (f->bucket_records.reserve(plan.shadow_bytes) != cudaSuccess) {
@@ -1124,7 +1053,7 @@ int dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* of
         }
         CU(cudaStreamSynchronize(st));
         if (last < first) return fail(DYIBF_ERR_ARG, "offsets not monotone");
-        if (s_cand && (f->build_mode != DYIBF_BUILD_AUTO || (last - first) * f->hp.h >= (32ull << 20))) {
+        if (s_cand && (f->build_mode != DYIBF_BUILD_AUTO || (last - first) * f->hp.h >= (256ull << 20))) {
             int src_ = sliced_begin(f, splan, last - first, switches, &sr);
             if (src_) return src_;
         }

@@ -6,6 +6,15 @@
 // a stream and a private set of buffers, so batch i+1 uploads and starts while batch i is still in the query kernel and
 // batch i-1's lists travel back: the GPU sees a continuous stream of work at the reference's batch size.
 //
+// Scheduling (measured, B200, 100 000-read batches from pinned memory, tools/debug/async_probe.py and the DYIBF_TRACE timeline):
+// every ticket has ONE stream of default priority and the query kernel keeps its persistent blocks.  2 / 3 / 4 tickets in
+// flight: 49.7 / 52.2 / 53.4 M reads/s (one large batch: 56.4 M).  What is left is a drain bubble: the compaction of batch i waits
+// until the query kernels of the batches queued behind it have released SM slots.  Tried and dropped: a high-priority
+// stream for copies / pack / compaction with the query kernel on a low-priority stream and short-lived blocks (one work item
+// per warp) so that the small kernels get slots at once — the timeline becomes gap-free, but three query kernels
+// interleaved block by block run at 45.5 M reads/s in total (each alone: 56.7 M in either block form), i.e. co-resident
+// query kernels cost more than the bubble; priorities with persistent blocks change nothing (52.3 M at 3 in flight).
+//
 // begin: H2D of the batch (straight from the caller's memory: truly asynchronous when it is pinned, staged by the driver
 //        when it is pageable), pack, query, compaction count + scan + fill, D2H of the bin offsets — all enqueued, nothing
 //        waited for.  The caller's seqs / offsets must stay valid until dyibf_classify_end.
@@ -22,7 +31,7 @@ struct Ticket {
     int           index = 0;
     bool          busy = false;
     Slot          sl;                         // stream + pack / query workspace
-    DevBuf        bytes, offsets, rows, compact_ws, csr_off, csr_ids;
+    DevBuf        bytes, offsets, rows, compact_ws, csr_off, csr_ids, text;
     uint64_t*     h_off = nullptr;            // pinned: bins + 1 bin offsets
     void*         h_in = nullptr; size_t h_in_cap = 0;   // pinned staging of a pageable caller's batch (bytes, then limits)
     cudaEvent_t   done = nullptr;
@@ -42,7 +51,7 @@ void free_tickets(dyibf_filter* f)
         if (t->h_in) cudaFreeHost(t->h_in);
         t->sl.in_bytes.release(); t->sl.in_offsets.release(); t->sl.packed.release(); t->sl.meta.release();
         t->sl.rows.release(); t->sl.counts.release(); t->sl.ctr.release();
-        t->bytes.release(); t->offsets.release(); t->rows.release(); t->compact_ws.release(); t->csr_off.release(); t->csr_ids.release();
+        t->bytes.release(); t->offsets.release(); t->rows.release(); t->compact_ws.release(); t->csr_off.release(); t->csr_ids.release(); t->text.release();
         delete t;
         f->tickets[i] = nullptr;
     }
@@ -70,6 +79,38 @@ static int acquire_ticket(dyibf_filter* f, Ticket** out)
         return DYIBF_OK;
     }
     return fail(DYIBF_ERR_BUSY, "dyibf_classify_begin: all %d tickets of this handle are in flight", DYIBF_MAX_TICKETS);
+}
+
+// compaction of the ticket's rows: count + scan, then the fill into a buffer sized for the usual case (<= 4 lists per row);
+// a batch that needs more is re-filled in dyibf_classify_end
+static int enqueue_compaction(Ticket* t, uint32_t n_rows)
+{
+    dyibf_filter* f = t->f;
+    const uint32_t bins = f->prm.bins;
+    cudaStream_t st = t->sl.st;
+    const uint64_t* d_rows = (const uint64_t*)t->rows.p;
+    const size_t ws_bytes = compact_workspace_bytes(bins, n_rows);
+    CU(t->compact_ws.reserve(ws_bytes));
+    t->ids_cap = std::max<uint64_t>(4ull * n_rows, 1024);
+    CU(t->csr_ids.reserve(t->ids_cap * 4));
+    t->ids_cap = t->csr_ids.cap / 4;
+    uint64_t* ws = (uint64_t*)t->compact_ws.p;
+    CU(cudaMemsetAsync(ws, 0, ws_bytes, st));
+    Scope sc(f, st, K_COMPACT, 6);
+    CU(launch_compact_count(d_rows, n_rows, bins, ws, st));
+    CU(launch_compact_scan(ws, bins, n_rows, (uint64_t*)t->csr_off.p, st));
+    CU(launch_compact_fill(d_rows, n_rows, bins, ws, (uint32_t*)t->csr_ids.p, t->ids_cap, 0, st));
+    return DYIBF_OK;
+}
+
+// the bin offsets travel back; the ticket is in flight from here on
+static int enqueue_finish(Ticket* t)
+{
+    cudaStream_t st = t->sl.st;
+    CU(cudaMemcpyAsync(t->h_off, t->csr_off.p, (uint64_t)(t->f->prm.bins + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(t->done, st));
+    t->busy = true;
+    return DYIBF_OK;
 }
 
 } // namespace dyibf
@@ -145,31 +186,132 @@ int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* o
         uint64_t* d_rows = (uint64_t*)t->rows.p;
         rc = query_on_device(f, t->sl, src, total_bytes, encoding, (uint32_t)group, derive_rc, threshold, max_len, d_rows, nullptr, st);
         if (rc) return rc;
-        // compaction: count + scan, then the fill into a buffer sized for the usual case (<= 4 lists per row); a batch
-        // that needs more is re-filled in dyibf_classify_end
-        const size_t ws_bytes = compact_workspace_bytes(bins, n_rows);
-        CU(t->compact_ws.reserve(ws_bytes));
-        t->ids_cap = std::max<uint64_t>(4ull * n_rows, 1024);
-        CU(t->csr_ids.reserve(t->ids_cap * 4));
-        t->ids_cap = t->csr_ids.cap / 4;
-        uint64_t* ws = (uint64_t*)t->compact_ws.p;
-        CU(cudaMemsetAsync(ws, 0, ws_bytes, st));
-        {
-            Scope sc(f, st, K_COMPACT, 6);
-            CU(launch_compact_count(d_rows, n_rows, bins, ws, st));
-            CU(launch_compact_scan(ws, bins, n_rows, (uint64_t*)t->csr_off.p, st));
-            CU(launch_compact_fill(d_rows, n_rows, bins, ws, (uint32_t*)t->csr_ids.p, t->ids_cap, 0, st));
-        }
+        rc = enqueue_compaction(t, n_rows);
+        if (rc) return rc;
         if (derive_rc) {
             t->batch.valid = true; t->batch.n_fwd = n_seqs; t->batch.group = (uint32_t)group; t->batch.encoding = (uint32_t)encoding;
             t->batch.first_off = offsets[0];
         }
     }
-    CU(cudaMemcpyAsync(t->h_off, t->csr_off.p, (uint64_t)(bins + 1) * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaEventRecord(t->done, st));
-    t->busy = true;
+    rc = enqueue_finish(t);
+    if (rc) return rc;
     *ticket = reinterpret_cast<dyibf_ticket*>(t);
     return DYIBF_OK;
+}
+
+/* loadReads + clasifyLoadedReads from the TEXT of the reads file(s), as a ticket: the text goes up on the ticket's stream,
+ * is tokenised on the device (two short waits for the record / base counts, which size the launches that follow), and the
+ * query + compaction are enqueued; the lists come back through dyibf_classify_end.  While this batch's query runs, the next
+ * dyibf_classify_text_begin uploads and parses its text on another ticket's stream: the double-buffered reader of
+ * src/file_prefetched.h:137-205, with the GPU as the consumer. */
+int dyibf_classify_text_begin(dyibf_filter* f, const char* reads_text, uint64_t reads_bytes, const char* mates_text, uint64_t mates_bytes,
+                              int format, int e_percent, uint32_t* n_reads, uint32_t* threshold, dyibf_ticket** ticket)
+{
+    if (!ticket) return fail(DYIBF_ERR_ARG, "ticket is NULL");
+    *ticket = nullptr;
+    if (!f || (reads_bytes && !reads_text) || (mates_bytes && !mates_text)) return fail(DYIBF_ERR_ARG, "dyibf_classify_text: NULL argument");
+    if (format != DYIBF_FMT_FASTA && format != DYIBF_FMT_FASTQ) return fail(DYIBF_ERR_ARG, "dyibf_classify_text: bad format");
+    const bool paired = mates_text != nullptr;
+    DeviceGuard guard(f->prm.device);
+    Ticket* t = nullptr;
+    int rc = acquire_ticket(f, &t);
+    if (rc) return rc;
+    const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
+    cudaStream_t st = t->sl.st;
+    t->n_rows = 0; t->batch.valid = false; t->ids_cap = 0;
+    CU(t->csr_off.reserve((uint64_t)(bins + 1) * 8));
+    // the text goes to the device once; the parsed forward read set ([reads] or [mates 1 | mates 2]) is the ticket's batch
+    const uint64_t off2 = (reads_bytes + 15) & ~15ull, all_bytes = off2 + mates_bytes;
+    CU(t->text.reserve(all_bytes + 32));
+    char* d_text = static_cast<char*>(t->text.p);
+    {
+        Scope sc(f, st, K_COPY, 0);
+        const char* src[2] = {reads_text, mates_text}; const uint64_t len[2] = {reads_bytes, mates_bytes}; char* dst[2] = {d_text, d_text + off2};
+        for (int i = 0; i < 2; ++i) {
+            if (!len[i]) continue;
+            if (len[i] >= (1u << 20) && is_pageable(src[i])) { rc = staged_h2d(dst[i], src[i], len[i], st); if (rc) return rc; }
+            else CU(cudaMemcpyAsync(dst[i], src[i], len[i], cudaMemcpyHostToDevice, st));
+        }
+    }
+    // a record is at least two bytes of text (FASTA ">\n"), four in FASTQ ("@\n+\n")
+    const uint64_t cap_seqs = (reads_bytes + mates_bytes) / (format == DYIBF_FMT_FASTQ ? 4 : 2) + 2;
+    CU(t->bytes.reserve(reads_bytes + mates_bytes + 32));
+    CU(t->offsets.reserve((cap_seqs + 2) * 8));
+    uint8_t* d_seqs = static_cast<uint8_t*>(t->bytes.p);
+    uint64_t* d_lim = static_cast<uint64_t*>(t->offsets.p);
+    uint64_t n1 = 0, b1 = 0, n2 = 0, b2 = 0;
+    rc = dyibf_parse_records(f->prm.device, d_text, reads_bytes, format, DYIBF_ALPHA_DNA5, d_seqs, reads_bytes + 16, d_lim, cap_seqs, 0,
+                             &n1, &b1, DYIBF_MEM_DEVICE, st);
+    if (rc) return rc;
+    if (paired) {
+        rc = dyibf_parse_records(f->prm.device, d_text + off2, mates_bytes, format, DYIBF_ALPHA_DNA5, d_seqs + b1, mates_bytes + 16,
+                                 d_lim + n1, cap_seqs - n1, b1, &n2, &b2, DYIBF_MEM_DEVICE, st);
+        if (rc) return rc;
+        if (n2 != n1) return fail(DYIBF_ERR_ARG, "dyibf_classify_text: %llu reads but %llu mates", (unsigned long long)n1, (unsigned long long)n2);
+    }
+    f->kernel_launches += paired ? 10 : 5;
+    const uint64_t n_fwd = n1 + n2, total_bytes = b1 + b2;
+    if (2 * n_fwd > 0xffffffffull) return fail(DYIBF_ERR_ARG, "too many sequences in one batch");
+    // the batch's threshold, d_mapper.h:313-315: average length over the whole read set (the rc half doubles both sums)
+    const uint16_t avg = (uint16_t)(n_fwd ? total_bytes / n_fwd : 0);
+    const uint32_t thr = dyibf_threshold(e_percent, f->prm.kmer, avg);
+    const uint32_t group = paired ? 4 : 2;
+    const uint32_t n_rows = (uint32_t)(2 * n_fwd / group);
+    if (n_reads) *n_reads = n_rows;
+    if (threshold) *threshold = thr;
+    t->n_rows = n_rows;
+    if (n_rows == 0) {
+        CU(cudaMemsetAsync(t->csr_off.p, 0, (uint64_t)(bins + 1) * 8, st));
+    } else {
+        CU(t->rows.reserve((uint64_t)n_rows * W * 8 + 8));
+        CU(t->sl.ctr.reserve(256));
+        unsigned long long* d_max = reinterpret_cast<unsigned long long*>(static_cast<char*>(t->sl.ctr.p) + 128);
+        CU(cudaMemsetAsync(d_max, 0, 8, st));
+        CU(launch_max_len(d_lim, n_fwd, d_max, st));
+        f->kernel_launches += 1;
+        unsigned long long max_len = 0;
+        CU(cudaMemcpyAsync(&max_len, d_max, 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (max_len >= f->hp.k && max_len - f->hp.k + 1 > 65535)
+            return fail(DYIBF_ERR_ARG, "a sequence of %llu bases has more than 65535 k-mers (uint16_t in the reference)", max_len);
+        PackSource src; memset(&src, 0, sizeof src);
+        src.n_ranges = 1; src.cnt = (uint32_t)n_fwd; src.bytes[0] = d_seqs; src.offsets[0] = d_lim;
+        rc = query_on_device(f, t->sl, src, total_bytes, DYIBF_ENC_ASCII, group, 1, thr, (uint32_t)std::max<unsigned long long>(max_len, 1),
+                             (uint64_t*)t->rows.p, nullptr, st);
+        if (rc) return rc;
+        rc = enqueue_compaction(t, n_rows);
+        if (rc) return rc;
+        t->batch.valid = true; t->batch.n_fwd = (uint32_t)n_fwd; t->batch.group = group; t->batch.encoding = DYIBF_ENC_ASCII;
+        t->batch.first_off = 0;
+    }
+    rc = enqueue_finish(t);
+    if (rc) return rc;
+    *ticket = reinterpret_cast<dyibf_ticket*>(t);
+    return DYIBF_OK;
+}
+
+/* the synchronous form: one ticket, begun and ended */
+int dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads_bytes, const char* mates_text, uint64_t mates_bytes,
+                        int format, int e_percent, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total,
+                        uint32_t* n_reads, uint32_t* threshold)
+{
+    if (!f || !bin_offsets || (capacity && !read_ids)) return fail(DYIBF_ERR_ARG, "dyibf_classify_text: NULL argument");
+    dyibf_ticket* t = nullptr;
+    int rc = dyibf_classify_text_begin(f, reads_text, reads_bytes, mates_text, mates_bytes, format, e_percent, n_reads, threshold, &t);
+    if (rc) return rc;
+    rc = dyibf_classify_end(t, bin_offsets, read_ids, capacity, total);
+    if (rc == DYIBF_ERR_CAPACITY) {
+        // the lists stay in HBM for dyibf_classify_fetch: hand the ticket's batch to the handle with a sizing call
+        std::string keep = last_error_string();
+        Ticket* tk = reinterpret_cast<Ticket*>(t);
+        std::vector<uint32_t> tmp((size_t)std::max<uint64_t>(tk->h_off[f->prm.bins], 1));
+        std::vector<uint64_t> off((size_t)f->prm.bins + 1);
+        uint64_t tot = 0;
+        int rc2 = dyibf_classify_end(t, off.data(), tmp.data(), tmp.size(), &tot);
+        if (rc2) return rc2;
+        set_last_error(keep);
+    }
+    return rc;
 }
 
 int dyibf_classify_poll(dyibf_ticket* ticket, int* ready)

@@ -56,7 +56,7 @@ struct Ticket;
 
 } // namespace dyibf
 
-static const int DYIBF_MAX_TICKETS = 4;
+static const int DYIBF_MAX_TICKETS = 8;
 
 struct dyibf_filter {
     dyibf_params prm;
@@ -87,7 +87,7 @@ struct dyibf_filter {
     double       ms[dyibf::K_N] = {0, 0, 0, 0, 0, 0, 0};
     uint64_t     launches[dyibf::K_N] = {0, 0, 0, 0, 0, 0, 0};
     uint64_t     kernel_launches = 0;     // every kernel this handle has launched (dyibf_launch_count)
-    dyibf::Ticket* tickets[DYIBF_MAX_TICKETS] = {nullptr, nullptr, nullptr, nullptr};
+    dyibf::Ticket* tickets[DYIBF_MAX_TICKETS] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 namespace dyibf {

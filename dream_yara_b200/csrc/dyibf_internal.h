@@ -101,13 +101,17 @@ cudaError_t launch_bucket_apply(uint64_t* filter, uint64_t data_words, const Buc
 
 // bit-sliced build (build_sliced.cu): per-bin Bloom bit vectors that live in the L2, then interleaved into the table.
 struct SlicedPlan {
-    uint64_t pw;               // 32-bit words per bin vector (ceil(P / 32), rounded up to 8)
-    uint32_t cols_per_group;   // word columns (64 bins each) per pass: 4, or fewer for narrow tables / small budgets
+    uint64_t pw;               // 32-bit words per bin vector (ceil(P / 32), rounded up to 32 = whole 128-byte lines)
+    uint64_t n_tiles;          // tiles of 1024 blocks (one line of every bin's vector): pw / 32
+    uint32_t cols_per_group;   // word columns (64 bins each) per pass: all W when the scratch fits, else 4 / 2 / 1
     uint32_t group_bins;       // 64 * cols_per_group
     uint32_t n_groups;         // passes that cover all W columns
     uint64_t shadow_bytes;     // group_bins * pw * 4
+    uint32_t scatter_blocks;   // grid of the scatter kernel (8 warps x 1024 bases per block in flight): sized so that the
+                               // bins in flight (window / average run of one bin) keep their vectors in the L2
 };
-static const uint64_t SLICED_WINDOW_BASES = 148ull * 8 * 8 * 1024;   // bases the resident warps of the scatter kernel span
+static const uint32_t SLICED_MAX_BLOCKS = 148 * 8, SLICED_MIN_BLOCKS = 74;
+static const uint64_t SLICED_BLOCK_BASES = 8 * 1024;                 // bases the 8 warps of one scatter block span
 bool        sliced_plan(const HashParams& hp, uint64_t budget_bytes, SlicedPlan* plan);
 // mask[g] = 1 for every group with a sequence; *switches = number of bin changes along the batch (device buffers)
 cudaError_t launch_sliced_presence(const uint32_t* bin_ids, uint32_t n_seqs, uint32_t bins, const SlicedPlan& plan, uint32_t* mask,

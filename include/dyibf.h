@@ -119,7 +119,9 @@ int  dyibf_save_file(dyibf_filter* f, const char* path);
 /* The loader / writer behind dyibf_load_file* / dyibf_save_file (and their group forms) streams the file through pinned
  * host buffers with several file threads (pread / pwrite) and one thread issuing the asynchronous copies; this is the stage the mapper prints as
  * "Filter loading time" (src/d_mapper.h:913-921); dyibf_upload_words / dyibf_download_words of whole blocks use the same
- * pipeline.  dyibf_set_io_threads: 1..64, default 8, process-wide.
+ * pipeline.  dyibf_set_io_threads: 1..64, 0 = default (the host's cores, between 4 and 16), process-wide.
+ * Measured on a B200 box with 16 host cores, 16 GiB filter in the page cache: 7.4 / 26 / 43 / 45 GB/s with 1 / 4 / 8 / 16 threads
+ * (pinned H2D of the box: 52 GB/s).
  * dyibf_last_io_stats: the calling thread's last load or save. */
 typedef struct dyibf_io_stats {
     uint64_t bytes;               /* data-word bytes moved between the file and HBM                         */
@@ -133,7 +135,7 @@ typedef struct dyibf_io_stats {
     uint64_t chunk_bytes;         /* bytes per pinned chunk                                                  */
 } dyibf_io_stats;
 int  dyibf_set_io_threads(int n);
-int  dyibf_set_io_chunk_mib(int mib);   /* 1..1024, 0 = default (DYIBF_IO_CHUNK_MIB from the environment, else 8) */
+int  dyibf_set_io_chunk_mib(int mib);   /* 1..1024, 0 = default (DYIBF_IO_CHUNK_MIB from the environment, else 4) */
 int  dyibf_last_io_stats(dyibf_io_stats* out);
 
 /* ---- build --------------------------------------------------------------------------------- */
@@ -191,7 +193,8 @@ int  dyibf_classify_fetch(dyibf_filter* f, uint64_t* bin_offsets, uint32_t* read
 /* Asynchronous form of dyibf_classify for the reference's real batching: clasifyLoadedReads is called once per 100 000
  * reads (src/mapper.h:109) while a prefetch thread already loads the next batch (src/file_prefetched.h:137-205).
  * dyibf_classify_begin enqueues upload, pack, query and compaction of one batch on a stream and buffers of its own and
- * returns a ticket at once; up to four tickets per handle may be in flight (DYIBF_ERR_BUSY beyond), so batch i+1 uploads
+ * returns a ticket at once; up to eight tickets per handle may be in flight (DYIBF_ERR_BUSY beyond; four is where the
+ * throughput levels off), so batch i+1 uploads
  * and starts while batch i is in the query kernel.  seqs / offsets must stay valid until dyibf_classify_end, which waits
  * for the ticket and copies the lists out exactly as dyibf_classify returns them.  On DYIBF_ERR_CAPACITY (bin_offsets and
  * *total are filled) the ticket stays in flight: call dyibf_classify_end again with a larger buffer.  After a successful
@@ -249,6 +252,12 @@ int  dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int for
 int  dyibf_classify_text(dyibf_filter* f, const char* reads_text, uint64_t reads_bytes, const char* mates_text, uint64_t mates_bytes,
                          int format, int e_percent, uint64_t* bin_offsets, uint32_t* read_ids, uint64_t capacity, uint64_t* total,
                          uint32_t* n_reads, uint32_t* threshold);
+/* The same as a ticket (see dyibf_classify_begin): upload + tokenising of this batch's text overlap the query of the batches
+ * begun before it — the double-buffered reader in front of the filter (src/file_prefetched.h:137-205).  The call returns once
+ * the records are counted (it waits for the text upload and the tokeniser, not for the query); the text may be reused then.
+ * The lists come back through dyibf_classify_end. */
+int  dyibf_classify_text_begin(dyibf_filter* f, const char* reads_text, uint64_t reads_bytes, const char* mates_text, uint64_t mates_bytes,
+                               int format, int e_percent, uint32_t* n_reads, uint32_t* threshold, dyibf_ticket** ticket);
 
 /* ---- several GPUs, one process ----------------------------------------------------------------
  *
@@ -311,9 +320,11 @@ int  dyibf_group_clear_bins(dyibf_group* g, const uint32_t* bins, uint32_t n);
  *   2 bucketed  the radix-split + apply build described at DYIBF_OPT_BUILD_BUCKET_MIB;
  *   3 sliced    per-bin Bloom bit vectors (P bits = 16 MiB at 16 GiB / 1024 bins) that stay in the L2 while a bin's genome is
  *               hashed, then interleaved into the table with bit-matrix transposes — one L2 atomic per update and two streaming
- *               passes; needs the batch clustered by bin (build_filter adds one FASTA file per bin) and a scratch of 256 bin
- *               vectors (4 GiB).
- * Auto picks sliced for bin-clustered batches of at least 32 M updates into tables larger than the L2, else bucketed / direct.
+ *               passes; needs the batch clustered by bin (build_filter adds one FASTA file per bin) and a scratch of all the
+ *               bins' vectors (as large as the table: 16 GiB at cfg2) or, when that does not fit half of the free HBM, of
+ *               256 / 128 / 64 bins' vectors with one pass per column group.
+ * Auto picks sliced for bin-clustered batches of at least 256 M updates into tables larger than the L2, else bucketed (at
+ * least 32 M updates) / direct.
  * The filter is bit-identical in every mode. */
 #define DYIBF_OPT_BUILD_MODE 5
 #define DYIBF_BUILD_AUTO     0

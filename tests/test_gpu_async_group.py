@@ -121,7 +121,7 @@ def test_classify_tickets_equal_synchronous(dy, oracle, paired):
     # against the oracle for one batch (the synchronous path is pinned elsewhere; this pins the comparison itself)
     _, _, _, (wo, wi) = _oracle_lists(oracle, contigs, batches[0], bins, h, k, nbits, thr, paired)
     assert np.array_equal(want[0][0], wo) and np.array_equal(want[0][1], wi)
-    # three tickets in flight, ended in order; then all four + one too many
+    # three tickets in flight, ended in order; then as many as the handle has (eight) + one too many
     tickets = [f.classifyBegin(b, thr, group=group, derive_rc=True) for b in batches[:3]]
     got = []
     for i in range(6):
@@ -131,9 +131,13 @@ def test_classify_tickets_equal_synchronous(dy, oracle, paired):
     for (o, i), (wo_, wi_) in zip(got, want):
         assert np.array_equal(o, wo_) and np.array_equal(i, wi_)
     four = [f.classifyBegin(b, thr, group=group, derive_rc=True) for b in batches[:4]]
+    more = [f.classifyBegin(batches[i % 6], thr, group=group, derive_rc=True) for i in range(4, 8)]
     with pytest.raises(dy.DyibfError) as ei:
         f.classifyBegin(batches[4], thr, group=group, derive_rc=True)
     assert ei.value.code == -8                                         # DYIBF_ERR_BUSY
+    for j, t in enumerate(more):
+        o, i = f.classifyEnd(t)
+        assert np.array_equal(o, want[(4 + j) % 6][0]) and np.array_equal(i, want[(4 + j) % 6][1])
     # ended out of order; a too-small buffer keeps the ticket alive
     o3, i3 = f.classifyEnd(four[3])
     assert np.array_equal(o3, want[3][0]) and np.array_equal(i3, want[3][1])

@@ -146,3 +146,46 @@ def test_classify_text_equals_parse_then_classify(dy, golden, gather_golden):
     offs, ids, n, thr = f.classifyText(b"", fmt=1, e_percent=3)
     assert n == 0 and ids.size == 0
     f.close()
+
+
+def test_classify_text_tickets_in_flight(dy, golden):
+    """dyibf_classify_text_begin: three text batches in flight on one handle (upload + tokenising of batch i+1 overlap the
+    query of batch i) give, batch by batch, the lists of the synchronous call; the ticket ended last is the resident batch;
+    a malformed text fails in begin and leaves the tickets usable."""
+    import ctypes as C
+    from dream_yara_b200._lib import check
+    L = dy.lib()
+    genomes, reads = ka.records(golden, "genomes"), ka.records(golden, "reads")
+    f = dy.SeqAnBloomFilter(64, 2, 19, ka.GIB_BITS)
+    f.addSequences(genomes, np.arange(64))
+    batches = [reads[i:i + 800] for i in range(0, 6400, 800)]
+    texts = [np.frombuffer(b"".join(b"@r%d\n%s\n+\n%s\n" % (i, r, b"F" * len(r)) for i, r in enumerate(b)), dtype=np.uint8) for b in batches]
+    want = [f.classifyText(t.tobytes(), fmt=1, e_percent=3) for t in texts]
+    q, got = [], []
+
+    def end():
+        t, n, thr = q.pop(0)
+        offs = np.zeros(65, dtype=np.uint64); ids = np.zeros(8 * 800, dtype=np.uint32); tot = C.c_uint64(0)
+        check(L.dyibf_classify_end(t, offs.ctypes.data, ids.ctypes.data, ids.size, C.byref(tot)))
+        got.append((offs, ids[:tot.value].copy(), n, thr))
+
+    for t in texts:
+        if len(q) == 3:
+            end()
+        tk, n, thr = C.c_void_p(), C.c_uint32(0), C.c_uint32(0)
+        check(L.dyibf_classify_text_begin(f._h, t.ctypes.data, t.size, None, 0, 1, 3, C.byref(n), C.byref(thr), C.byref(tk)))
+        q.append((tk, n.value, thr.value))
+    bad = np.frombuffer(b"@x\nACGT\n+\nII\n", dtype=np.uint8)           # quality shorter than the sequence
+    tk = C.c_void_p()
+    assert L.dyibf_classify_text_begin(f._h, bad.ctypes.data, bad.size, None, 0, 1, 3, None, None, C.byref(tk)) == -4 and not tk.value
+    while q:
+        end()
+    for (o1, i1, n1, t1), (o0, i0, n0, t0) in zip(got, want):
+        assert (n1, t1) == (n0, t0) and np.array_equal(o1, o0) and np.array_equal(i1, i0)
+    # the batch ended last is resident: its first bin's reads come back
+    offs = got[-1][0]
+    b = int(np.argmax(np.diff(offs.astype(np.int64))))
+    seq_bytes, limits, gids = f.gatherReads(b)
+    first = int(gids[0])
+    assert seq_bytes[int(limits[0]):int(limits[1])].tobytes() == batches[-1][first]
+    f.close()

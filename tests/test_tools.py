@@ -166,5 +166,20 @@ def test_filter_reads_cli_vs_reference_mapper_output(tools, dy, golden, tmp_path
     assert int(sizes.sum()) == 6538
     want = ka.bits_from_rows(golden["ka1_rows"], 64)
     assert np.array_equal(sizes[2], want[2000:3000].sum(axis=0))
+    # layouts the line cutter hands over whole (junk before the first record; trailing blank lines are plain white space):
+    # same batches, same sizes
+    with open(tmp_path / "junk.fa", "wb") as fh:
+        fh.write(b"; a comment line\n" + open(tmp_path / "reads.fa", "rb").read() + b"\n\n  \n")
+    r2 = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-rb", "1000", "-vv", str(tmp_path / "junk.fa")], capture_output=True, text=True)
+    assert r2.returncode == 0, r2.stderr
+    assert [l for l in r2.stderr.splitlines() if l.startswith("bin ")] == [l for l in r.stderr.splitlines() if l.startswith("bin ")]
+    with open(tmp_path / "tail.fq", "wb") as fh:
+        for i, s_ in enumerate(reads):
+            fh.write(b"@r%d\n%s\n+\n%s\n" % (i, s_, b"I" * len(s_)))
+        fh.write(b"\n \n")
+    r3 = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-rb", "1000", "-vv", str(tmp_path / "tail.fq")], capture_output=True, text=True)
+    assert r3.returncode == 0, r3.stderr
+    assert [l for l in r3.stderr.splitlines() if l.startswith("bin ")] == [l for l in r.stderr.splitlines() if l.startswith("bin ")]
+    assert "Reads count:\t\t\t6400" in r3.stderr
     r = subprocess.run([exe, "-fi", str(tmp_path / "nope.filter"), str(tmp_path / "reads.fa")], capture_output=True, text=True)
     assert r.returncode == 1 and "could not be read" in r.stderr

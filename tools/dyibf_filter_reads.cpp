@@ -5,28 +5,39 @@
 //   dyibf_filter_reads -fi <FILTER> [-e 5] [-rb 100000] [-v|-vv] [-o lists.txt] [--device 0 | --devices 0,1,..] [--inflight 3]
 //                      <READS> [<MATES>]
 //
-// The batches are filtered asynchronously, as the reference's prefetching reader (src/file_prefetched.h:137-205) would feed
-// them: up to --inflight batches are in flight (dyibf_classify_begin / dyibf_classify_end), so the upload of batch i+1 and
-// the list download of batch i-1 overlap the query of batch i; results are consumed in batch order.  With --devices the
-// filter is replicated over several GPUs of this one process (dyibf_group_load_file) and successive batches go to
-// successive GPUs.
+// The reads file(s) are STREAMED: a reader thread inflates / reads them piece by piece and cuts the text into batches of
+// -rb records (four-line FASTQ: every fourth line; FASTA: every '>' at a line start), exactly the batches the mapper's
+// loadReads forms (src/mapper.h:109, d_mapper.h:870-896); the main thread hands each batch's TEXT to the GPU as a ticket
+// (dyibf_classify_text_begin): it is uploaded, tokenised on the device (SeqAn's readRecords, dyibf_parse_records), filtered
+// and compacted there, and only the per-bin lists come back (dyibf_classify_end).  Up to --inflight batches are in flight, so
+// file reading, the upload + tokenising of batch i+1, the query of batch i and the list download of batch i-1 all overlap —
+// the reference's prefetching reader (src/file_prefetched.h:137-205) with the GPU as the consumer.  Text the cutter cannot
+// split by lines alone (FASTQ wrapped over several lines, '>' inside a FASTA line, junk before the first record) is handed
+// over whole from that record on: it is tokenised in one piece on the device and batched from the parsed records.
+// With --devices the filter is replicated over several GPUs of this one process (dyibf_group_load_file) and successive
+// batches go to successive GPUs.
 //
-// Per batch of -rb reads (pairs), as the mapper loads them (src/mapper.h:109, d_mapper.h:870-896): the records are
-// tokenised ON THE DEVICE (dyibf_parse_records = SeqAn's readRecords; the host only reads / inflates the file), the
-// threshold comes from the batch's average read length (d_mapper.h:313-315), dyibf_classify fills origReadIdMap.
+// Per batch: the threshold comes from the batch's average read length (d_mapper.h:313-315), the lists are origReadIdMap.
 // -vv prints "bin <b>\t<size>" per batch (:380-386); -v the timers and "Avg reads per bin" (:947-958); -o writes, per
 // batch, one line per bin in sortedBins order (:843-854): "<batch> <bin> <n> id id ...".
 #include <zlib.h>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
+#include <emmintrin.h>
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <iostream>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "dyibf.h"
@@ -46,7 +57,7 @@ double now() { return std::chrono::duration<double>(std::chrono::steady_clock::n
                  "  -v / -vv                   statistics / per-bin list sizes\n"
                  "       --device INT          CUDA device (default 0)\n"
                  "       --devices LIST        several GPUs, e.g. 0,1,2,3 or all: one replica each, batches round-robin\n"
-                 "       --inflight INT        batches in flight, 1..16 (default 3; 1 = synchronous calls)\n";
+                 "       --inflight INT        batches in flight, 1..16 (default 4; 1 = synchronous calls)\n";
     exit(msg ? 1 : 0);
 }
 
@@ -65,22 +76,7 @@ int formatOf(std::string path, const std::vector<char> & data)
     return !data.empty() && data[0] == '@' ? DYIBF_FMT_FASTQ : DYIBF_FMT_FASTA;
 }
 
-void readAll(const std::string & path, std::vector<char> & out)
-{
-    gzFile gz = gzopen(path.c_str(), "rb");                       // plain files pass through
-    if (!gz) { std::cerr << "Unable to open reads file: " << path << std::endl; exit(1); }
-    gzbuffer(gz, 1 << 20);
-    out.clear();
-    std::vector<char> buf(8 << 20);
-    int n;
-    while ((n = gzread(gz, buf.data(), (unsigned)buf.size())) > 0) out.insert(out.end(), buf.begin(), buf.begin() + n);
-    gzclose(gz);
-    if (n < 0) { std::cerr << "Error while reading: " << path << std::endl; exit(1); }
-}
-
-struct Records { std::vector<uint8_t> seqs; std::vector<uint64_t> limits; };
-
-// the batch handed to dyibf_classify lives in pinned host memory (its upload then runs at PCIe speed), grown on demand
+// batch text lives in pinned host memory (its upload then runs at PCIe speed), grown on demand
 struct PinnedBytes
 {
     uint8_t * p = nullptr; size_t cap = 0, n = 0;
@@ -102,12 +98,189 @@ struct PinnedBytes
     }
 };
 
-void parse(int device, const std::string & path, Records & r)
+// the text of one batch from one file: a view into the mapped file, or an own pinned copy (inflated input)
+struct Piece
 {
-    std::vector<char> text;
-    readAll(path, text);
+    PinnedBytes own;
+    const uint8_t * p = nullptr; size_t n = 0;
+    void clear() { own.clear(); p = nullptr; n = 0; }
+    void view(const uint8_t * src, size_t len) { p = src; n = len; }
+    void copy(const uint8_t * src, size_t len) { own.append(src, len); p = own.p; n = own.n; }
+};
+
+// position behind the want-th '\n' of [p, p + n), or n (and *found < want) when there are fewer
+size_t skipLines(const char * p, size_t n, uint64_t want, uint64_t * found)
+{
+    uint64_t cnt = 0;
+    size_t i = 0;
+    const __m128i nl = _mm_set1_epi8('\n');
+    // whole 64-byte blocks while the remaining lines cannot end inside one
+    while (i + 64 <= n && cnt + 64 < want)
+    {
+        const unsigned m0 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i)), nl));
+        const unsigned m1 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i + 16)), nl));
+        const unsigned m2 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i + 32)), nl));
+        const unsigned m3 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i + 48)), nl));
+        cnt += (uint64_t)__builtin_popcountll((uint64_t)m0 | ((uint64_t)m1 << 16) | ((uint64_t)m2 << 32) | ((uint64_t)m3 << 48));
+        i += 64;
+    }
+    for (; i < n && cnt < want; ++i) cnt += p[i] == '\n';
+    *found = cnt;
+    return i;
+}
+
+// One input file cut into batches of whole records.  A plain file is mapped and the batches are views into the mapping (no
+// copy in this program: the library stages pageable memory through pinned pieces with its helper threads); a gzip file is
+// inflated piece by piece into a buffer and the batches are pinned copies.
+struct Source
+{
+    gzFile gz = nullptr;
+    std::string path;
+    std::vector<char> buf;            // inflated text (gzip input)
+    const char * map = nullptr; size_t mapSize = 0;
+    size_t begin = 0, end = 0;        // unread text: [begin, end) of data()
+    bool eof = false, started = false;
+    int fmt = -1;
+
+    const char * data() const { return map ? map : buf.data(); }
+    void open(const std::string & p)
+    {
+        path = p;
+        unsigned char magic[2] = {0, 0};
+        FILE * fp = fopen(p.c_str(), "rb");
+        if (!fp) { std::cerr << "Unable to open reads file: " << p << std::endl; exit(1); }
+        const size_t got = fread(magic, 1, 2, fp);
+        fseeko(fp, 0, SEEK_END);
+        const off_t size = ftello(fp);
+        fclose(fp);
+        if (!(got == 2 && magic[0] == 0x1f && magic[1] == 0x8b) && size > 0)
+        {
+            const int fd = ::open(p.c_str(), O_RDONLY);
+            void * m = fd >= 0 ? mmap(nullptr, (size_t)size, PROT_READ, MAP_PRIVATE, fd, 0) : MAP_FAILED;
+            if (fd >= 0) close(fd);
+            if (m != MAP_FAILED)
+            {
+                map = (const char *)m; mapSize = end = (size_t)size; eof = true;
+                madvise(m, mapSize, MADV_SEQUENTIAL);
+            }
+        }
+        if (!map)
+        {
+            gz = gzopen(p.c_str(), "rb");                          // plain files that could not be mapped pass through
+            if (!gz) { std::cerr << "Unable to open reads file: " << p << std::endl; exit(1); }
+            gzbuffer(gz, 1 << 20);
+            buf.resize(32 << 20);
+            more();
+        }
+        fmt = formatOf(p, std::vector<char>(data(), data() + std::min<size_t>(end, 1)));
+    }
+    ~Source() { if (gz) gzclose(gz); if (map) munmap((void *)map, mapSize); }
+    // more text behind `end` (positions stay valid: the buffer only grows here); false at the end of the file
+    bool more()
+    {
+        if (eof) return false;
+        if (end == buf.size()) buf.resize(buf.size() * 2);
+        const int n = gzread(gz, buf.data() + end, (unsigned)std::min<size_t>(buf.size() - end, 1u << 30));
+        if (n < 0) { std::cerr << "Error while reading: " << path << std::endl; exit(1); }
+        if (n == 0) { eof = true; return false; }
+        end += (size_t)n;
+        return true;
+    }
+    bool have(size_t p) { while (p >= end) if (!more()) return false; return true; }
+    static bool blank(char c) { return c == '\n' || c == '\r' || c == ' ' || c == '\t'; }
+    // The text of the next (up to) `want` records -> out; returns the records cut.  *irregular: the text that follows is not
+    // something lines alone can split (nothing of it was consumed).
+    uint64_t cut(uint64_t want, Piece & out, bool * irregular)
+    {
+        *irregular = false;
+        if (!map && begin > 0) { memmove(buf.data(), buf.data() + begin, end - begin); end -= begin; begin = 0; }
+        size_t pos = begin;                                        // records [begin, pos) are complete
+        uint64_t n = 0;
+        if (!started)
+        {
+            if (!have(pos)) return 0;                              // empty file
+            if (data()[pos] != (fmt == DYIBF_FMT_FASTQ ? '@' : '>')) { *irregular = true; return 0; }
+            started = true;
+        }
+        while (n < want && have(pos))
+        {
+            if (blank(data()[pos]))
+            {
+                // white space after a record: fine when nothing but white space follows (SeqAn skips it, fasta_fastq.h:339)
+                size_t p = pos;
+                while (have(p) && blank(data()[p])) ++p;
+                if (!have(p)) { pos = end; break; }
+                *irregular = true;
+                break;
+            }
+            if (fmt == DYIBF_FMT_FASTQ)
+            {
+                // Four lines per record: the batch ends behind its 4 * n-th newline.  Only the first line is looked at here; the
+                // device tokeniser checks the layout of every record ('@' / '+' lines, lengths) and refuses what is not
+                // four-line FASTQ, so a cut at the wrong place cannot go unnoticed.
+                if (data()[pos] != '@') { *irregular = true; break; }
+                uint64_t found = 0;
+                const uint64_t lines = 4 * (want - n);
+                size_t p = pos;
+                for (;;)
+                {
+                    uint64_t f = 0;
+                    p += skipLines(data() + p, end - p, lines - found, &f);
+                    found += f;
+                    if (found == lines || !more()) break;
+                }
+                if (found < lines)
+                {
+                    // the file ends here: white space behind the last record does not count (SeqAn skips it), and the last
+                    // line may lack its newline
+                    size_t e = end;
+                    while (e > pos && blank(data()[e - 1])) --e;
+                    skipLines(data() + pos, e - pos, ~0ull, &found);
+                    found += e > pos ? 1 : 0;
+                    p = end;
+                }
+                const uint64_t recs = found / 4;
+                if (found % 4 != 0 || recs == 0) { *irregular = true; break; }     // the file ends inside a record: the tokeniser reports it
+                n += recs; pos = p;
+            }
+            else
+            {
+                // '>' at a line start opens a record; it runs to the next such '>'.  SeqAn ends a record at ANY '>': one inside
+                // a line makes the layout irregular
+                size_t p = pos;
+                bool ok = data()[p] == '>';
+                for (++p; ok;)
+                {
+                    if (!have(p)) { p = end; break; }
+                    const char * gt = (const char *)memchr(data() + p, '>', end - p);
+                    if (!gt) { p = end; continue; }
+                    p = (size_t)(gt - data());
+                    ok = data()[p - 1] == '\n';
+                    break;
+                }
+                if (!ok) { *irregular = true; break; }
+                pos = p; ++n;
+            }
+        }
+        if (map) out.view((const uint8_t *)data() + begin, pos - begin);
+        else out.copy((const uint8_t *)data() + begin, pos - begin);
+        begin = pos;
+        return n;
+    }
+    // everything that is left
+    void rest(std::vector<char> & out)
+    {
+        while (more()) {}
+        out.assign(data() + begin, data() + end);
+        begin = end;
+    }
+};
+
+struct Records { std::vector<uint8_t> seqs; std::vector<uint64_t> limits; };
+
+void parseText(int device, const std::string & path, int fmt, const std::vector<char> & text, Records & r)
+{
     uint64_t n = 0, nb = 0;
-    const int fmt = formatOf(path, text);
     int rc = dyibf_parse_records(device, text.data(), text.size(), fmt, DYIBF_ALPHA_DNA5, nullptr, 0, nullptr, 0, 0, &n, &nb, DYIBF_MEM_HOST, nullptr);
     if (rc == DYIBF_OK)
     {
@@ -118,13 +291,30 @@ void parse(int device, const std::string & path, Records & r)
     if (rc != DYIBF_OK) { std::cerr << path << ": " << dyibf_last_error() << std::endl; exit(1); }
 }
 
+// a batch of text on its way from the reader thread to the GPU
+struct TextBatch
+{
+    Piece text[2];
+    uint64_t n = 0;                   // records (pairs) in it
+    bool rest = false, last = false;  // rest: restText holds everything from here on (irregular layout)
+    std::vector<char> restText[2];
+};
+
+struct BatchQueue
+{
+    std::mutex m; std::condition_variable cv;
+    std::vector<TextBatch *> ready, spare;
+    TextBatch * take(std::vector<TextBatch *> & q) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return !q.empty(); }); TextBatch * b = q.front(); q.erase(q.begin()); return b; }
+    void give(std::vector<TextBatch *> & q, TextBatch * b) { { std::lock_guard<std::mutex> l(m); q.push_back(b); } cv.notify_all(); }
+};
+
 } // namespace
 
 int main(int argc, char ** argv)
 {
     std::string filterFile, outFile;
     std::vector<std::string> inputs;
-    int e = 5, verbose = 0, device = 0, inflight = 3;
+    int e = 5, verbose = 0, device = 0, inflight = 4;
     std::vector<int> devices;
     uint64_t readsBatch = 100000;
     for (int i = 1; i < argc; ++i)
@@ -152,7 +342,7 @@ int main(int argc, char ** argv)
     }
     if (filterFile.empty() || inputs.empty() || inputs.size() > 2) usage("need -fi FILTER and one or two reads files");
     const bool paired = inputs.size() == 2;
-    inflight = std::min<int>(inflight, 4 * (int)std::max<size_t>(devices.size(), 1));   // four tickets per GPU (dyibf.h)
+    inflight = std::min<int>(inflight, 8 * (int)std::max<size_t>(devices.size(), 1));   // eight tickets per GPU (dyibf.h)
 
     const double t0 = now();
     dyibf_filter * filter = nullptr;
@@ -169,24 +359,64 @@ int main(int argc, char ** argv)
     if (grp) dyibf_group_get_params(grp, &prm, nullptr, nullptr); else dyibf_get_params(filter, &prm);
     const double loadFilter = now() - t0;
 
-    const double t1 = now();
-    Records m1, m2;
-    parse(device, inputs[0], m1);
-    if (paired)
+    // ---- the reader thread: files -> batches of text ----
+    Source src[2];
+    src[0].open(inputs[0]);
+    if (paired) { src[1].open(inputs[1]); if (src[1].fmt != src[0].fmt) { std::cerr << "The two reads files differ in format." << std::endl; return 1; } }
+    const int fmt = src[0].fmt;
+    BatchQueue bq;
+    std::vector<TextBatch> pool((size_t)inflight + 3);
+    for (auto & b : pool) bq.spare.push_back(&b);
+    double loadReads = 0;
+    std::thread reader([&]
     {
-        parse(device, inputs[1], m2);
-        if (m2.limits.size() != m1.limits.size()) { std::cerr << "The two reads files hold different numbers of records." << std::endl; return 1; }
-    }
-    const uint64_t nReads = m1.limits.size() - 1;                        // reads, or pairs
-    const double loadReads = now() - t1;
+        for (bool done = false; !done;)
+        {
+            TextBatch * b = bq.take(bq.spare);
+            const double ta = now();
+            b->text[0].clear(); b->text[1].clear(); b->rest = false; b->last = false;
+            b->restText[0].clear(); b->restText[1].clear();
+            bool irr0 = false, irr1 = false;
+            const uint64_t n0 = src[0].cut(readsBatch, b->text[0], &irr0);
+            const uint64_t n1 = paired ? src[1].cut(n0, b->text[1], &irr1) : n0;   // the mates: the same number of records
+            b->n = n0;
+            if (!irr0 && !irr1 && n1 == n0)
+            {
+                b->last = done = n0 < readsBatch;                    // a short batch: the end of the file
+                loadReads += now() - ta;
+                bq.give(bq.ready, b);
+                continue;
+            }
+            // From here on lines alone cannot split the text (or the two files fell out of step): the rest of the file(s) goes
+            // over in one piece.  Records cut in step just before go first as a normal batch; otherwise their text leads the rest.
+            TextBatch * r = b;
+            if (n1 == n0 && n0 > 0)
+            {
+                bq.give(bq.ready, b);
+                r = bq.take(bq.spare);
+                r->text[0].clear(); r->text[1].clear(); r->restText[0].clear(); r->restText[1].clear();
+            }
+            else
+                for (int i = 0; i < 2; ++i) r->restText[i].assign((const char *)b->text[i].p, (const char *)b->text[i].p + b->text[i].n);
+            std::vector<char> tail;
+            for (int i = 0; i < (paired ? 2 : 1); ++i)
+            {
+                src[i].rest(tail);
+                r->restText[i].insert(r->restText[i].end(), tail.begin(), tail.end());
+            }
+            r->n = 0; r->rest = true; r->last = done = true;
+            loadReads += now() - ta;
+            bq.give(bq.ready, r);
+        }
+    });
 
     std::ofstream out;
     if (!outFile.empty()) { out.open(outFile); if (!out) { std::cerr << "Unable to open " << outFile << std::endl; return 1; } }
     double filterReads = 0;
-    uint64_t filteredReads = 0, batchNo = 0;
+    uint64_t filteredReads = 0, batchNo = 0, nReads = 0;
     std::vector<uint64_t> binOffsets(prm.bins + 1); std::vector<uint32_t> ids, order(prm.bins);
-    // a ring of batches in flight: each owns its pinned read bytes and limits until its ticket has ended
-    struct InFlight { PinnedBytes seqs; std::vector<uint64_t> limits; dyibf_ticket * ticket = nullptr; uint64_t n = 0, batchNo = 0; uint16_t threshold = 0; };
+    // a ring of batches in flight: each owns its ticket (and, on the parsed path, its pinned read bytes and limits) until it has ended
+    struct InFlight { PinnedBytes seqs; std::vector<uint64_t> limits; dyibf_ticket * ticket = nullptr; uint64_t n = 0, batchNo = 0; uint32_t threshold = 0; TextBatch * text = nullptr; };
     std::vector<InFlight> ring((size_t)inflight);
     auto finish = [&](InFlight & fl) -> bool
     {
@@ -199,6 +429,7 @@ int main(int argc, char ** argv)
             rc = dyibf_classify_end(fl.ticket, binOffsets.data(), ids.data(), ids.size(), &total);
         }
         fl.ticket = nullptr;
+        if (fl.text) { bq.give(bq.spare, fl.text); fl.text = nullptr; }
         if (rc != DYIBF_OK) { std::cerr << dyibf_last_error() << std::endl; return false; }
         // threshold 0: the reference pushes every read id (of the SE numbering) to every bin first and then still runs the loop (:320-333)
         const uint64_t pre = fl.threshold == 0 ? (paired ? 2 * fl.n : fl.n) : 0;
@@ -219,45 +450,99 @@ int main(int argc, char ** argv)
         }
         return true;
     };
-    const double tFilter = now();
-    for (uint64_t first = 0; first < nReads; first += readsBatch, ++batchNo)
+    auto warnZero = [] {
+        std::cerr << "[WARNING!] 0 k-mer is required to filter a read!\nAll reads will pass filteration and be mapped everywhere.\n "
+                     "This will be extremly slow.\n Choose an approprate error rate based on kmer size and read length\n";
+    };
+    // the parsed path: batches cut from parsed records (irregular layouts)
+    auto runParsed = [&](const Records & m1, const Records & m2) -> bool
     {
-        InFlight & fl = ring[batchNo % ring.size()];
-        if (fl.ticket && !finish(fl)) return 1;                          // the oldest batch leaves the ring, in batch order
-        const uint64_t n = std::min(readsBatch, nReads - first);
-        // the batch's forward read set: [reads] or [mates 1 | mates 2] (src/file_pair.h:82-88)
-        fl.seqs.clear(); fl.limits.assign(1, 0); fl.n = n; fl.batchNo = batchNo;
-        for (const Records * r : {(const Records *)&m1, paired ? (const Records *)&m2 : (const Records *)nullptr})
+        const uint64_t nRec = m1.limits.size() - 1;
+        for (uint64_t first = 0; first < nRec; first += readsBatch, ++batchNo)
         {
-            if (!r) continue;
-            const uint64_t b0 = r->limits[first], b1 = r->limits[first + n];
-            const uint64_t base = fl.seqs.n;
-            fl.seqs.append(r->seqs.data() + b0, b1 - b0);
-            for (uint64_t i = 1; i <= n; ++i) fl.limits.push_back(base + r->limits[first + i] - b0);
+            InFlight & fl = ring[batchNo % ring.size()];
+            if (fl.ticket && !finish(fl)) return false;                  // the oldest batch leaves the ring, in batch order
+            const uint64_t n = std::min(readsBatch, nRec - first);
+            // the batch's forward read set: [reads] or [mates 1 | mates 2] (src/file_pair.h:82-88)
+            fl.seqs.clear(); fl.limits.assign(1, 0); fl.n = n; fl.batchNo = batchNo;
+            for (const Records * r : {(const Records *)&m1, paired ? (const Records *)&m2 : (const Records *)nullptr})
+            {
+                if (!r) continue;
+                const uint64_t b0 = r->limits[first], b1 = r->limits[first + n];
+                const uint64_t base = fl.seqs.n;
+                fl.seqs.append(r->seqs.data() + b0, b1 - b0);
+                for (uint64_t i = 1; i <= n; ++i) fl.limits.push_back(base + r->limits[first + i] - b0);
+            }
+            // clasifyLoadedReads, d_mapper.h:308-375
+            const uint64_t nSeqs = fl.limits.size() - 1;                 // forward sequences; the set the reference sees is twice that
+            const uint16_t avgReadLen = (uint16_t)(nSeqs ? fl.limits.back() / nSeqs : 0);   // lengthSum / (2 numReads), both doubled by the rc half
+            fl.threshold = dyibf_threshold(e, prm.kmer, avgReadLen);
+            if (fl.threshold == 0) warnZero();
+            if (fl.seqs.n == 0) { const uint8_t zero = 0; fl.seqs.append(&zero, 1); }
+            const int rc = grp ? dyibf_group_classify_begin(grp, fl.seqs.p, fl.limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, fl.threshold, &fl.ticket)
+                               : dyibf_classify_begin(filter, fl.seqs.p, fl.limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, fl.threshold, &fl.ticket);
+            if (rc != DYIBF_OK) { std::cerr << dyibf_last_error() << std::endl; return false; }
+            nReads += n;
         }
-        // clasifyLoadedReads, d_mapper.h:308-375
-        const uint64_t nSeqs = fl.limits.size() - 1;                     // forward sequences; the set the reference sees is twice that
-        const uint16_t avgReadLen = (uint16_t)(nSeqs ? fl.limits.back() / nSeqs : 0);   // lengthSum / (2 numReads), both doubled by the rc half
-        fl.threshold = dyibf_threshold(e, prm.kmer, avgReadLen);
-        if (fl.threshold == 0)
-            std::cerr << "[WARNING!] 0 k-mer is required to filter a read!\nAll reads will pass filteration and be mapped everywhere.\n "
-                         "This will be extremly slow.\n Choose an approprate error rate based on kmer size and read length\n";
-        if (fl.seqs.n == 0) { const uint8_t zero = 0; fl.seqs.append(&zero, 1); }
-        const int rc = grp ? dyibf_group_classify_begin(grp, fl.seqs.p, fl.limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, fl.threshold, &fl.ticket)
-                           : dyibf_classify_begin(filter, fl.seqs.p, fl.limits.data(), (uint32_t)nSeqs, DYIBF_ENC_ASCII, paired ? 4 : 2, 1, fl.threshold, &fl.ticket);
-        if (rc != DYIBF_OK) { std::cerr << dyibf_last_error() << std::endl; return 1; }
+        return true;
+    };
+    const double tFilter = now();
+    bool ok = true;
+    for (bool last = false; ok && !last;)
+    {
+        TextBatch * b = bq.take(bq.ready);
+        last = b->last;
+        if (b->rest)
+        {
+            Records m1, m2;
+            const double ta = now();
+            parseText(device, inputs[0], fmt, b->restText[0], m1);
+            if (paired)
+            {
+                parseText(device, inputs[1], fmt, b->restText[1], m2);
+                if (m2.limits.size() != m1.limits.size()) { std::cerr << "The two reads files hold different numbers of records." << std::endl; ok = false; }
+            }
+            loadReads += now() - ta;
+            ok = ok && runParsed(m1, m2);
+            bq.give(bq.spare, b);
+            continue;
+        }
+        if (b->n == 0) { bq.give(bq.spare, b); continue; }
+        InFlight & fl = ring[batchNo % ring.size()];
+        if (fl.ticket && !finish(fl)) { ok = false; break; }
+        fl.n = b->n; fl.batchNo = batchNo++; fl.text = b;
+        uint32_t nr = 0;
+        // several GPUs: successive batches to successive replicas, through the member handles
+        dyibf_filter * target = filter;
+        if (grp) dyibf_group_member(grp, (int)(fl.batchNo % devices.size()), &target, nullptr, nullptr);
+        const int rc = dyibf_classify_text_begin(target, (const char *)b->text[0].p, b->text[0].n, paired ? (const char *)b->text[1].p : nullptr,
+                                                 paired ? b->text[1].n : 0, fmt, e, &nr, &fl.threshold, &fl.ticket);
+        if (rc != DYIBF_OK) { std::cerr << dyibf_last_error() << std::endl; ok = false; break; }
+        if (nr != b->n) { std::cerr << "batch " << fl.batchNo << ": " << nr << " records tokenised, " << b->n << " cut" << std::endl; ok = false; break; }
+        if (fl.threshold == 0) warnZero();
+        nReads += b->n;
+        bq.give(bq.spare, b); fl.text = nullptr;                         // the text is on the device: the reader may refill the buffer
     }
-    for (uint64_t i = 0; i < ring.size(); ++i)                           // drain, oldest first
+    for (uint64_t i = 0; ok && i < ring.size(); ++i)                     // drain, oldest first
     {
         InFlight & fl = ring[(batchNo + i) % ring.size()];
-        if (fl.ticket && !finish(fl)) return 1;
+        if (fl.ticket && !finish(fl)) ok = false;
     }
+    if (!ok)
+    {
+        // unblock and join the reader before leaving
+        for (auto & fl : ring) if (fl.ticket) dyibf_classify_cancel(fl.ticket);
+        std::thread drain([&] { for (;;) { TextBatch * b = bq.take(bq.ready); const bool l = b->last; bq.give(bq.spare, b); if (l) break; } });
+        reader.join(); drain.detach();
+        return 1;
+    }
+    reader.join();
     filterReads = now() - tFilter;
     if (verbose > 0)
     {
         const double total = (now() - t0) / 100.0;
         std::cerr << "\nFilter loading time:\t\t" << loadFilter << " sec\t\t" << loadFilter / total << " %" << std::endl;
-        std::cerr << "Reads loading time:\t\t" << loadReads << " sec\t\t" << loadReads / total << " %" << std::endl;
+        std::cerr << "Reads loading time:\t\t" << loadReads << " sec\t\t" << loadReads / total << " %  (reader thread, overlapped)" << std::endl;
         std::cerr << "Reads filtering time:\t\t" << filterReads << " sec\t\t" << filterReads / total << " %" << std::endl;
         std::cerr << "Reads count:\t\t\t" << nReads * (paired ? 2 : 1) << std::endl;
         std::cerr << "Avg reads per bin:\t\t" << (double)filteredReads / prm.bins << std::endl;
