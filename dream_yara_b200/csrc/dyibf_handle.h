@@ -71,7 +71,7 @@ struct dyibf_filter {
     dyibf::DevBuf batch_bytes, batch_offsets, csr_off, csr_ids, gather_ws, gather_out, gather_ids;
     dyibf::ResidentBatch batch;
     std::vector<uint64_t> h_csr_off;
-    uint32_t     query_flags = 0;         // QUERY_* (dyibf_set_option)
+    uint32_t     query_flags = dyibf::QUERY_EARLY_EXIT;   // QUERY_* (dyibf_set_option); early exit is on by default
     int64_t      bucket_mib = -1;         // DYIBF_OPT_BUILD_BUCKET_MIB: -1 auto, 0 direct atomics only
     int64_t      query_chunk_mib = 0;     // DYIBF_OPT_QUERY_CHUNK_MIB: 0 = auto
     int64_t      build_chunk_mib = 0;     // DYIBF_OPT_BUILD_CHUNK_MIB: bases per host-mode build chunk (0 = auto)

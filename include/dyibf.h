@@ -302,12 +302,14 @@ int  dyibf_group_clear_bins(dyibf_group* g, const uint32_t* bins, uint32_t n);
 
 /* ---- options ------------------------------------------------------------------------------- */
 
-/* DYIBF_OPT_EARLY_EXIT (default 0).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it
+/* DYIBF_OPT_EARLY_EXIT (default 1).  whichBins (d_bloom_filter.h:178-217) looks every k-mer of a sequence up before it
  * thresholds the counts (:219-223).  With this option on, and when no per-bin counts are requested, the query kernel
  * stops a sequence as soon as its bin set is decided: every bin has either reached the threshold, was already selected
  * by an earlier strand/mate of the same row (the selection only ever ORs), or cannot reach the threshold with the
- * k-mers left (count + remaining < threshold).  The rows are bit-identical to the full pass; only memory traffic
- * drops (e.g. 150 bp, k=18, e=3: ~57 % of the lookups). */
+ * k-mers left (count + remaining < threshold).  The rows are bit-identical to the full pass (checked against the oracle at
+ * every threshold in tests/test_gpu_parity.py); only memory traffic drops (150 bp, k=18, e=3: 59 % of the lookups, 1.66 x
+ * the reads/s).  On by default since round 2 — the mapper never asks for counts; 0 restores the reference's every-k-mer
+ * pass, which is what bench.py's headline value / e2e / roofline measure (fixed algorithmic bytes per read). */
 #define DYIBF_OPT_EARLY_EXIT 1
 /* DYIBF_OPT_BUILD_BUCKET_MIB (default -1 = auto: what the call's updates need, up to 64 GiB, at most half of the free HBM; 0 = off).  _insertKmer's
  * single-bit ORs land at uniformly random words of the table.  For tables larger than the L2 and calls with at least 32 M

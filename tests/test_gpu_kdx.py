@@ -27,6 +27,7 @@ def test_kdx_ka1_file_rows_counts_and_add(dy, golden, kdx_golden, tmp_path):
     assert f.save(path)
     assert ka.md5_file(path) == str(kdx_golden["kx1_md5"])
     assert np.array_equal(f.download_words(f.n_words - 4, 4), kdx_golden["kx1_trailer"])
+    f.set_early_exit(False)
     assert np.array_equal(f.whichBinsBatch(reads, 53, group=2, derive_rc=True), kdx_golden["kx1_rows"])
     f.set_early_exit(True)
     assert np.array_equal(f.whichBinsBatch(reads, 53, group=2, derive_rc=True), kdx_golden["kx1_rows"])

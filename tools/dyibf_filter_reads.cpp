@@ -27,6 +27,7 @@
 #include <emmintrin.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <cstdint>
@@ -141,6 +142,8 @@ struct Source
     size_t begin = 0, end = 0;        // unread text: [begin, end) of data()
     bool eof = false, started = false;
     int fmt = -1;
+    std::vector<std::thread> prefault;
+    std::atomic<bool> stopPrefault{false};
 
     const char * data() const { return map ? map : buf.data(); }
     void open(const std::string & p)
@@ -162,6 +165,22 @@ struct Source
             {
                 map = (const char *)m; mapSize = end = (size_t)size; eof = true;
                 madvise(m, mapSize, MADV_SEQUENTIAL);
+                // page-cache pages are mapped on first touch (~0.5 us per 4 KiB page: 0.4 s for a 3 GB file, as long as the
+                // whole scan): four helper threads populate the page tables ahead of the cutter, stripe by stripe
+                for (int t = 0; t < 4; ++t)
+                    prefault.emplace_back([this, t]
+                    {
+                        const size_t stripe = 32u << 20;
+                        for (size_t off = (size_t)t * stripe; off < mapSize && !stopPrefault; off += 4 * stripe)
+                        {
+                            const size_t len = std::min(stripe, mapSize - off);
+#ifdef MADV_POPULATE_READ
+                            if (madvise((void *)(map + off), len, MADV_POPULATE_READ) == 0) continue;
+#endif
+                            volatile char sink = 0;
+                            for (size_t i = 0; i < len; i += 4096) sink = sink + map[off + i];
+                        }
+                    });
             }
         }
         if (!map)
@@ -174,7 +193,13 @@ struct Source
         }
         fmt = formatOf(p, std::vector<char>(data(), data() + std::min<size_t>(end, 1)));
     }
-    ~Source() { if (gz) gzclose(gz); if (map) munmap((void *)map, mapSize); }
+    ~Source()
+    {
+        stopPrefault = true;
+        for (auto & t : prefault) t.join();
+        if (gz) gzclose(gz);
+        if (map) munmap((void *)map, mapSize);
+    }
     // more text behind `end` (positions stay valid: the buffer only grows here); false at the end of the file
     bool more()
     {
