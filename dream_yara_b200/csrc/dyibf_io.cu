@@ -10,7 +10,7 @@
 // In HBM only the P*W data words are kept; the (all-zero) gap before the trailer and the trailer itself are
 // synthesised when the filter is downloaded or saved, so a saved file is byte-identical to the reference's.
 //
-// Pipeline: T file threads (default: the host's cores, 4..16) pread chunks (4 MiB) of the data words into a ring of 2 T pinned buffers (allocated
+// Pipeline: T file threads (default: half of the host's cores, 4..16) pread chunks (4 MiB) of the data words into a ring of 2 T pinned buffers (allocated
 // once per process); ONE thread issues the copies in file order: cudaMemcpyAsync(H2D) -> (replicas: cudaMemcpyPeerAsync
 // device 0 -> the others over NVLink, on the same stream), so that file reads, PCIe and NVLink all overlap.  A bin shard
 // (device r of G owns word columns [r W/G, (r+1) W/G) of every block) is a pitched copy out of the same pinned chunk.
@@ -32,7 +32,7 @@ using namespace dyibf;
 
 namespace dyibf {
 
-static std::atomic<int> g_io_threads{0};            // 0 = not set: the host's cores, between 4 and 16
+static std::atomic<int> g_io_threads{0};            // 0 = not set: half of the host's cores, between 4 and 16
 
 // Pinned staging for the transfer threads: allocated once per process and kept (cudaMallocHost costs ~0.6 s per GiB, as
 // much as the transfer of several GiB).  2 buffers x IO_CHUNK_BYTES per thread slot.
@@ -156,7 +156,7 @@ static int stream_words(int fd, const char* path, char* host, bool to_device, ui
     const uint64_t bpc = blocks_per_chunk(W, chunk_bytes);
     const int64_t n_chunks = (int64_t)((n_blocks + bpc - 1) / bpc);
     int T = g_io_threads.load();
-    if (T < 1) T = (int)std::min(16u, std::max(4u, std::thread::hardware_concurrency()));
+    if (T < 1) T = (int)std::min(16u, std::max(4u, std::thread::hardware_concurrency() / 2));   // 8 on a 16-core box: 50.6 GB/s (16 threads: 43.6)
     if ((int64_t)T > n_chunks) T = (int)std::max<int64_t>(n_chunks, 1);
     const int N = 2 * T;                                              // slots: T being read or written, T in the copy queue
     const size_t buf_bytes = (size_t)(bpc * W * 8);

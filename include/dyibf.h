@@ -119,9 +119,9 @@ int  dyibf_save_file(dyibf_filter* f, const char* path);
 /* The loader / writer behind dyibf_load_file* / dyibf_save_file (and their group forms) streams the file through pinned
  * host buffers with several file threads (pread / pwrite) and one thread issuing the asynchronous copies; this is the stage the mapper prints as
  * "Filter loading time" (src/d_mapper.h:913-921); dyibf_upload_words / dyibf_download_words of whole blocks use the same
- * pipeline.  dyibf_set_io_threads: 1..64, 0 = default (the host's cores, between 4 and 16), process-wide.
- * Measured on a B200 box with 16 host cores, 16 GiB filter in the page cache: 7.4 / 26 / 43 / 45 GB/s with 1 / 4 / 8 / 16 threads
- * (pinned H2D of the box: 52 GB/s).
+ * pipeline.  dyibf_set_io_threads: 1..64, 0 = default (half of the host's cores, between 4 and 16), process-wide.
+ * Measured on B200 boxes with 16 host cores, 16 GiB filter in the page cache: 7.3 / 26–33 / 43–51 / 44–45 GB/s with 1 / 4 / 8 / 16
+ * threads (pinned H2D of the box: 52 GB/s).
  * dyibf_last_io_stats: the calling thread's last load or save. */
 typedef struct dyibf_io_stats {
     uint64_t bytes;               /* data-word bytes moved between the file and HBM                         */

@@ -86,6 +86,28 @@ def test_build_and_update_cli(tools, golden, oracle, tmp_path):
     _write_fasta(u / "64.fna", [("x", genomes[0])])
     r = subprocess.run([update, str(filt), str(u / "64.fna")], capture_output=True, text=True)
     assert r.returncode == 1 and "has only 64 Bins" in r.stderr
+    # SeqAn's reader rules (readRecord into an IupacString): a '>' in the middle of a FASTA line starts a new record, a character
+    # outside the IUPAC alphabet aborts.  The device tokeniser (dyibf_parse_records, pinned against the compiled reference) says
+    # what the records are; the tool must add exactly those.
+    from dream_yara_b200.ingest import parseRecords
+    text = b">r1 x\n" + genomes[3][:700] + b">mid line\n" + genomes[3][700:1500] + b"\n>short\nACGT\n"
+    with open(u / "7.fa", "wb") as fh:
+        fh.write(text)
+    r = subprocess.run([update, str(filt), str(u / "7.fa")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    seqs, limits = parseRecords(text, 0, iupac=True)
+    assert limits.size - 1 == 3
+    oracle.clear_bins(words, p, [7])
+    for i in range(limits.size - 1):
+        rec = seqs[int(limits[i]):int(limits[i + 1])]
+        if rec.size >= 19:
+            oracle.add_kmers(words, p, oracle.encode_ascii(rec.tobytes()), 7)
+    oracle.save(words, p, tmp_path / "want2.filter")
+    assert ka.md5_file(filt) == ka.md5_file(tmp_path / "want2.filter")
+    with open(u / "8.fa", "wb") as fh:
+        fh.write(b">bad\nACGTACGTACGTACGTACGT-ACGTACGTACGTACGT\n")
+    r = subprocess.run([update, str(filt), str(u / "8.fa")], capture_output=True, text=True)
+    assert r.returncode == 1 and "ParseError" in r.stderr
 
 
 @pytest.mark.gpu

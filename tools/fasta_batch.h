@@ -63,8 +63,23 @@ struct Batch
     bool empty() const { return binIds.empty(); }
 };
 
-// Reads FASTA or FASTQ (decided by the first non-blank character), plain or gzip.  Multi-line FASTA records are
-// joined; whitespace inside sequence lines is dropped.  Records shorter than k are skipped.
+// Reads FASTA or FASTQ (decided by the first '>' or '@'), plain or gzip, with the rules of SeqAn's readRecord into an
+// IupacString (seq_io/fasta_fastq.h:268-345), which is what addFastaFile uses: a FASTA record ends at ANY '>' (not only at a
+// line start); white space inside the sequence is dropped; a character outside the IUPAC alphabet is a ParseError (the
+// reference tool aborts: here a std::runtime_error, the tools print it and exit 1); FASTQ qualities are counted without
+// white space until there are as many as bases, and the next record must follow.  Records shorter than k are skipped.
+// (The device tokeniser dyibf_parse_records(DYIBF_ALPHA_IUPAC) applies the same rules; tests/test_tools.py feeds both the
+// same malformed files.)
+inline bool iupacChar(char c)
+{
+    switch (c >= 'a' && c <= 'z' ? c - 32 : c)
+    {
+        case 'A': case 'C': case 'G': case 'T': case 'U': case 'M': case 'R': case 'W': case 'S': case 'Y': case 'K':
+        case 'V': case 'H': case 'D': case 'B': case 'N': return true;
+        default: return false;
+    }
+}
+
 inline void appendFastaRecords(Batch & out, const std::string & path, uint32_t binNo, uint32_t k)
 {
     gzFile gz = gzopen(path.c_str(), "rb");
@@ -73,7 +88,7 @@ inline void appendFastaRecords(Batch & out, const std::string & path, uint32_t b
     gzbuffer(gz, 1 << 20);
     std::vector<char> buf(1 << 20);
     enum { START, HEADER, SEQ, FQ_SEQ, FQ_PLUS, FQ_QUAL } st = START;
-    bool fastq = false;
+    bool fastq = false, afterFastqRecord = false;
     uint64_t recStart = out.concat.size();
     uint64_t qualLeft = 0;
     auto finish = [&]() {
@@ -81,7 +96,11 @@ inline void appendFastaRecords(Batch & out, const std::string & path, uint32_t b
         else out.concat.resize(recStart);
         recStart = out.concat.size();
     };
-    bool lineStart = true;
+    auto blank = [](char c) { return c == '\n' || c == '\r' || c == ' ' || c == '\t' || c == '\v' || c == '\f'; };
+    auto base = [&](char c) {
+        if (!iupacChar(c)) { gzclose(gz); throw std::runtime_error("ParseError in " + path + ": character '" + std::string(1, c) + "' is not in the IUPAC alphabet"); }
+        out.concat.push_back((uint8_t)c);
+    };
     int n;
     while ((n = gzread(gz, buf.data(), (unsigned)buf.size())) > 0)
     {
@@ -91,28 +110,27 @@ inline void appendFastaRecords(Batch & out, const std::string & path, uint32_t b
             switch (st)
             {
                 case START:
-                    if (c == '>') { fastq = false; st = HEADER; }
+                    if (c == '>' && !afterFastqRecord) { fastq = false; st = HEADER; }
                     else if (c == '@') { fastq = true; st = HEADER; }
+                    else if (afterFastqRecord && !blank(c))
+                    { gzclose(gz); throw std::runtime_error("ParseError in " + path + ": Fastq quality string is expected to be of the same length as the sequence"); }
                     break;
                 case HEADER:
-                    if (c == '\n') { st = fastq ? FQ_SEQ : SEQ; recStart = out.concat.size(); lineStart = true; }
+                    if (c == '\n') { st = fastq ? FQ_SEQ : SEQ; recStart = out.concat.size(); }
                     break;
                 case SEQ:
-                    if (c == '\n') lineStart = true;
-                    else if (lineStart && c == '>') { finish(); st = HEADER; }
-                    else { lineStart = false; if (c != '\r' && c != ' ' && c != '\t') out.concat.push_back((uint8_t)c); }
+                    if (c == '>') { finish(); st = HEADER; }
+                    else if (!blank(c)) base(c);
                     break;
                 case FQ_SEQ:
-                    if (c == '\n') lineStart = true;
-                    else if (lineStart && c == '+') { st = FQ_PLUS; qualLeft = out.concat.size() - recStart; }
-                    else { lineStart = false; if (c != '\r' && c != ' ' && c != '\t') out.concat.push_back((uint8_t)c); }
+                    if (c == '+') { st = FQ_PLUS; qualLeft = out.concat.size() - recStart; }
+                    else if (!blank(c)) base(c);
                     break;
                 case FQ_PLUS:
-                    if (c == '\n') { st = FQ_QUAL; if (qualLeft == 0) { finish(); st = START; } }
+                    if (c == '\n') { st = FQ_QUAL; if (qualLeft == 0) { finish(); st = START; afterFastqRecord = true; } }
                     break;
                 case FQ_QUAL:
-                    if (c == '\n' || c == '\r') { if (qualLeft == 0) { finish(); st = START; } }
-                    else if (qualLeft) --qualLeft;
+                    if (!blank(c) && --qualLeft == 0) { finish(); st = START; afterFastqRecord = true; }
                     break;
             }
         }
@@ -121,7 +139,9 @@ inline void appendFastaRecords(Batch & out, const std::string & path, uint32_t b
     gzclose(gz);
     if (bad)
         throw std::runtime_error("Error while reading contigs File: " + path);
-    if (st == SEQ || st == FQ_SEQ || st == FQ_QUAL || st == FQ_PLUS) finish();
+    if (st == SEQ) finish();
+    else if (st == FQ_SEQ || st == FQ_QUAL || st == FQ_PLUS || (st == HEADER && fastq))
+        throw std::runtime_error("UnexpectedEnd in " + path + ": the file ends inside a record");
 }
 
 } // namespace dyibf_tools
