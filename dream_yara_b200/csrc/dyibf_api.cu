@@ -755,16 +755,51 @@ int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int form
     CU(launch_ingest_count(d_text, n_bytes, format, iupac, ws, st));
     uint64_t tot[6];
     CU(ingest_read_totals(ws, n_bytes, tot, st));
-    static const char* const what[] = {"", "character outside the sequence alphabet", "not in the four-line FASTQ layout",
-                                       "quality string and sequence differ in length", "truncated FASTQ record"};
+    static const char* const what[] = {"", "character outside the sequence alphabet", "not a FASTQ record",
+                                       "quality string and sequence differ in length", "truncated FASTQ record",
+                                       "a FASTQ record that starts right behind the previous qualities, without white space (not supported by the device reader)"};
     auto format_error = [&](uint64_t word) {
         const uint64_t pos = word >> 8; const unsigned code = (unsigned)(word & 0xff);
-        return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: %s at byte %llu", code < 5 ? what[code] : "parse error", (unsigned long long)pos);
+        return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: %s at byte %llu", code < 6 ? what[code] : "parse error", (unsigned long long)pos);
+    };
+    // FASTQ the four-line tokeniser refuses (wrapped lines, blank lines between records, or a real error): SeqAn's sequential
+    // rules through the speculative parser of ingest_general.cu, which either yields the records or the reference's error
+    auto general_fastq = [&]() -> int {
+        FastqGeneral fq;
+        uint64_t ns = 0, nb = 0, errw = ~0ull;
+        int rc = fq.count(d_text, n_bytes, iupac, st, &ns, &nb, &errw);
+        if (rc) return rc;
+        if (errw != ~0ull) return format_error(errw);
+        *n_seqs = ns; *n_bases = nb;
+        if (sizing) return DYIBF_OK;
+        if (!out_limits || (nb && !out_seqs)) return fail(DYIBF_ERR_ARG, "dyibf_parse_records: NULL output");
+        if (ns > capacity_seqs || nb > capacity_bytes)
+            return fail(DYIBF_ERR_CAPACITY, "dyibf_parse_records: %llu records / %llu sequence characters do not fit the output buffers",
+                        (unsigned long long)ns, (unsigned long long)nb);
+        uint8_t* d_seqs = out_seqs; uint64_t* d_limits = out_limits;
+        if (mem == DYIBF_MEM_HOST) {
+            CU(cudaMalloc(&tmp.p[2], nb + 16));
+            CU(cudaMalloc(&tmp.p[3], (ns + 1) * 8));
+            d_seqs = static_cast<uint8_t*>(tmp.p[2]); d_limits = static_cast<uint64_t*>(tmp.p[3]);
+        }
+        rc = fq.emit(d_seqs, d_limits, limit_base, st);
+        if (rc) return rc;
+        if (mem == DYIBF_MEM_HOST) {
+            if (nb) CU(cudaMemcpyAsync(out_seqs, d_seqs, nb, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(out_limits, d_limits, (ns + 1) * 8, cudaMemcpyDeviceToHost, st));
+        }
+        CU(cudaStreamSynchronize(st));                                // the record table is freed when fq goes out of scope
+        return DYIBF_OK;
+    };
+    auto needs_general = [&](uint64_t word) {
+        const unsigned code = (unsigned)(word & 0xff);
+        return format == DYIBF_FMT_FASTQ && word != ~0ull && (code == 2 || code == 3 || code == 4);
     };
     if (format == DYIBF_FMT_FASTA && tot[3] == ~0ull)
         return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: no '>' in a non-empty FASTA text (SeqAn: UnexpectedEnd)");
     if (format == DYIBF_FMT_FASTQ && tot[4] == 0)
         return fail(DYIBF_ERR_FORMAT, "dyibf_parse_records: no '@' in a non-empty FASTQ text (SeqAn: UnexpectedEnd)");
+    if (needs_general(tot[5])) return general_fastq();
     if (tot[5] != ~0ull) return format_error(tot[5]);
     *n_seqs = tot[0]; *n_bases = tot[1];
     if (sizing && format == DYIBF_FMT_FASTA) return DYIBF_OK;             // FASTQ: the length checks run in the last pass
@@ -780,6 +815,12 @@ int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int form
     }
     CU(launch_ingest_emit(d_text, n_bytes, format, iupac, ws, d_seqs, d_limits, limit_base, tot[0], tot[1], st));
     CU(ingest_read_totals(ws, n_bytes, tot, st));
+    if (needs_general(tot[5])) {                                     // a length mismatch only the last pass sees
+        *n_seqs = 0; *n_bases = 0;
+        if (tmp.p[2]) { cudaFree(tmp.p[2]); tmp.p[2] = nullptr; }
+        if (tmp.p[3]) { cudaFree(tmp.p[3]); tmp.p[3] = nullptr; }
+        return general_fastq();
+    }
     if (tot[5] != ~0ull) { *n_seqs = 0; *n_bases = 0; return format_error(tot[5]); }
     if (mem == DYIBF_MEM_HOST && !sizing) {
         if (tot[1]) CU(cudaMemcpyAsync(out_seqs, d_seqs, tot[1], cudaMemcpyDeviceToHost, st));

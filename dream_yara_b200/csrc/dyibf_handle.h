@@ -147,6 +147,18 @@ int staged_h2d(void* d_dst, const void* h_src, size_t n, cudaStream_t st);   // 
 // bulk word transfer between one table and host memory through the threaded pinned pipeline of dyibf_io.cu
 int io_copy_words(dyibf_filter* f, uint64_t* host_words, uint64_t first_block, uint64_t n_blocks, bool to_device);
 
+// ingest_general.cu: FASTQ in SeqAn's full generality (wrapped sequences / qualities, blank lines between records) — the fall-back
+// of dyibf_parse_records for texts the four-line tokeniser refuses.  count() leaves the record table on the device for emit().
+class FastqGeneral {
+public:
+    int count(const uint8_t* text, uint64_t n, int iupac, cudaStream_t st, uint64_t* n_records, uint64_t* n_bases, uint64_t* err_word);
+    int emit(uint8_t* out_seqs, uint64_t* out_limits, uint64_t limit_base, cudaStream_t st);
+    ~FastqGeneral();
+private:
+    const uint8_t* text_ = nullptr; uint64_t n_ = 0, n_cand_ = 0;
+    DevBuf globals_, tiles_, cand_, rec_, jump_, mark_, scan_a_, scan_b_;
+};
+
 struct FileHeader { uint64_t nbits; uint32_t bins, h, k; uint64_t file_size; };
 int read_file_header(FILE* fp, const char* path, FileHeader* fh);
 

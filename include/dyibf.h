@@ -234,10 +234,13 @@ int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64
  * dyibf_add_sequences with DYIBF_ENC_ASCII) and out_limits[n_seqs + 1] = limit_base + the start of every record
  * (a ConcatDirect StringSet's limits).  Ids and qualities are not extracted: the filter does not read them.
  * *n_seqs / *n_bases always receive the sizes; out_seqs == NULL and out_limits == NULL is a sizing call.
+ * FASTQ in the four-line layout goes through the streaming tokeniser (330 GB/s of text); anything else SeqAn's sequential
+ * reader accepts — sequences / qualities wrapped over several lines, blank lines between records — through a speculative
+ * one (every '@' after white space is parsed as if it opened a record, pointer jumping picks the real ones; tens of GB/s).
  * Errors: DYIBF_ERR_FORMAT where SeqAn throws (a character outside the alphabet, no record in a non-empty text, a
- * FASTQ quality string whose length differs from its sequence's) — and for FASTQ that is not in the four-line layout
- * (sequence / qualities wrapped over several lines, blank lines between records), which SeqAn's sequential reader
- * accepts and this parser refuses rather than mis-parses; DYIBF_ERR_CAPACITY when an output buffer is too small.
+ * FASTQ quality string whose length differs from its sequence's) — and for the one layout SeqAn accepts and this parser does
+ * not: a FASTQ record that starts right behind the previous record's qualities with no white space in between;
+ * DYIBF_ERR_CAPACITY when an output buffer is too small.
  * mem says where text, out_seqs and out_limits live (all three on the same side). */
 int  dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int format, int alphabet,
                          uint8_t* out_seqs, uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs,

@@ -1,7 +1,9 @@
 """FASTA / FASTQ texts for the record-reader parity tests (oracle vs the reference's SeqAn reader vs the device parser).
 
 Each case: (name, format 0=FASTA/1=FASTQ, iupac alphabet?, text, device_ok) — device_ok False marks inputs the reference
-accepts but the device parser deliberately rejects (multi-line FASTQ, blank lines between FASTQ records)."""
+accepts but the device parser deliberately rejects (a FASTQ record that starts right behind the previous record's qualities
+without white space).  Multi-line FASTQ and blank lines between FASTQ records go through the general (speculative) parser of
+csrc/ingest_general.cu."""
 import numpy as np
 
 
@@ -44,8 +46,15 @@ def cases():
     out.append(("fq_bad_char", 1, False, b"@r1\nAC-T\n+\nIIII\n", True))
     out.append(("fq_missing_plus", 1, False, b"@r1\nACGT\n", True))
     out.append(("fq_empty", 1, False, b"", True))
-    out.append(("fq_multiline", 1, False, b"@r1\nACGT\nACGT\n+\nIIII\nIIII\n@r2\nAC\n+\nII\n", False))
-    out.append(("fq_blank_between", 1, False, b"@r1\nACGT\n+\nIIII\n\n@r2\nAC\n+\nII\n", False))
+    out.append(("fq_multiline", 1, False, b"@r1\nACGT\nACGT\n+\nIIII\nIIII\n@r2\nAC\n+\nII\n", True))
+    out.append(("fq_blank_between", 1, False, b"@r1\nACGT\n+\nIIII\n\n@r2\nAC\n+\nII\n", True))
+    # the general parser: qualities cut short by the end of the text are accepted; junk before the first '@'; '+' line with text;
+    # an error deep inside a wrapped file; a record glued to the previous qualities (reference: fine, device: refused)
+    out.append(("fq_multiline_short_quals_at_end", 1, False, b"@r1\nACGT\nAC\n+\nIIII\nII\n@r2\nACGTA\nCC\n+r2 again\nIII\nI", True))
+    out.append(("fq_multiline_leading_junk", 1, False, b"junk line\n\n@r1\nAC\nGT\n+\nII\nII\n", True))
+    out.append(("fq_multiline_bad_quals", 1, False, b"@r1\nACGT\nACGT\n+\nIIII\nIIIII\n@r2\nAC\n+\nII\n", True))      # ParseError
+    out.append(("fq_multiline_bad_char", 1, False, b"@r1\nACGT\nAC-T\n+\nIIII\nIIII\n", True))                          # ParseError
+    out.append(("fq_nospace", 1, False, b"@r1\nACGT\n+\nIIII@r2\nAC\n+\nII\n", False))
     recs = []
     for i in range(2000):
         n = int(rng.integers(1, 260))
@@ -53,6 +62,22 @@ def cases():
         q = bytes(rng.integers(33, 127, n, dtype=np.uint8).tobytes())           # includes '@', '+', '>'
         recs.append(b"@read%d/1 x\n" % i + s + b"\n+\n" + q + b"\n")
     out.append(("fq_random", 1, False, b"".join(recs), True))
+    # wrapped at random widths, blank lines between some records, qualities from the whole printable range: wrapped quality
+    # lines that start with '@' or '+' are candidates that are not records
+    recs = []
+    for i in range(700):
+        n = int(rng.integers(0, 400))
+        s = _rand_seq(rng, n, b"ACGT" if i % 13 else b"ACGTNacgtn")
+        q = bytearray(rng.integers(33, 127, n, dtype=np.uint8).tobytes())
+        ws_, wq = int(rng.integers(7, 120)), int(rng.integers(5, 90))
+        for j in range(0, n, wq):
+            if rng.random() < 0.3:
+                q[j] = ord("@") if rng.random() < 0.7 else ord("+")
+        q = bytes(q)
+        wrap = lambda x, w: b"\n".join(x[j:j + w] for j in range(0, len(x), w)) if x else b""
+        recs.append(b"@read%d wrapped\n" % i + wrap(s, ws_) + b"\n+" + (b"read%d" % i if i % 3 == 0 else b"") + b"\n" + wrap(q, wq) + b"\n"
+                    + (b"\n" * int(rng.integers(0, 3)) if i % 5 == 0 else b""))
+    out.append(("fq_random_wrapped", 1, False, b"".join(recs), True))
     return out
 
 

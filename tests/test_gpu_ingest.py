@@ -175,7 +175,7 @@ def test_classify_text_tickets_in_flight(dy, golden):
         tk, n, thr = C.c_void_p(), C.c_uint32(0), C.c_uint32(0)
         check(L.dyibf_classify_text_begin(f._h, t.ctypes.data, t.size, None, 0, 1, 3, C.byref(n), C.byref(thr), C.byref(tk)))
         q.append((tk, n.value, thr.value))
-    bad = np.frombuffer(b"@x\nACGT\n+\nII\n", dtype=np.uint8)           # quality shorter than the sequence
+    bad = np.frombuffer(b"@x\nACGT\n+\nIIII\n@y\nAC-T\n+\nIIII\n", dtype=np.uint8)     # a character outside the alphabet: ParseError
     tk = C.c_void_p()
     assert L.dyibf_classify_text_begin(f._h, bad.ctypes.data, bad.size, None, 0, 1, 3, None, None, C.byref(tk)) == -4 and not tk.value
     while q:

@@ -203,5 +203,15 @@ def test_filter_reads_cli_vs_reference_mapper_output(tools, dy, golden, tmp_path
     assert r3.returncode == 0, r3.stderr
     assert [l for l in r3.stderr.splitlines() if l.startswith("bin ")] == [l for l in r.stderr.splitlines() if l.startswith("bin ")]
     assert "Reads count:\t\t\t6400" in r3.stderr
+    # FASTQ with sequences and qualities wrapped at 50 columns and blank lines between some records: the head check sends the
+    # file to the whole-text path, the device reader's general FASTQ parser tokenises it
+    with open(tmp_path / "wrapped.fq", "wb") as fh:
+        for i, s_ in enumerate(reads):
+            q_ = b"@" + b"I" * (len(s_) - 1)                                   # every quality line group starts with '@'
+            fh.write(b"@r%d\n" % i + b"\n".join(s_[j:j + 50] for j in range(0, len(s_), 50)) + b"\n+\n"
+                     + b"\n".join(q_[j:j + 50] for j in range(0, len(q_), 50)) + b"\n" + (b"\n" if i % 7 == 0 else b""))
+    r4 = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-rb", "1000", "-vv", str(tmp_path / "wrapped.fq")], capture_output=True, text=True)
+    assert r4.returncode == 0, r4.stderr
+    assert [l for l in r4.stderr.splitlines() if l.startswith("bin ")] == [l for l in r.stderr.splitlines() if l.startswith("bin ")]
     r = subprocess.run([exe, "-fi", str(tmp_path / "nope.filter"), str(tmp_path / "reads.fa")], capture_output=True, text=True)
     assert r.returncode == 1 and "could not be read" in r.stderr

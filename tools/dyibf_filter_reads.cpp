@@ -235,6 +235,18 @@ struct Source
     }
     bool have(size_t p) { while (p >= end) if (!more()) return false; return true; }
     static bool blank(char c) { return c == '\n' || c == '\r' || c == ' ' || c == '\t'; }
+    // position behind the next newline at or after p; `end` (with *open_line set) when the file ends inside the line
+    size_t lineEnd(size_t p, bool * open_line)
+    {
+        *open_line = false;
+        for (;;)
+        {
+            if (!have(p)) { *open_line = true; return end; }
+            const char * nl = (const char *)memchr(data() + p, '\n', end - p);
+            if (nl) return (size_t)(nl - data()) + 1;
+            p = end;
+        }
+    }
     // The text of the next (up to) `want` records -> out; returns the records cut.  *irregular: the text that follows is not
     // something lines alone can split (nothing of it was consumed).
     uint64_t cut(uint64_t want, Piece & out, bool * irregular)
@@ -247,6 +259,38 @@ struct Source
         {
             if (!have(pos)) return 0;                              // empty file
             if (data()[pos] != (fmt == DYIBF_FMT_FASTQ ? '@' : '>')) { *irregular = true; return 0; }
+            if (fmt == DYIBF_FMT_FASTQ)
+            {
+                // Is this four-line FASTQ at all?  The head of the file is checked line by line ('@' / sequence / '+' / qualities
+                // of equal length, 256 records); a wrapped or blank-line-separated file goes over whole (the device reader's
+                // general FASTQ parser handles it).  Later batches are cut by counting lines only; the record count the
+                // tokeniser reports must then equal the number cut, so a layout change in mid-file cannot go unnoticed.
+                size_t p = pos;
+                for (int r = 0; r < 256 && have(p); ++r)
+                {
+                    size_t len[4]; bool open_line = false, ok = true;
+                    const size_t rec0 = p;
+                    for (int line = 0; line < 4 && ok; ++line)
+                    {
+                        ok = have(p) && (line != 0 || data()[p] == '@') && (line != 2 || data()[p] == '+');
+                        if (!ok) break;
+                        const size_t q = lineEnd(p, &open_line);
+                        size_t e = q;
+                        while (e > p && (data()[e - 1] == '\n' || data()[e - 1] == '\r')) --e;
+                        len[line] = e - p;
+                        if (open_line && line != 3) ok = false;
+                        p = q;
+                    }
+                    if (ok && len[1] != len[3]) ok = false;
+                    if (!ok)
+                    {
+                        // white space only behind the last record is fine
+                        size_t w = rec0; while (have(w) && blank(data()[w])) ++w;
+                        if (!have(w) && r > 0) break;
+                        *irregular = true; return 0;
+                    }
+                }
+            }
             started = true;
         }
         while (n < want && have(pos))
