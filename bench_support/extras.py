@@ -607,6 +607,32 @@ def single_process(ctx, steps=4):
                "limiter": "one host thread per GPU issues the copies; the batch is read once from host memory at host_read_gbs"}
         if not same:
             raise AssertionError("single-process group lists are not consistent with rank 0's own lists")
+        # ---- the same filter built by ALL devices of the group (build_filter's bins-over-threads, d_build_filter.cpp:227-260, with
+        # GPUs as the threads): every sequence goes to the device that owns its bin's word column, the replicas then exchange
+        # the columns over NVLink.  Must equal the table one GPU built.
+        from dream_yara_b200 import dist as D
+        g2 = dy.FilterGroup(bins, H, K, ctx.nbits, devices=list(range(world)), mode="read")
+        bin_ids = np.arange(bins, dtype=np.uint32)
+        t0 = time.perf_counter()
+        g2.addSequences((ctx.genomes.reshape(-1), goff), bin_ids)
+        t_gb = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        g2.addSequences((ctx.genomes.reshape(-1), goff), bin_ids)          # second call: scratch allocated, same bits (idempotent)
+        t_gb2 = time.perf_counter() - t0
+        nd = ctx.P * ctx.W
+        eq = True
+        for i in sorted({0, world - 1}):
+            a_, _, _ = g.member(i); b_, _, _ = g2.member(i)
+            dev_i = torch.device("cuda", i)
+            eq = eq and bool(torch.equal(D._tensor_from_ptr(a_.device_words(), nd, dev_i), D._tensor_from_ptr(b_.device_words(), nd, dev_i)))
+        kmers = bins * (ctx.args.genome_len - K + 1)
+        out["group_build"] = {"seconds_first_call": t_gb, "seconds": t_gb2, "kmers_per_s": kmers / t_gb2, "unit": "k-mers/s",
+                              "single_gpu_build_s": t_build, "words_equal_single_gpu_build": eq,
+                              "call": "dyibf_group_add_sequences: %d bins x %d bp from one pageable host buffer, routed by bin column to %d GPUs, "
+                                      "columns exchanged over NVLink so that every replica holds the whole filter" % (bins, ctx.args.genome_len, world)}
+        g2.close()
+        if not eq:
+            raise AssertionError("group-built filter differs from the single-GPU build")
         g.close()
         L.dyibf_host_free(hp); L.dyibf_host_free(ip)
     finally:
