@@ -241,16 +241,22 @@ bool sliced_plan(const HashParams& hp, uint64_t budget_bytes, SlicedPlan* p)
     if (pw * 4 > (32ull << 20)) return false;                       // a bin's vector must sit comfortably in the L2
     if (pw * 4 < (64ull << 10)) return false;                       // tiny tables: direct atomics are L2 hits anyway
     const uint64_t n_tiles = pw / 32;                               // tiles of 1024 blocks = one line per bin
-    // all W columns in one pass when the scratch allows (the interleave then streams whole table rows); else 4, 2 or 1
-    uint32_t cols = hp.W;
-    const char* env_cols = getenv("DYIBF_SLICED_MAX_COLS");         // tests: force the narrow groups a small scratch would get
-    const uint32_t max_cols = env_cols && atoi(env_cols) > 0 ? (uint32_t)atoi(env_cols) : 16u;
-    if (cols > max_cols || n_tiles * (cols * 64 + 1) * 128 > budget_bytes) cols = (hp.W >= 4 && max_cols >= 4) ? 4 : (hp.W >= 2 && max_cols >= 2) ? 2 : 1;
-    while (cols > 1 && n_tiles * (cols * 64 + 1) * 128 > budget_bytes) cols >>= 1;
-    if ((uint64_t)cols * 64 * pw * 4 > budget_bytes) return false;
+    // One group of all W columns when the scratch allows (the interleave then streams whole table rows: 16 GiB at cfg2).  Narrower
+    // groups (W > 16, small budgets, DYIBF_SLICED_MAX_COLS) get TWO shadow buffers: while group g+1 is scattered, group g is
+    // interleaved into the table and zeroed again on a second stream.  That overlap does not pay by itself — measured on
+    // 1024 bins x 4 Mbp: four groups of 4 columns 105.8 ms per step against 83.0 ms for the one whole-table group (the
+    // partial-row interleave is slow and contends with the scatter for the L2) — it only hides what narrow groups cost anyway.
+    const char* env_cols = getenv("DYIBF_SLICED_MAX_COLS");
+    uint32_t cols = env_cols && atoi(env_cols) > 0 ? (uint32_t)atoi(env_cols) : 16u;
+    if (cols > 16) cols = 16;
+    if (cols > hp.W) cols = hp.W;
+    auto bytes_for = [&](uint32_t c) { return (uint64_t)(c < hp.W ? 2 : 1) * c * 64 * pw * 4; };
+    while (cols > 1 && bytes_for(cols) > budget_bytes) cols >>= 1;
+    if (bytes_for(cols) > budget_bytes) return false;
     p->pw = pw; p->n_tiles = n_tiles; p->cols_per_group = cols; p->group_bins = cols * 64;
     p->n_groups = (hp.W + cols - 1) / cols;
-    p->shadow_bytes = n_tiles * (cols * 64 + 1) * 128;
+    p->shadow_bytes = (uint64_t)cols * 64 * pw * 4;
+    p->n_buffers = p->n_groups > 1 ? 2 : 1;
     p->scatter_blocks = SLICED_MAX_BLOCKS;
     return true;
 }

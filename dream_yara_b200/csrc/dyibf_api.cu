@@ -181,6 +181,8 @@ void dyibf_destroy(dyibf_filter* f)
     drain_profile(f);
     for (auto e : f->ev_pool) cudaEventDestroy(e);
     if (f->trace_base) cudaEventDestroy(f->trace_base);
+    if (f->sliced_aux) { cudaStreamSynchronize(f->sliced_aux); cudaStreamDestroy(f->sliced_aux); }
+    for (int i = 0; i < 2; ++i) { if (f->sliced_filled[i]) cudaEventDestroy(f->sliced_filled[i]); if (f->sliced_free[i]) cudaEventDestroy(f->sliced_free[i]); }
     for (int i = 0; i < 2; ++i) {
         Slot& s = f->slot[i];
         s.in_bytes.release(); s.in_offsets.release(); s.packed.release(); s.meta.release(); s.rows.release(); s.counts.release(); s.ctr.release();
@@ -309,7 +311,7 @@ namespace dyibf {
 // to answer queries or is saved gives it back here
 void trim_build_scratch(dyibf_filter* f)
 {
-    if (f->bucket_records.cap > (1ull << 30)) { cudaDeviceSynchronize(); f->bucket_records.release(); }
+    if (f->bucket_records.cap > (1ull << 30)) { cudaDeviceSynchronize(); f->bucket_records.release(); f->sliced_clean_ptr = nullptr; }
 }
 
 // pack + query of one device-resident batch on stream st, using the workspace of slot sl
@@ -867,6 +869,7 @@ int buckets_begin(dyibf_filter* f, uint64_t expected_records, BucketRun* br)
     const uint64_t per_rec = br->plan.bytes_per_record_x4;          // bytes per record of final capacity, times 4
     const uint64_t want = expected_records * per_rec / 4 + expected_records * per_rec / 32 + (256ull << 20);
     if (budget > want && !bucket_plan(f->data_words, want, &br->plan)) return DYIBF_OK;
+    f->sliced_clean_ptr = nullptr;                                   // the buffer is about to hold records
     if (f->bucket_records.reserve(br->plan.bytes_final + br->plan.bytes_level1) != cudaSuccess) {
         cudaGetLastError();                                          // not enough memory: direct atomics
         return DYIBF_OK;
@@ -982,10 +985,17 @@ void buckets_end(dyibf_filter* f, BucketRun* br)
 }
 
 // ---- the bit-sliced build (build_sliced.cu): per-bin bit vectors in the L2, then interleaved --------------------------
+// One shadow buffer when the plan has one group (the usual case: all W columns); with several groups, two buffers and an
+// auxiliary stream: when the batch moves on to the next column group, the filled buffer is handed to the auxiliary stream
+// (interleave into the table, then zero it again) while the scatter of the next group fills the other one.  The buffers are
+// left zeroed, so the next call on the handle starts without a memset.
 struct SlicedRun {
     bool active = false;
     SlicedPlan plan;
-    int cur = -1;                                   // group whose updates the shadow holds (-1: none)
+    int cur = -1;                                   // group whose updates the current buffer holds (-1: none)
+    int buf = 0;                                    // shadow buffer being filled
+    bool zeroed[2] = {false, false};                // the buffer has been zeroed in this call (by the caller's stream or the aux stream)
+    bool busy[2] = {false, false};                  // the aux stream still works on the buffer: wait for free_ev before filling it
 };
 
 // may this call use the sliced build at all (mode, table size, call size) — and with which plan
@@ -995,21 +1005,33 @@ bool sliced_candidate(dyibf_filter* f, uint64_t expected_records, SlicedPlan* pl
     if (mode == DYIBF_BUILD_DIRECT || mode == DYIBF_BUILD_BUCKETED || f->hp.direct) return false;
     if (mode == DYIBF_BUILD_AUTO) {
         if (f->data_words * 8 <= (256ull << 20)) return false;     // table (nearly) fits the L2: direct atomics are L2 hits
-        // too few updates to pay for the zero / interleave passes (~11 ms for a 16 GiB table: the break-even against direct
-        // atomics at 21 G updates/s is ~280 M updates; calls between 32 M and that go to the bucketed build)
+        // too few updates to pay for the zero / interleave passes (a group's passes move ~4 x its share of the table: the
+        // break-even against direct atomics at 21 G updates/s is ~70 M updates per group; calls between 32 M and 256 M updates
+        // go to the bucketed build)
         if (expected_records < (256ull << 20)) return false;
     }
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return false;
     free_b += f->bucket_records.cap;
-    const uint64_t budget = std::min<uint64_t>(free_b / 2, 17ull << 30);   // all 1024 bins of a 16 GiB table: 16 GiB + pad lines
+    const uint64_t budget = std::min<uint64_t>(free_b / 2, 17ull << 30);
     return sliced_plan(f->hp, budget, plan);
+}
+
+int sliced_resources(dyibf_filter* f)
+{
+    if (f->sliced_aux) return DYIBF_OK;
+    CU(cudaStreamCreateWithFlags(&f->sliced_aux, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaEventCreateWithFlags(&f->sliced_filled[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&f->sliced_free[i], cudaEventDisableTiming));
+    }
+    return DYIBF_OK;
 }
 
 // bin changes along the batch decide whether the vectors of the bins in flight fit the L2
 int sliced_begin(dyibf_filter* f, const SlicedPlan& plan, uint64_t total_bases, uint64_t switches, SlicedRun* sr)
 {
-    sr->active = false; sr->plan = plan; sr->cur = -1;
+    *sr = SlicedRun(); sr->plan = plan;
     // the scatter kernel's window (bases its resident warps span) is cut to about 1.5 average runs of one bin, so that two
     // or three bins' vectors are being filled at any time; the smallest useful grid still spans SLICED_MIN_BLOCKS * 8192 bases
     const uint64_t avg_run = std::max<uint64_t>(total_bases / (switches + 1), 1);
@@ -1019,43 +1041,76 @@ int sliced_begin(dyibf_filter* f, const SlicedPlan& plan, uint64_t total_bases, 
         const uint64_t bins_in_flight = sr->plan.scatter_blocks * SLICED_BLOCK_BASES / avg_run + 2;
         if (bins_in_flight * plan.pw * 4 > (80ull << 20)) return DYIBF_OK;   // not clustered by bin: bucketed / direct
     }
-    if (f->bucket_records.reserve(plan.shadow_bytes) != cudaSuccess) {
+    if (f->bucket_records.reserve(plan.shadow_bytes * plan.n_buffers) != cudaSuccess) {
         cudaGetLastError();                                          // not enough memory: the other builds
         return DYIBF_OK;
     }
     CU(f->bucket_cursors.reserve(256));
+    int rc = sliced_resources(f);
+    if (rc) return rc;
+    // the last sliced build left its buffers zeroed (the auxiliary stream zeroes a buffer after interleaving it): no memset then
+    if (f->sliced_clean_ptr == f->bucket_records.p && f->sliced_clean_bytes >= plan.shadow_bytes * plan.n_buffers)
+        sr->zeroed[0] = sr->zeroed[1] = true;
+    f->sliced_clean_ptr = nullptr;                                   // dirty from here on, until sliced_finish_group says otherwise
     sr->active = true;
     return DYIBF_OK;
 }
 
-// the shadow's group goes into the table (stream-ordered on st)
-int sliced_finish_group(dyibf_filter* f, SlicedRun* sr, cudaStream_t st)
+inline void* sliced_buffer(dyibf_filter* f, const SlicedRun* sr, int i) { return static_cast<char*>(f->bucket_records.p) + (size_t)i * sr->plan.shadow_bytes; }
+
+// the filled buffer goes to the auxiliary stream: interleave into the table, zero again.  `st` has the group's scatters.
+int sliced_hand_over(dyibf_filter* f, SlicedRun* sr, cudaStream_t st)
 {
-    if (!sr->active || sr->cur < 0) return DYIBF_OK;
-    Scope sc(f, st, K_APPLY);
-    CU(launch_sliced_interleave(f->hp, f->d_words, f->bucket_records.p, sr->plan, (uint32_t)sr->cur, st));
+    const int b = sr->buf;
+    CU(cudaEventRecord(f->sliced_filled[b], st));
+    CU(cudaStreamWaitEvent(f->sliced_aux, f->sliced_filled[b], 0));
+    {
+        Scope sc(f, f->sliced_aux, K_APPLY);
+        CU(launch_sliced_interleave(f->hp, f->d_words, sliced_buffer(f, sr, b), sr->plan, (uint32_t)sr->cur, f->sliced_aux));
+    }
+    CU(launch_sliced_zero(sliced_buffer(f, sr, b), sr->plan, f->sliced_aux));
+    CU(cudaEventRecord(f->sliced_free[b], f->sliced_aux));
+    sr->busy[b] = true; sr->zeroed[b] = true;
     sr->cur = -1;
     return DYIBF_OK;
 }
 
-// the updates of group g's sequences of one packed batch -> the shadow; switches the shadow to g first where needed.
-// both_streams: the call alternates between the two slot streams (host mode) — emptying / zeroing the shadow is ordered
-// against the other stream with events; scatters of different chunks may overlap (atomics).
+// end of the call: the last group goes into the table and `st` waits for everything the auxiliary stream still does
+int sliced_finish_group(dyibf_filter* f, SlicedRun* sr, cudaStream_t st)
+{
+    if (!sr->active) return DYIBF_OK;
+    if (sr->cur >= 0) { int rc = sliced_hand_over(f, sr, st); if (rc) return rc; }
+    for (int b = 0; b < 2; ++b)
+        if (sr->busy[b]) { CU(cudaStreamWaitEvent(st, f->sliced_free[b], 0)); sr->busy[b] = false; }
+    bool all_clean = true;
+    for (uint32_t b = 0; b < sr->plan.n_buffers; ++b) all_clean = all_clean && sr->zeroed[b];
+    if (all_clean) { f->sliced_clean_ptr = f->bucket_records.p; f->sliced_clean_bytes = sr->plan.shadow_bytes * sr->plan.n_buffers; }
+    return DYIBF_OK;
+}
+
+// the updates of group g's sequences of one packed batch -> the shadow; switches to the other buffer first where the group
+// changes.  both_streams: the call alternates between the two slot streams (host mode) — the switch is ordered against the
+// other stream with events; scatters of different chunks into one buffer may overlap (atomics).
 int sliced_scatter_group(dyibf_filter* f, SlicedRun* sr, uint32_t g, const uint64_t* packed, const SeqMeta* meta,
                          const uint32_t* bin_ids, uint32_t n_seqs, uint64_t words, bool both_streams, cudaStream_t st)
 {
     if (sr->cur != (int)g) {
         if (both_streams) { int rc = join_streams(f, st); if (rc) return rc; }
-        int rc = sliced_finish_group(f, sr, st);
-        if (rc) return rc;
-        CU(launch_sliced_zero(f->bucket_records.p, sr->plan, st));
-        if (both_streams) { rc = fork_streams(f, st); if (rc) return rc; }
+        if (sr->cur >= 0) {
+            int rc = sliced_hand_over(f, sr, st);
+            if (rc) return rc;
+            sr->buf = (sr->buf + 1) % (int)sr->plan.n_buffers;
+        }
+        const int b = sr->buf;
+        if (sr->busy[b]) { CU(cudaStreamWaitEvent(st, f->sliced_free[b], 0)); sr->busy[b] = false; }   // interleaved and zeroed again
+        if (!sr->zeroed[b]) { CU(launch_sliced_zero(sliced_buffer(f, sr, b), sr->plan, st)); sr->zeroed[b] = true; }
+        if (both_streams) { int rc = fork_streams(f, st); if (rc) return rc; }
         sr->cur = (int)g;
     }
     Scope sc(f, st, K_BUILD);
     // one work counter per slot stream: scatters of successive chunks may overlap
     unsigned long long* ctr = static_cast<unsigned long long*>(f->bucket_cursors.p) + (st == f->slot[1].st ? 8 : 0);
-    CU(launch_sliced_scatter(f->hp, f->bucket_records.p, sr->plan, g, packed, meta, bin_ids, n_seqs, words, ctr, st));
+    CU(launch_sliced_scatter(f->hp, sliced_buffer(f, sr, sr->buf), sr->plan, g, packed, meta, bin_ids, n_seqs, words, ctr, st));
     return DYIBF_OK;
 }
 

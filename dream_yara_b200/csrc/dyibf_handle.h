@@ -78,6 +78,10 @@ struct dyibf_filter {
     int64_t      build_mode = 0;          // DYIBF_OPT_BUILD_MODE
     int          last_build_mode = 0;     // what the last dyibf_add_sequences used (DYIBF_BUILD_*)
     dyibf::DevBuf bucket_records, bucket_cursors;
+    cudaStream_t sliced_aux = nullptr;    // sliced build: interleave + zero of the filled shadow buffer run here, beside the next scatter
+    cudaEvent_t  sliced_filled[2] = {nullptr, nullptr}, sliced_free[2] = {nullptr, nullptr};
+    const void*  sliced_clean_ptr = nullptr;   // bucket_records.p when its first sliced_clean_bytes bytes are known to be zero (left so by the last sliced build)
+    uint64_t     sliced_clean_bytes = 0;
     void*        stage[2] = {nullptr, nullptr};   // pinned
     cudaEvent_t  stage_ev[2] = {nullptr, nullptr};
     bool         profiling = false;

@@ -103,10 +103,11 @@ cudaError_t launch_bucket_apply(uint64_t* filter, uint64_t data_words, const Buc
 struct SlicedPlan {
     uint64_t pw;               // 32-bit words per bin vector (ceil(P / 32), rounded up to 32 = whole 128-byte lines)
     uint64_t n_tiles;          // tiles of 1024 blocks (one line of every bin's vector): pw / 32
-    uint32_t cols_per_group;   // word columns (64 bins each) per pass: all W when the scratch fits, else 4 / 2 / 1
+    uint32_t cols_per_group;   // word columns (64 bins each) per group: 4, fewer for narrow tables / small budgets
     uint32_t group_bins;       // 64 * cols_per_group
     uint32_t n_groups;         // passes that cover all W columns
-    uint64_t shadow_bytes;     // group_bins * pw * 4
+    uint64_t shadow_bytes;     // group_bins * pw * 4: one shadow buffer
+    uint32_t n_buffers;        // 2 when there are several groups (scatter of group g+1 overlaps the interleave of group g), else 1
     uint32_t scatter_blocks;   // grid of the scatter kernel (8 warps x 1024 bases per block in flight): sized so that the
                                // bins in flight (window / average run of one bin) keep their vectors in the L2
 };

@@ -399,12 +399,13 @@ def test_bucketed_build_equals_direct_and_oracle(dy, oracle, log2_bits):
 
 @pytest.mark.parametrize("bins,nbits,h,k", [(1000, (1 << 32) + 256, 3, 18), (130, 3 * (1 << 30) + 777, 2, 19), (64, (1 << 30) + 256, 3, 12),
                                             (200, (1 << 31) + 256, 5, 20)])
-@pytest.mark.parametrize("max_cols", [0, 2])
+@pytest.mark.parametrize("max_cols", [0, 2, 4])
 def test_sliced_build_equals_oracle(dy, oracle, bins, nbits, h, k, max_cols, monkeypatch):
     """The bit-sliced build (DYIBF_OPT_BUILD_MODE = 3: per-bin Bloom bit vectors in the L2, then interleaved with bit-matrix
     transposes) against the oracle: W = 16 (all columns in one pass: whole table rows), W = 3 (odd, non-power-of-two P,
     unaligned trailer), W = 1, W = 4 with bins that are not a multiple of 64 and the generic hash count; the same with the
-    column groups a small scratch would get (max_cols = 2: several passes, partial rows); sequences in bin order
+    narrower column groups a small scratch would get (max_cols = 2 / 4: the interleave of one group overlaps the scatter of
+    the next through two shadow buffers and a second stream); sequences in bin order
     and shuffled, host buffers in several chunks and device buffers, leading-N and short sequences, onto a table that already
     holds other bits (the interleave ORs)."""
     if max_cols:
@@ -432,7 +433,7 @@ def test_sliced_build_equals_oracle(dy, oracle, bins, nbits, h, k, max_cols, mon
         oracle.add_kmers(words, p, s_, b)
     nd = p.P * p.W
     order = rng.permutation(len(seqs))
-    for variant in ("host", "host_chunks_shuffled", "device"):
+    for variant in ("host", "host_chunks_shuffled", "device", "host_two_calls"):
         f = dy.SeqAnBloomFilter(bins, h, k, nbits)
         f.addSequences([pre], [bins - 1])                              # pre-existing content
         f.set_build_mode(BUILD_SLICED)
@@ -442,6 +443,11 @@ def test_sliced_build_equals_oracle(dy, oracle, bins, nbits, h, k, max_cols, mon
         elif variant == "host_chunks_shuffled":
             f.set_build_chunk_mib(1)
             f.addSequences([seqs[i] for i in order], [ids[i] for i in order])
+        elif variant == "host_two_calls":                              # the second call finds the shadow buffers zeroed by the first
+            half = len(seqs) // 2
+            f.addSequences(seqs[half:], ids[half:])
+            assert f.last_build_mode() == BUILD_SLICED
+            f.addSequences(seqs[:half], ids[:half])
         else:
             cat, off, enc = dy.as_batch(seqs)
             d_seq = torch.from_numpy(cat).cuda(); d_off = torch.from_numpy(off.view(np.int64)).cuda()
