@@ -81,6 +81,7 @@ SYMBOLS = {
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "dyibf_classify_text_begin": (C.c_int, [_P, _P, C.c_uint64, _P, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_uint32),
                                             C.POINTER(C.c_uint32), C.POINTER(C.c_void_p)]),
+    "dyibf_add_fasta_texts": (C.c_int, [_P, _P, _P, _P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
     "dyibf_set_option": (C.c_int, [_P, C.c_int, C.c_int64]),
     "dyibf_get_option": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int64)]),
     "dyibf_profile_enable": (C.c_int, [_P, C.c_int]),

@@ -714,10 +714,15 @@ int dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64_
     return DYIBF_OK;
 }
 
+} // extern "C"
+
+namespace dyibf {
 /* ---- ingest: SeqAn's readRecords on the device (ingest_kernel.cu) ---------------------------------------- */
-int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int format, int alphabet, uint8_t* out_seqs,
-                        uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs, uint64_t limit_base,
-                        uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream)
+// out_rec_pos (device memory, capacity_seqs entries, MEM_DEVICE only, may be NULL): the text offset of every record's start
+// character — what dyibf_add_fasta_texts needs to tell which file of a concatenation a record came from
+int parse_records_impl(int device, const char* text, uint64_t n_bytes, int format, int alphabet, uint8_t* out_seqs,
+                       uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs, uint64_t limit_base,
+                       uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream, uint64_t* out_rec_pos)
 {
     if (!n_seqs || !n_bases) return fail(DYIBF_ERR_ARG, "dyibf_parse_records: NULL size output");
     if ((format != DYIBF_FMT_FASTA && format != DYIBF_FMT_FASTQ) || (alphabet != DYIBF_ALPHA_DNA5 && alphabet != DYIBF_ALPHA_IUPAC) ||
@@ -815,7 +820,8 @@ int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int form
         CU(cudaMalloc(&tmp.p[3], (tot[0] + 1) * 8));
         d_seqs = static_cast<uint8_t*>(tmp.p[2]); d_limits = static_cast<uint64_t*>(tmp.p[3]);
     }
-    CU(launch_ingest_emit(d_text, n_bytes, format, iupac, ws, d_seqs, d_limits, limit_base, tot[0], tot[1], st));
+    CU(launch_ingest_emit(d_text, n_bytes, format, iupac, ws, d_seqs, d_limits, limit_base, tot[0], tot[1], st,
+                          mem == DYIBF_MEM_DEVICE && !sizing ? out_rec_pos : nullptr));
     CU(ingest_read_totals(ws, n_bytes, tot, st));
     if (needs_general(tot[5])) {                                     // a length mismatch only the last pass sees
         *n_seqs = 0; *n_bases = 0;
@@ -830,6 +836,17 @@ int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int form
         CU(cudaStreamSynchronize(st));
     }
     return DYIBF_OK;
+}
+} // namespace dyibf
+
+extern "C" {
+
+int dyibf_parse_records(int device, const char* text, uint64_t n_bytes, int format, int alphabet, uint8_t* out_seqs,
+                        uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs, uint64_t limit_base,
+                        uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream)
+{
+    return parse_records_impl(device, text, n_bytes, format, alphabet, out_seqs, capacity_bytes, out_limits, capacity_seqs, limit_base,
+                              n_seqs, n_bases, mem, stream, nullptr);
 }
 
 } // extern "C"

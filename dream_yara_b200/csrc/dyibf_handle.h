@@ -163,6 +163,10 @@ private:
     DevBuf globals_, tiles_, cand_, rec_, jump_, mark_, scan_a_, scan_b_;
 };
 
+int parse_records_impl(int device, const char* text, uint64_t n_bytes, int format, int alphabet, uint8_t* out_seqs,
+                       uint64_t capacity_bytes, uint64_t* out_limits, uint64_t capacity_seqs, uint64_t limit_base,
+                       uint64_t* n_seqs, uint64_t* n_bases, int mem, void* stream, uint64_t* out_rec_pos);
+
 struct FileHeader { uint64_t nbits; uint32_t bins, h, k; uint64_t file_size; };
 int read_file_header(FILE* fp, const char* path, FileHeader* fh);
 

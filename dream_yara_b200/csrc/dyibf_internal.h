@@ -162,7 +162,8 @@ cudaError_t launch_ingest_count(const uint8_t* text, uint64_t n, int format, int
 // (offset << 8 | code; all ones = none); synchronises the stream
 cudaError_t ingest_read_totals(const uint64_t* ws, uint64_t n, uint64_t totals[6], cudaStream_t st);
 cudaError_t launch_ingest_emit(const uint8_t* text, uint64_t n, int format, int iupac, uint64_t* ws, uint8_t* out_seqs,
-                               uint64_t* out_limits, uint64_t limit_base, uint64_t n_records, uint64_t n_bases, cudaStream_t st);
+                               uint64_t* out_limits, uint64_t limit_base, uint64_t n_records, uint64_t n_bases, cudaStream_t st,
+                               uint64_t* out_rec_pos = nullptr);    // optional (device): text offset of every record's start character
 cudaError_t launch_max_len(const uint64_t* limits, uint64_t n, unsigned long long* out, cudaStream_t st);
 
 } // namespace dyibf

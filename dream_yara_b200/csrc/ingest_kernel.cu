@@ -262,6 +262,7 @@ struct WalkArgs {
     const uint64_t* entry;                 // per tile: FASTA kind of the last delimiter before it, FASTQ newlines before it
     uint64_t *rec, *seq, *qual;            // per tile: counts (pass 3 writes) / their exclusive prefix sums (pass 5 reads)
     uint8_t* out_seqs; uint64_t* out_limits; uint64_t limit_base;
+    uint64_t* out_rec_pos;                 // optional: text offset of every record's start character
     unsigned long long* g;
 };
 
@@ -312,6 +313,7 @@ __global__ void __launch_bounds__(IT) ingest_walk_kernel(const WalkArgs a)
     // limits[r] at every record start
     for (uint32_t r = m.rec; r; r &= r - 1) {
         const uint32_t below = (1u << (__ffs(r) - 1)) - 1u;
+        if (a.out_rec_pos) a.out_rec_pos[rec_at] = i0 + (uint32_t)(__ffs(r) - 1);
         a.out_limits[rec_at++] = a.limit_base + seq_at + __popc(m.seq & below);
     }
     if (FMT == DYIBF_FMT_FASTQ) {
@@ -386,7 +388,7 @@ cudaError_t launch_ingest_count(const uint8_t* text, uint64_t n, int format, int
     const bool aligned = (reinterpret_cast<uintptr_t>(text) & 15u) == 0;
     ingest_init_globals<<<1, 1, 0, st>>>(g);
     WalkArgs a; a.text = text; a.n = n; a.aligned = aligned; a.iupac = iupac; a.entry = entry; a.rec = rec; a.seq = seq; a.qual = qual;
-    a.out_seqs = nullptr; a.out_limits = nullptr; a.limit_base = 0; a.g = g;
+    a.out_seqs = nullptr; a.out_limits = nullptr; a.limit_base = 0; a.out_rec_pos = nullptr; a.g = g;
     cudaError_t e;
     if (format == DYIBF_FMT_FASTA) {
         ingest_summary_kernel<DYIBF_FMT_FASTA><<<(unsigned)n_tiles, IT, 0, st>>>(text, n, aligned, entry, g);
@@ -421,13 +423,14 @@ cudaError_t ingest_read_totals(const uint64_t* ws, uint64_t n, uint64_t totals[6
 
 // Pass 5: out_seqs[n_bases], out_limits[n_records + 1] (device), limits offset by limit_base.
 cudaError_t launch_ingest_emit(const uint8_t* text, uint64_t n, int format, int iupac, uint64_t* ws, uint8_t* out_seqs,
-                               uint64_t* out_limits, uint64_t limit_base, uint64_t n_records, uint64_t n_bases, cudaStream_t st)
+                               uint64_t* out_limits, uint64_t limit_base, uint64_t n_records, uint64_t n_bases, cudaStream_t st,
+                               uint64_t* out_rec_pos)
 {
     const uint64_t n_tiles = (n + TILE - 1) / TILE;
     const size_t se = scan_workspace_elems(n_tiles);
     WalkArgs a; a.text = text; a.n = n; a.aligned = (reinterpret_cast<uintptr_t>(text) & 15u) == 0; a.iupac = iupac;
     a.entry = ws; a.rec = ws + n_tiles + 1; a.seq = a.rec + se; a.qual = a.seq + se;
-    a.out_seqs = out_seqs; a.out_limits = out_limits; a.limit_base = limit_base;
+    a.out_seqs = out_seqs; a.out_limits = out_limits; a.limit_base = limit_base; a.out_rec_pos = out_rec_pos;
     a.g = reinterpret_cast<unsigned long long*>(a.qual + se);
     if (format == DYIBF_FMT_FASTA) ingest_walk_kernel<DYIBF_FMT_FASTA, true><<<(unsigned)n_tiles, IT, 0, st>>>(a);
     else                           ingest_walk_kernel<DYIBF_FMT_FASTQ, true><<<(unsigned)n_tiles, IT, 0, st>>>(a);

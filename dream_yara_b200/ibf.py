@@ -262,6 +262,25 @@ class SeqAnBloomFilter:
         check(lib().dyibf_device_errors(self._h, C.byref(fl), int(reset)))
         return int(fl.value)
 
+    def addFastaTexts(self, texts, bin_ids, formats=None):
+        """addFastaFile for many files at once, from their text (bytes each; FASTA unless formats says 1 = FASTQ): tokenised on
+        the device with SeqAn's rules, all records added in one build call.  Raises DyibfError(ERR_FORMAT) where SeqAn throws;
+        the exception's `bad_index` is the offending text."""
+        n = len(texts)
+        keep = [np.frombuffer(bytes(t), dtype=np.uint8) for t in texts]
+        ptrs = (C.c_void_p * n)(*[C.c_void_p(k.ctypes.data) if k.size else None for k in keep])
+        sizes = np.array([k.size for k in keep], dtype=np.uint64)
+        bins = np.ascontiguousarray(bin_ids, dtype=np.uint32)
+        fm = None if formats is None else np.ascontiguousarray(formats, dtype=np.int32)
+        bad = C.c_uint32(0)
+        rc = lib().dyibf_add_fasta_texts(self._h, C.cast(ptrs, C.c_void_p), _ptr(sizes), _ptr(bins), None if fm is None else _ptr(fm), n, C.byref(bad))
+        if rc:
+            try:
+                check(rc)
+            except _lib.DyibfError as e:
+                e.bad_index = bad.value
+                raise
+
     def classifyText(self, reads_text, mates_text=None, fmt=1, e_percent=5, capacity=None):
         """loadReads + clasifyLoadedReads from the text of the reads file(s) (bytes; fmt 0 FASTA / 1 FASTQ): only text goes up,
         only the lists come back.  Returns (bin_offsets, read_ids, n_reads, threshold)."""

@@ -146,6 +146,15 @@ int  dyibf_last_io_stats(dyibf_io_stats* out);
  * cannot: a device-resident bin id >= bins adds nothing and sets DYIBF_DEVERR_BIN_RANGE (dyibf_device_errors). */
 int  dyibf_add_sequences(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
                          const uint32_t* bin_ids, int encoding, int mem, void* stream);
+/* addFastaFile(fileName, binNo), d_bloom_filter.h:127-147, for n files at once and from their TEXT (uncompressed FASTA or FASTQ,
+ * host memory; formats[i] DYIBF_FMT_*, NULL = all FASTA): text i holds the contigs of bin bins[i].  The texts go up once, SeqAn's
+ * readRecord loop runs on the device (the rules of dyibf_parse_records with DYIBF_ALPHA_IUPAC: every record a sequence, a FASTA
+ * record ends at any '>', a character outside the IUPAC alphabet is an error), records shorter than k are skipped (:142), and all
+ * records are added with ONE build call, so a batch of whole files takes the sliced build.  On DYIBF_ERR_FORMAT nothing of
+ * the batch has been added and *bad_index (may be NULL) is the offending text (0xffffffff when it cannot be told).
+ * Measured: tools/dyibf_build_filter reads 1024 FASTA files of 4 Mbp through this call. */
+int  dyibf_add_fasta_texts(dyibf_filter* f, const char* const* texts, const uint64_t* sizes, const uint32_t* bins, const int* formats,
+                           uint32_t n, uint32_t* bad_index);
 /* clearBins(bins2clear, threads), d_bloom_filter.h:99-123 */
 int  dyibf_clear_bins(dyibf_filter* f, const uint32_t* bins, uint32_t n);
 

@@ -189,3 +189,63 @@ def test_classify_text_tickets_in_flight(dy, golden):
     first = int(gids[0])
     assert seq_bytes[int(limits[0]):int(limits[1])].tobytes() == batches[-1][first]
     f.close()
+
+
+def test_add_fasta_texts_equals_add_sequences(dy):
+    """dyibf_add_fasta_texts (addFastaFile for many files from their text, tokenised on the device) against the same records
+    added through dyibf_add_sequences: the joined one-pass form (FASTA texts that start with '>') and the one-by-one form
+    (FASTQ, text before the first '>'); a character outside the IUPAC alphabet names its text."""
+    from dream_yara_b200.ingest import parseRecords
+    rng = np.random.default_rng(11)
+    bins, h, k = 130, 3, 18
+    nbits = (1 << 30) + 256
+
+    def rand(n, alphabet=b"ACGT"):
+        return bytes(rng.choice(np.frombuffer(alphabet, dtype=np.uint8), n).tobytes())
+
+    def wrap(s, w):
+        return b"\n".join(s[j:j + w] for j in range(0, len(s), w))
+
+    texts, ids = [], []
+    for b in range(0, bins, 3):
+        recs = [rand(int(rng.integers(0, 3000)), b"ACGTacgtNRYKM" if b % 9 == 0 else b"ACGT") for _ in range(int(rng.integers(1, 5)))]
+        t = b"".join(b">c%d_%d text > more\n" % (b, i) + wrap(r, int(rng.integers(30, 90))) + b"\n" for i, r in enumerate(recs))
+        if b % 12 == 0:
+            t = t[:-1]                                               # no newline at the end of the file
+        if b % 15 == 0:
+            t += b">cut short by the end of the file"                # an id line without a newline
+        if b % 21 == 0:
+            t += b">x\nACGTACGTACGTACGTACGTAC>a record that starts in the middle of a line\nGGGGGGGGGGGGGGGGGGGGGGGGG\n"
+        texts.append(t); ids.append(b)
+    texts.append(b""); ids.append(1)                                 # an empty file
+
+    def reference(texts_, ids_, fmts=None):
+        g = dy.SeqAnBloomFilter(bins, h, k, nbits)
+        seqs, sb = [], []
+        for j, (t, b) in enumerate(zip(texts_, ids_)):
+            if not t:
+                continue
+            s_, lim = parseRecords(t, 0 if fmts is None else fmts[j], iupac=True)
+            for i in range(lim.size - 1):
+                seqs.append(s_[int(lim[i]):int(lim[i + 1])]); sb.append(b)
+        g.addSequences(seqs, sb, encoding=2)
+        w = g.download_words(); g.close()
+        return w
+
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addFastaTexts(texts, ids)
+    assert np.array_equal(f.download_words(), reference(texts, ids)) and f.device_errors() == 0
+    f.close()
+    # one by one: a FASTQ file and a FASTA file with text before its first '>'
+    mixed = [texts[0], b"@q1\n" + rand(400) + b"\n+\n" + b"I" * 400 + b"\n@q2\nACGTN\n+\nIIIII\n", b"; comment\n" + texts[2]]
+    mids, fmts = [5, 77, 129], [0, 1, 0]
+    f = dy.SeqAnBloomFilter(bins, h, k, nbits)
+    f.addFastaTexts(mixed, mids, fmts)
+    assert np.array_equal(f.download_words(), reference(mixed, mids, fmts))
+    # ParseError: names the text, adds nothing
+    before = f.download_words()
+    with pytest.raises(dy.DyibfError) as ei:
+        f.addFastaTexts([texts[0], b">bad\nACGTACGTACGTACGT-ACGTACGTACGT\n", texts[1]], [1, 2, 3])
+    assert ei.value.code == -4 and ei.value.bad_index == 1 and "of text 1" in str(ei.value)
+    assert np.array_equal(f.download_words(), before)
+    f.close()

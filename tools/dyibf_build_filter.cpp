@@ -5,6 +5,7 @@
 // by the atomic-OR kernel in batches of whole files.
 //
 //   dyibf_build_filter [-b 64] [-t 1] [-k 20] [-nh 4] [-bs 1] [-o out.filter] [-v] [--device 0] <REFERENCE FILES DIR>
+#include <atomic>
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
@@ -133,33 +134,50 @@ int main(int argc, char ** argv)
     const uint32_t numThr = options.threadsCount;
     uint32_t batchSize = options.numberOfBins / numThr;
     if (batchSize * numThr < options.numberOfBins) ++batchSize;
-    std::mutex gpuMutex, logMutex;
-    const uint64_t flushBytes = 256ull << 20;
+    // Reader tasks own contiguous bin ranges; what they have read goes into ONE shared batch (whole files, in the order the
+    // tasks hand them over: every file is a run of one bin), and whoever makes it reach ~1 GiB of text feeds the GPU with it
+    // while the others keep reading: few large build calls instead of one per task.
+    std::mutex gpuMutex, poolMutex, logMutex;
+    const uint64_t flushBytes = 1ull << 30, handBytes = 64ull << 20;
+    TextBatch pool;
+    auto hand_over = [&](TextBatch & mine, bool last) {
+        TextBatch full;
+        {
+            std::lock_guard<std::mutex> lock(poolMutex);
+            for (size_t i = 0; i < mine.texts.size(); ++i)
+            {
+                pool.bytes += mine.texts[i].size();
+                pool.texts.push_back(std::move(mine.texts[i])); pool.binIds.push_back(mine.binIds[i]); pool.formats.push_back(mine.formats[i]);
+            }
+            mine.clear();
+            if (pool.bytes >= flushBytes || last) std::swap(full, pool);
+        }
+        if (full.empty()) return;
+        std::lock_guard<std::mutex> lock(gpuMutex);
+        addTextBatch(filter, full);
+    };
+    std::atomic<uint32_t> running(numThr);
     std::vector<std::future<void>> tasks;
     for (uint32_t taskNo = 0; taskNo < numThr; ++taskNo)
     {
         tasks.emplace_back(std::async(std::launch::async, [&, taskNo] {
-            Batch batch;
-            auto flush = [&]() {
-                if (batch.empty()) return;
-                std::lock_guard<std::mutex> lock(gpuMutex);
-                if (dyibf_add_sequences(filter, batch.concat.data(), batch.limits.data(), (uint32_t)batch.binIds.size(),
-                                        batch.binIds.data(), DYIBF_ENC_ASCII, DYIBF_MEM_HOST, nullptr) != DYIBF_OK)
-                    throw std::runtime_error(dyibf_last_error());
-                batch.clear();
-            };
-            for (uint32_t binNo = taskNo * batchSize; binNo < options.numberOfBins && binNo < (taskNo + 1) * batchSize; ++binNo)
+            TextBatch batch;
+            try
             {
-                const double tb = now();
-                appendFastaRecords(batch, options.contigsDir + std::to_string(binNo) + comExt, binNo, options.kmerSize);
-                if (batch.concat.size() >= flushBytes) flush();
-                if (options.verbose)
+                for (uint32_t binNo = taskNo * batchSize; binNo < options.numberOfBins && binNo < (taskNo + 1) * batchSize; ++binNo)
                 {
-                    std::lock_guard<std::mutex> lock(logMutex);
-                    std::cerr << "[bin " << binNo << "] Done adding kmers!\t\t\t" << now() - tb << " sec" << std::endl;
+                    const double tb = now();
+                    appendFileText(batch, options.contigsDir + std::to_string(binNo) + comExt, binNo);
+                    if (batch.bytes >= handBytes) hand_over(batch, false);
+                    if (options.verbose)
+                    {
+                        std::lock_guard<std::mutex> lock(logMutex);
+                        std::cerr << "[bin " << binNo << "] Done adding kmers!\t\t\t" << now() - tb << " sec" << std::endl;
+                    }
                 }
             }
-            flush();
+            catch (...) { --running; throw; }
+            hand_over(batch, --running == 0);                        // the last task to finish flushes what is left
         }));
     }
     try { for (auto & t : tasks) t.get(); }

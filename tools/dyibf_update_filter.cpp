@@ -104,23 +104,16 @@ int main(int argc, char ** argv)
         std::cerr << "dyibf_update_filter: " << dyibf_last_error() << std::endl;
         return 1;
     }
-    Batch batch;
+    TextBatch batch;
     try
     {
         for (auto const & kv : binContigs)
         {
             const double tb = now();
-            appendFastaRecords(batch, kv.second, kv.first, prm.kmer);
+            appendFileText(batch, kv.second, kv.first);
             if (verbose)
                 std::cerr << "[bin " << kv.first << "] updated using " << kv.second << "!\t\t" << now() - tb << " sec" << std::endl;
-            if (batch.concat.size() >= (256ull << 20) || kv.first == binContigs.rbegin()->first)
-            {
-                if (!batch.empty() &&
-                    dyibf_add_sequences(filter, batch.concat.data(), batch.limits.data(), (uint32_t)batch.binIds.size(),
-                                        batch.binIds.data(), DYIBF_ENC_ASCII, DYIBF_MEM_HOST, nullptr) != DYIBF_OK)
-                    throw std::runtime_error(dyibf_last_error());
-                batch.clear();
-            }
+            if (batch.bytes >= (1ull << 30) || kv.first == binContigs.rbegin()->first) addTextBatch(filter, batch);
         }
     }
     catch (std::exception const & e) { std::cerr << "dyibf_update_filter: " << e.what() << std::endl; return 1; }

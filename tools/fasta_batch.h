@@ -1,21 +1,25 @@
-// tools/fasta_batch.h — host-side FASTA/FASTQ(.gz) reading and batching for the standalone builder/updater.
+// tools/fasta_batch.h — file reading and batching for the standalone builder/updater.
 //
-// Mirrors what SeqAnBloomFilter::addFastaFile (temehi/dream_yara src/d_bloom_filter.h:127-147) does on the host:
-// every record of the file is one sequence (no k-mers across records), records shorter than k are skipped (:142),
-// and the characters go through Iupac -> Dna5 (ACGTU any case -> 0..3, everything else -> N; on the device,
-// DYIBF_ENC_ASCII).  Reader threads parse files concurrently (the reference's std::async bin ranges,
-// src/d_build_filter.cpp:227-260, become host readers); one thread feeds the GPU with batches of whole files.
+// SeqAnBloomFilter::addFastaFile (temehi/dream_yara src/d_bloom_filter.h:127-147) reads a file record by record on the host and
+// hashes every record of at least k characters into the file's bin.  Here the host only reads (and inflates) the files: their
+// TEXT goes to the device in batches of whole files (dyibf_add_fasta_texts), where SeqAn's reader rules and the Iupac -> Dna5
+// conversion (ACGTU any case -> 0..3, everything else -> N) are applied and the records are added in one build call.  Reader
+// threads own contiguous bin ranges (the reference's std::async tasks, src/d_build_filter.cpp:227-260); whoever holds a full
+// batch feeds the GPU.
 #ifndef DYIBF_TOOLS_FASTA_BATCH_H_
 #define DYIBF_TOOLS_FASTA_BATCH_H_
 
 #include <zlib.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
+
+#include "dyibf.h"
 
 namespace dyibf_tools {
 
@@ -53,95 +57,81 @@ inline std::string commonExtension(const std::string & dir, uint32_t numberOfBin
     exit(1);
 }
 
-// one file's records, appended to a batch: concat bytes (ASCII), limits, bin ids
-struct Batch
+// the text of whole files on its way to the device: dyibf_add_fasta_texts tokenises it there with SeqAn's rules
+// (addFastaFile, src/d_bloom_filter.h:127-147: every record of a file is a sequence of the file's bin, a FASTA record ends at
+// any '>', characters outside the IUPAC alphabet abort, records shorter than k are skipped) and adds all of it in one build call
+struct TextBatch
 {
-    std::vector<uint8_t>  concat;
-    std::vector<uint64_t> limits{0};
+    std::vector<std::vector<char>> texts;
     std::vector<uint32_t> binIds;
-    void clear() { concat.clear(); limits.assign(1, 0); binIds.clear(); }
-    bool empty() const { return binIds.empty(); }
+    std::vector<int> formats;
+    uint64_t bytes = 0;
+    void clear() { texts.clear(); binIds.clear(); formats.clear(); bytes = 0; }
+    bool empty() const { return texts.empty(); }
 };
 
-// Reads FASTA or FASTQ (decided by the first '>' or '@'), plain or gzip, with the rules of SeqAn's readRecord into an
-// IupacString (seq_io/fasta_fastq.h:268-345), which is what addFastaFile uses: a FASTA record ends at ANY '>' (not only at a
-// line start); white space inside the sequence is dropped; a character outside the IUPAC alphabet is a ParseError (the
-// reference tool aborts: here a std::runtime_error, the tools print it and exit 1); FASTQ qualities are counted without
-// white space until there are as many as bases, and the next record must follow.  Records shorter than k are skipped.
-// (The device tokeniser dyibf_parse_records(DYIBF_ALPHA_IUPAC) applies the same rules; tests/test_tools.py feeds both the
-// same malformed files.)
-inline bool iupacChar(char c)
+inline bool endsWith(const std::string & s, const char * suf)
 {
-    switch (c >= 'a' && c <= 'z' ? c - 32 : c)
-    {
-        case 'A': case 'C': case 'G': case 'T': case 'U': case 'M': case 'R': case 'W': case 'S': case 'Y': case 'K':
-        case 'V': case 'H': case 'D': case 'B': case 'N': return true;
-        default: return false;
-    }
+    const std::string t = suf;
+    return s.size() >= t.size() && s.compare(s.size() - t.size(), t.size(), t) == 0;
 }
 
-inline void appendFastaRecords(Batch & out, const std::string & path, uint32_t binNo, uint32_t k)
+// SeqFileIn picks the format from the extension (".gz" aside)
+inline int formatOfPath(std::string path)
 {
-    gzFile gz = gzopen(path.c_str(), "rb");
+    if (endsWith(path, ".gz")) path.resize(path.size() - 3);
+    return endsWith(path, ".fq") || endsWith(path, ".fastq") ? 1 /* DYIBF_FMT_FASTQ */ : 0 /* DYIBF_FMT_FASTA */;
+}
+
+// the (inflated) bytes of one file become one text of the batch
+inline void appendFileText(TextBatch & out, const std::string & path, uint32_t binNo)
+{
+    gzFile gz = gzopen(path.c_str(), "rb");                          // plain files pass through
     if (!gz)
         throw std::runtime_error("Unable to open contigs File: " + path);
     gzbuffer(gz, 1 << 20);
-    std::vector<char> buf(1 << 20);
-    enum { START, HEADER, SEQ, FQ_SEQ, FQ_PLUS, FQ_QUAL } st = START;
-    bool fastq = false, afterFastqRecord = false;
-    uint64_t recStart = out.concat.size();
-    uint64_t qualLeft = 0;
-    auto finish = [&]() {
-        if (out.concat.size() - recStart >= k) { out.limits.push_back(out.concat.size()); out.binIds.push_back(binNo); }
-        else out.concat.resize(recStart);
-        recStart = out.concat.size();
-    };
-    auto blank = [](char c) { return c == '\n' || c == '\r' || c == ' ' || c == '\t' || c == '\v' || c == '\f'; };
-    auto base = [&](char c) {
-        if (!iupacChar(c)) { gzclose(gz); throw std::runtime_error("ParseError in " + path + ": character '" + std::string(1, c) + "' is not in the IUPAC alphabet"); }
-        out.concat.push_back((uint8_t)c);
-    };
-    int n;
-    while ((n = gzread(gz, buf.data(), (unsigned)buf.size())) > 0)
+    // a plain file's size is known (one allocation, no regrowth); a gzip file's text is a few times its size
+    std::vector<char> text;
     {
-        for (int i = 0; i < n; ++i)
-        {
-            const char c = buf[i];
-            switch (st)
-            {
-                case START:
-                    if (c == '>' && !afterFastqRecord) { fastq = false; st = HEADER; }
-                    else if (c == '@') { fastq = true; st = HEADER; }
-                    else if (afterFastqRecord && !blank(c))
-                    { gzclose(gz); throw std::runtime_error("ParseError in " + path + ": Fastq quality string is expected to be of the same length as the sequence"); }
-                    break;
-                case HEADER:
-                    if (c == '\n') { st = fastq ? FQ_SEQ : SEQ; recStart = out.concat.size(); }
-                    break;
-                case SEQ:
-                    if (c == '>') { finish(); st = HEADER; }
-                    else if (!blank(c)) base(c);
-                    break;
-                case FQ_SEQ:
-                    if (c == '+') { st = FQ_PLUS; qualLeft = out.concat.size() - recStart; }
-                    else if (!blank(c)) base(c);
-                    break;
-                case FQ_PLUS:
-                    if (c == '\n') { st = FQ_QUAL; if (qualLeft == 0) { finish(); st = START; afterFastqRecord = true; } }
-                    break;
-                case FQ_QUAL:
-                    if (!blank(c) && --qualLeft == 0) { finish(); st = START; afterFastqRecord = true; }
-                    break;
-            }
-        }
+        FILE * fp = fopen(path.c_str(), "rb");
+        long long sz = 0;
+        if (fp) { if (fseeko(fp, 0, SEEK_END) == 0) sz = (long long)ftello(fp); fclose(fp); }
+        const bool gzip = endsWith(path, ".gz");
+        text.resize((size_t)std::max<long long>(gzip ? 4 * sz : sz + 1, 1 << 16));
+    }
+    size_t used = 0;
+    int n;
+    while ((n = gzread(gz, text.data() + used, (unsigned)std::min<size_t>(text.size() - used, 1u << 30))) > 0)
+    {
+        used += (size_t)n;
+        if (used == text.size()) text.resize(text.size() * 2);
     }
     const bool bad = n < 0;
     gzclose(gz);
     if (bad)
         throw std::runtime_error("Error while reading contigs File: " + path);
-    if (st == SEQ) finish();
-    else if (st == FQ_SEQ || st == FQ_QUAL || st == FQ_PLUS || (st == HEADER && fastq))
-        throw std::runtime_error("UnexpectedEnd in " + path + ": the file ends inside a record");
+    text.resize(used);
+    out.bytes += used;
+    out.texts.push_back(std::move(text));
+    out.binIds.push_back(binNo);
+    out.formats.push_back(formatOfPath(path));
+}
+
+// one build call for the batch; throws what the library reports (a ParseError names the file)
+inline void addTextBatch(dyibf_filter * filter, TextBatch & batch, const std::vector<std::string> * names = nullptr)
+{
+    if (batch.empty()) return;
+    std::vector<const char *> ptrs; std::vector<uint64_t> sizes;
+    for (auto const & t : batch.texts) { ptrs.push_back(t.data()); sizes.push_back(t.size()); }
+    uint32_t bad = 0xffffffffu;
+    if (dyibf_add_fasta_texts(filter, ptrs.data(), sizes.data(), batch.binIds.data(), batch.formats.data(), (uint32_t)ptrs.size(), &bad) != DYIBF_OK)
+    {
+        std::string msg = dyibf_last_error();
+        if (bad != 0xffffffffu) msg = "ParseError in the contigs of bin " + std::to_string(batch.binIds[bad]) +
+                                      (names && bad < names->size() ? " (" + (*names)[bad] + ")" : std::string()) + ": " + msg;
+        throw std::runtime_error(msg);
+    }
+    batch.clear();
 }
 
 } // namespace dyibf_tools
