@@ -528,6 +528,15 @@ def run_b200(args):
             from bench_support import extras as X
             pinned_b = None if paired else [h_reads[i * rb:(i + 1) * rb].reshape(-1) for i in range(n_calls)]
             dropin["asynchronous"] = X.dropin_async(mk_ctx(), batches, pinned_b, per_call, rb, group)
+            # the same tickets as a caller gets them by default (early exit on): identical lists, fewer lookups
+            f.set_early_exit(True)
+            try:
+                ee = X.dropin_async(mk_ctx(), batches, pinned_b, per_call, rb, group)
+            finally:
+                f.set_early_exit(False)
+            dropin["asynchronous_early_exit_default"] = {"value": ee["value"], "pinned_input": ee.get("pinned_input"), "unit": args.unit,
+                                                         "lists_equal_synchronous": ee["lists_equal_synchronous"],
+                                                         "note": "the same ticketed batches with the library's default DYIBF_OPT_EARLY_EXIT = 1"}
 
     # ---- extra (not the headline): the same step with DYIBF_OPT_EARLY_EXIT — identical rows, fewer lookups
     early = None
