@@ -213,5 +213,15 @@ def test_filter_reads_cli_vs_reference_mapper_output(tools, dy, golden, tmp_path
     r4 = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-rb", "1000", "-vv", str(tmp_path / "wrapped.fq")], capture_output=True, text=True)
     assert r4.returncode == 0, r4.stderr
     assert [l for l in r4.stderr.splitlines() if l.startswith("bin ")] == [l for l in r.stderr.splitlines() if l.startswith("bin ")]
+    # several GPUs of this one process (a replica each, successive batches to successive GPUs): same lists, through the text
+    # tickets (regular layout) and through the parsed path (wrapped FASTQ)
+    import ctypes as C
+    ndev = C.c_int(0); dy.lib().dyibf_device_count(C.byref(ndev))
+    if ndev.value >= 2:
+        for name in ("reads.fa", "wrapped.fq"):
+            r5 = subprocess.run([exe, "-fi", str(filt), "-e", "3", "-rb", "1000", "-vv", "--devices", "0,1", str(tmp_path / name)],
+                                capture_output=True, text=True)
+            assert r5.returncode == 0, r5.stderr
+            assert [l for l in r5.stderr.splitlines() if l.startswith("bin ")] == [l for l in r.stderr.splitlines() if l.startswith("bin ")], name
     r = subprocess.run([exe, "-fi", str(tmp_path / "nope.filter"), str(tmp_path / "reads.fa")], capture_output=True, text=True)
     assert r.returncode == 1 and "could not be read" in r.stderr
