@@ -621,11 +621,9 @@ int main(int argc, char ** argv)
     }
     if (!ok)
     {
-        // unblock and join the reader before leaving
-        for (auto & fl : ring) if (fl.ticket) dyibf_classify_cancel(fl.ticket);
-        std::thread drain([&] { for (;;) { TextBatch * b = bq.take(bq.ready); const bool l = b->last; bq.give(bq.spare, b); if (l) break; } });
-        reader.join(); drain.detach();
-        return 1;
+        // the reader thread may be blocked on the batch queue: leave without unwinding it (everything worth flushing is on std::cerr)
+        std::cerr.flush();
+        std::_Exit(1);
     }
     reader.join();
     filterReads = now() - tFilter;
