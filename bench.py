@@ -628,7 +628,7 @@ def run_b200(args):
         ingest = {"value": n_ing / (ing_ms / 1e3), "unit": "reads/s", "text_gbs": d_text.numel() / (ing_ms / 1e3) / 1e9,
                   "ms": ing_ms, "reads": n_ing, "text_bytes": int(d_text.numel()), "output_equal_reads": True,
                   "note": "dyibf_parse_records (FASTQ, device-resident text of the first reads of the workload -> sequence "
-                          "characters + limits, 5 passes incl. per-call scratch allocation); not part of value/e2e"}
+                          "characters + limits; two reads of the text: summary + class counts, scans, emit); not part of value/e2e"}
         del d_text, d_seq_out, d_lim_out, rec
 
     # ---- roofline of the dominant kernel (query) against the measured HBM peak

@@ -243,7 +243,7 @@ int  dyibf_gather_reads(dyibf_filter* f, uint32_t bin, uint8_t* out_seqs, uint64
  * dyibf_add_sequences with DYIBF_ENC_ASCII) and out_limits[n_seqs + 1] = limit_base + the start of every record
  * (a ConcatDirect StringSet's limits).  Ids and qualities are not extracted: the filter does not read them.
  * *n_seqs / *n_bases always receive the sizes; out_seqs == NULL and out_limits == NULL is a sizing call.
- * FASTQ in the four-line layout goes through the streaming tokeniser (330 GB/s of text); anything else SeqAn's sequential
+ * FASTQ in the four-line layout goes through the streaming tokeniser (405 GB/s of text); anything else SeqAn's sequential
  * reader accepts — sequences / qualities wrapped over several lines, blank lines between records — through a speculative
  * one (every '@' after white space is parsed as if it opened a record, pointer jumping picks the real ones; tens of GB/s).
  * Errors: DYIBF_ERR_FORMAT where SeqAn throws (a character outside the alphabet, no record in a non-empty text, a
