@@ -809,7 +809,7 @@ int parse_records_impl(int device, const char* text, uint64_t n_bytes, int forma
     if (needs_general(tot[5])) return general_fastq();
     if (tot[5] != ~0ull) return format_error(tot[5]);
     *n_seqs = tot[0]; *n_bases = tot[1];
-    if (sizing && format == DYIBF_FMT_FASTA) return DYIBF_OK;             // FASTQ: the length checks run in the last pass
+    // a sizing call runs the emit pass into scratch as well: that pass is the one that validates (alphabet, FASTQ layout / lengths)
     if (!sizing && (!out_limits || (tot[1] && !out_seqs))) return fail(DYIBF_ERR_ARG, "dyibf_parse_records: NULL output");
     if (!sizing && (tot[0] > capacity_seqs || tot[1] > capacity_bytes))
         return fail(DYIBF_ERR_CAPACITY, "dyibf_parse_records: %llu records / %llu sequence characters do not fit the output buffers",

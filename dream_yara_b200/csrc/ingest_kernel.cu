@@ -6,16 +6,18 @@
 // :302-345 (Fastq), stream/tokenization.h:51-58 (IsInAlphabet), :145-149 (whitespace = ' ' '\t' '\n' '\r').
 //
 // Both formats are state machines whose state at a byte is a prefix function of the text, so the text is cut into tiles
-// of 8 KiB (256 threads x 32 bytes) and parsed in five streaming passes:
-//   1 summary : per tile, what a later tile needs to know about it (below);       one read of the text
-//   2 scan    : tile summaries -> state at the start of every tile                (n/4096 elements)
-//   3 count   : per tile, records started / sequence characters / quality characters, and validation;  second read
+// of 8 KiB (256 threads x 32 bytes) and parsed in streaming passes:
+//   1 summary : per tile, what a later tile needs to know about it, and its counts under every state it can be entered in;
+//               one read of the text
+//   2 scan    : tile summaries -> state at the start of every tile                (n/8192 elements)
+//   3 select  : per tile, records started / sequence characters / quality characters for the state it IS entered in
 //   4 scan    : exclusive prefix sums of those counts over the tiles
-//   5 emit    : sequence characters to out_seqs, limits[r] at every record start;  third read
-// FASTQ reads the text only twice (round 2): pass 1 also counts, per class of LOCAL line number mod 4, the non-white-space
-// characters and the lines opening with '@'; after the scan of the newline counts the class that holds sequences / qualities /
-// record starts is known per tile and pass 3 is a selection over the tile table (ingest_select_fastq) instead of a second read;
-// the validation of pass 3 moves into the emit pass.  330 -> 405 GB/s of text.
+//   5 emit    : validation, sequence characters to out_seqs, limits[r] at every record start;  second read
+// (Round 1 counted in a pass of its own over the text — three reads.)
+// Pass 1's counts per entry state — FASTQ: per class of LOCAL line number mod 4, the non-white-space characters and the lines opening with '@'; FASTA: the
+// record / sequence counts for "entered outside an id", "entered inside an id" and "holds the first '>' of the text" — make
+// pass 3 a selection over the tile table (ingest_select_fastq / _fasta); the validation sits in the emit pass (a sizing call
+// therefore runs the emit pass into scratch).  FASTQ: 330 -> 405 GB/s of text.
 // FASTA  — SeqAn: skip to the next '>', the rest of that line is the id, then every non-whitespace character up to the
 //   next '>' (anywhere, not only at a line start) is sequence.  An id ends at a newline and a '>' inside an id is text, so
 //   "inside an id" at byte i <=> the last of {'\n', '\r', '>'} before i is a '>': the tile summary is the kind of its last
@@ -23,8 +25,8 @@
 // FASTQ  — the four-line layout ('@' id / sequence / '+' / qualities, one line each): the state is the number of '\n'
 //   before the byte, mod 4; the tile summary is its newline count, the scan a prefix sum.  SeqAn also accepts sequences
 //   and qualities wrapped over several lines and blank lines between records; those need the sequential reader (the
-//   number of quality characters to consume is the length of the sequence read so far) and are REJECTED here with
-//   DYIBF_ERR_FORMAT instead of being mis-parsed: every '@' line must open a line whose number is 0 mod 4, every third
+//   number of quality characters to consume is the length of the sequence read so far) and are handed to the general parser
+//   (ingest_general.cu) when this tokeniser finds the layout violated: every '@' line must open a line whose number is 0 mod 4, every third
 //   line must open with '+', and at every end of a quality line the running totals of sequence and quality characters
 //   must agree — which is also SeqAn's own check (:341-344).  Trailing whitespace after the last record is ignored.
 // Characters outside the target alphabet are SeqAn ParseErrors (reads: ACGTN, contigs: the 16 IUPAC letters; either
@@ -234,7 +236,26 @@ __global__ void __launch_bounds__(IT) ingest_summary_kernel(const uint8_t* __res
         const uint32_t mine = (gt | nl) ? (gt > nl ? D_GT : D_NL) : D_NONE;      // the higher mask holds the later byte
         const uint32_t any = __ballot_sync(FULL, gt != 0);                         // the warp's first '>' is its lowest lane's
         if (any && (threadIdx.x & 31) == (uint32_t)(__ffs(any) - 1)) atomicMin(&g[G_BEGIN], (unsigned long long)(i0 + __ffs(gt) - 1));
-        block_excl_scan<uint32_t>(mine, OpLast(), sm, &total);
+        const uint32_t state = block_excl_scan<uint32_t>(mine, OpLast(), sm, &total);
+        // Counts under the three views a tile can be in: A — it is entered outside an id; B — it is entered inside an id;
+        // C — it holds the first '>' of the text, everything before that '>' is skipped.  Threads behind a delimiter of the tile
+        // know their state; only the ones before the tile's first delimiter differ between A and B.
+        __shared__ unsigned long long tile_first_gt;
+        if (threadIdx.x == 0) tile_first_gt = ~0ull;
+        __syncthreads();
+        if (any && (threadIdx.x & 31) == (uint32_t)(__ffs(any) - 1)) atomicMin(&tile_first_gt, (unsigned long long)(i0 + __ffs(gt) - 1));
+        __syncthreads();
+        const uint64_t fg = tile_first_gt;
+        const uint32_t ws = mask_of(c, ByteTest::White());
+        const Marks ma = mark_fasta(c, gt, nl, ws, state == D_NONE ? false : state == D_GT, i0, 0);
+        const Marks mb = state == D_NONE ? mark_fasta(c, gt, nl, ws, true, i0, 0) : ma;
+        const uint32_t after = fg == ~0ull || fg >= i0 + 32 ? 0u : (fg <= i0 ? FULL : ~((1u << (uint32_t)(fg - i0)) - 1u));
+        const uint64_t seqs = (uint64_t)__popc(ma.seq) | ((uint64_t)__popc(mb.seq) << 16) | ((uint64_t)__popc(ma.seq & after) << 32);
+        const uint64_t recs = (uint64_t)__popc(ma.rec) | ((uint64_t)__popc(mb.rec) << 16) | ((uint64_t)__popc(ma.rec & after) << 32);
+        uint64_t t_seqs, t_recs;
+        block_excl_scan<uint64_t>(seqs, OpSum(), sm64, &t_seqs);         // each field at most 8192 per tile
+        block_excl_scan<uint64_t>(recs, OpSum(), sm64, &t_recs);
+        if (threadIdx.x == 0) { cls[2 * (uint64_t)blockIdx.x] = t_seqs; cls[2 * (uint64_t)blockIdx.x + 1] = t_recs; }
     } else {
         const uint32_t nl = mask_of(c, ByteTest::Char{'\n'}), graph = c.valid & ~mask_of(c, ByteTest::White());
         const uint64_t e = graph ? i0 + 32 - __clz(graph) : 0;                     // one past this thread's last non-whitespace byte
@@ -267,6 +288,20 @@ __global__ void __launch_bounds__(IT) ingest_summary_kernel(const uint8_t* __res
         if (threadIdx.x == 0) { cls[2 * (uint64_t)blockIdx.x] = t_nonws; cls[2 * (uint64_t)blockIdx.x + 1] = t_ats; }
     }
     if (threadIdx.x == 0) summary[blockIdx.x] = total;
+}
+
+// FASTA: the tile's record / sequence counts from its three views, the state it is entered in and the first '>' of the text
+__global__ void __launch_bounds__(256) ingest_select_fasta(const uint64_t* __restrict__ entry, const uint64_t* __restrict__ cls, uint64_t n_tiles,
+                                                           const unsigned long long* __restrict__ g, uint64_t* __restrict__ rec,
+                                                           uint64_t* __restrict__ seq, uint64_t* __restrict__ qual)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    const uint64_t begin = g[G_BEGIN], tb = begin == ~0ull ? ~0ull : begin / TILE;
+    const int view = t < tb ? -1 : (t == tb ? 2 : (entry[t] == D_GT ? 1 : 0));
+    rec[t] = view < 0 ? 0 : (cls[2 * t + 1] >> (16 * view)) & 0xffffu;
+    seq[t] = view < 0 ? 0 : (cls[2 * t] >> (16 * view)) & 0xffffu;
+    qual[t] = 0;
 }
 
 // FASTQ: the tile's record / sequence / quality counts from its class counts and the lines before it
@@ -338,7 +373,7 @@ __global__ void __launch_bounds__(IT) ingest_walk_kernel(const WalkArgs a)
         const bool prev_nl = i0 == 0 || (c.valid && __ldg(a.text + i0 - 1) == '\n');
         m = mark_fastq(c, nl, ws, mask_of(c, ByteTest::Char{'@'}), mask_of(c, ByteTest::Char{'+'}), line0, prev_nl);
     }
-    if (!EMIT || FMT == DYIBF_FMT_FASTQ) {                  // SeqAn's ParseErrors, reported once (FASTA: the counting pass; FASTQ: the emit pass)
+    if (EMIT) {                                             // SeqAn's ParseErrors, reported once: the emit pass is the one that looks at every byte's role
         const uint32_t foreign = m.seq & ~mask_of(c, ByteTest::Alpha{a.iupac});
         if (foreign) report(a.g, i0 + __ffs(foreign) - 1, E_ALPHABET);
         if (m.bad)   report(a.g, i0 + __ffs(m.bad) - 1, E_FQ_LAYOUT);
@@ -437,9 +472,11 @@ cudaError_t launch_ingest_count(const uint8_t* text, uint64_t n, int format, int
     a.out_seqs = nullptr; a.out_limits = nullptr; a.limit_base = 0; a.out_rec_pos = nullptr; a.g = g;
     cudaError_t e;
     if (format == DYIBF_FMT_FASTA) {
-        ingest_summary_kernel<DYIBF_FMT_FASTA><<<(unsigned)n_tiles, IT, 0, st>>>(text, n, aligned, entry, g, nullptr);
+        uint64_t* cls = reinterpret_cast<uint64_t*>(g + G_N);
+        ingest_summary_kernel<DYIBF_FMT_FASTA><<<(unsigned)n_tiles, IT, 0, st>>>(text, n, aligned, entry, g, cls);
         ingest_propagate_kernel<<<1, 1024, 0, st>>>(entry, n_tiles);
-        ingest_walk_kernel<DYIBF_FMT_FASTA, false><<<(unsigned)n_tiles, IT, 0, st>>>(a);
+        // no second read of the text for counting: the tile's counts are picked from its three views
+        ingest_select_fasta<<<(unsigned)((n_tiles + 255) / 256), 256, 0, st>>>(entry, cls, n_tiles, g, rec, seq, qual);
     } else {
         uint64_t* cls = reinterpret_cast<uint64_t*>(g + G_N);
         ingest_summary_kernel<DYIBF_FMT_FASTQ><<<(unsigned)n_tiles, IT, 0, st>>>(text, n, aligned, entry, g, cls);
