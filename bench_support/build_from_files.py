@@ -88,7 +88,7 @@ def main():
         same, detail = files_equal(filt, want)
         out["file_identical_to_library_build"] = same
         out["detail"] = detail
-        out["tail"] = r.stderr.strip().splitlines()[-3:]
+        out["tail"] = [l for l in r.stderr.strip().splitlines() if not l.startswith("[bin ")][-6:]
         for p in (filt, want):
             os.unlink(p)
     finally:
