@@ -607,6 +607,30 @@ def single_process(ctx, steps=4):
                "limiter": "one host thread per GPU issues the copies; the batch is read once from host memory at host_read_gbs"}
         if not same:
             raise AssertionError("single-process group lists are not consistent with rank 0's own lists")
+        # ---- A/B: the same batch in a pinned buffer spread over the host's NUMA nodes (DYIBF_HOST_ALLOC_INTERLEAVE): several GPUs
+        # on different sockets read it at once
+        if world >= 4:
+            try:
+                os.environ["DYIBF_HOST_ALLOC_INTERLEAVE"] = "1"
+                hp2 = C.c_void_p(); check(L.dyibf_host_alloc(C.byref(hp2), n * RL))
+                os.environ.pop("DYIBF_HOST_ALLOC_INTERLEAVE", None)
+                h2 = np.ctypeslib.as_array(C.cast(hp2, C.POINTER(C.c_uint8)), shape=(n, RL)); h2[:] = h_reads
+
+                def step2():
+                    check(L.dyibf_group_classify(g._g, hp2, _vp(h_off), n, ENC_DNA5, 2, 1, ctx.thr, _vp(h_boff), ip, cap, C.byref(tot)))
+                step2()
+                t0 = time.perf_counter()
+                for _ in range(steps):
+                    step2()
+                dt2 = time.perf_counter() - t0
+                out["interleaved_host_buffer"] = {"value": n * steps / dt2, "unit": ctx.args.unit, "host_read_gbs": n * RL / (dt2 / steps) / 1e9,
+                                                  "note": "the same calls with the batch in a pinned buffer whose pages are interleaved over the "
+                                                          "host's NUMA nodes (DYIBF_HOST_ALLOC_INTERLEAVE=1 at allocation)"}
+                L.dyibf_host_free(hp2)
+            except Exception as ex:                                    # an A/B, never a reason to lose the line
+                out["interleaved_host_buffer"] = {"error": str(ex)[:200]}
+            finally:
+                os.environ.pop("DYIBF_HOST_ALLOC_INTERLEAVE", None)
         # ---- the same filter built by ALL devices of the group (build_filter's bins-over-threads, d_build_filter.cpp:227-260, with
         # GPUs as the threads): every sequence goes to the device that owns its bin's word column, the replicas then exchange
         # the columns over NVLink.  Must equal the table one GPU built.

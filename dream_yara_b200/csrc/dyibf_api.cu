@@ -9,6 +9,9 @@
 // synthesised when the filter is downloaded or saved.
 #include "dyibf_handle.h"
 
+#include <sys/syscall.h>
+#include <unistd.h>
+
 #include <cmath>
 
 using namespace dyibf;
@@ -1475,10 +1478,41 @@ int dyibf_device_errors(dyibf_filter* f, uint32_t* flags, int reset)
 
 uint64_t dyibf_launch_count(const dyibf_filter* f) { return f ? f->kernel_launches : 0; }
 
+// Large pinned buffers can be spread over the host's NUMA nodes (DYIBF_HOST_ALLOC_INTERLEAVE=1): a buffer that several GPUs on
+// different sockets read at once (dyibf_group_classify from one batch) is then served by all memory controllers instead of one.
+// Off by default: a buffer read by one GPU is best on that GPU's own socket, which the first-touch default usually gives.
+static bool interleave_policy(bool on)
+{
+#if defined(__linux__) && defined(SYS_set_mempolicy)
+    unsigned long mask[16];                                          // the nodes that are online: "0-1", "0,2-3", ...
+    FILE* fp = fopen("/sys/devices/system/node/online", "r");
+    if (!fp) return false;
+    int lo = 0, hi = 0; char sep = 0;
+    memset(mask, 0, sizeof mask);
+    bool any = false;
+    while (fscanf(fp, "%d", &lo) == 1) {
+        hi = lo;
+        if (fscanf(fp, "%c", &sep) == 1 && sep == '-') { if (fscanf(fp, "%d", &hi) != 1) hi = lo; if (fscanf(fp, "%c", &sep) != 1) sep = 0; }
+        for (int n = lo; n <= hi && n < 1024; ++n) { mask[n / (8 * sizeof(long))] |= 1ul << (n % (8 * sizeof(long))); any = true; }
+        if (sep != ',') break;
+    }
+    fclose(fp);
+    if (!any || hi == 0) return false;                               // one node: nothing to interleave
+    const int MPOL_DEFAULT_ = 0, MPOL_INTERLEAVE_ = 3;
+    return syscall(SYS_set_mempolicy, on ? MPOL_INTERLEAVE_ : MPOL_DEFAULT_, on ? mask : nullptr, on ? 1024ul : 0ul) == 0;
+#else
+    (void)on; return false;
+#endif
+}
+
 int dyibf_host_alloc(void** ptr, size_t bytes)
 {
     if (!ptr) return fail(DYIBF_ERR_ARG, "ptr is NULL");
-    CU(cudaMallocHost(ptr, bytes ? bytes : 1));
+    const char* env = getenv("DYIBF_HOST_ALLOC_INTERLEAVE");
+    const bool spread = env && atoi(env) != 0 && bytes >= (64u << 20) && interleave_policy(true);
+    cudaError_t e = cudaMallocHost(ptr, bytes ? bytes : 1);
+    if (spread) interleave_policy(false);
+    if (e != cudaSuccess) return fail(DYIBF_ERR_CUDA, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
     return DYIBF_OK;
 }
 

@@ -55,6 +55,20 @@ __global__ void __launch_bounds__(256) exchange_columns_kernel(PeerTables peers,
     }
 }
 
+// Read-sharded lists -> the caller's CSR when the caller's buffer is pinned (device-accessible) host memory: bin b's list of
+// this member goes to out[pre[b] ...] straight over PCIe, one warp per bin, instead of a download into a staging buffer and
+// 1024 host memcpys per member (the members' host threads all write one array: ~20 ms per 80 M-read batch on 8 GPUs).
+__global__ void __launch_bounds__(256) scatter_lists_kernel(const uint32_t* __restrict__ ids, const uint64_t* __restrict__ off,
+                                                            const uint64_t* __restrict__ pre, uint32_t bins, uint32_t* __restrict__ out)
+{
+    const uint32_t lane = threadIdx.x & 31, n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < bins; b += n_warps) {
+        const uint64_t a = off[b], c = off[b + 1] - a;
+        uint32_t* dst = out + pre[b];
+        for (uint64_t k = lane; k < c; k += 32) dst[k] = ids[a + k];
+    }
+}
+
 class Pool {                                                          // one persistent host thread per device
 public:
     explicit Pool(int n) : n_(n), busy_(0), gen_(0), stop_(false) {
@@ -250,10 +264,30 @@ static int group_fetch(dyibf_group* g, uint64_t* bin_offsets, uint32_t* read_ids
     bin_offsets[bins] = tot = pos;
     if (total) *total = tot;
     if (tot > capacity) return fail(DYIBF_ERR_CAPACITY, "%llu (read,bin) pairs exceed the capacity of %llu", (unsigned long long)tot, (unsigned long long)capacity);
+    // a pinned output buffer is written by the devices themselves (mapped host memory under UVA)
+    bool direct = false;
+    if (tot) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, read_ids) == cudaSuccess) direct = at.type == cudaMemoryTypeHost && at.devicePointer != nullptr;
+        else cudaGetLastError();
+        if (getenv("DYIBF_GROUP_STAGED_LISTS")) direct = false;      // A/B
+    }
     run_members(g, [&](int i) -> int {
         dyibf_filter* f = g->member[i];
         const uint64_t mine = f->h_csr_off[bins];
         if (!mine) return DYIBF_OK;
+        if (direct) {
+            cudaStream_t st = f->slot[0].st;
+            CU(f->misc.reserve((uint64_t)bins * 8 + 64));
+            CU(cudaMemcpyAsync(f->misc.p, pre.data() + (size_t)i * bins, (uint64_t)bins * 8, cudaMemcpyHostToDevice, st));
+            f->kernel_launches += 1;
+            const unsigned blocks = (unsigned)std::min<uint32_t>((bins + 7) / 8, (uint32_t)f->sm_count * 8);
+            scatter_lists_kernel<<<blocks, 256, 0, st>>>(static_cast<const uint32_t*>(f->csr_ids.p), static_cast<const uint64_t*>(f->csr_off.p),
+                                                         static_cast<const uint64_t*>(f->misc.p), bins, read_ids);
+            CU(cudaGetLastError());
+            CU(cudaStreamSynchronize(st));
+            return DYIBF_OK;
+        }
         int rc = ensure_h_ids(g, i, mine * 4);
         if (rc) return rc;
         CU(cudaMemcpyAsync(g->h_ids[i], f->csr_ids.p, mine * 4, cudaMemcpyDeviceToHost, f->slot[0].st));

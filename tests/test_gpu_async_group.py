@@ -273,6 +273,13 @@ def test_group_two_gpus_read_and_bin_sharded(dy, oracle, tmp_path, paired):
         ids = np.zeros(wi.size, dtype=np.uint32)
         assert L.dyibf_group_classify_fetch(g._g, C.c_void_p(offs.ctypes.data), C.c_void_p(ids.ctypes.data), ids.size, C.byref(tot)) == 0
         assert np.array_equal(ids, wi)
+        # a pinned output buffer: the devices scatter their lists into it themselves (no staging, no host memcpy); a guard word
+        # behind the lists stays untouched
+        hp = C.c_void_p(); assert L.dyibf_host_alloc(C.byref(hp), (wi.size + 4) * 4) == 0
+        pin = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint32)), shape=(wi.size + 4,)); pin[:] = 0xdeadbeef
+        assert L.dyibf_group_classify_fetch(g._g, C.c_void_p(offs.ctypes.data), hp, wi.size, C.byref(tot)) == 0
+        assert np.array_equal(pin[:wi.size], wi) and np.all(pin[wi.size:] == 0xdeadbeef) and np.array_equal(offs, wo), mode
+        L.dyibf_host_free(hp)
         # every member's table: replicas are identical to the single-device build (column exchange over NVLink);
         # shards are the column slices of it
         for m in range(2):
