@@ -69,6 +69,7 @@ SYMBOLS = {
     "dyibf_query_batch": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                     _U64P, _U16P, C.c_int, _P]),
     "dyibf_compact": (C.c_int, [_P, _U64P, C.c_uint32, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64), C.c_int, _P]),
+    "dyibf_compact_static": (C.c_int, [C.c_int, C.c_uint32, _U64P, C.c_uint32, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64), _P]),
     "dyibf_classify": (C.c_int, [_P, _U8P, _U64P, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_uint32,
                                  _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),
     "dyibf_classify_fetch": (C.c_int, [_P, _U64P, _U32P, C.c_uint64, C.POINTER(C.c_uint64)]),

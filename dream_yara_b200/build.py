@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIB = os.path.join(HERE, "libdyibf.so")
-SOURCES = ["dyibf_api.cu", "dyibf_io.cu", "dyibf_async.cu", "dyibf_hostcopy.cu", "dyibf_group.cu", "pack_kernel.cu", "query_kernel.cu", "build_kernel.cu", "build_bucket.cu", "build_sliced.cu", "compact_kernel.cu", "gather_kernel.cu", "ingest_kernel.cu", "ingest_general.cu", "dyibf_fasta.cu"]
+SOURCES = ["dyibf_api.cu", "dyibf_io.cu", "dyibf_async.cu", "dyibf_hostcopy.cu", "dyibf_group.cu", "pack_kernel.cu", "query_kernel.cu", "build_kernel.cu", "build_bucket.cu", "build_sliced.cu", "compact_kernel.cu", "compact_static.cu", "gather_kernel.cu", "ingest_kernel.cu", "ingest_general.cu", "dyibf_fasta.cu"]
 HEADERS = ["dyibf_internal.h", "dyibf_handle.h", "ibf_hash.cuh", os.path.join("..", "..", "include", "dyibf.h")]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

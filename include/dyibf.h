@@ -189,6 +189,32 @@ int  dyibf_query_batch(dyibf_filter* f, const uint8_t* seqs, const uint64_t* off
 int  dyibf_compact(dyibf_filter* f, const uint64_t* rows, uint32_t n_rows, uint64_t* bin_offsets,
                    uint32_t* read_ids, uint64_t capacity, uint64_t* total, int mem, void* stream);
 
+/* dyibf_compact for a caller that must not allocate device memory.  No counterpart in the reference (its lists are
+ * std::vector push_backs on the host heap).
+ * Why it exists: dyibf_compact keeps its per-bin counters in a workspace that it cudaMallocs on first use and re-allocates
+ * when a larger batch arrives.  A host program that has given the card away before the mapper stage runs — a 64 GiB filter
+ * shard plus another component's memory pool, a process under a fixed MPS memory limit — cannot count on that cudaMalloc to
+ * succeed, and a service thread feeding 100 000-read batches cannot afford the device-wide stall an allocation causes.  This
+ * entry point needs no handle and calls no cudaMalloc / cudaFree (nor anything else that allocates): rows, bin_offsets and
+ * read_ids are DEVICE pointers from the caller's own arena on `device`, and the counters live in one array of
+ * DYIBF_COMPACT_STATIC_BYTES (8 MiB) inside the library's image — every GPU that loads libdyibf.so carries those 8 MiB until
+ * the process exits, whether or not this function is ever called.
+ *   bins, rows (n_rows x ceil(bins/64) u64), bin_offsets[bins+1], read_ids[capacity], *total (host, may be NULL), stream:
+ *   as dyibf_compact with mem = DYIBF_MEM_DEVICE; the lists are identical to its lists.  DYIBF_ERR_CAPACITY likewise.
+ * Limit: the counters of the batch must fit the array, else DYIBF_ERR_NOMEM and nothing is launched.  Needed are
+ * 8 * (c + ceil(c / 4096) + 2) bytes with c = bins * ceil(n_rows / r), r = n_rows * ceil(bins / 1024) / 768 rounded up to a
+ * multiple of 32 and clamped to [32, 2048].  That admits about 2 000 000 rows at 1024 bins and 260 000 rows at 8192 bins;
+ * cut larger batches into pieces (ids of a piece start at 0: add the piece's first row).
+ * Sharing: there is ONE array per GPU and every call on that GPU uses it.  The call clears what it reads, so earlier
+ * contents never matter — but the last kernel (the one that writes read_ids) still reads the array after the call has
+ * returned, so two calls whose work can overlap on the GPU (different streams, or two host threads) corrupt each other.
+ * Keep all calls for one GPU on one stream, or wait for the stream before the next call from elsewhere.
+ * First call on each GPU: looks up where the array lives on that GPU (cudaGetSymbolAddress, which makes the driver load the
+ * library's device code there) and remembers it.  Make that first call at start-up, before any stream capture begins. */
+#define DYIBF_COMPACT_STATIC_BYTES (8ull << 20)
+int  dyibf_compact_static(int device, uint32_t bins, const uint64_t* rows, uint32_t n_rows, uint64_t* bin_offsets,
+                          uint32_t* read_ids, uint64_t capacity, uint64_t* total, void* stream);
+
 /* clasifyLoadedReads (d_mapper.h:308-375) in one call, host buffers: query + compaction with the rows kept in
  * HBM, so only the per-bin lists come back.  Arguments as dyibf_query_batch / dyibf_compact. */
 int  dyibf_classify(dyibf_filter* f, const uint8_t* seqs, const uint64_t* offsets, uint32_t n_seqs,
