@@ -111,6 +111,28 @@ def test_build_and_update_cli(tools, golden, oracle, tmp_path):
 
 
 @pytest.mark.gpu
+def test_build_cli_many_threads_small_files(tools, tmp_path):
+    """Every file must reach the filter whichever reader task finishes last (a task that was not the last to
+    finish could push its files after the final flush): 64 reader tasks over 64 small files, several times, against the
+    one-task build of the same directory."""
+    build, _ = tools
+    rng = np.random.default_rng(11)
+    d = tmp_path / "bins"; d.mkdir()
+    for b in range(64):
+        _write_fasta(d / ("%d.fna" % b), [("bin%d" % b, bytes(rng.choice(list(b"ACGT"), 400 + 37 * b).astype(np.uint8)))])
+    common = ["-b", "64", "-k", "19", "-nh", "3", "-bs", "1", str(d)]
+    one = tmp_path / "one.filter"
+    r = subprocess.run([build, "-t", "1", "-o", str(one)] + common, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want = ka.md5_file(one)
+    for rep in range(3):
+        many = tmp_path / "many.filter"
+        r = subprocess.run([build, "-t", "64", "-o", str(many)] + common, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert ka.md5_file(many) == want, "run %d with 64 reader tasks lost or changed bins" % rep
+
+
+@pytest.mark.gpu
 def test_build_cli_kmer_direct(tools, golden, oracle, dy, tmp_path):
     """dream_yara_build_filter -ft kmer_direct (d_build_filter.cpp:305-313): 4^k * bins + 256 bits, trailer [bins, 0, k, 0]"""
     build, update = tools

@@ -189,7 +189,15 @@ int main(int argc, char ** argv)
             hand_over(batch, --running == 0);                        // the last task to finish flushes what is left
         }));
     }
-    try { for (auto & t : tasks) t.get(); if (!created.get()) throw std::runtime_error(createError); }
+    try
+    {
+        for (auto & t : tasks) t.get();
+        // "last" above is decided outside poolMutex: a task that was not last can still push its files after the last one has
+        // flushed.  Whatever is in the pool once every task has returned goes to the GPU here.
+        TextBatch none;
+        hand_over(none, true);
+        if (!created.get()) throw std::runtime_error(createError);
+    }
     catch (std::exception const & e) { std::cerr << "dyibf_build_filter: " << e.what() << std::endl; return 1; }
     if (options.verbose)
     {
