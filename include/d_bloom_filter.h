@@ -75,17 +75,8 @@ namespace seqan
                          int device = -1)
         {
             std::vector<int> devs = _devicesFor(device);
-            if (devs.size() > 1)
-            {
-                uint64_t nbits = 0;
-                _exitOnLoadFailure(dyibf_peek_file(fileName, nullptr, nullptr, nullptr, &nbits));
-                if (nbits != vec_size)
-                {
-                    std::cerr << "Size mismatch: \n\t Loaded file \t" << nbits << " bits\n\t expected\t" << vec_size << std::endl;
-                    exit(1);
-                }
-                _exitOnLoadFailure(dyibf_group_load_file(fileName, devs.data(), (int)devs.size(), _envMode(), &_g));
-            }
+            if (devs.size() > 1)    // the caller's parameters, not the trailer's, as on one device and in the reference
+                _exitOnLoadFailure(dyibf_group_load_file_expect(fileName, n_bins, n_hash_func, kmer_size, vec_size, devs.data(), (int)devs.size(), _envMode(), &_g));
             else
                 _exitOnLoadFailure(dyibf_load_file_expect(fileName, n_bins, n_hash_func, kmer_size, vec_size, devs[0], &_h));
             _cacheParams();
@@ -117,7 +108,11 @@ namespace seqan
         // the object owns a device handle: movable, not copyable (the reference object was never copied either)
         SeqAnBloomFilter(SeqAnBloomFilter const &) = delete;
         SeqAnBloomFilter & operator=(SeqAnBloomFilter const &) = delete;
-        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _g(o._g), _prm(o._prm), _mtx(std::move(o._mtx)) { o._h = nullptr; o._g = nullptr; }
+        SeqAnBloomFilter(SeqAnBloomFilter && o) : _h(o._h), _g(o._g), _nDevices(o._nDevices), _mode(o._mode), _prm(o._prm), _mtx(std::move(o._mtx))
+        {
+            o._h = nullptr; o._g = nullptr;
+            o._mtx.reset(new std::mutex);               // the moved-from object stays destructible and lockable
+        }
 
         // d_bloom_filter.h:91
         void addKmers(TString const & text, uint32_t const & binNo)

@@ -103,7 +103,11 @@ int main(int argc, char ** argv)
         }
         if (mode == "query" && argc == 6)
         {
-            SeqAnBloomFilter<> filter(argv[2]);
+            // through the move constructor: the moved-to object must still know its devices and sharding (DYIBF_DEVICES /
+            // DYIBF_GROUP_MODE=bin: whichBins has to ask every bin shard, not member 0 only)
+            SeqAnBloomFilter<> loaded(argv[2]);
+            SeqAnBloomFilter<> filter(std::move(loaded));
+            std::cerr << "devices " << filter.deviceCount() << std::endl;
             uint16_t thr = (uint16_t)std::stoul(argv[4]);
             SeqFileIn in(argv[3]);
             std::ofstream out(argv[5]);

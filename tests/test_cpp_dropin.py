@@ -49,9 +49,36 @@ def test_dropin_build_query_classify(golden, tmp_path):
     _write_fasta(tmp_path / "reads400.fa", [("r%d" % i, r) for i, r in enumerate(reads[:400])])
     r = subprocess.run([BIN, "query", str(filt), str(tmp_path / "reads400.fa"), "25", str(tmp_path / "q.txt")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+    assert "devices 1" in r.stderr
     want = ka.bits_from_rows(golden["ka1_rows"][:400], 64)
     for i, line in enumerate(open(tmp_path / "q.txt")):
         assert [int(x) for x in line.split()] == list(np.nonzero(want[i])[0]), i
+    # the same through a MOVED multi-GPU object, bin-sharded and read-sharded (the move constructor dropped the device
+    # count and the mode, so whichBins asked member 0 only); needs 2 GPUs
+    import torch
+    if torch.cuda.device_count() >= 2:
+        # the gold filter has one word per hash block (read-sharded only); a 128-bin filter of its own for the bin shards
+        rng = np.random.default_rng(5)
+        d128 = tmp_path / "bins128"; d128.mkdir()
+        contigs = [bytes(rng.choice(list(b"ACGT"), 2500).astype(np.uint8)) for _ in range(128)]
+        for b, g in enumerate(contigs):
+            _write_fasta(d128 / ("%d.fa" % b), [("bin%d" % b, g)])
+        f128 = tmp_path / "f128.filter"
+        r = subprocess.run([BIN, "build", "128", "2", "19", str((1 << 26) + 256), str(d128), str(f128)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        some = [contigs[(7 * i) % 128][100 + i: 200 + i] for i in range(60)]
+        _write_fasta(tmp_path / "reads60.fa", [("r%d" % i, x) for i, x in enumerate(some)])
+        outs = {}
+        for tag, env in (("one", {}), ("bin", dict(DYIBF_DEVICES="0,1", DYIBF_GROUP_MODE="bin")), ("read", dict(DYIBF_DEVICES="0,1", DYIBF_GROUP_MODE="read"))):
+            r = subprocess.run([BIN, "query", str(f128), str(tmp_path / "reads60.fa"), "60", str(tmp_path / ("q_%s.txt" % tag))],
+                               capture_output=True, text=True, env=dict(os.environ, **env))
+            assert r.returncode == 0, r.stderr
+            assert ("devices 2" if env else "devices 1") in r.stderr
+            outs[tag] = open(tmp_path / ("q_%s.txt" % tag)).read()
+        lines = outs["one"].split("\n")
+        assert all(str((7 * i) % 128) in lines[i].split() for i in range(60))          # every read finds its own bin
+        assert any(int(x) >= 64 for ln in lines for x in ln.split())                      # ... incl. bins of the second shard
+        assert outs["bin"] == outs["one"] and outs["read"] == outs["one"]
     # the batched clasifyLoadedReads replacement, SE and PE, vs the reference's own clasifyLoadedReads
     for tag, paired in (("se", 0), ("pe", 1)):
         out = tmp_path / ("c_%s.txt" % tag)
