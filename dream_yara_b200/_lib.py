@@ -100,6 +100,7 @@ SYMBOLS = {
     "dyibf_shard_reads": (C.c_int, [C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "dyibf_group_create": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(_P)]),
     "dyibf_group_load_file": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(_P)]),
+    "dyibf_group_load_file_expect": (C.c_int, [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(C.c_int), C.c_int, C.c_int, C.POINTER(_P)]),
     "dyibf_group_destroy": (None, [_P]),
     "dyibf_group_get_params": (C.c_int, [_P, C.POINTER(Params), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "dyibf_group_member": (C.c_int, [_P, C.c_int, C.POINTER(_P), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),

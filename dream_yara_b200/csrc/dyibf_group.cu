@@ -270,20 +270,25 @@ static int group_fetch(dyibf_group* g, uint64_t* bin_offsets, uint32_t* read_ids
         cudaPointerAttributes at;
         if (cudaPointerGetAttributes(&at, read_ids) == cudaSuccess) direct = at.type == cudaMemoryTypeHost && at.devicePointer != nullptr;
         else cudaGetLastError();
-        if (getenv("DYIBF_GROUP_STAGED_LISTS")) direct = false;      // A/B
+        static const bool staged_lists = getenv("DYIBF_GROUP_STAGED_LISTS") != nullptr;   // A/B, read once
+        if (staged_lists) direct = false;
     }
     run_members(g, [&](int i) -> int {
         dyibf_filter* f = g->member[i];
         const uint64_t mine = f->h_csr_off[bins];
         if (!mine) return DYIBF_OK;
-        if (direct) {
+        // the address THIS device reaches the pinned buffer under (it equals the host address only under unified addressing
+        // with a portable registration); a device that cannot map it takes the staged path for its part
+        void* dev_ids = nullptr;
+        if (direct && (cudaHostGetDevicePointer(&dev_ids, read_ids, 0) != cudaSuccess || !dev_ids)) { cudaGetLastError(); dev_ids = nullptr; }
+        if (dev_ids) {
             cudaStream_t st = f->slot[0].st;
             CU(f->misc.reserve((uint64_t)bins * 8 + 64));
             CU(cudaMemcpyAsync(f->misc.p, pre.data() + (size_t)i * bins, (uint64_t)bins * 8, cudaMemcpyHostToDevice, st));
             f->kernel_launches += 1;
             const unsigned blocks = (unsigned)std::min<uint32_t>((bins + 7) / 8, (uint32_t)f->sm_count * 8);
             scatter_lists_kernel<<<blocks, 256, 0, st>>>(static_cast<const uint32_t*>(f->csr_ids.p), static_cast<const uint64_t*>(f->csr_off.p),
-                                                         static_cast<const uint64_t*>(f->misc.p), bins, read_ids);
+                                                         static_cast<const uint64_t*>(f->misc.p), bins, static_cast<uint32_t*>(dev_ids));
             CU(cudaGetLastError());
             CU(cudaStreamSynchronize(st));
             return DYIBF_OK;
@@ -370,13 +375,20 @@ int dyibf_group_create(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t n
     return DYIBF_OK;
 }
 
-int dyibf_group_load_file(const char* path, const int* devices, int n_devices, int mode, dyibf_group** out)
+// expect: the caller's bins / h / k / nbits describe the file (only the bit count is checked against it), as
+// dyibf_load_file_expect does for one device; else all four come from the trailer
+static int group_load(const char* path, bool expect, uint32_t bins, uint32_t h, uint32_t k, uint64_t nbits, const int* devices,
+                      int n_devices, int mode, dyibf_group** out)
 {
     if (!path || !out) return fail(DYIBF_ERR_ARG, "NULL argument");
     *out = nullptr;
-    uint32_t bins = 0, h = 0, k = 0; uint64_t nbits = 0;
-    int rc = dyibf_peek_file(path, &bins, &h, &k, &nbits);
+    uint32_t fbins = 0, fh = 0, fk = 0; uint64_t fnbits = 0;
+    int rc = dyibf_peek_file(path, &fbins, &fh, &fk, &fnbits);
     if (rc) return rc;
+    if (expect) {
+        if (fnbits != nbits) return fail(DYIBF_ERR_SIZE_MISMATCH, "Size mismatch: \n\t Loaded file \t%llu bits\n\t expected\t%llu",
+                                         (unsigned long long)fnbits, (unsigned long long)nbits);
+    } else { bins = fbins; h = fh; k = fk; nbits = fnbits; }
     dyibf_params prm; HashParams hp;
     rc = init_params(bins, h, k, nbits, &prm, &hp);
     if (rc) return rc;
@@ -397,6 +409,17 @@ int dyibf_group_load_file(const char* path, const int* devices, int n_devices, i
     if (rc) { std::string keep = last_error_string(); dyibf_group_destroy(g); set_last_error(keep); return rc; }
     *out = g;
     return DYIBF_OK;
+}
+
+int dyibf_group_load_file(const char* path, const int* devices, int n_devices, int mode, dyibf_group** out)
+{
+    return group_load(path, false, 0, 0, 0, 0, devices, n_devices, mode, out);
+}
+
+int dyibf_group_load_file_expect(const char* path, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits,
+                                 const int* devices, int n_devices, int mode, dyibf_group** out)
+{
+    return group_load(path, true, bins, n_hash, kmer, nbits, devices, n_devices, mode, out);
 }
 
 void dyibf_group_destroy(dyibf_group* g)

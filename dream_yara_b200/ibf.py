@@ -400,6 +400,7 @@ class FilterGroup:
 
         FilterGroup(n_bins, n_hash_func, kmer_size, vec_size, devices=[0, 1], mode="read")
         FilterGroup(fileName, devices=[...], mode=...)
+        FilterGroup(fileName, n_bins, n_hash_func, kmer_size, vec_size, devices=[...], mode=...)   the caller's parameters win
     """
 
     def __init__(self, *args, devices=(0,), mode="read"):
@@ -412,8 +413,12 @@ class FilterGroup:
         elif len(args) == 1:
             rc = L.dyibf_group_load_file(str(args[0]).encode(), devs, len(devices), m, C.byref(self._g))
             SeqAnBloomFilter._exit_like_reference(rc)
+        elif len(args) == 5:                                      # (fileName, n_bins, n_hash_func, kmer_size, vec_size), :59-77
+            rc = L.dyibf_group_load_file_expect(str(args[0]).encode(), args[1], args[2], args[3], args[4], devs, len(devices), m,
+                                                C.byref(self._g))
+            SeqAnBloomFilter._exit_like_reference(rc)
         else:
-            raise TypeError("FilterGroup(n_bins, n_hash_func, kmer_size, vec_size) | (fileName)")
+            raise TypeError("FilterGroup(n_bins, n_hash_func, kmer_size, vec_size) | (fileName) | (fileName, n_bins, n_hash_func, kmer_size, vec_size)")
         p = _lib.Params(); nd, md = C.c_int(0), C.c_int(0)
         check(L.dyibf_group_get_params(self._g, C.byref(p), C.byref(nd), C.byref(md)))
         self._noOfBins, self._noOfHashFunc, self._kmerSize = p.bins, p.n_hash, p.kmer

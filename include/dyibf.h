@@ -321,6 +321,11 @@ int  dyibf_shard_reads(uint32_t n_reads, int rank, int nranks, uint32_t* first, 
 int  dyibf_group_create(uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits, const int* devices, int n_devices,
                         int mode, dyibf_group** out);
 int  dyibf_group_load_file(const char* path, const int* devices, int n_devices, int mode, dyibf_group** out);
+/* SeqAnBloomFilter(fileName, n_bins, n_hash_func, kmer_size, vec_size), d_bloom_filter.h:59-77, over several GPUs: like
+ * dyibf_load_file_expect the members take bins / n_hash / kmer from the CALLER and only the file's bit count is checked
+ * (DYIBF_ERR_SIZE_MISMATCH, the reference's message); the trailer's own values are not consulted */
+int  dyibf_group_load_file_expect(const char* path, uint32_t bins, uint32_t n_hash, uint32_t kmer, uint64_t nbits,
+                                  const int* devices, int n_devices, int mode, dyibf_group** out);
 void dyibf_group_destroy(dyibf_group* g);
 int  dyibf_group_get_params(const dyibf_group* g, dyibf_params* whole, int* n_devices, int* mode);
 int  dyibf_group_member(dyibf_group* g, int index, dyibf_filter** member, uint32_t* first_bin, uint32_t* n_bins);

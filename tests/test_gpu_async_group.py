@@ -321,3 +321,41 @@ def test_group_two_gpus_read_and_bin_sharded(dy, oracle, tmp_path, paired):
             assert np.array_equal(mf0.download_words(), mf1.download_words())
         g.close()
     single.close()
+
+
+def test_group_load_file_expect_takes_the_callers_parameters(dy, oracle, tmp_path):
+    """SeqAnBloomFilter(fileName, n_bins, n_hash_func, kmer_size, vec_size) over a group: like
+    dyibf_load_file_expect and the reference (d_bloom_filter.h:59-77) the members hash with the CALLER's bins / h / k, only
+    the bit count is checked against the file.  Runs on one GPU (a group of one); with two it covers both sharding modes."""
+    contigs, reads = _case(77, 128, 600, k=16, L=80)
+    nbits = (1 << 24) + 256
+    f = dy.SeqAnBloomFilter(128, 2, 16, nbits)
+    f.addSequences(contigs, np.arange(128))
+    path = tmp_path / "g.filter"
+    f.save(path)
+    # a trailer that disagrees with what the caller will say: h = 3, k = 20 written over [bins, h, k, 0] at the file's end
+    raw = bytearray(path.read_bytes())
+    trailer = np.frombuffer(raw, dtype=np.uint64, count=4, offset=len(raw) - 32).copy()
+    assert list(trailer[:3]) == [128, 2, 16]
+    trailer[1], trailer[2] = 3, 20
+    raw[len(raw) - 32:] = trailer.tobytes()
+    path.write_bytes(bytes(raw))
+    assert dy.readFilterMetadata(path) == (128, 20)
+    thr = 30
+    want_off, want_ids = f.classify(reads, thr, group=2, derive_rc=True)
+    single = dy.SeqAnBloomFilter(path, 128, 2, 16, nbits)
+    a, b = single.classify(reads, thr, group=2, derive_rc=True)
+    assert np.array_equal(a, want_off) and np.array_equal(b, want_ids)
+    single.close()
+    devs = [0, 1] if _n_gpus(dy) >= 2 else [0]
+    for mode in ("read", "bin"):
+        g = dy.FilterGroup(path, 128, 2, 16, nbits, devices=devs, mode=mode)
+        assert (g.getNumberOfBins(), g._noOfHashFunc, g.getKmerSize()) == (128, 2, 16)
+        a, b = g.classify(reads, thr, group=2, derive_rc=True)
+        assert np.array_equal(a, want_off) and np.array_equal(b, want_ids), mode
+        g.close()
+    h = C.c_void_p()
+    d = (C.c_int * len(devs))(*devs)
+    rc = dy.lib().dyibf_group_load_file_expect(str(path).encode(), 128, 2, 16, nbits + 64, d, len(devs), 0, C.byref(h))
+    assert rc == -5 and b"Size mismatch" in dy.lib().dyibf_last_error() and not h.value
+    f.close()
