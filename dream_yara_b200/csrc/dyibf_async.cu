@@ -81,6 +81,16 @@ static int acquire_ticket(dyibf_filter* f, Ticket** out)
     return fail(DYIBF_ERR_BUSY, "dyibf_classify_begin: all %d tickets of this handle are in flight", DYIBF_MAX_TICKETS);
 }
 
+// A begin call that fails after its first asynchronous copy has been enqueued must not return while the DMA engine still
+// reads the caller's buffers (or the ticket's pinned h_in, which the next begin on that ticket overwrites): unless
+// released, the guard waits for the ticket's stream on the way out.
+struct DrainOnError {
+    cudaStream_t st; bool armed = true;
+    explicit DrainOnError(cudaStream_t s) : st(s) {}
+    ~DrainOnError() { if (armed) { cudaStreamSynchronize(st); cudaGetLastError(); } }
+    void release() { armed = false; }
+};
+
 // compaction of the ticket's rows: count + scan, then the fill into a buffer sized for the usual case (<= 4 lists per row);
 // a batch that needs more is re-filled in dyibf_classify_end
 static int enqueue_compaction(Ticket* t, uint32_t n_rows)
@@ -133,6 +143,7 @@ int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* o
     const uint64_t n_total = derive_rc ? 2ull * n_seqs : n_seqs;
     const uint32_t n_rows = (uint32_t)(n_total / group);
     cudaStream_t st = t->sl.st;
+    DrainOnError drain(st);
     t->n_rows = n_rows; t->batch.valid = false; t->ids_cap = 0;
     CU(t->csr_off.reserve((uint64_t)(bins + 1) * 8));
     if (n_rows == 0) {
@@ -195,6 +206,7 @@ int dyibf_classify_begin(dyibf_filter* f, const uint8_t* seqs, const uint64_t* o
     }
     rc = enqueue_finish(t);
     if (rc) return rc;
+    drain.release();
     *ticket = reinterpret_cast<dyibf_ticket*>(t);
     return DYIBF_OK;
 }
@@ -218,6 +230,7 @@ int dyibf_classify_text_begin(dyibf_filter* f, const char* reads_text, uint64_t 
     if (rc) return rc;
     const uint32_t bins = f->prm.bins, W = f->prm.words_per_block;
     cudaStream_t st = t->sl.st;
+    DrainOnError drain(st);
     t->n_rows = 0; t->batch.valid = false; t->ids_cap = 0;
     CU(t->csr_off.reserve((uint64_t)(bins + 1) * 8));
     // the text goes to the device once; the parsed forward read set ([reads] or [mates 1 | mates 2]) is the ticket's batch
@@ -286,6 +299,7 @@ int dyibf_classify_text_begin(dyibf_filter* f, const char* reads_text, uint64_t 
     }
     rc = enqueue_finish(t);
     if (rc) return rc;
+    drain.release();
     *ticket = reinterpret_cast<dyibf_ticket*>(t);
     return DYIBF_OK;
 }
