@@ -487,7 +487,7 @@ cudaError_t launch_bucket_split(const HashParams& hp, uint64_t* filter, const ui
     if (e != cudaSuccess) return e;
     const uint64_t items = (total_words - word_begin + SPLIT1_ITEM - 1) / SPLIT1_ITEM;
     uint64_t blocks = (items + 7) / 8;
-    if (blocks > 148ull * 6) blocks = 148ull * 6;                  // what fits (32 KiB of staging lines per block); items are claimed
+    if (blocks > sm_count_current() * 6) blocks = sm_count_current() * 6;                  // what fits (32 KiB of staging lines per block); items are claimed
     char* base = static_cast<char*>(records);
     if (p.n_super <= 1)                                            // single level: straight into the final buckets
         return split1_launch<uint32_t>(hp, filter, packed, meta, bin_ids, n_seqs, word_begin, total_words, p.R, (uint32_t)p.cap,
@@ -510,7 +510,7 @@ cudaError_t launch_bucket_split2(uint64_t* filter, const BucketPlan& p, void* re
     cudaError_t e = cudaMemsetAsync(work_counters, 0, 32 * sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     uint64_t blocks = (((fill1 + SPLIT2_ITEM - 1) / SPLIT2_ITEM) * p.n_super + 7) / 8;
-    if (blocks > 148ull * 6) blocks = 148ull * 6;
+    if (blocks > sm_count_current() * 6) blocks = sm_count_current() * 6;
     if (blocks < 4) blocks = 4;                                    // 32 warps: every super-bucket has at least one
     const size_t smem = 8 * WARP_STAGE * sizeof(uint32_t);
     const bool match = split_use_match();

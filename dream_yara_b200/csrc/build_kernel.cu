@@ -82,7 +82,7 @@ cudaError_t launch_build(const HashParams& hp, uint64_t* filter, const uint64_t*
     if (n_seqs == 0 || total_words == 0) return cudaSuccess;
     uint64_t tiles = (total_words + 31) / 32;
     uint64_t blocks = (tiles + 7) / 8;
-    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    if (blocks > sm_count_current() * 32) blocks = sm_count_current() * 32;
     dim3 grid((unsigned)blocks), block(256);
     switch (hp.h) {
         case 2:  build_kernel<2><<<grid, block, 0, st>>>(hp, filter, packed, meta, bin_ids, n_seqs, total_words); break;
@@ -117,7 +117,7 @@ cudaError_t launch_clear(const HashParams& hp, uint64_t* filter, const uint32_t*
     if (n_cols == 0) return cudaSuccess;
     uint64_t total = hp.P * n_cols;
     uint64_t blocks = (total + 255) / 256;
-    if (blocks > 148ull * 16) blocks = 148ull * 16;
+    if (blocks > sm_count_current() * 16) blocks = sm_count_current() * 16;
     clear_kernel<<<(unsigned)blocks, 256, 0, st>>>(filter, hp.P, hp.W, cols, masks, n_cols);
     return cudaGetLastError();
 }

@@ -246,7 +246,7 @@ bool sliced_plan(const HashParams& hp, uint64_t budget_bytes, SlicedPlan* p)
     // interleaved into the table and zeroed again on a second stream.  That overlap does not pay by itself — measured on
     // 1024 bins x 4 Mbp: four groups of 4 columns 105.8 ms per step against 83.0 ms for the one whole-table group (the
     // partial-row interleave is slow and contends with the scatter for the L2) — it only hides what narrow groups cost anyway.
-    const char* env_cols = getenv("DYIBF_SLICED_MAX_COLS");
+    const char* env_cols = getenv("DYIBF_SLICED_MAX_COLS");   // per plan (one getenv per build call): the tests switch it inside one process
     uint32_t cols = env_cols && atoi(env_cols) > 0 ? (uint32_t)atoi(env_cols) : 16u;
     if (cols > 16) cols = 16;
     if (cols > hp.W) cols = hp.W;
@@ -314,7 +314,7 @@ cudaError_t launch_sliced_interleave(const HashParams& hp, uint64_t* filter, con
     static const int sw = getenv("DYIBF_SLICED_SW") ? atoi(getenv("DYIBF_SLICED_SW")) : 8;
     const uint32_t* sh = static_cast<const uint32_t*>(shadow);
     uint64_t blocks = p.n_tiles;
-    if (blocks > 148ull * 16) blocks = 148ull * 16;
+    if (blocks > sm_count_current() * 16) blocks = sm_count_current() * 16;
 #define DYIBF_IL(SWV) do { \
         const size_t smem = (size_t)SWV * 32 * (n_cols | 1u) * 8; \
         if (smem > 48 * 1024) {                                     /* per device, so per launch (a group spans several GPUs) */ \

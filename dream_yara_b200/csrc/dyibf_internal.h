@@ -6,6 +6,20 @@
 
 namespace dyibf {
 
+// SMs of the CURRENT device (148 on a B200), looked up once per device: launchers size their grids in multiples of it
+inline unsigned long long sm_count_current()
+{
+    static int cached[64];                       // zero = not looked up yet; a benign race writes the same value twice
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cached[dev];
+    if (!n) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 148; }
+        cached[dev] = n;
+    }
+    return (unsigned long long)n;
+}
+
 // Everything a kernel needs to turn a k-mer value into h block indices
 // (reference: _init d_bloom_filter.h:245-254, getHashValue :286-291).
 struct HashParams {

@@ -73,7 +73,7 @@ cudaError_t launch_gather_plan(const GatherArgs& a, uint64_t* lens, uint32_t* ou
     const uint64_t n_out = (uint64_t)a.m * a.group;
     if (n_out == 0) return cudaSuccess;
     uint64_t blocks = (n_out + 255) / 256;
-    if (blocks > 148ull * 8) blocks = 148ull * 8;
+    if (blocks > sm_count_current() * 8) blocks = sm_count_current() * 8;
     gather_plan_kernel<<<(unsigned)blocks, 256, 0, st>>>(a, lens, out_ids);
     return cudaGetLastError();
 }
@@ -83,7 +83,7 @@ cudaError_t launch_gather_copy(const GatherArgs& a, const uint64_t* limits, uint
     const uint64_t n_out = (uint64_t)a.m * a.group;
     if (n_out == 0) return cudaSuccess;
     uint64_t blocks = (n_out + 7) / 8;
-    if (blocks > 148ull * 16) blocks = 148ull * 16;
+    if (blocks > sm_count_current() * 16) blocks = sm_count_current() * 16;
     gather_copy_kernel<<<(unsigned)blocks, 256, 0, st>>>(a, limits, out_bytes);
     return cudaGetLastError();
 }

@@ -528,7 +528,7 @@ cudaError_t launch_max_len(const uint64_t* limits, uint64_t n, unsigned long lon
 {
     if (n == 0) return cudaSuccess;
     uint64_t blocks = (n + 255) / 256;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > sm_count_current() * 8) blocks = sm_count_current() * 8;
     ingest_max_len_kernel<<<(unsigned)blocks, 256, 0, st>>>(limits, n, out);
     return cudaGetLastError();
 }

@@ -195,7 +195,7 @@ cudaError_t launch_pack(const PackSource& src, int encoding, int derive_rc, uint
     if (total_words == 0) return cudaSuccess;
     uint64_t tiles = (total_words + 31) / 32;
     uint64_t blocks = (tiles + 7) / 8;
-    if (blocks > 148ull * 64) blocks = 148ull * 64;
+    if (blocks > sm_count_current() * 64) blocks = sm_count_current() * 64;
     dim3 grid((unsigned)blocks), block(256);
 #define DYIBF_PACK(E) do { \
         if (src.n_ranges == 1) pack_kernel<E, true><<<grid, block, 0, st>>>(src, derive_rc, packed, meta, rc_word_base, total_words); \
