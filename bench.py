@@ -741,6 +741,36 @@ def run_b200(args):
         line.update(extras)
         if sweep is not None:
             line["e_sweep"] = sweep
+        # the verdicts and rates of the extras once more, LAST and small: a reader who keeps only the tail of the line still sees them
+        summary = {}
+        try:
+            pick = lambda d, keys: {k: d.get(k) for k in keys} if isinstance(d, dict) else None       # noqa: E731
+            if extras.get("multi_gpu_parity"):
+                summary["multi_gpu_parity"] = pick(extras["multi_gpu_parity"], ("read_sharded", "bin_sharded"))
+            sp = extras.get("single_process")
+            if sp:
+                summary["single_process"] = pick(sp, ("value", "lists_equal_reference", "lists_consistent_with_rank0"))
+                summary["single_process"]["bin_sharded_group"] = pick(sp.get("bin_sharded_group"), ("lists_equal_reference", "words_equal_reference"))
+                summary["group_build"] = pick(sp.get("group_build"), ("kmers_per_s", "words_equal_reference", "words_equal_single_gpu_build"))
+            if replication is not None:
+                summary["filter_replication_gbs"] = replication["gbs"]
+            if dropin:
+                summary["dropin_batches"] = {"value": dropin["value"], "pinned_input": dropin.get("pinned_input"),
+                                             "asynchronous": (dropin.get("asynchronous") or {}).get("value")}
+            c4 = extras.get("cfg4")
+            if c4:
+                summary["cfg4"] = {"value": c4.get("value"), "frac": (c4.get("roofline") or {}).get("frac"), "skipped": c4.get("skipped"),
+                                   "shard_vs_reference": pick(c4.get("shard_vs_reference"), ("rows_equal_reference", "lists_equal_reference", "skipped"))}
+            if extras.get("cfg3"):
+                summary["cfg3"] = pick(extras["cfg3"], ("value",))
+            c5 = extras.get("cfg5")
+            if c5:
+                summary["cfg5"] = {"value": c5.get("value"), "e2e": (c5.get("e2e") or {}).get("value"),
+                                   "words_equal_reference": (c5.get("cpu_baseline") or {}).get("filter_words_equal_gpu")}
+            summary["headline"] = {"value": value, "e2e": e2e["value"] if e2e else None, "frac": roofline["frac"], "n_gpus": world}
+        except Exception as ex:                                            # a summary must never cost the line
+            summary["error"] = repr(ex)[:200]
+        line["summary"] = summary
         print(json.dumps(line), flush=True)
     if f is not None:
         f.close()

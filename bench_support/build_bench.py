@@ -38,6 +38,35 @@ def _spread_bins(n_seqs, bins):
     return (i % ncol) * 64 + (i // ncol) % 64
 
 
+def sliced_roofline(kmers_step, h, table_bytes, build_ms, apply_ms, split2_ms, hbm_peak):
+    """The sliced build (DYIBF_BUILD_SLICED) does NOT move the random read-modify-write traffic SURVEY 8(d) models (192 B per
+    k-mer): its updates are L2 atomics into per-bin vectors and only the interleave streams DRAM.  Two kernels, two bounds:
+      interleave: read the shadow (= table size), read + write the table -> 3 x table bytes against the measured HBM peak
+      scatter   : h REDs per k-mer against the divergent L2 RED.OR rate tools/red_bench.cu measured (profiles/l2_red_peak.json)"""
+    scatter_ms = build_ms - apply_ms - split2_ms
+    inter = 3 * table_bytes / (apply_ms / 1e3) / 1e9
+    red_rate = kmers_step * h / (scatter_ms / 1e3)
+    red_peak, red_src = None, "profiles/l2_red_peak.json absent: no measured RED peak, no scatter fraction"
+    try:
+        rp = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "l2_red_peak.json")))
+        red_peak, red_src = float(rp["g_red_per_s"]) * 1e9, rp.get("source")
+    except Exception:
+        pass
+    return {"bound": "hbm", "kernel": "sliced_interleave_kernel<8>", "achieved": inter, "peak": hbm_peak, "unit": "GB/s",
+            "frac": inter / hbm_peak, "kernel_ms": apply_ms, "algorithmic_bytes_per_launch": 3 * table_bytes,
+            "traffic": 78998419000.0 * table_bytes / float(1 << 34),
+            "traffic_source": "DERIVED, not measured in this run: profiles/r02_sliced_interleave_ncu.md (dram__bytes_read 61.86 GB + "
+                              "dram__bytes_write 17.14 GB per 16 GiB pass, round 2; kernel unchanged since), scaled by table size",
+            "build_kernels_ms": build_ms, "scatter_ms": scatter_ms, "split2_ms": split2_ms,
+            "scatter": {"bound": "l2 atomics", "kernel": "sliced_scatter_kernel<%d>" % h, "achieved": red_rate / 1e9, "unit": "G RED/s",
+                        "peak": red_peak / 1e9 if red_peak else None, "frac": red_rate / red_peak if red_peak else None,
+                        "peak_source": red_src, "reds_per_launch": kmers_step * h},
+            "sector_model_gbs": kmers_step * h * 64 / (build_ms / 1e3) / 1e9,
+            "note": "build mode 3 (sliced).  frac = the interleave pass against HBM; the scatter is bound by the L2's divergent RED rate "
+                    "(scatter.frac).  sector_model_gbs is SURVEY 8(d)'s 192 B per k-mer random-RMW model over the whole step: it exceeds "
+                    "the HBM peak because this build does not move those bytes, so it is an equivalence, not a roofline"}
+
+
 def _cpu_build(cf, genomes, bin_of_seq):
     """reference build_filter (d_build_filter.cpp:217-272): bins over threads, addKmers per bin.  The reference's threads
     own contiguous bin ranges and do a non-atomic `word |= mask` (d_bloom_filter.h:300): with 1024 bins and 16 threads a
@@ -341,6 +370,12 @@ def run_b200(args, B):
                 "bucketed_model_bytes_per_step": model, "bucketed_model_gbs": model / (build_ms / 1e3) / 1e9,
                 "note": "algorithmic bytes = the random-RMW sector model (192 B/k-mer); the bucketed build moves "
                         "~%.0f B/k-mer instead (records + one table sweep per step)" % (model / kmers_step)}
+    try:
+        if f_dev.last_build_mode() == 3:                                   # sliced: the 192 B model is not what this build moves
+            roofline = dict(sliced_roofline(kmers_step, H, P * W * 8, build_ms, apply_ms, split2_ms, peak), peak_source=peak_src,
+                            pack_kernel_ms=pack_ms)
+    except Exception:
+        pass
     if rank == 0:
         line = {"metric": args.metric, "value": value, "unit": args.unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",

@@ -43,6 +43,15 @@ def _lists_from_rows(rows, bins):
 # asynchronous drop-in batches: dyibf_classify_begin / _end at the reference's batch size (src/mapper.h:109), as a
 # prefetching caller (src/file_prefetched.h:137-205) feeds them
 # ---------------------------------------------------------------------------------------------------------------------
+def _restrict(boff, ids, bins, lo, hi):
+    """the per-bin lists (CSR) restricted to the ids in [lo, hi), renumbered from 0: what a classify of those rows alone returns"""
+    binno = np.repeat(np.arange(bins, dtype=np.uint32), np.diff(boff.astype(np.int64)))
+    m = (ids >= lo) & (ids < hi)
+    off = np.zeros(bins + 1, dtype=np.uint64)
+    off[1:] = np.cumsum(np.bincount(binno[m], minlength=bins))
+    return off, (ids[m] - np.uint32(lo)).astype(np.uint32)
+
+
 def dropin_async(ctx, batches_pageable, batches_pinned, per_call, rb, group, depth=4):
     L, f, bins = ctx.L, ctx.f, ctx.bins
     from dream_yara_b200._lib import ENC_DNA5, check
@@ -209,8 +218,7 @@ def multi_gpu_parity(ctx):
     dist.all_gather_into_tensor(g, torch.from_numpy(mine).to(ctx.dev))
     ok_read = True; t_cpu = 0.0
     if rank == 0:
-        cf = B.CpuFilter(ctx.bins, H, K, ctx.nbits)
-        check(L.dyibf_download_words(ctx.f._h, _vp(cf.words), 0, ctx.P * ctx.W))
+        cf = ctx.cpu_filter()                                         # the reference's object with this GPU's words (cached for the other checks)
         allr = g.cpu().numpy()
         t0 = time.perf_counter()
         rows = cf.classify(B.full_layout_codes(allr), ctx.thr, False)
@@ -218,7 +226,7 @@ def multi_gpu_parity(ctx):
         woffs, wids = _lists_from_rows(rows, ctx.bins)
         ok_read = bool(np.array_equal(woffs, moffs) and np.array_equal(wids, mids))
         out["read_sharded_cpu_s"] = t_cpu
-        del cf, rows
+        del rows
     out["reads"] = world * m
     # ---- bin-sharded, small table (the reference needs the whole table in host RAM): Wr = 2 word columns per rank
     sb = 128; tb = sb * world; nbits_t = (1 << 33) + 256
@@ -401,12 +409,25 @@ def cfg5(ctx, steps=3):
         p = fb.profile(reset=True); fb.profile_enable(False)
         ms, bms, ams, sms = _maxr(ctx, [e0.elapsed_time(e1), p["build_ms"] / steps, p["build_apply_ms"] / steps, p["build_split2_ms"] / steps])
         value = ctx.world * kmers_step * steps / (ms / 1e3)
-        alg = kmers_step * H * 64
-        out.update({"value": value, "ms_per_step": ms / steps,
-                    "roofline": {"bound": "hbm", "achieved": alg / (bms / 1e3) / 1e9, "peak": ctx.peak, "unit": "GB/s",
-                                 "frac": alg / (bms / 1e3) / 1e9 / ctx.peak, "kernel_ms": bms, "split1_ms": bms - ams - sms,
-                                 "split2_ms": sms, "apply_ms": ams, "algorithmic_bytes_per_launch": alg,
-                                 "note": "192 B per k-mer: the random read-modify-write sector model of SURVEY.md 8(d)"}})
+        table_bytes = ctx.P * ctx.W * 8
+        scatter_ms = bms - ams - sms
+        sliced = None
+        try:
+            mode = fb.last_build_mode()
+            if mode == 3:
+                from bench_support.build_bench import sliced_roofline
+                sliced = sliced_roofline(kmers_step, H, table_bytes, bms, ams, sms, ctx.peak)
+        except Exception:
+            mode = -1
+        if sliced is not None:
+            out.update({"value": value, "ms_per_step": ms / steps, "roofline": sliced})
+        else:
+            alg = kmers_step * H * 64
+            out.update({"value": value, "ms_per_step": ms / steps,
+                        "roofline": {"bound": "hbm", "achieved": alg / (bms / 1e3) / 1e9, "peak": ctx.peak, "unit": "GB/s",
+                                     "frac": alg / (bms / 1e3) / 1e9 / ctx.peak, "kernel_ms": bms, "split1_ms": scatter_ms,
+                                     "split2_ms": sms, "apply_ms": ams, "algorithmic_bytes_per_launch": alg, "build_mode": mode,
+                                     "note": "192 B per k-mer: the random read-modify-write sector model of SURVEY.md 8(d)"}})
         # ---- host buffers in (pinned), then the finished table out once
         hstep(0)
         ctx.barrier()
@@ -519,9 +540,44 @@ def cfg4(ctx, steps=3, shard_gib=64, n_reads=10_000_000, read_len=100):
         tots = _maxr(ctx, [float(tot.value)])
         pair_sum = torch.tensor([float(tot.value)], dtype=torch.float64, device=ctx.dev)
         dist.all_reduce(pair_sum)
+        # rank 0's shard at its REAL shape (1024 bins, 64 GiB, P = 2^29 blocks, query_kernel<16,3,3,8>) against the reference's loop:
+        # the shard's words are downloaded into the reference's own filter object on the host (needs that much RAM)
+        shard_ref = {"skipped": "rank != 0"}
+        if rank == 0:
+            try:
+                import psutil
+                avail = psutil.virtual_memory().available
+            except Exception:
+                avail = 0
+            if avail < (shard_gib << 30) + (32 << 30):
+                shard_ref = {"skipped": "host has %.0f GiB available, the reference filter object needs %d GiB" % (avail / 2**30, shard_gib)}
+            else:
+              try:
+                m = 65536
+                t0 = time.perf_counter()
+                cf = B.CpuFilter(bins, H, K, nbits)
+                Pw = (nbits - 256) // (64 * W) * W
+                check(L.dyibf_download_words(fs._h, _vp(cf.words), 0, Pw))
+                t_dl = time.perf_counter() - t0
+                t0 = time.perf_counter()
+                rows_ref = cf.classify(B.full_layout_codes(h_reads[:m]), thr, False)
+                t_cl = time.perf_counter() - t0
+                rows_gpu = d_rows.view(n, W)[:m].cpu().numpy().view(np.uint64)
+                wo, wi = _lists_from_rows(rows_ref, bins)
+                go, gi = _restrict(h_boff, h_ids[: int(tot.value)], bins, 0, m)
+                shard_ref = {"rows_equal_reference": bool(np.array_equal(rows_ref, rows_gpu)),
+                             "lists_equal_reference": bool(np.array_equal(wo, go) and np.array_equal(wi, gi)),
+                             "reads": m, "pairs": int(wo[-1]), "host_filter_s": t_dl, "cpu_classify_s": t_cl,
+                             "what": "rank 0's shard (%d bins, %d GiB) downloaded into the reference's SeqAnBloomFilter on the host; its "
+                                     "whichBins loop on the first %d reads vs the GPU rows and the ids < %d of the GPU lists" % (bins, shard_gib, m, m)}
+                del cf, rows_ref
+              except Exception as ex:
+                shard_ref = {"skipped": "checker failed: " + repr(ex)[:200]}
         L.dyibf_host_free(hp); L.dyibf_host_free(ip)
         if not same:
             raise AssertionError("cfg4: host-mode lists != device-mode lists")
+        if shard_ref.get("rows_equal_reference") is False or shard_ref.get("lists_equal_reference") is False:
+            raise AssertionError("cfg4: rank 0's shard differs from the reference: %r" % shard_ref)
         return {"workload": "cfg4: synthetic %d-bin %d GiB IBF (k=%d, h=%d) bin-sharded over %d GPUs (%d bins, %d GiB per GPU), %d "
                             "single-end %d bp reads per step seen by every GPU, e=3 (threshold %d)"
                             % (bins * world, shard_gib * world, K, H, world, bins, shard_gib, n, read_len, thr),
@@ -532,7 +588,7 @@ def cfg4(ctx, steps=3, shard_gib=64, n_reads=10_000_000, read_len=100):
                 "roofline": {"bound": "hbm", "achieved": n * per_read / (qms / 1e3) / 1e9, "peak": ctx.peak, "unit": "GB/s",
                              "frac": n * per_read / (qms / 1e3) / 1e9 / ctx.peak, "kernel_ms": qms,
                              "algorithmic_bytes_per_launch": n * per_read, "per": "GPU (each gathers its own 128-byte slice of every block)"},
-                "read_bin_pairs_per_step": int(pair_sum.item()), "host_lists_equal_device": True}
+                "read_bin_pairs_per_step": int(pair_sum.item()), "host_lists_equal_device": True, "shard_vs_reference": shard_ref}
     finally:
         fs.close()
 
@@ -596,7 +652,27 @@ def single_process(ctx, steps=4):
         for b in range(0, bins, 37):
             seg = h_ids[int(h_boff[b]):int(h_boff[b + 1])]
             same = same and np.array_equal(seg[seg < ctx.n], i0[int(o0[b]):int(o0[b + 1])]) and bool(np.all(np.diff(seg.astype(np.int64)) > 0))
+        # ... and against the REFERENCE's loop (src/d_mapper.h:338-375, oracle/_ref) on 131 072 rows that straddle device boundaries
+        # (device r filters rows [r n/G, (r+1) n/G)): the group's lists restricted to those rows, ALL bins; outside every timed region
+        cuts = [ctx.n] if world == 2 else [ctx.n, (world - 1) * ctx.n]
+        half = 131072 // (2 * len(cuts))
+        ref_equal, t_ref, ref_err = True, time.perf_counter(), None
+        try:
+            cf = ctx.cpu_filter()                                     # the words of rank 0's table = what member 0 built and broadcast
+            for c in cuts:
+                lo, hi = c - half, c + half
+                rows_ref = cf.classify(B.full_layout_codes(h_reads[lo:hi]), ctx.thr, False)
+                wo, wi = _lists_from_rows(rows_ref, bins)
+                go, gi = _restrict(h_boff, h_ids[: int(tot.value)], bins, lo, hi)
+                ref_equal = ref_equal and bool(np.array_equal(wo, go) and np.array_equal(wi, gi))
+        except Exception as ex:                                       # the checker itself failed (memory, ...): say so, keep the line
+            ref_equal, ref_err = None, "checker failed: " + repr(ex)[:200]
+        t_ref = time.perf_counter() - t_ref
         out = {"value": n * steps / dt, "unit": ctx.args.unit, "reads_per_call": n, "steps": steps, "ms_per_step": dt / steps * 1e3,
+               "lists_equal_reference": ref_equal, "reference_check_error": ref_err,
+               "reference_check": "rows [c - %d, c + %d) around the device boundaries c = %s of the %d-read batch: the group's per-bin lists "
+                                  "restricted to those rows == the reference's clasifyLoadedReads loop on them, all %d bins (%.1f s of CPU, untimed)"
+                                  % (half, half, cuts, n, bins, t_ref),
                "h2d_bytes_per_step": n * RL + (n + 1) * 8, "d2h_bytes_per_step": int(tot.value) * 4 + (bins + 1) * 8,
                "host_read_gbs": n * RL / (dt / steps) / 1e9,
                "filter_build_s": t_build, "broadcast_s": t_bc, "broadcast_gbs_per_replica": ctx.P * ctx.W * 8 / t_bc / 1e9,
@@ -607,6 +683,39 @@ def single_process(ctx, steps=4):
                "limiter": "one host thread per GPU issues the copies; the batch is read once from host memory at host_read_gbs"}
         if not same:
             raise AssertionError("single-process group lists are not consistent with rank 0's own lists")
+        if ref_equal is False:
+            raise AssertionError("single-process group lists differ from the reference's on the rows around the device boundaries")
+        # ---- the same entry points on a BIN-SHARDED group (one filter's word columns over the N devices), built by the group itself
+        # (dyibf_group_add_sequences routes every contig to the device that owns its bin) and checked against the reference's own
+        # build + filtering loop: table words of every shard and all lists
+        try:
+            sb = 128; tb = sb * world; nbits_t = (1 << 33) + 256; glen_b = 200_000
+            Wt = tb // 64; Pt = (nbits_t - 256) // (64 * Wt); Wr = Wt // world
+            gen_b = synth.genomes(tb, glen_b, first_bin=5000)
+            gb = dy.FilterGroup(tb, H, K, nbits_t, devices=list(range(world)), mode="bin")
+            gb.addSequences((gen_b.reshape(-1), np.arange(tb + 1, dtype=np.uint64) * glen_b), np.arange(tb, dtype=np.uint32))
+            qn = 32768
+            qb_ = synth.reads(gen_b, 4, 0, qn, 100)
+            thr_b = int(L.dyibf_threshold(3, K, 100))
+            bo, bi = gb.classify((qb_.reshape(-1), np.arange(qn + 1, dtype=np.uint64) * 100), thr_b, group=2, derive_rc=True, encoding=ENC_DNA5)
+            cfb = B.CpuFilter(tb, H, K, nbits_t)
+            cfb.build(gen_b)
+            wo, wi = _lists_from_rows(cfb.classify(B.full_layout_codes(qb_), thr_b, False), tb)
+            table = cfb.words[: Pt * Wt].reshape(Pt, Wt)
+            words_eq = True
+            for i in range(world):
+                mi, _, _ = gb.member(i)
+                words_eq = words_eq and bool(np.array_equal(mi.download_words()[: Pt * Wr].reshape(Pt, Wr), table[:, i * Wr:(i + 1) * Wr]))
+            out["bin_sharded_group"] = {"lists_equal_reference": bool(np.array_equal(wo, bo) and np.array_equal(wi, bi)),
+                                        "words_equal_reference": words_eq, "pairs": int(wo[-1]),
+                                        "config": "%d bins over %d GPUs in one process (%d word columns each), 1 GiB table built by dyibf_group_add_sequences "
+                                                  "from %d x %d bp, %d reads x 100 bp; checker: the reference's addKmers + clasifyLoadedReads loop"
+                                                  % (tb, world, Wr, tb, glen_b, qn)}
+            gb.close(); del cfb, table
+        except Exception as ex:
+            out["bin_sharded_group"] = {"lists_equal_reference": None, "words_equal_reference": None, "error": "checker failed: " + repr(ex)[:200]}
+        if out["bin_sharded_group"]["lists_equal_reference"] is False or out["bin_sharded_group"]["words_equal_reference"] is False:
+            raise AssertionError("bin-sharded in-process group differs from the reference: %r" % out["bin_sharded_group"])
         # ---- A/B: the same batch in a pinned buffer spread over the host's NUMA nodes (DYIBF_HOST_ALLOC_INTERLEAVE): several GPUs
         # on different sockets read it at once
         if world >= 4:
@@ -649,14 +758,45 @@ def single_process(ctx, steps=4):
             a_, _, _ = g.member(i); b_, _, _ = g2.member(i)
             dev_i = torch.device("cuda", i)
             eq = eq and bool(torch.equal(D._tensor_from_ptr(a_.device_words(), nd, dev_i), D._tensor_from_ptr(b_.device_words(), nd, dev_i)))
+        # ... and the REFERENCE's addKmers (oracle/_ref) for 64 bins, four in every 64-bin word column: those bins' bits of the
+        # group-built table (last member: every one of its columns but its own came over NVLink) must be exactly the reference's
+        eq_ref, t_rb, sel, last = None, 0.0, np.zeros(4, dtype=np.uint32), world - 1
+        try:
+            from bench_support.build_bench import _cpu_build, _spread_bins
+            sel = _spread_bins(64, bins)
+            cfn = B.CpuFilter(bins, H, K, ctx.nbits)
+            t_rb, _ = _cpu_build(cfn, ctx.genomes[sel], sel)
+            colmask = np.zeros(ctx.W, dtype=np.uint64)
+            for b_sel in sel:
+                colmask[int(b_sel) // 64] |= np.uint64(1) << np.uint64(int(b_sel) % 64)
+            last = world - 1
+            dev_l = torch.device("cuda", last)
+            tbl = D._tensor_from_ptr(g2.member(last)[0].device_words(), nd, dev_l)
+            piece = (1 << 27) // ctx.W * ctx.W                               # ~1 GiB of whole hash blocks per comparison
+            eq_ref = True
+            with torch.cuda.device(dev_l):
+                mask_t = torch.from_numpy(colmask.view(np.int64)).to(dev_l).repeat(piece // ctx.W)
+                for a0 in range(0, nd, piece):
+                    a1 = min(a0 + piece, nd)
+                    ref_t = torch.from_numpy(cfn.words[a0:a1].view(np.int64)).to(dev_l)
+                    eq_ref = eq_ref and bool(torch.equal(tbl[a0:a1] & mask_t[: a1 - a0], ref_t))
+                    del ref_t
+            del cfn
+        except Exception as ex:
+            eq_ref = None; out["group_build_reference_error"] = "checker failed: " + repr(ex)[:200]
         kmers = bins * (ctx.args.genome_len - K + 1)
-        out["group_build"] = {"seconds_first_call": t_gb, "seconds": t_gb2, "kmers_per_s": kmers / t_gb2, "unit": "k-mers/s",
+        out["group_build"] = {"words_equal_reference": eq_ref,
+                              "reference_check": "bins %s...: the reference's addKmers on their %d contigs (%.1f s of CPU) == those bins' bits of "
+                                                 "member %d's table, every hash block" % (list(map(int, sel[:4])), len(sel), t_rb, last),
+                              "seconds_first_call": t_gb, "seconds": t_gb2, "kmers_per_s": kmers / t_gb2, "unit": "k-mers/s",
                               "single_gpu_build_s": t_build, "words_equal_single_gpu_build": eq,
                               "call": "dyibf_group_add_sequences: %d bins x %d bp from one pageable host buffer, routed by bin column to %d GPUs, "
                                       "columns exchanged over NVLink so that every replica holds the whole filter" % (bins, ctx.args.genome_len, world)}
         g2.close()
         if not eq:
             raise AssertionError("group-built filter differs from the single-GPU build")
+        if eq_ref is False:
+            raise AssertionError("group-built filter differs from the reference's addKmers on the sampled bins")
         g.close()
         L.dyibf_host_free(hp); L.dyibf_host_free(ip)
     finally:
